@@ -1,0 +1,58 @@
+"""Generate tests/golden/* from the UNMODIFIED reference (oracle/_ref/ref_driver).
+
+Run in the build container (needs /root/reference):   python tests/golden/make_golden.py
+Writes, per fixture matrix:
+  tests/golden/mtx/<suitesparse-name>.mtx.gz   the public SuiteSparse input the reference ships as
+                                               example/matrix{,2,3,4,5}.mtx (data, not code)
+  tests/golden/ref_<name>.npz                  what the reference's own code produced for it:
+      f_row_ptr/f_col/f_val   SparseMatrix<float> loader rows  (src/sparse_matrix.cpp:11-119)
+      i_row_ptr/i_col/i_val   SparseMatrix<int>   loader rows
+      scc_val                 values after scc_normalise      (src/sparse_matrix.cpp:433-456)
+      pr_val                  values after pagerank_normalise (src/sparse_matrix.cpp:409-431; all
+                              truncated to 0 by Q2 -- that IS the reference's behaviour)
+      gold_x0 / gold_x1       Gold<float>::spmv (inc/spmv_gold.h:9-28), x == 1 and x[i]=((7i+3)%11)-5
+"""
+import gzip
+import os
+import shutil
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import oracle as orc  # noqa: E402
+
+REF = "/root/reference/example"
+FIXTURES = {  # reference file -> SuiteSparse name
+    "matrix.mtx": "1138_bus",
+    "matrix2.mtx": "ca-AstroPh",
+    "matrix3.mtx": "Trefethen_20",
+    "matrix4.mtx": "GD96_b",
+    "matrix5.mtx": "arc130",
+}
+
+
+def main():
+    orc.build(ref=True)
+    out = os.path.join(ROOT, "tests", "golden")
+    os.makedirs(os.path.join(out, "mtx"), exist_ok=True)
+    for ref_name, name in FIXTURES.items():
+        src = os.path.join(REF, ref_name)
+        with open(src, "rb") as fi, gzip.GzipFile(os.path.join(out, "mtx", name + ".mtx.gz"), "wb", mtime=0) as fo:
+            shutil.copyfileobj(fi, fo)
+        h, w, frp, fc, fv = orc.ref_rows(src, "float", "none")
+        _, _, irp, ic, iv = orc.ref_rows(src, "int", "none")
+        _, _, srp, sc, sv = orc.ref_rows(src, "int", "scc")
+        _, _, prp, pc, pv = orc.ref_rows(src, "float", "pr")
+        assert (srp == irp).all() and (sc == ic).all() and (prp == frp).all() and (pc == fc).all()
+        g0 = orc.ref_gold(src, 0)
+        g1 = orc.ref_gold(src, 1)
+        np.savez_compressed(os.path.join(out, f"ref_{name}.npz"), shape=np.array([h, w], np.int64),
+                            f_row_ptr=frp, f_col=fc, f_val=fv, i_row_ptr=irp, i_col=ic, i_val=iv,
+                            scc_val=sv, pr_val=pv, gold_x0=g0, gold_x1=g1)
+        print(f"{name}: {h}x{w} stored={len(fc)} maxrow={int(np.diff(frp).max())} gold0[:8]={g0[:8]} sum={g0.astype(np.float64).sum()}")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,78 @@
+"""Pins the CPU oracle (oracle/shb_oracle.c) to the reference's own outputs.
+
+tests/golden/ref_*.npz were produced by the UNMODIFIED reference code (oracle/_ref/ref_driver, see
+tests/golden/make_golden.py): loader rows (src/sparse_matrix.cpp:11-119), normalisations (:409-456)
+and Gold<float>::spmv (inc/spmv_gold.h:9-28).  Everything here is bit-exact.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import FIXTURES, GOLDEN
+
+NAMES = list(FIXTURES.values())
+
+
+def _gold(name):
+    return np.load(os.path.join(GOLDEN, f"ref_{name}.npz"))
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_loader_matches_reference_rows(orc, mtx_dir, name):
+    g = _gold(name)
+    h, w, rp, col, val = orc.mm_load_csr(mtx_dir[name], "float")
+    assert (h, w) == tuple(g["shape"])
+    assert np.array_equal(rp, g["f_row_ptr"]) and np.array_equal(col, g["f_col"])
+    assert np.array_equal(val.view(np.int32), g["f_val"].view(np.int32))  # Q1-Q4 incl. int truncation
+    _, _, rp, col, val = orc.mm_load_csr(mtx_dir[name], "int")
+    assert np.array_equal(rp, g["i_row_ptr"]) and np.array_equal(col, g["i_col"]) and np.array_equal(val, g["i_val"])
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_normalisations_match_reference(orc, mtx_dir, name):
+    g = _gold(name)
+    _, _, _, _, val = orc.mm_load_csr(mtx_dir[name], "int", normalise="scc")
+    assert np.array_equal(val, g["scc_val"])
+    _, _, _, _, val = orc.mm_load_csr(mtx_dir[name], "float", normalise="pr")
+    assert np.array_equal(val.view(np.int32), g["pr_val"].view(np.int32))
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("xmode", [0, 1])
+def test_gold_and_kernel_restatement_match_reference_gold(orc, mtx_dir, name, xmode):
+    g = _gold(name)
+    h, w, rp, col, val = orc.mm_load_csr(mtx_dir[name], "float")
+    x = orc.xmode_vector(h, xmode)
+    y = np.zeros(h, np.float32)
+    want = g[f"gold_x{xmode}"]
+    got = orc.gold_spmv(rp, col, val, x, y)
+    assert np.array_equal(got.view(np.int32), want.view(np.int32))
+    # the kernel restatement (device formula), both accumulation orders, 1 and N threads
+    for order in (0, 1):
+        for threads in (1, 4):
+            out = orc.spmv(orc.PLUS_TIMES, rp, col, val, x, y, 1.0, 0.0, order=order, threads=threads)
+            assert np.array_equal(out, want), (order, threads)
+
+
+def test_known_answers_from_survey(orc):
+    # values obtained by running the reference; regenerated here from the npz
+    g = _gold("1138_bus")["gold_x0"]
+    assert list(g[:8]) == [1460, 1, 2, 2, 0, 2, 3, 1] and g.astype(np.float64).sum() == 2270
+    assert _gold("ca-AstroPh")["gold_x0"][0] == 43 and _gold("ca-AstroPh")["gold_x0"].astype(np.float64).sum() == 396160
+    t = _gold("Trefethen_20")["gold_x0"]
+    assert t[0] == 7 and t[1] == 9 and t.sum() == 777
+    assert _gold("GD96_b")["gold_x0"][0] == 47 and _gold("GD96_b")["gold_x0"].sum() == 193
+    assert _gold("arc130")["gold_x0"][0] == 1 and _gold("arc130")["gold_x0"].astype(np.float64).sum() == -4717836
+
+
+def test_live_reference_when_present(orc, mtx_dir):
+    """In the build container the reference binary itself is compared (skipped on the GPU box)."""
+    if not (orc.ref_available() and os.path.isdir("/root/reference")):
+        pytest.skip("oracle/_ref/ref_driver or /root/reference not present")
+    for name in ("Trefethen_20", "GD96_b"):
+        h, w, rp, col, val = orc.ref_rows(mtx_dir[name], "float")
+        _, _, rp2, col2, val2 = orc.mm_load_csr(mtx_dir[name], "float")
+        assert np.array_equal(rp, rp2) and np.array_equal(col, col2) and np.array_equal(val, val2)
+        assert np.array_equal(orc.ref_gold(mtx_dir[name], 1),
+                              orc.gold_spmv(rp2, col2, val2, orc.xmode_vector(h, 1), np.zeros(h, np.float32)))

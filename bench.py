@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the semiring CSR SpMV hot path (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--extras 0|1]
+
+A "step" is one SpMV pass (out = A x, float plus-times, alpha 1 beta 0) over the synthetic
+uniform-random CSR operator of config 2: 16 777 216 rows x 16 nnz/row per GPU, columns uniform in
+[0, 16 777 216) (seeds 0x5EED0002 / 0x5EED0003), generated on the device, resident in HBM
+before the timed region.  N > 1 (torchrun, one rank per GPU): every rank owns an independent block of
+16M rows of a (N*16M) x 16M operator with x replicated -- no data-path collective, weak scaling.
+Metric: effective HBM GB/s = algorithmic bytes / time, algorithmic bytes per SpMV =
+nnz*(4+4) + (rows+1)*4 + cols*4 [x once] + rows*4 [out] = 2 348 810 244 B per GPU.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ROWS_PER_GPU = 1 << 24
+NNZ_PER_ROW = 16
+N_COLS = 1 << 24
+ALGO_BYTES = ROWS_PER_GPU * NNZ_PER_ROW * 8 + (ROWS_PER_GPU + 1) * 4 + N_COLS * 4 + ROWS_PER_GPU * 4  # 2 348 810 244
+FLOPS = 2 * ROWS_PER_GPU * NNZ_PER_ROW
+CPU_SAMPLE_ROWS = 1 << 21  # bounded CPU sample: first 2M rows (32M non-zeros) of the same operator
+WORKLOAD = ("configs[1]: synthetic uniform-random CSR, 16777216 rows x 16 nnz/row per GPU, float plus-times SpMV "
+            "(alpha=1, beta=0)")
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+        except Exception:
+            pass
+    return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clock + throttle reasons of one GPU while the timed region runs (NVML, 50 ms period)."""
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:  # pragma: no cover
+            self.nv, self.err = None, repr(e)
+
+    def _loop(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4,
+                 "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def __enter__(self):
+        if self.nv:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def cpu_sample_inputs(orc):
+    rp, col, val = orc.gen_uniform(ROWS_PER_GPU, N_COLS, NNZ_PER_ROW, row_begin=0, row_count=CPU_SAMPLE_ROWS)
+    x = orc.gen_vector(N_COLS)
+    nbytes = len(col) * 8 + (CPU_SAMPLE_ROWS + 1) * 4 + N_COLS * 4 + CPU_SAMPLE_ROWS * 4
+    return rp, col, val, x, nbytes
+
+
+def time_cpu(orc, rp, col, val, x, threads, steps, warmup):
+    y = np.zeros(CPU_SAMPLE_ROWS, np.float32)
+    for _ in range(warmup):
+        orc.spmv(orc.PLUS_TIMES, rp, col, val, x, y, 1.0, 0.0, order=0, threads=threads)
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        orc.spmv(orc.PLUS_TIMES, rp, col, val, x, y, 1.0, 0.0, order=0, threads=threads)
+        times.append(time.perf_counter() - t0)
+    return times
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path for this operator on the host cores.  The reference's own
+    Gold<float>::spmv only accepts a Matrix Market FILE through its fscanf loader (a 16M x 16 operator is a
+    ~6 GB text file and > 10 GB of COO tuples), so the timed code is the oracle's restatement of that loop
+    (inc/spmv_gold.h:17-26, same forward order) run over rows with OpenMP on every host core (kind "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import oracle as orc
+    rp, col, val, x, nbytes = cpu_sample_inputs(orc)
+    threads = orc.num_threads()
+    times = time_cpu(orc, rp, col, val, x, threads, args.steps, args.warmup)
+    mean = float(np.mean(times))
+    gbs = nbytes / mean / 1e9
+    sample = f"first {CPU_SAMPLE_ROWS} rows ({len(col)} non-zeros) of the config-2 operator, x full length, {threads} OpenMP threads"
+    line = {"impl": "reference", "metric": "spmv_effective_hbm_gbs", "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": mean * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": sample},
+            "gflops": 2 * len(col) / mean / 1e9,
+            "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def graph_extras(ctx, shb, orc):
+    """GTEPS of the graph drivers on one GPU (configs 3-5 families), reported next to the headline line."""
+    out = {}
+
+    def guarded(name, fn):
+        try:
+            out[name] = fn()
+        except Exception as e:  # keep the headline line alive
+            out[name] = {"error": repr(e)[:300]}
+
+    def bfs():
+        A = ctx.synth_rmat(24, 16, seed=0x5EED0024, symmetrise=True)
+        info = A.info
+        rp = A.download(0, 4096)[0]
+        root = int(np.argmax(np.diff(rp) > 0))
+        best = None
+        for _ in range(3):
+            levels, st = ctx.bfs(A, root, AT=A)
+            levels.free()
+            if best is None or st.total_ns < best.total_ns:
+                best = st
+        undirected = best.edges_traversed / 2
+        r = {"graph": "RMAT scale 24 edgefactor 16 symmetrised+deduplicated", "n": info.n_rows, "nnz": info.nnz,
+             "levels": best.iterations, "reached": best.reached, "ms": best.total_ns / 1e6,
+             "gteps": undirected / best.total_ns, "teps_edges": undirected}
+        A.free()
+        return r
+
+    def sssp():
+        G = ctx.synth_grid2d(8192, 8192, seed=0x5EED0004)
+        info = G.info
+        dist, st = ctx.sssp(G, 0, AT=G)
+        dist.free()
+        r = {"graph": "2-D grid 8192x8192 4-neighbour, integer weights 1..255", "n": info.n_rows, "nnz": info.nnz,
+             "rounds": st.iterations, "converged": bool(st.converged), "ms": st.total_ns / 1e6,
+             "gteps": st.edges_traversed / st.total_ns}
+        G.free()
+        return r
+
+    def pagerank():
+        A = ctx.synth_rmat(24, 16, seed=0x5EED0026, symmetrise=False, value_mode=1)
+        info = A.info
+        res, st = ctx.pagerank(A, delta=0.0, max_iters=20, check_every=20)  # fixed 20 sweeps
+        res.free()
+        r = {"graph": "RMAT scale 24 edgefactor 16 directed (config 5 family; scale 26 needs the multi-GPU partition)",
+             "n": info.n_rows, "nnz": info.nnz, "sweeps": st.iterations, "ms": st.total_ns / 1e6,
+             "gteps": info.nnz * st.iterations / st.total_ns,
+             "effective_gbs": info.algorithmic_bytes_spmv * st.iterations / st.total_ns}
+        A.free()
+        return r
+
+    guarded("bfs", bfs)
+    guarded("sssp", sssp)
+    guarded("pagerank", pagerank)
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(local)
+    n_gpus = world
+
+    import sparseharness_b200 as shb  # raises if libshb.so is missing: no fallback path exists
+    from oracle import oracle as orc  # checker + cpu_baseline only
+
+    ctx = shb.Context(local)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- inputs resident in HBM
+    n_rows_total = ROWS_PER_GPU * world
+    A = ctx.synth_uniform(n_rows_total, N_COLS, NNZ_PER_ROW, seed=0x5EED0002, val_mode=0,
+                          row_begin=rank * ROWS_PER_GPU, row_count=ROWS_PER_GPU)
+    info = A.info
+    assert info.algorithmic_bytes_spmv == ALGO_BYTES, (info.algorithmic_bytes_spmv, ALGO_BYTES)
+    x = ctx.synth_vector(N_COLS, seed=0x5EED0003, mode=0)
+    out = ctx.empty(ROWS_PER_GPU * 4)
+    cfg = shb.launch_cfg()  # SHB_VARIANT_AUTO
+    W = max(args.warmup, 3)
+    K = args.steps
+
+    # ---- device-resident throughput ("value")
+    for _ in range(W):
+        ctx.spmv(A, shb.PLUS_TIMES, x, None, 1.0, 0.0, out, cfg, timed=False)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        ev0.record()
+        for _ in range(K):
+            ctx.spmv(A, shb.PLUS_TIMES, x, None, 1.0, 0.0, out, cfg, timed=False)
+        ev1.record()
+        barrier()
+        dev_ms = ev0.elapsed_time(ev1)
+
+        # ---- end to end through the host-vector C-ABI call: x from pinned host memory, out back to it
+        xh = torch.empty(N_COLS, dtype=torch.float32, pin_memory=True)
+        oh = torch.empty(ROWS_PER_GPU, dtype=torch.float32, pin_memory=True)
+        xh.copy_(torch.from_numpy(x.download(np.float32, N_COLS)))
+        xh_np, oh_np = xh.numpy(), oh.numpy()
+        Ke = max(5, min(K, 50))
+        for _ in range(3):
+            ctx.spmv_host(A, shb.PLUS_TIMES, xh_np, None, 1.0, 0.0, oh_np, cfg)
+        barrier()
+        t0 = time.perf_counter()
+        e2e_dev_ns = 0
+        for _ in range(Ke):
+            tot, _ker = ctx.spmv_host(A, shb.PLUS_TIMES, xh_np, None, 1.0, 0.0, oh_np, cfg)
+            e2e_dev_ns += tot
+        barrier()
+        e2e_s = time.perf_counter() - t0
+    times = torch.tensor([dev_ms, e2e_s * 1e3, e2e_dev_ns / 1e6], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms, _ = [float(v) for v in times.tolist()]
+
+    # ---- parity spot check outside the timed region (the oracle is the checker)
+    got = out.download(np.float32, 4096)
+    rp, col, val = orc.gen_uniform(n_rows_total, N_COLS, NNZ_PER_ROW, row_begin=rank * ROWS_PER_GPU, row_count=4096)
+    xs = orc.gen_vector(N_COLS)
+    want = orc.spmv(orc.PLUS_TIMES, rp, col, val, xs, np.zeros(4096, np.float32), 1.0, 0.0)
+    parity_ok = bool(np.abs(got - want).max() <= 1e-5 * np.abs(want).max()) and bool(np.array_equal(oh_np[:4096], got))
+    if not parity_ok:
+        raise SystemExit("bench: SpMV result differs from the oracle -- refusing to report a number")
+
+    ms_per_step = dev_ms / K
+    value = ALGO_BYTES * n_gpus / (ms_per_step * 1e-3) / 1e9
+    per_gpu = ALGO_BYTES / (ms_per_step * 1e-3) / 1e9
+    peak, peak_src = measured_peak_gbs()
+    e2e_value = ALGO_BYTES * n_gpus / (e2e_ms / Ke * 1e-3) / 1e9
+    clocks = clk.summary()
+
+    line = {
+        "metric": "spmv_effective_hbm_gbs", "value": value, "unit": "GB/s", "n_gpus": n_gpus, "steps": K, "warmup": W,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "rows_per_gpu": ROWS_PER_GPU, "nnz_per_gpu": ROWS_PER_GPU * NNZ_PER_ROW,
+                   "algorithmic_bytes_per_step_per_gpu": ALGO_BYTES, "parallelism": f"rows x{n_gpus}, x replicated, no collective",
+                   "kernel": f"variant={info.auto_variant} lanes={info.auto_lanes} (SHB_VARIANT_AUTO)",
+                   "l2": "inputs 2.35 GB per GPU >> 126 MB L2, no flush between steps (x, 64 MB, may stay L2 resident)"},
+        "gflops": FLOPS * n_gpus / (ms_per_step * 1e-3) / 1e9,
+        "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
+                     "traffic": None, "peak_source": peak_src, "kernel": "spmv_vector_kernel<PlusTimesF32,4,4,true,true>",
+                     "note": "achieved = 2348810244 B / mean launch time over the timed region (CUDA events on the launch stream)"},
+        "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": N_COLS * 4, "d2h_bytes_per_step": ROWS_PER_GPU * 4,
+                "ms_per_step": e2e_ms / Ke, "steps": Ke,
+                "api": "shb_spmv_host: x from pinned host memory, kernel, out to pinned host memory, operator resident"},
+        "gpu_launches": K * n_gpus, "clocks": clocks, "parity_checked": parity_ok,
+    }
+    traffic_file = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
+    if os.path.exists(traffic_file):
+        try:
+            line["roofline"]["traffic"] = json.load(open(traffic_file))["dram_bytes_per_launch"]
+        except Exception:
+            pass
+
+    if rank == 0 and n_gpus == 1:
+        rp, col, val, xs, nbytes = cpu_sample_inputs(orc)
+        threads = orc.num_threads()
+        t = time_cpu(orc, rp, col, val, xs, threads, steps=max(3, min(40, args.cpu_steps)), warmup=1)
+        best = float(np.min(t))
+        line["cpu_baseline"] = {"value": nbytes / best / 1e9, "unit": "GB/s", "cores": threads, "kind": "port",
+                                "gflops": 2 * len(col) / best / 1e9, "ms_per_pass": best * 1e3,
+                                "sample": f"first {CPU_SAMPLE_ROWS} rows ({len(col)} non-zeros) of the same operator, x full "
+                                          f"length; oracle restatement of inc/spmv_gold.h:17-26, OpenMP over rows, best of {len(t)}"}
+        t1 = time_cpu(orc, rp, col, val, xs, 1, steps=3, warmup=0)
+        line["cpu_baseline"]["single_thread_gbs"] = nbytes / float(np.min(t1)) / 1e9
+        del rp, col, val
+    A.free(); x.free(); out.free()
+    if rank == 0 and n_gpus == 1 and args.extras:
+        line["graph_gteps"] = graph_extras(ctx, shb, orc)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=int(os.environ.get("WORLD_SIZE", "1")))
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--extras", type=int, default=1, help="also report BFS/SSSP/PageRank GTEPS on 1 GPU")
+    ap.add_argument("--cpu-steps", type=int, default=12)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,207 @@
+/*
+ * shb.h -- C ABI of libshb.so: the B200-native replacement for the device side of
+ * AdamBrouwersHarries/sparseharness (semiring CSR SpMV  out = alpha*(A (x) x) (+) beta*y  and the
+ * iterative BFS / SSSP / PageRank / SCC loops built on it).
+ *
+ * It replaces, in the reference (paths relative to the reference repo):
+ *   inc/opencl_utils.h          (device query, error strings, checkCLError)
+ *   inc/cl_memory_manager.h     (the bag of cl_mem handles)
+ *   inc/harness.h:13-82         (context / queue / JIT of the Lift "KERNEL")
+ *   inc/harness.h:149-411       (executeKernel, allocateBuffers, create/upload/fill/read buffers)
+ *   app/{sssp,bfs,pr,scc}.cpp executeRun  (the host-driven fixed-point loops, now device-resident)
+ *   example/<alg>/kernel*.json "source"   (the Lift-generated OpenCL kernels)
+ *
+ * Conventions: plain C types only; every function returns an shb_status (0 = ok) and never exits
+ * or throws -- the C++ Harness wrapper (host/inc/harness.h) turns a non-zero status into the
+ * reference's "log and exit(1)" behaviour (inc/opencl_utils.h:15-23).  All sizes are 64-bit (the
+ * reference's unsigned-int byte sizes cap at 4 GB, inc/kernel_utils.h:27-30).  Functions taking a
+ * `uint64_t *ns` time the device work with a cudaEvent pair on the context's stream and
+ * synchronise (the reference's event-profiling semantics, inc/harness.h:183-194); pass NULL to
+ * enqueue asynchronously.  A context is single-threaded like the reference's in-order queue.
+ * There is NO CPU fallback: without a CUDA device shb_ctx_create fails.
+ */
+#ifndef SHB_H
+#define SHB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SHB_ABI_VERSION 1
+
+typedef struct shb_ctx shb_ctx; /* one device + one in-order stream   (inc/harness.h:19-81)        */
+typedef struct shb_buf shb_buf; /* one device buffer                   (cl_mem)                      */
+typedef struct shb_csr shb_csr; /* device-resident CSR operator + its launch schedule metadata      */
+
+typedef enum {
+  SHB_OK = 0,
+  SHB_ERR_INVALID = 1,     /* bad argument                                                       */
+  SHB_ERR_CUDA = 2,        /* a CUDA runtime call failed; see shb_last_error()                   */
+  SHB_ERR_NO_DEVICE = 3,   /* "No OpenCL devices found!" analogue (inc/harness.h:24-27)          */
+  SHB_ERR_OOM = 4,         /* allocation exceeds device memory (src/sparse_matrix.cpp:231-233)   */
+  SHB_ERR_UNSUPPORTED = 5, /* semiring / type / variant combination not available                */
+  SHB_ERR_TOO_LARGE = 6,   /* nnz >= 2^31 in one partition                                       */
+  SHB_ERR_NOT_CONVERGED = 7 /* iteration cap reached (the reference loops forever, Q8)           */
+} shb_status;
+
+/* The harness's semirings (example/<alg>/kernel*.json user functions) */
+typedef enum {
+  SHB_PLUS_TIMES_F32 = 0, /* spmv/, pr/ : mult l*r, add x+y, epi dp*alpha + y*beta, ZERO 0.0f              */
+  SHB_MIN_PLUS_F32 = 1,   /* sssp/      : |a|+|b|, min(|a|,|b|), min(|dp|+|alpha|,|y|+|beta|), ZERO FLT_MAX */
+  SHB_OR_AND_I32 = 2,     /* bfs/       : a&&b, a||b, (dp&&alpha)||(y&&beta), ZERO 0                       */
+  SHB_MAX_MIN_I32 = 3     /* scc/       : min, max, max(min(dp,alpha),min(y,beta)), ZERO INT_MIN           */
+} shb_semiring;
+
+/* Kernel schedule variants (what the seven Lift schedules, kernel{,2..7}.json, map onto) */
+typedef enum {
+  SHB_VARIANT_AUTO = 0,   /* chosen from row-length statistics                                            */
+  SHB_VARIANT_SCALAR = 1, /* thread per row, forward order (glb-sdp / glb-sdp-rsa, kernel5/6.json)        */
+  SHB_VARIANT_VECTOR = 2, /* sub-warp of `lanes` threads per row, 128-bit loads, shuffle reduction        */
+  SHB_VARIANT_STREAM = 3  /* nnz-split load-balanced tiles staged through shared memory (power-law rows)   */
+} shb_variant;
+
+enum { SHB_F_NO_CACHE_HINTS = 1u, /* plain ld.global for every stream (A/B experiments)          */
+       SHB_F_NO_Y_SKIP = 2u,      /* always read y, even when beta makes it irrelevant            */
+       SHB_F_REVERSED_ORDER = 4u  /* SCALAR: accumulate a row from its last entry to its first, the
+                                     order of the ELL schedules (kernel{,3,5}.json write products
+                                     reversed into the temp buffer)                               */ };
+
+typedef struct {
+  int32_t variant;        /* shb_variant                                                          */
+  int32_t lanes;          /* VECTOR: threads per row 1,2,4,8,16,32; 0 = auto                      */
+  int32_t rows_per_group; /* VECTOR: rows in flight per sub-warp (ILP); 0 = auto                   */
+  int32_t block_threads;  /* 0 = auto (reference: Run.local1, src/run.cpp:12)                      */
+  int32_t grid_blocks;    /* 0 = auto (reference: Run.global1 / local1)                            */
+  uint32_t flags;         /* SHB_F_*                                                               */
+} shb_launch_cfg;
+
+typedef struct {
+  int64_t n_rows, n_cols, nnz;
+  int64_t max_row_len, min_row_len, empty_rows;
+  double mean_row_len;
+  int32_t has_values;     /* 0 = pattern (every stored value is the semiring one)                  */
+  int32_t elem_bytes;     /* 4                                                                    */
+  int32_t auto_variant, auto_lanes; /* what SHB_VARIANT_AUTO resolves to                           */
+  int64_t stream_tiles, straddling_rows;
+  uint64_t device_bytes;  /* bytes held on the device by this operator                            */
+  uint64_t algorithmic_bytes_spmv; /* nnz*(4+vb) + (N+1)*4 + 2*N*4, beta == 0        */
+} shb_csr_info;
+
+/* ---- library / device (inc/opencl_utils.h:173-226, inc/harness.h:100-108) -------------------- */
+int shb_abi_version(void);
+const char *shb_status_string(int status);      /* <- getErrorString, inc/opencl_utils.h:25        */
+const char *shb_last_error(void);               /* detail of the last failure on this thread       */
+int shb_device_count(int *count);
+int shb_device_max_alloc_bytes(int device, uint64_t *bytes); /* <- deviceGetMaxAllocSize :216      */
+int shb_device_props(int device, char *name, size_t name_cap, int *sm_count, int *cc_major, int *cc_minor,
+                     uint64_t *total_mem, uint64_t *l2_bytes);
+
+int shb_ctx_create(int device, shb_ctx **ctx);  /* <- Harness ctor, inc/harness.h:13-82            */
+int shb_ctx_destroy(shb_ctx *ctx);
+int shb_ctx_set_stream(shb_ctx *ctx, void *cuda_stream); /* run on a caller-owned cudaStream_t      */
+int shb_ctx_synchronize(shb_ctx *ctx);
+int shb_ctx_device_name(shb_ctx *ctx, char *name, size_t cap); /* <- getDeviceName :100             */
+int shb_ctx_device(shb_ctx *ctx, int *device);
+
+/* ---- buffers (inc/harness.h:266-391) ------------------------------------------------------------ */
+int shb_buf_create(shb_ctx *ctx, uint64_t bytes, shb_buf **buf);                       /* createGlobalArg  */
+int shb_buf_wrap(shb_ctx *ctx, void *device_ptr, uint64_t bytes, shb_buf **buf);       /* caller-owned mem */
+int shb_buf_destroy(shb_buf *buf);
+int shb_buf_upload(shb_ctx *ctx, shb_buf *buf, uint64_t offset, const void *host, uint64_t bytes,
+                   uint64_t *ns);                                                      /* writeToGlobalArg */
+int shb_buf_download(shb_ctx *ctx, const shb_buf *buf, uint64_t offset, void *host, uint64_t bytes,
+                     uint64_t *ns);                                                    /* readFromGlobalArg */
+int shb_buf_fill_zero(shb_ctx *ctx, shb_buf *buf, uint64_t offset, uint64_t bytes, uint64_t *ns); /* fillGlobalArg */
+int shb_buf_fill_u32(shb_ctx *ctx, shb_buf *buf, uint64_t offset_elems, uint64_t n_elems, uint32_t pattern);
+int shb_buf_copy(shb_ctx *ctx, shb_buf *dst, const shb_buf *src, uint64_t bytes);
+int shb_buf_size(const shb_buf *buf, uint64_t *bytes);
+int shb_buf_device_ptr(const shb_buf *buf, void **ptr);
+int shb_host_alloc_pinned(uint64_t bytes, void **ptr);
+int shb_host_free_pinned(void *ptr);
+
+/* ---- the operator: CSR on the device (replaces the ELL / RSA blobs of SparseMatrix::cl_encode,
+ *      src/sparse_matrix.cpp:122-399; arguments 0 "idx" and 1 "vals" of the kernel ABI) ----------- */
+int shb_csr_create(shb_ctx *ctx, int64_t n_rows, int64_t n_cols, int64_t nnz, const int64_t *row_ptr,
+                   const int32_t *col_idx, const void *vals /* NULL = pattern */, int elem_bytes,
+                   shb_csr **csr, uint64_t *upload_ns);
+int shb_csr_destroy(shb_csr *csr);
+int shb_csr_get_info(const shb_csr *csr, shb_csr_info *info);
+int shb_csr_download(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int64_t row_count,
+                     int64_t *row_ptr /* row_count+1, rebased to 0 */, int32_t *col_idx, void *vals);
+int shb_csr_transpose(shb_ctx *ctx, const shb_csr *csr, shb_csr **transposed); /* push-side adjacency */
+
+/* ---- the hot path: one semiring SpMV (<- Harness::executeKernel, inc/harness.h:149-195) ---------
+ * out[r] = epi( (+)_k mult(x[col k], val k), alpha, y[r], beta ), x <- ZERO for col out of range.
+ * alpha/beta point at one element of the semiring's type.  out must not alias x; y may alias x. */
+int shb_spmv(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const shb_buf *x,
+             const shb_buf *y, const void *alpha, const void *beta, shb_buf *out, uint64_t *kernel_ns);
+
+/* Same call with HOST vectors (the reference-facing plugin boundary: x upload, kernel, out download,
+ * all inside *total_ns; A stays resident like the reference's idx/vals buffers). */
+int shb_spmv_host(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const void *x_host,
+                  const void *y_host /* NULL when beta makes y irrelevant */, const void *alpha, const void *beta,
+                  void *out_host, uint64_t *total_ns, uint64_t *kernel_ns);
+
+/* ---- device-resident fixed-point iteration (<- app/{sssp,bfs,pr,scc}.cpp executeRun) ------------
+ * x_{k+1} = KERNEL(x_k, y_k); y_0 = y0, y_k = x_k afterwards when y_rebind (app/sssp.cpp:150, Q9).
+ * term_mode 0: stop when all |x_k[i]-x_{k+1}[i]| < delta (sssp, pr); 1: all equal (bfs, scc).
+ * The convergence test runs on the device inside the kernel's epilogue; the host looks at a
+ * 4-byte flag once per `check_every` launches.  x and work are ping-pong buffers of n elements;
+ * *result_in_work tells which one holds the last output.  per_iter_ns (cap max_iters) optional. */
+enum { SHB_TERM_ABSDIFF = 0, SHB_TERM_EQUAL = 1 };
+int shb_iterate(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, shb_buf *x,
+                const shb_buf *y0, const void *alpha, const void *beta, shb_buf *work, double delta,
+                int term_mode, int y_rebind, uint32_t max_iters, uint32_t check_every, uint64_t *per_iter_ns,
+                uint32_t *n_iters, int *result_in_work, uint64_t *total_ns);
+
+/* ---- graph drivers on the semirings (north_star: frontier / vectors / flag stay on the device) -- */
+typedef struct {
+  uint32_t iterations;      /* levels (bfs) / relaxation rounds (sssp) / sweeps (pagerank)        */
+  uint32_t converged;
+  int64_t edges_traversed;  /* TEPS numerator: sum of in-degrees of reached vertices              */
+  int64_t reached;
+  uint64_t total_ns;        /* device time, first launch to last                                  */
+  uint64_t launches;
+} shb_graph_stats;
+
+/* BFS levels under or-and: level[root]=0, frontier_{k+1} = (A (x) frontier_k) AND NOT visited,
+ * level[v] = first k with v in frontier, -1 when unreached (SURVEY.md Q8 build decision).
+ * AT (optional transpose) enables push steps for small frontiers. */
+int shb_bfs(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64_t root, shb_buf *levels,
+            uint32_t max_levels, shb_graph_stats *stats);
+/* SSSP under min-plus to the exact fixed point (delta -> no change), frontier-aware. */
+int shb_sssp(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64_t source, shb_buf *dist,
+             uint32_t max_rounds, shb_graph_stats *stats);
+/* Canonical PageRank (Q9): x_{k+1} = A x_k + beta (y == 1 not re-bound), stop on |dx| < delta. */
+int shb_pagerank(shb_ctx *ctx, const shb_csr *A, const shb_launch_cfg *cfg, shb_buf *x, shb_buf *work,
+                 float x_init, float beta, double delta, uint32_t max_iters, uint32_t check_every,
+                 int *result_in_work, shb_graph_stats *stats);
+
+/* ---- synthetic workloads generated on the device (bit-identical to the oracle's
+ *      generators so results can be cross-checked) ---------------------------------------------- */
+int shb_synth_uniform(shb_ctx *ctx, int64_t n_rows, int64_t n_cols, int k, uint64_t seed, int val_mode,
+                      int64_t row_begin, int64_t row_count, shb_csr **csr);
+int shb_synth_vector(shb_ctx *ctx, shb_buf *x, int64_t n, uint64_t seed, int mode);
+int shb_synth_rmat(shb_ctx *ctx, int scale, int64_t n_edges, uint64_t seed, int symmetrise, int value_mode,
+                   float damping, shb_csr **csr);
+int shb_synth_grid2d(shb_ctx *ctx, int64_t w, int64_t h, uint64_t seed, shb_csr **csr);
+
+/* ---- multi-GPU: 1-D row partition, x exchanged every iteration (new capability) ----
+ * One process per GPU.  Each rank exports its x buffers once with CUDA IPC; the fused kernel
+ * writes every finished out[r] straight into all peers' next-x buffers over NVLink. */
+#define SHB_IPC_HANDLE_BYTES 64
+int shb_ipc_export(shb_buf *buf, void *handle /* SHB_IPC_HANDLE_BYTES */);
+int shb_ipc_open(shb_ctx *ctx, const void *handle, uint64_t bytes, shb_buf **buf);
+int shb_ipc_close(shb_buf *buf);
+/* out slice [row_offset, row_offset + A.n_rows) of every dst[i] (i < n_dst) receives the result */
+int shb_spmv_scatter(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const shb_buf *x,
+                     const shb_buf *y, const void *alpha, const void *beta, shb_buf *const *dst, int n_dst,
+                     int64_t row_offset, double delta, int term_mode, shb_buf *changed_flag, uint64_t *kernel_ns);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SHB_H */

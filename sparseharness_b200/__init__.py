@@ -1,0 +1,9 @@
+"""sparseharness_b200 -- B200-native semiring CSR SpMV (the hot path of AdamBrouwersHarries/sparseharness).
+
+The product is the C-ABI CUDA library lib/libshb.so (include/shb.h) plus the C++ harness host under
+host/.  This Python package is only a thin ctypes view of that ABI for tests and bench.py.
+"""
+from .api import (  # noqa: F401
+    MAX_MIN, MIN_PLUS, OR_AND, PLUS_TIMES, TERM_ABSDIFF, TERM_EQUAL, VARIANT_AUTO, VARIANT_SCALAR, VARIANT_STREAM,
+    VARIANT_VECTOR, F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER, Buffer, Context, Csr, ShbError, device_count,
+    launch_cfg)

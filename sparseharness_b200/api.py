@@ -1,0 +1,283 @@
+"""Thin Python view of the C ABI (include/shb.h): Context / Buffer / Csr wrappers over ctypes.
+
+Every compute call goes through libshb.so; nothing here computes on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import CsrInfo, GraphStats, LaunchCfg, lib
+
+PLUS_TIMES, MIN_PLUS, OR_AND, MAX_MIN = 0, 1, 2, 3
+VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_STREAM = 0, 1, 2, 3
+TERM_ABSDIFF, TERM_EQUAL = 0, 1
+F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER = 1, 2, 4
+_DTYPE = {PLUS_TIMES: np.float32, MIN_PLUS: np.float32, OR_AND: np.int32, MAX_MIN: np.int32}
+
+
+class ShbError(RuntimeError):
+    def __init__(self, status: int):
+        self.status = status
+        super().__init__(f"{lib.shb_status_string(status).decode()}: {lib.shb_last_error().decode()}")
+
+
+def _ck(status: int) -> None:
+    if status != 0:
+        raise ShbError(status)
+
+
+def device_count() -> int:
+    n = C.c_int(0)
+    _ck(lib.shb_device_count(C.byref(n)))
+    return n.value
+
+
+def launch_cfg(variant=VARIANT_AUTO, lanes=0, rows_per_group=0, block_threads=0, grid_blocks=0, flags=0):
+    return LaunchCfg(variant, lanes, rows_per_group, block_threads, grid_blocks, flags)
+
+
+def _scalar(semiring, v):
+    return np.array([v], dtype=_DTYPE[semiring])
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Buffer:
+    def __init__(self, ctx: "Context", handle, nbytes: int):
+        self.ctx, self.h, self.nbytes = ctx, handle, nbytes
+
+    def upload(self, arr: np.ndarray, offset: int = 0) -> int:
+        arr = np.ascontiguousarray(arr)
+        ns = C.c_uint64(0)
+        _ck(lib.shb_buf_upload(self.ctx.h, self.h, offset, _ptr(arr), arr.nbytes, C.byref(ns)))
+        return ns.value
+
+    def download(self, dtype, count: int | None = None, offset: int = 0) -> np.ndarray:
+        dtype = np.dtype(dtype)
+        count = (self.nbytes - offset) // dtype.itemsize if count is None else count
+        out = np.empty(count, dtype=dtype)
+        _ck(lib.shb_buf_download(self.ctx.h, self.h, offset, _ptr(out), out.nbytes, None))
+        return out
+
+    def zero(self):
+        _ck(lib.shb_buf_fill_zero(self.ctx.h, self.h, 0, self.nbytes, None))
+
+    def fill_u32(self, pattern: int, n: int | None = None):
+        _ck(lib.shb_buf_fill_u32(self.ctx.h, self.h, 0, self.nbytes // 4 if n is None else n, pattern))
+
+    @property
+    def device_ptr(self) -> int:
+        p = C.c_void_p()
+        _ck(lib.shb_buf_device_ptr(self.h, C.byref(p)))
+        return p.value
+
+    def ipc_handle(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        _ck(lib.shb_ipc_export(self.h, buf))
+        return buf.raw
+
+    def free(self):
+        if self.h:
+            lib.shb_buf_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Csr:
+    def __init__(self, ctx: "Context", handle):
+        self.ctx, self.h = ctx, handle
+
+    @property
+    def info(self) -> CsrInfo:
+        i = CsrInfo()
+        _ck(lib.shb_csr_get_info(self.h, C.byref(i)))
+        return i
+
+    def download(self, row_begin=0, row_count=None, dtype=np.float32):
+        inf = self.info
+        row_count = inf.n_rows - row_begin if row_count is None else row_count
+        rp = np.empty(row_count + 1, dtype=np.int64)
+        _ck(lib.shb_csr_download(self.ctx.h, self.h, row_begin, row_count, _ptr(rp), None, None))
+        nnz = int(rp[-1])
+        col = np.empty(nnz, dtype=np.int32)
+        val = np.empty(nnz, dtype=dtype) if inf.has_values else None
+        _ck(lib.shb_csr_download(self.ctx.h, self.h, row_begin, row_count, _ptr(rp), _ptr(col), _ptr(val)))
+        return rp, col, val
+
+    def transpose(self) -> "Csr":
+        h = C.c_void_p()
+        _ck(lib.shb_csr_transpose(self.ctx.h, self.h, C.byref(h)))
+        return Csr(self.ctx, h)
+
+    def free(self):
+        if self.h:
+            lib.shb_csr_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Context:
+    """One device + one in-order stream (the reference Harness's context/queue, inc/harness.h:19-81)."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        _ck(lib.shb_ctx_create(device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    @property
+    def device_name(self) -> str:
+        b = C.create_string_buffer(256)
+        _ck(lib.shb_ctx_device_name(self.h, b, 256))
+        return b.value.decode()
+
+    def set_stream(self, cuda_stream: int):
+        _ck(lib.shb_ctx_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def synchronize(self):
+        _ck(lib.shb_ctx_synchronize(self.h))
+
+    # ---- buffers
+    def empty(self, nbytes: int) -> Buffer:
+        h = C.c_void_p()
+        _ck(lib.shb_buf_create(self.h, nbytes, C.byref(h)))
+        return Buffer(self, h, nbytes)
+
+    def array(self, arr: np.ndarray) -> Buffer:
+        arr = np.ascontiguousarray(arr)
+        b = self.empty(max(arr.nbytes, 4))
+        if arr.nbytes:
+            b.upload(arr)
+        return b
+
+    def wrap(self, device_ptr: int, nbytes: int) -> Buffer:
+        h = C.c_void_p()
+        _ck(lib.shb_buf_wrap(self.h, C.c_void_p(device_ptr), nbytes, C.byref(h)))
+        return Buffer(self, h, nbytes)
+
+    def ipc_open(self, handle: bytes, nbytes: int) -> Buffer:
+        h = C.c_void_p()
+        _ck(lib.shb_ipc_open(self.h, handle, nbytes, C.byref(h)))
+        return Buffer(self, h, nbytes)
+
+    # ---- operators
+    def csr(self, n_rows, n_cols, row_ptr, col, val=None) -> Csr:
+        row_ptr = np.ascontiguousarray(row_ptr, dtype=np.int64)
+        col = np.ascontiguousarray(col, dtype=np.int32)
+        if val is not None:
+            val = np.ascontiguousarray(val)
+            assert val.dtype.itemsize == 4
+        h = C.c_void_p()
+        _ck(lib.shb_csr_create(self.h, n_rows, n_cols, len(col), _ptr(row_ptr), _ptr(col), _ptr(val), 4, C.byref(h), None))
+        return Csr(self, h)
+
+    def synth_uniform(self, n_rows, n_cols, k=16, seed=0x5EED0002, val_mode=0, row_begin=0, row_count=None) -> Csr:
+        row_count = n_rows - row_begin if row_count is None else row_count
+        h = C.c_void_p()
+        _ck(lib.shb_synth_uniform(self.h, n_rows, n_cols, k, seed, val_mode, row_begin, row_count, C.byref(h)))
+        return Csr(self, h)
+
+    def synth_vector(self, n, seed=0x5EED0003, mode=0) -> Buffer:
+        b = self.empty(max(n, 1) * 4)
+        _ck(lib.shb_synth_vector(self.h, b.h, n, seed, mode))
+        return b
+
+    def synth_rmat(self, scale, edgefactor=16, seed=0x5EED0024, symmetrise=True, value_mode=0, damping=0.85) -> Csr:
+        h = C.c_void_p()
+        _ck(lib.shb_synth_rmat(self.h, scale, (1 << scale) * edgefactor, seed, int(symmetrise), value_mode, damping,
+                               C.byref(h)))
+        return Csr(self, h)
+
+    def synth_grid2d(self, w, h_, seed=0x5EED0004) -> Csr:
+        h = C.c_void_p()
+        _ck(lib.shb_synth_grid2d(self.h, w, h_, seed, C.byref(h)))
+        return Csr(self, h)
+
+    # ---- the hot path
+    def spmv(self, A: Csr, semiring, x: Buffer, y: Buffer | None, alpha, beta, out: Buffer, cfg: LaunchCfg | None = None,
+             timed: bool = True) -> int:
+        a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
+        ns = C.c_uint64(0)
+        _ck(lib.shb_spmv(self.h, A.h, semiring, C.byref(cfg) if cfg else None, x.h, y.h if y else None, _ptr(a), _ptr(b),
+                         out.h, C.byref(ns) if timed else None))
+        return ns.value
+
+    def spmv_host(self, A: Csr, semiring, x: np.ndarray, y: np.ndarray | None, alpha, beta, out: np.ndarray,
+                  cfg: LaunchCfg | None = None):
+        a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
+        tot, ker = C.c_uint64(0), C.c_uint64(0)
+        _ck(lib.shb_spmv_host(self.h, A.h, semiring, C.byref(cfg) if cfg else None, _ptr(x), _ptr(y), _ptr(a), _ptr(b),
+                              _ptr(out), C.byref(tot), C.byref(ker)))
+        return tot.value, ker.value
+
+    def spmv_scatter(self, A: Csr, semiring, x: Buffer, y: Buffer | None, alpha, beta, dst: list[Buffer], row_offset,
+                     delta=0.0, term=TERM_ABSDIFF, changed: Buffer | None = None, cfg: LaunchCfg | None = None,
+                     timed=False) -> int:
+        a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
+        arr = (C.c_void_p * len(dst))(*[d.h for d in dst])
+        ns = C.c_uint64(0)
+        _ck(lib.shb_spmv_scatter(self.h, A.h, semiring, C.byref(cfg) if cfg else None, x.h, y.h if y else None, _ptr(a),
+                                 _ptr(b), arr, len(dst), row_offset, delta, term, changed.h if changed else None,
+                                 C.byref(ns) if timed else None))
+        return ns.value
+
+    def iterate(self, A: Csr, semiring, x: Buffer, y0: Buffer | None, alpha, beta, work: Buffer, delta=1e-4, term=None,
+                y_rebind=True, max_iters=1000, check_every=16, per_iter=False, cfg: LaunchCfg | None = None):
+        """Returns (result_buffer, n_iters, total_ns, per_iter_ns|None, converged)."""
+        term = (TERM_ABSDIFF if semiring in (PLUS_TIMES, MIN_PLUS) else TERM_EQUAL) if term is None else term
+        a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
+        n_it, in_work, tot = C.c_uint32(0), C.c_int(0), C.c_uint64(0)
+        per = np.zeros(max_iters, dtype=np.uint64) if per_iter else None
+        st = lib.shb_iterate(self.h, A.h, semiring, C.byref(cfg) if cfg else None, x.h, y0.h if y0 else None, _ptr(a),
+                             _ptr(b), work.h, delta, term, int(y_rebind), max_iters, check_every,
+                             per.ctypes.data_as(_capi.u64p) if per is not None else None, C.byref(n_it),
+                             C.byref(in_work), C.byref(tot))
+        if st not in (0, 7):
+            raise ShbError(st)
+        res = work if in_work.value else x
+        return res, n_it.value, tot.value, (per[: n_it.value] if per is not None else None), st == 0
+
+    def bfs(self, A: Csr, root=0, AT: Csr | None = None, max_levels=0):
+        levels = self.empty(A.info.n_rows * 4)
+        st = GraphStats()
+        _ck(lib.shb_bfs(self.h, A.h, AT.h if AT else None, root, levels.h, max_levels, C.byref(st)))
+        return levels, st
+
+    def sssp(self, A: Csr, source=0, AT: Csr | None = None, max_rounds=0):
+        dist = self.empty(A.info.n_rows * 4)
+        st = GraphStats()
+        _ck(lib.shb_sssp(self.h, A.h, AT.h if AT else None, source, dist.h, max_rounds, C.byref(st)))
+        return dist, st
+
+    def pagerank(self, A: Csr, damping=0.85, delta=1e-4, max_iters=1000, check_every=8, cfg: LaunchCfg | None = None):
+        n = A.info.n_rows
+        x, work = self.empty(n * 4), self.empty(n * 4)
+        x_init = np.float32(1.0) / np.float32(n)
+        beta = (np.float32(1.0) - np.float32(damping)) / np.float32(n)
+        in_work = C.c_int(0)
+        st = GraphStats()
+        s = lib.shb_pagerank(self.h, A.h, C.byref(cfg) if cfg else None, x.h, work.h, C.c_float(x_init), C.c_float(beta),
+                             delta, max_iters, check_every, C.byref(in_work), C.byref(st))
+        if s not in (0, 7):
+            raise ShbError(s)
+        return (work if in_work.value else x), st
+
+    def close(self):
+        if self.h:
+            lib.shb_ctx_destroy(self.h)
+            self.h = None

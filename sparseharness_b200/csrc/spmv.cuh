@@ -1,0 +1,335 @@
+// spmv.cuh -- the hot path: hand-written sm_100a semiring CSR SpMV kernels.
+//
+// Replaces the Lift-generated OpenCL "KERNEL" of the reference (example/<alg>/kernel{,2..7}.json:3):
+//   out[r] = epi( (+)_k mult( guard(x, col[k]), val[k] ), alpha, y[r], beta )
+// Three schedules, all templated on the semiring:
+//   spmv_scalar_kernel  thread per row, forward (or reversed) sequential order == the reference's
+//                       glb-sdp / glb-sdp-rsa schedules (kernel5/6.json) and the gold loop order
+//   spmv_vector_kernel  sub-warp of L lanes per row, R rows in flight per sub-warp, 128-bit
+//                       coalesced loads of col/val for the 16-byte aligned body of a row, scalar
+//                       predicated loads for the <=3-element head and tail, shuffle reduction,
+//                       fused epilogue + convergence test + (multi-GPU) scatter to peer buffers
+//   spmv_stream_kernel  nnz-split tiles (perfect load balance for power-law rows): a CTA streams
+//                       SHB_TILE_NNZ consecutive non-zeros, multiplies, parks the products in
+//                       padded shared memory, then reduces the rows of the tile (thread per short
+//                       row piece, warp per long piece); pieces of rows that straddle tiles go to
+//                       carry buffers and are combined in tile order by spmv_fixup_kernel
+//                       (deterministic: no float atomics)
+// Padding entries (col = -1) gather ZERO, and mult(ZERO, v) is the additive identity in all four
+// semirings -- the same property the reference's ELL padding relies on (src/sparse_matrix.cpp:318-328).
+#pragma once
+#include "ldst.cuh"
+#include "semiring.cuh"
+#include "shb_internal.cuh"
+
+#define SHB_MAX_DST 8
+
+template <class T> struct SpmvArgs {
+  const int32_t *row_ptr;
+  const int32_t *col;
+  const T *val;  // nullptr = pattern
+  const T *x;
+  const T *y;    // indexed by row_offset + r
+  T alpha, beta;
+  T *out[SHB_MAX_DST];  // every destination receives out[row_offset + r]
+  int n_out;
+  int use_y;            // 0: epilogue ignores y, 1: read y[row_offset + r], 2: y is the semiring one everywhere
+  int reversed;         // scalar kernel only: accumulate from the row's last entry to its first
+  int64_t row_offset;
+  int64_t n_rows;
+  uint32_t vlength;
+  IterCtl ctl;
+};
+
+template <class S>
+__device__ __forceinline__ void shb_finish_row(const SpmvArgs<typename S::T> &a, int64_t r, typename S::T dp,
+                                               bool &differs) {
+  typedef typename S::T T;
+  const int64_t gr = a.row_offset + r;
+  const T yv = a.use_y == 1 ? a.y[gr] : (a.use_y == 2 ? S::one() : S::zero());
+  const T o = S::epi(dp, a.alpha, yv, a.beta);
+#pragma unroll 1
+  for (int i = 0; i < a.n_out; ++i) a.out[i][gr] = o;
+  if (a.ctl.changed) differs |= shb_row_differs(a.x[gr], o, a.ctl.delta, a.ctl.term_mode);
+}
+
+__device__ __forceinline__ void shb_publish_changed(const IterCtl &ctl, bool differs) {
+  if (ctl.changed) {
+    const bool any = __any_sync(0xffffffffu, differs);
+    if (any && (threadIdx.x & 31) == 0 && shb_ld_volatile_u32(ctl.changed) == 0) *ctl.changed = 1u;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// scalar: thread per row
+// ---------------------------------------------------------------------------------------------
+template <class S, bool HAS_VAL>
+__global__ void __launch_bounds__(256) spmv_scalar_kernel(const __grid_constant__ SpmvArgs<typename S::T> a) {
+  typedef typename S::T T;
+  if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
+  bool differs = false;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n_padded = (a.n_rows + 31) / 32 * 32;  // keep warps converged for the ballot
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += stride) {
+    if (r < a.n_rows) {
+      const int s = a.row_ptr[r], e = a.row_ptr[r + 1];
+      T acc = S::zero();
+      for (int i = 0; i < e - s; ++i) {
+        const int k = a.reversed ? (e - 1 - i) : (s + i);
+        const int32_t c = __ldg(a.col + k);
+        const T xv = ((uint32_t)c < a.vlength) ? __ldg(a.x + c) : S::zero();
+        const T v = HAS_VAL ? __ldg(a.val + k) : S::one();
+        acc = S::add(acc, S::mult(xv, v));
+      }
+      shb_finish_row<S>(a, r, acc, differs);
+    }
+  }
+  shb_publish_changed(a.ctl, differs);
+}
+
+// ---------------------------------------------------------------------------------------------
+// vector: L lanes per row, R rows in flight per lane group
+// ---------------------------------------------------------------------------------------------
+template <class S, int L, int R, bool HAS_VAL, bool HINTS>
+__global__ void __launch_bounds__(256) spmv_vector_kernel(const __grid_constant__ SpmvArgs<typename S::T> a) {
+  typedef typename S::T T;
+  if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
+  constexpr int G = 32 / L;  // rows handled side by side in one warp
+  constexpr int ROWS_PER_WARP = G * R;
+  const int lane = threadIdx.x & 31;
+  const int g = lane / L, li = lane % L;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t base = warp * ROWS_PER_WARP;
+  const uint64_t pol_stream = HINTS ? shb_policy_evict_first() : 0ull;
+  const uint64_t pol_keep = HINTS ? shb_policy_evict_last() : 0ull;
+  const uint32_t zbits = shb_bits<T>(S::zero());
+  const uint32_t obits = shb_bits<T>(S::one());
+
+  int s[R], e[R], ha[R], tb[R];
+  T acc[R];
+#pragma unroll
+  for (int j = 0; j < R; ++j) {
+    const int64_t r = base + (int64_t)j * G + g;
+    const bool valid = r < a.n_rows;
+    s[j] = valid ? __ldg(a.row_ptr + r) : 0;
+    e[j] = valid ? __ldg(a.row_ptr + r + 1) : 0;
+    ha[j] = min(e[j], (s[j] + 3) & ~3);  // end of the unaligned head
+    tb[j] = max(ha[j], e[j] & ~3);       // start of the unaligned tail
+    acc[j] = S::zero();
+  }
+
+  // head + tail: at most 3 + 3 scalar elements per row, spread over the lanes of the group
+  constexpr int EDGE_STEPS = (6 + L - 1) / L;
+#pragma unroll
+  for (int k = 0; k < EDGE_STEPS; ++k) {
+    uint32_t cb[R], vb[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const int idx = k * L + li;
+      const int nh = ha[j] - s[j];
+      const int pos = idx < nh ? s[j] + idx : tb[j] + (idx - nh);
+      const bool p = pos < e[j];
+      cb[j] = shb_ld_stream_b32<HINTS>(a.col + pos, p, 0xffffffffu, pol_stream);
+      vb[j] = HAS_VAL ? shb_ld_stream_b32<HINTS>(a.val + pos, p, zbits, pol_stream) : obits;
+    }
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const T xv = shb_from_bits<T>(shb_gather_b32<HINTS>(a.x, (int32_t)cb[j], a.vlength, zbits, pol_keep));
+      acc[j] = S::add(acc[j], S::mult(xv, shb_from_bits<T>(vb[j])));
+    }
+  }
+
+  // aligned body: 128-bit loads, 4 elements per lane per step
+  int p[R];
+  bool more = false;
+#pragma unroll
+  for (int j = 0; j < R; ++j) {
+    p[j] = ha[j] + 4 * li;
+    more |= (p[j] + 4 <= tb[j]);
+  }
+  while (more) {
+    more = false;
+    uint4 c4[R], v4[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const bool pr = p[j] + 4 <= tb[j];
+      c4[j] = shb_ld_stream_v4<HINTS>(a.col + p[j], pr, 0xffffffffu, pol_stream);
+      if (HAS_VAL) v4[j] = shb_ld_stream_v4<HINTS>(a.val + p[j], pr, zbits, pol_stream);
+      else v4[j] = make_uint4(obits, obits, obits, obits);
+    }
+    uint32_t xb[R][4];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      xb[j][0] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[j].x, a.vlength, zbits, pol_keep);
+      xb[j][1] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[j].y, a.vlength, zbits, pol_keep);
+      xb[j][2] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[j].z, a.vlength, zbits, pol_keep);
+      xb[j][3] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[j].w, a.vlength, zbits, pol_keep);
+    }
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      acc[j] = S::add(acc[j], S::mult(shb_from_bits<T>(xb[j][0]), shb_from_bits<T>(v4[j].x)));
+      acc[j] = S::add(acc[j], S::mult(shb_from_bits<T>(xb[j][1]), shb_from_bits<T>(v4[j].y)));
+      acc[j] = S::add(acc[j], S::mult(shb_from_bits<T>(xb[j][2]), shb_from_bits<T>(v4[j].z)));
+      acc[j] = S::add(acc[j], S::mult(shb_from_bits<T>(xb[j][3]), shb_from_bits<T>(v4[j].w)));
+      p[j] += 4 * L;
+      more |= (p[j] + 4 <= tb[j]);
+    }
+  }
+
+  // butterfly reduction inside each lane group: afterwards every lane of the group holds the row sum
+#pragma unroll
+  for (int j = 0; j < R; ++j) {
+#pragma unroll
+    for (int off = L / 2; off > 0; off >>= 1) acc[j] = S::add(acc[j], __shfl_xor_sync(0xffffffffu, acc[j], off));
+  }
+
+  // epilogue: lane li of group g finishes the rows j with j % L == li, so the warp's stores cover
+  // ROWS_PER_WARP consecutive rows
+  bool differs = false;
+  if (R <= L) {
+    T mine = acc[0];
+#pragma unroll
+    for (int j = 1; j < R; ++j)
+      if (li == j) mine = acc[j];
+    const int64_t r = base + (int64_t)li * G + g;
+    if (li < R && r < a.n_rows) shb_finish_row<S>(a, r, mine, differs);
+  } else {
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const int64_t r = base + (int64_t)j * G + g;
+      if ((j % L) == li && r < a.n_rows) shb_finish_row<S>(a, r, acc[j], differs);
+    }
+  }
+  shb_publish_changed(a.ctl, differs);
+}
+
+// ---------------------------------------------------------------------------------------------
+// stream: nnz-split tiles through shared memory
+// ---------------------------------------------------------------------------------------------
+#define SHB_STREAM_THREADS 256
+#define SHB_LONG_PIECE 64
+__device__ __forceinline__ int shb_pad(int i) { return i + (i >> 5); }  // 1 pad word per 32: conflict-free strides
+
+template <class S, bool HAS_VAL, bool HINTS>
+__global__ void __launch_bounds__(SHB_STREAM_THREADS)
+    spmv_stream_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, const int32_t *__restrict__ tile_row,
+                       int n_tiles, int32_t nnz, typename S::T *__restrict__ carry_tail,
+                       typename S::T *__restrict__ carry_head) {
+  typedef typename S::T T;
+  if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
+  __shared__ T prod[SHB_TILE_NNZ + SHB_TILE_NNZ / 32];
+  __shared__ int long_rows[SHB_TILE_NNZ / SHB_LONG_PIECE + 2];
+  __shared__ int n_long;
+  const int tid = threadIdx.x;
+  const int t = blockIdx.x;
+  const int lo = t * SHB_TILE_NNZ;
+  const int hi = min(nnz, lo + SHB_TILE_NNZ);
+  const uint64_t pol_stream = HINTS ? shb_policy_evict_first() : 0ull;
+  const uint64_t pol_keep = HINTS ? shb_policy_evict_last() : 0ull;
+  const uint32_t zbits = shb_bits<T>(S::zero());
+  const uint32_t obits = shb_bits<T>(S::one());
+  if (tid == 0) n_long = 0;
+
+  // phase 1: stream the tile's non-zeros (the arrays are padded to a tile multiple with col = -1)
+  constexpr int STEPS = SHB_TILE_NNZ / (SHB_STREAM_THREADS * 4);
+  uint4 c4[STEPS], v4[STEPS];
+#pragma unroll
+  for (int k = 0; k < STEPS; ++k) {
+    const int i = lo + 4 * (tid + SHB_STREAM_THREADS * k);
+    c4[k] = shb_ld_stream_v4<HINTS>(a.col + i, true, 0xffffffffu, pol_stream);
+    if (HAS_VAL) v4[k] = shb_ld_stream_v4<HINTS>(a.val + i, true, zbits, pol_stream);
+    else v4[k] = make_uint4(obits, obits, obits, obits);
+  }
+  uint32_t xb[STEPS][4];
+#pragma unroll
+  for (int k = 0; k < STEPS; ++k) {
+    xb[k][0] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[k].x, a.vlength, zbits, pol_keep);
+    xb[k][1] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[k].y, a.vlength, zbits, pol_keep);
+    xb[k][2] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[k].z, a.vlength, zbits, pol_keep);
+    xb[k][3] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[k].w, a.vlength, zbits, pol_keep);
+  }
+#pragma unroll
+  for (int k = 0; k < STEPS; ++k) {
+    const int i = 4 * (tid + SHB_STREAM_THREADS * k);
+    prod[shb_pad(i + 0)] = S::mult(shb_from_bits<T>(xb[k][0]), shb_from_bits<T>(v4[k].x));
+    prod[shb_pad(i + 1)] = S::mult(shb_from_bits<T>(xb[k][1]), shb_from_bits<T>(v4[k].y));
+    prod[shb_pad(i + 2)] = S::mult(shb_from_bits<T>(xb[k][2]), shb_from_bits<T>(v4[k].z));
+    prod[shb_pad(i + 3)] = S::mult(shb_from_bits<T>(xb[k][3]), shb_from_bits<T>(v4[k].w));
+  }
+  __syncthreads();
+
+  // phase 2: the rows of this tile.  Row r's piece is [max(s,lo), min(e,hi)).
+  const int r_first = tile_row[t];
+  const int r_last = (t + 1 < n_tiles) ? tile_row[t + 1] : (int)(a.n_rows - 1);
+  bool differs = false;
+  const int n_iter = (r_last - r_first + 1 + SHB_STREAM_THREADS - 1) / SHB_STREAM_THREADS;
+  for (int it = 0; it < n_iter; ++it) {
+    const int r = r_first + it * SHB_STREAM_THREADS + tid;
+    if (r <= r_last) {
+      const int s = a.row_ptr[r], e = a.row_ptr[r + 1];
+      if (e == s) {
+        // empty row: owned by the tile with lo < s <= hi (or tile 0 when s == 0)
+        if ((s > lo && s <= hi) || (s == 0 && t == 0)) shb_finish_row<S>(a, r, S::zero(), differs);
+      } else {
+        const int ps = max(s, lo), pe = min(e, hi);
+        if (pe > ps) {
+          if (pe - ps > SHB_LONG_PIECE) {
+            long_rows[atomicAdd(&n_long, 1)] = r;
+          } else {
+            T acc = S::zero();
+            for (int k = ps; k < pe; ++k) acc = S::add(acc, prod[shb_pad(k - lo)]);
+            if (s >= lo && e <= hi) shb_finish_row<S>(a, r, acc, differs);
+            else if (e > hi) carry_tail[t] = acc;  // continues into the next tile
+            else carry_head[t] = acc;               // started in an earlier tile, ends here
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  // phase 3: long pieces, one warp each (lanes stride, butterfly reduce)
+  const int nl = n_long;
+  for (int q = tid >> 5; q < nl; q += SHB_STREAM_THREADS / 32) {
+    const int r = long_rows[q];
+    const int s = a.row_ptr[r], e = a.row_ptr[r + 1];
+    const int ps = max(s, lo), pe = min(e, hi);
+    T acc = S::zero();
+    for (int k = ps + (tid & 31); k < pe; k += 32) acc = S::add(acc, prod[shb_pad(k - lo)]);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) acc = S::add(acc, __shfl_xor_sync(0xffffffffu, acc, off));
+    if ((tid & 31) == 0) {
+      if (s >= lo && e <= hi) shb_finish_row<S>(a, r, acc, differs);
+      else if (e > hi) carry_tail[t] = acc;
+      else carry_head[t] = acc;
+    }
+  }
+  shb_publish_changed(a.ctl, differs);
+}
+
+// Rows that straddle tile boundaries: the tile in which such a row ENDS (t >= 1, row = tile_row[t],
+// s < lo, e <= hi) combines carry_tail of the tiles it crossed, in tile order, with its own head.
+template <class S>
+__global__ void __launch_bounds__(256)
+    spmv_fixup_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, const int32_t *__restrict__ tile_row,
+                      int n_tiles, int32_t nnz, const typename S::T *carry_tail, const typename S::T *carry_head) {
+  typedef typename S::T T;
+  if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
+  bool differs = false;
+  const int n_padded = (n_tiles + 31) / 32 * 32;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_padded; t += gridDim.x * blockDim.x) {
+    if (t >= 1 && t < n_tiles) {
+      const int lo = t * SHB_TILE_NNZ;
+      const int hi = min(nnz, lo + SHB_TILE_NNZ);
+      const int r = tile_row[t];
+      const int s = a.row_ptr[r], e = a.row_ptr[r + 1];
+      if (s < lo && e > lo && e <= hi) {
+        const int t0 = s / SHB_TILE_NNZ;
+        T acc = carry_tail[t0];
+        for (int tt = t0 + 1; tt < t; ++tt) acc = S::add(acc, carry_tail[tt]);
+        acc = S::add(acc, carry_head[t]);
+        shb_finish_row<S>(a, r, acc, differs);
+      }
+    }
+  }
+  shb_publish_changed(a.ctl, differs);
+}

@@ -1,0 +1,87 @@
+"""-m gpu: BASELINE.json's full-size configurations, checked through size-independent properties
+(the oracle would need minutes on them): sampled row blocks against the oracle, agreement of
+independent schedules, and graph invariants."""
+import numpy as np
+import pytest
+
+import sparseharness_b200 as shb
+
+pytestmark = pytest.mark.gpu
+N2 = 1 << 24  # config 2: 16M rows x 16 nnz/row
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = shb.Context(0)
+    yield c
+    c.close()
+
+
+def test_config2_full_size_spmv(ctx, orc):
+    out = ctx.empty(N2 * 4)
+    for val_mode, xmode in ((1, 1), (0, 0)):  # integer-valued (exact) and uniform[-1,1) floats (1e-5)
+        A = ctx.synth_uniform(N2, N2, 16, val_mode=val_mode)
+        info = A.info
+        assert info.nnz == N2 * 16 and info.algorithmic_bytes_spmv == 2348810244 and info.max_row_len == 16
+        x = ctx.synth_vector(N2, mode=xmode)
+        xh = x.download(np.float32, N2)
+        results = {}
+        for label, cfg in (("auto", {}), ("scalar", dict(variant=shb.VARIANT_SCALAR)),
+                           ("stream", dict(variant=shb.VARIANT_STREAM)), ("vector8", dict(variant=shb.VARIANT_VECTOR, lanes=8))):
+            out.fill_u32(0xDEADBEEF)
+            ctx.spmv(A, shb.PLUS_TIMES, x, None, 1.0, 0.0, out, shb.launch_cfg(**cfg))
+            results[label] = out.download(np.float32, N2)
+        # sampled row blocks against the oracle (first, middle, last)
+        for begin in (0, N2 // 2 - 1234, N2 - 4096):
+            rp, col, val = A.download(begin, 4096)
+            orp, ocol, oval = orc.gen_uniform(N2, N2, 16, val_mode=val_mode, row_begin=begin, row_count=4096)
+            assert np.array_equal(col, ocol) and np.array_equal(val.view(np.int32), oval.view(np.int32))
+            want = orc.spmv(orc.PLUS_TIMES, rp, col, val, xh, np.zeros(4096, np.float32), 1.0, 0.0)
+            for label, r in results.items():
+                got = r[begin:begin + 4096]
+                if val_mode == 1 or label in ("scalar", "stream"):
+                    assert np.array_equal(got, want), (label, begin)
+                else:
+                    assert np.abs(got - want).max() <= 1e-5 * np.abs(want).max(), (label, begin)
+        # independent schedules agree on ALL 16M rows
+        assert np.array_equal(results["scalar"], results["stream"])
+        if val_mode == 1:
+            assert np.array_equal(results["auto"], results["scalar"]) and np.array_equal(results["vector8"], results["scalar"])
+            assert results["scalar"].astype(np.float64).sum() == results["auto"].astype(np.float64).sum()
+        else:
+            s = np.abs(results["scalar"]).max()
+            assert np.abs(results["auto"] - results["scalar"]).max() <= 1e-5 * s
+            assert np.abs(results["vector8"] - results["scalar"]).max() <= 1e-5 * s
+        A.free(); x.free()
+
+
+def test_config4_grid_sssp_against_dijkstra_4m_vertices(ctx, orc):
+    """2048 x 2048 slice of config 4's grid family: frontier SSSP == CPU Dijkstra bit for bit, and
+    distances satisfy the Bellman optimality conditions (size-independent property)."""
+    W = H = 2048
+    G = ctx.synth_grid2d(W, H)
+    dist, st = ctx.sssp(G, 0, AT=G)
+    n = W * H
+    d = dist.download(np.float32, n)
+    rp, col, val = G.download()
+    assert st.converged and st.reached == n and st.edges_traversed == len(col)
+    assert np.array_equal(d, orc.sssp(rp, col, val, 0))
+    # optimality: d[r] == min_k d[col k] + w_k for r != source, and no edge can relax further
+    cand = d[col] + val
+    rowmin = np.minimum.reduceat(cand, rp[:-1])
+    assert d[0] == 0 and np.array_equal(rowmin[1:], d[1:])
+
+
+def test_config3_bfs_scale20_properties(ctx, orc):
+    """RMAT scale 20 (config 3's family): levels == CPU queue BFS; every edge spans at most one level."""
+    A = ctx.synth_rmat(20, 16, seed=orc.SEED_C3, symmetrise=True)
+    rp, col, _ = A.download()
+    n = len(rp) - 1
+    root = int(np.argmax(np.diff(rp) > 0))
+    levels, st = ctx.bfs(A, root, AT=A)
+    lv = levels.download(np.int32, n)
+    want, nlev, edges = orc.bfs_levels(rp, col, None, root)
+    assert np.array_equal(lv, want) and st.iterations == nlev and st.edges_traversed == edges
+    rows = np.repeat(np.arange(n), np.diff(rp))
+    reached = lv[rows] >= 0
+    assert (lv[col][reached] >= 0).all() and np.abs(lv[rows][reached] - lv[col][reached]).max() <= 1

@@ -1,0 +1,173 @@
+"""-m gpu: device-resident fixed-point loops and graph drivers against the CPU oracle (bit-exact for
+BFS levels, min-plus distances, max-min labels; 1e-5 relative for PageRank)."""
+import numpy as np
+import pytest
+
+import sparseharness_b200 as shb
+from gpu_util import ALL_CFGS, random_ragged
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = shb.Context(0)
+    yield c
+    c.close()
+
+
+def _iterate(ctx, A, semiring, x0, y0, alpha, beta, dt, **kw):
+    n = len(x0)
+    xb, yb, wb = ctx.array(x0.astype(dt)), ctx.array(y0.astype(dt)), ctx.empty(n * 4)
+    wb.zero()
+    res, iters, total_ns, per, ok = ctx.iterate(A, semiring, xb, yb, alpha, beta, wb, **kw)
+    return res.download(dt, n), iters, per, ok
+
+
+def test_sssp_example_faithful_iteration(ctx, orc, mtx_dir):
+    """scripts/example/sssp.sh: sssp_harness on matrix3, x = y = (0, FLT_MAX...), alpha = beta = 0,
+    loop of app/sssp.cpp:112-153 with y re-bound to the input; same result AND same launch count."""
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir["Trefethen_20"], "float")
+    x0 = np.full(n, orc.FLT_MAX, np.float32); x0[0] = 0
+    want, want_iters = orc.iterate(orc.MIN_PLUS, rp, col, val, x0, x0.copy(), 0.0, 0.0, delta=1e-4)
+    A = ctx.csr(n, n, rp, col, val)
+    for check_every in (1, 3, 16):
+        for label, cfg in ALL_CFGS[:6]:
+            got, iters, per, ok = _iterate(ctx, A, shb.MIN_PLUS, x0, x0.copy(), 0.0, 0.0, np.float32, delta=1e-4,
+                                           check_every=check_every, per_iter=True, cfg=shb.launch_cfg(**cfg))
+            assert ok and iters == want_iters and len(per) == iters and (per > 0).all(), (label, check_every)
+            assert np.array_equal(got, want), (label, check_every)
+
+
+@pytest.mark.parametrize("name", ["1138_bus", "GD96_b", "arc130", "ca-AstroPh"])
+def test_faithful_loops_all_apps(ctx, orc, mtx_dir, name):
+    cap = 40
+    # bfs (app/bfs.cpp:209-216: x = y = e_0, alpha 1, beta 0; stop on equality; may never stop -> cap, Q8)
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir[name], "int")
+    x0 = np.zeros(n, np.int32); x0[0] = 1
+    want, wi = orc.iterate(orc.OR_AND, rp, col, val, x0, x0.copy(), 1, 0, max_iters=cap)
+    A = ctx.csr(n, n, rp, col, val)
+    got, gi, _, ok = _iterate(ctx, A, shb.OR_AND, x0, x0.copy(), 1, 0, np.int32, max_iters=cap, check_every=7)
+    assert gi == wi and np.array_equal(got, want) and (ok or wi == cap)
+    # scc (app/scc.cpp:197-222: x[i] = i, y = INT_MIN, alpha INT_MAX, beta INT_MIN, scc_normalise)
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir[name], "int", normalise="scc")
+    x0 = np.arange(n, dtype=np.int32); y0 = np.full(n, orc.INT_MIN, np.int32)
+    want, wi = orc.iterate(orc.MAX_MIN, rp, col, val, x0, y0, orc.INT_MAX, orc.INT_MIN, max_iters=cap)
+    A = ctx.csr(n, n, rp, col, val)
+    got, gi, _, _ = _iterate(ctx, A, shb.MAX_MIN, x0, y0, int(orc.INT_MAX), int(orc.INT_MIN), np.int32, max_iters=cap)
+    assert gi == wi and np.array_equal(got, want)
+    # pr (app/pr.cpp:182-201: x = 1/N, y = 1, alpha 1, beta (1-d)/N, pagerank_normalise then Q2 truncation, y re-bound)
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir[name], "float", normalise="pr")
+    x0 = np.full(n, np.float32(1.0) / np.float32(n), np.float32); y0 = np.ones(n, np.float32)
+    beta = (np.float32(1.0) - np.float32(0.85)) / np.float32(n)
+    want, wi = orc.iterate(orc.PLUS_TIMES, rp, col, val, x0, y0, 1.0, beta, delta=1e-4, max_iters=cap)
+    A = ctx.csr(n, n, rp, col, val)
+    got, gi, _, _ = _iterate(ctx, A, shb.PLUS_TIMES, x0, y0, 1.0, float(beta), np.float32, delta=1e-4, max_iters=cap,
+                             cfg=shb.launch_cfg(variant=shb.VARIANT_SCALAR))
+    assert gi == wi and np.array_equal(got.view(np.int32), want.view(np.int32))
+    # sssp
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir[name], "float")
+    x0 = np.full(n, orc.FLT_MAX, np.float32); x0[0] = 0
+    want, wi = orc.iterate(orc.MIN_PLUS, rp, col, val, x0, x0.copy(), 0.0, 0.0, delta=1e-4, max_iters=400)
+    A = ctx.csr(n, n, rp, col, val)
+    got, gi, _, _ = _iterate(ctx, A, shb.MIN_PLUS, x0, x0.copy(), 0.0, 0.0, np.float32, delta=1e-4, max_iters=400)
+    assert gi == wi and np.array_equal(got, want)
+    # frontier-aware SSSP reaches the same fixed point as the dense sweeps and as Dijkstra, bit for bit
+    dist, st = ctx.sssp(A, 0)
+    d = dist.download(np.float32, n)
+    assert st.converged and np.array_equal(d, orc.sssp(rp, col, val, 0))
+    if wi < 400:
+        assert np.array_equal(d, want)
+
+
+def test_iteration_cap_reports_not_converged(ctx, orc):
+    # 2-cycle: or-and walk parity never settles (Q8 / TODO.md:7-9) -> cap, status NOT_CONVERGED, no hang
+    rp = np.array([0, 1, 2], np.int64); col = np.array([1, 0], np.int32); val = np.ones(2, np.int32)
+    A = ctx.csr(2, 2, rp, col, val)
+    x0 = np.array([1, 0], np.int32)
+    got, iters, _, ok = _iterate(ctx, A, shb.OR_AND, x0, x0.copy(), 1, 0, np.int32, max_iters=11, check_every=4)
+    assert not ok and iters == 11
+    want, wi = orc.iterate(orc.OR_AND, rp, col, val, x0, x0.copy(), 1, 0, max_iters=11)
+    assert wi == 11 and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("with_transpose", [False, True])
+@pytest.mark.parametrize("scale,ef", [(8, 4), (13, 16)])
+def test_bfs_levels_rmat(ctx, orc, scale, ef, with_transpose):
+    A = ctx.synth_rmat(scale, ef, seed=orc.SEED_C3, symmetrise=True)
+    rp, col, _ = A.download()
+    deg = np.diff(rp)
+    root = int(np.argmax(deg > 0))
+    want, nlev, edges = orc.bfs_levels(rp, col, None, root)
+    levels, st = ctx.bfs(A, root, AT=A if with_transpose else None)  # symmetric: A is its own transpose
+    got = levels.download(np.int32, len(rp) - 1)
+    assert np.array_equal(got, want)
+    assert st.converged and st.iterations == nlev and st.reached == int((want >= 0).sum()) and st.edges_traversed == edges
+
+
+def test_bfs_directed_with_zero_valued_edges(ctx, orc):
+    rng = np.random.default_rng(8)
+    n = 1500
+    rp, col = random_ragged(rng, n, n, mean_len=3, long_rows=[(7, 900)], empty_frac=0.2)
+    val = (rng.random(len(col)) < 0.8).astype(np.int32) * rng.integers(1, 5, len(col)).astype(np.int32)
+    A = ctx.csr(n, n, rp, col, val)
+    want, nlev, edges = orc.bfs_levels(rp, col, val, 3)
+    for AT in (None, A.transpose()):
+        levels, st = ctx.bfs(A, 3, AT=AT)
+        assert np.array_equal(levels.download(np.int32, n), want) and st.iterations == nlev
+
+
+def test_sssp_grid_and_directed(ctx, orc):
+    G = ctx.synth_grid2d(96, 61)
+    rp, col, val = G.download()
+    n = len(rp) - 1
+    dist, st = ctx.sssp(G, 0, AT=G)  # symmetric weights: G is its own transpose
+    assert st.converged and st.reached == n and st.edges_traversed == len(col)
+    assert np.array_equal(dist.download(np.float32, n), orc.sssp(rp, col, val, 0))
+    # directed graph with non-integer weights: exact as well (monotone rounding)
+    rp, col, val = orc.gen_uniform(4000, 4000, 6)
+    A = ctx.csr(4000, 4000, rp, col, val)
+    dist, st = ctx.sssp(A, 5)
+    assert np.array_equal(dist.download(np.float32, 4000).view(np.int32), orc.sssp(rp, col, val, 5).view(np.int32))
+
+
+def test_pagerank_canonical(ctx, orc):
+    A = ctx.synth_rmat(12, 16, seed=orc.SEED_C5, symmetrise=False, value_mode=1)
+    rp, col, val = A.download()
+    n = len(rp) - 1
+    want, wi = orc.pagerank(rp, col, val, delta=1e-7, max_iters=300, acc_double=True)
+    wf, wif = orc.pagerank(rp, col, val, delta=1e-7, max_iters=300, acc_double=False)
+    for cfg in (None, shb.launch_cfg(variant=shb.VARIANT_SCALAR), shb.launch_cfg(variant=shb.VARIANT_STREAM)):
+        res, st = ctx.pagerank(A, delta=1e-7, max_iters=300, cfg=cfg)
+        got = res.download(np.float32, n)
+        assert st.converged and abs(int(st.iterations) - wif) <= 2
+        assert np.abs(got - want).max() <= 1e-5 * np.abs(want).max()
+        assert np.abs(got - wf).max() <= 1e-5 * np.abs(wf).max()
+    # the scalar schedule keeps the CPU loop's order: identical bits and identical sweep count
+    res, st = ctx.pagerank(A, delta=1e-7, max_iters=300, cfg=shb.launch_cfg(variant=shb.VARIANT_SCALAR))
+    assert st.iterations == wif and np.array_equal(res.download(np.float32, n).view(np.int32), wf.view(np.int32))
+
+
+def test_scatter_to_several_destinations_row_partitioned(ctx, orc):
+    """The multi-GPU kernel on one device: two row blocks with global column ids, each writing its
+    slice of the result into BOTH destination vectors (what every rank does over NVLink)."""
+    n = 6000
+    rp, col, val = orc.gen_uniform(n, n, 16, val_mode=1)
+    x = orc.xmode_vector(n, 1)
+    want = orc.spmv(orc.PLUS_TIMES, rp, col, val, x, x, 1.0, 0.5)
+    xb = ctx.array(x)
+    d0, d1 = ctx.empty(n * 4), ctx.empty(n * 4)
+    flag = ctx.empty(4); flag.zero()
+    cut = 2500
+    for lo, hi in ((0, cut), (cut, n)):
+        part = ctx.csr(hi - lo, n, rp[lo:hi + 1] - rp[lo], col[rp[lo]:rp[hi]], val[rp[lo]:rp[hi]])
+        ctx.spmv_scatter(part, shb.PLUS_TIMES, xb, None, 1.0, 0.5, [d0, d1], lo, delta=1e-4, changed=flag)
+    ctx.synchronize()
+    assert np.array_equal(d0.download(np.float32, n), want) and np.array_equal(d1.download(np.float32, n), want)
+    assert flag.download(np.uint32, 1)[0] == 1
+    # fixed point: x = out -> flag stays 0 (identity operator)
+    eye = ctx.csr(n, n, np.arange(n + 1), np.arange(n, dtype=np.int32), np.ones(n, np.float32))
+    flag.zero()
+    ctx.spmv_scatter(eye, shb.PLUS_TIMES, xb, None, 1.0, 0.0, [d0], 0, delta=1e-4, changed=flag)
+    ctx.synchronize()
+    assert flag.download(np.uint32, 1)[0] == 0 and np.array_equal(d0.download(np.float32, n), x)

@@ -40,7 +40,8 @@ def launch_cfg(variant=VARIANT_AUTO, lanes=0, rows_per_group=0, block_threads=0,
 
 
 def _scalar(semiring, v):
-    return np.array([v], dtype=_DTYPE[semiring])
+    # an unknown semiring id is rejected by the library (SHB_ERR_UNSUPPORTED), not here
+    return np.array([v], dtype=_DTYPE.get(semiring, np.float32))
 
 
 def _ptr(a):

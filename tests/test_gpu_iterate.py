@@ -64,7 +64,11 @@ def test_faithful_loops_all_apps(ctx, orc, mtx_dir, name):
     A = ctx.csr(n, n, rp, col, val)
     got, gi, _, _ = _iterate(ctx, A, shb.PLUS_TIMES, x0, y0, 1.0, float(beta), np.float32, delta=1e-4, max_iters=cap,
                              cfg=shb.launch_cfg(variant=shb.VARIANT_SCALAR))
-    assert gi == wi and np.array_equal(got.view(np.int32), want.view(np.int32))
+    # (on several fixtures the reference recurrence diverges to inf/NaN -- 'non-working' per TODO.md; the
+    #  device must diverge identically: same launch count, same values, NaN where the CPU has NaN)
+    assert gi == wi and np.array_equal(got, want, equal_nan=True)
+    fin = np.isfinite(want)
+    assert np.array_equal(got[fin].view(np.int32), want[fin].view(np.int32))
     # sssp
     n, _, rp, col, val = orc.mm_load_csr(mtx_dir[name], "float")
     x0 = np.full(n, orc.FLT_MAX, np.float32); x0[0] = 0

@@ -1,0 +1,10 @@
+#!/bin/bash
+# ncu evidence for the dominant kernel of bench.py (launch list + one full capture).  Plain run first.
+mkdir -p gpurun_out
+CMD="python bench.py --steps 5 --warmup 3 --extras 0 --cpu-steps 3"
+$CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -20 gpurun_out/plain.log; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
+echo "launch list rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:spmv_vector_kernel -s 3 -c 2 -o gpurun_out/prof_spmv $CMD > gpurun_out/ncu_full.log 2>&1
+echo "full capture rc=$?"
+ls -la gpurun_out

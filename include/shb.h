@@ -65,9 +65,11 @@ typedef enum {
 
 enum { SHB_F_NO_CACHE_HINTS = 1u, /* plain ld.global for every stream (A/B experiments)          */
        SHB_F_NO_Y_SKIP = 2u,      /* always read y, even when beta makes it irrelevant            */
-       SHB_F_REVERSED_ORDER = 4u  /* SCALAR: accumulate a row from its last entry to its first, the
+       SHB_F_REVERSED_ORDER = 4u, /* SCALAR: accumulate a row from its last entry to its first, the
                                      order of the ELL schedules (kernel{,3,5}.json write products
-                                     reversed into the temp buffer)                               */ };
+                                     reversed into the temp buffer)                               */
+       SHB_F_Y_IS_ONE = 8u        /* y is the semiring one in every element (canonical PageRank's
+                                     y == 1, app/pr.cpp:183): the y argument is not read          */ };
 
 typedef struct {
   int32_t variant;        /* shb_variant                                                          */
@@ -132,6 +134,11 @@ int shb_csr_get_info(const shb_csr *csr, shb_csr_info *info);
 int shb_csr_download(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int64_t row_count,
                      int64_t *row_ptr /* row_count+1, rebased to 0 */, int32_t *col_idx, void *vals);
 int shb_csr_transpose(shb_ctx *ctx, const shb_csr *csr, shb_csr **transposed); /* push-side adjacency */
+/* 1-D row partition: row_bounds[0..parts] with row_bounds[k] = first row whose prefix nnz
+ * reaches k*nnz/parts (contiguous blocks balanced by non-zeros); slice_rows copies one block, on the
+ * device, into an operator of its own that keeps GLOBAL column ids. */
+int shb_csr_balance_rows(shb_ctx *ctx, const shb_csr *csr, int parts, int64_t *row_bounds);
+int shb_csr_slice_rows(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int64_t row_count, shb_csr **slice);
 
 /* ---- the hot path: one semiring SpMV (<- Harness::executeKernel, inc/harness.h:149-195) ---------
  * out[r] = epi( (+)_k mult(x[col k], val k), alpha, y[r], beta ), x <- ZERO for col out of range.
@@ -196,10 +203,15 @@ int shb_synth_grid2d(shb_ctx *ctx, int64_t w, int64_t h, uint64_t seed, shb_csr 
 int shb_ipc_export(shb_buf *buf, void *handle /* SHB_IPC_HANDLE_BYTES */);
 int shb_ipc_open(shb_ctx *ctx, const void *handle, uint64_t bytes, shb_buf **buf);
 int shb_ipc_close(shb_buf *buf);
-/* out slice [row_offset, row_offset + A.n_rows) of every dst[i] (i < n_dst) receives the result */
+/* out slice [row_offset, row_offset + A.n_rows) of every dst[i] (i < n_dst) receives the result.
+ * y == NULL means y is x (the re-bound y of the iterative apps) unless cfg->flags has SHB_F_Y_IS_ONE.
+ * changed_flag (optional, >= 4 bytes): set to 1 when a row of this block fails the termination test
+ * against x[row_offset + r].  prev_changed (optional): when its first word is 0 the launch returns at
+ * once -- the fixed point was reached in the previous iteration (all ranks see the all-reduced flag). */
 int shb_spmv_scatter(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const shb_buf *x,
                      const shb_buf *y, const void *alpha, const void *beta, shb_buf *const *dst, int n_dst,
-                     int64_t row_offset, double delta, int term_mode, shb_buf *changed_flag, uint64_t *kernel_ns);
+                     int64_t row_offset, double delta, int term_mode, shb_buf *changed_flag,
+                     const shb_buf *prev_changed, uint64_t *kernel_ns);
 
 #ifdef __cplusplus
 }

@@ -74,6 +74,8 @@ SIGNATURES = {
     "shb_csr_get_info": (C.c_int, [C.c_void_p, C.POINTER(CsrInfo)]),
     "shb_csr_download": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "shb_csr_transpose": (C.c_int, [C.c_void_p, C.c_void_p, c_void_pp]),
+    "shb_csr_balance_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "shb_csr_slice_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, c_void_pp]),
     "shb_spmv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p, C.c_void_p,
                            C.c_void_p, C.c_void_p, u64p]),
     "shb_spmv_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p,
@@ -95,7 +97,7 @@ SIGNATURES = {
     "shb_ipc_close": (C.c_int, [C.c_void_p]),
     "shb_spmv_scatter": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, c_void_pp, C.c_int, C.c_int64, C.c_double, C.c_int,
-                                   C.c_void_p, u64p]),
+                                   C.c_void_p, C.c_void_p, u64p]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

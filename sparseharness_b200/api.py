@@ -14,7 +14,7 @@ from ._capi import CsrInfo, GraphStats, LaunchCfg, lib
 PLUS_TIMES, MIN_PLUS, OR_AND, MAX_MIN = 0, 1, 2, 3
 VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_STREAM = 0, 1, 2, 3
 TERM_ABSDIFF, TERM_EQUAL = 0, 1
-F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER = 1, 2, 4
+F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER, F_Y_IS_ONE = 1, 2, 4, 8
 _DTYPE = {PLUS_TIMES: np.float32, MIN_PLUS: np.float32, OR_AND: np.int32, MAX_MIN: np.int32}
 
 
@@ -118,6 +118,17 @@ class Csr:
     def transpose(self) -> "Csr":
         h = C.c_void_p()
         _ck(lib.shb_csr_transpose(self.ctx.h, self.h, C.byref(h)))
+        return Csr(self.ctx, h)
+
+    def balance_rows(self, parts: int) -> np.ndarray:
+        """Row bounds of `parts` contiguous blocks balanced by non-zeros."""
+        b = np.zeros(parts + 1, dtype=np.int64)
+        _ck(lib.shb_csr_balance_rows(self.ctx.h, self.h, parts, _ptr(b)))
+        return b
+
+    def slice_rows(self, row_begin: int, row_count: int) -> "Csr":
+        h = C.c_void_p()
+        _ck(lib.shb_csr_slice_rows(self.ctx.h, self.h, row_begin, row_count, C.byref(h)))
         return Csr(self.ctx, h)
 
     def free(self):
@@ -228,13 +239,13 @@ class Context:
 
     def spmv_scatter(self, A: Csr, semiring, x: Buffer, y: Buffer | None, alpha, beta, dst: list[Buffer], row_offset,
                      delta=0.0, term=TERM_ABSDIFF, changed: Buffer | None = None, cfg: LaunchCfg | None = None,
-                     timed=False) -> int:
+                     timed=False, prev_changed: Buffer | None = None) -> int:
         a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
         arr = (C.c_void_p * len(dst))(*[d.h for d in dst])
         ns = C.c_uint64(0)
         _ck(lib.shb_spmv_scatter(self.h, A.h, semiring, C.byref(cfg) if cfg else None, x.h, y.h if y else None, _ptr(a),
                                  _ptr(b), arr, len(dst), row_offset, delta, term, changed.h if changed else None,
-                                 C.byref(ns) if timed else None))
+                                 prev_changed.h if prev_changed else None, C.byref(ns) if timed else None))
         return ns.value
 
     def iterate(self, A: Csr, semiring, x: Buffer, y0: Buffer | None, alpha, beta, work: Buffer, delta=1e-4, term=None,

@@ -506,6 +506,75 @@ SHB_API int shb_csr_download(shb_ctx *c, const shb_csr *A, int64_t row_begin, in
   return SHB_OK;
 }
 
+// ---- 1-D row partition helpers (multi-GPU) ---------------------------------------------
+__global__ void balance_rows_kernel(const int32_t *row_ptr, int64_t n_rows, int64_t nnz, int parts, int64_t *bounds) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > parts) return;
+  if (k == parts) {
+    bounds[k] = n_rows;
+    return;
+  }
+  const int64_t target = (nnz * (int64_t)k) / parts;
+  int64_t lo = 0, hi = n_rows;  // first r with row_ptr[r] >= target
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if ((int64_t)row_ptr[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  bounds[k] = k == 0 ? 0 : lo;
+}
+
+SHB_API int shb_csr_balance_rows(shb_ctx *c, const shb_csr *A, int parts, int64_t *row_bounds) {
+  SHB_REQUIRE(c && A && row_bounds, "bad arguments");
+  SHB_REQUIRE(parts >= 1 && parts <= 1024, "parts must be in 1..1024");
+  SHB_CUDA(cudaSetDevice(c->device));
+  int64_t *d = nullptr;
+  SHB_CUDA(cudaMalloc(&d, (size_t)(parts + 1) * 8));
+  balance_rows_kernel<<<(parts + 1 + 127) / 128, 128, 0, c->stream>>>(A->row_ptr, A->n_rows, A->nnz, parts, d);
+  SHB_CUDA(cudaGetLastError());
+  SHB_CUDA(cudaMemcpyAsync(row_bounds, d, (size_t)(parts + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+  SHB_CUDA(cudaStreamSynchronize(c->stream));
+  SHB_CUDA(cudaFree(d));
+  return SHB_OK;
+}
+
+__global__ void rebase_rows32_kernel(const int32_t *row_ptr, int64_t row_begin, int64_t count, int32_t *out) {
+  const int32_t base = row_ptr[row_begin];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= count; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = row_ptr[row_begin + i] - base;
+}
+
+SHB_API int shb_csr_slice_rows(shb_ctx *c, const shb_csr *A, int64_t row_begin, int64_t row_count, shb_csr **out) {
+  SHB_REQUIRE(c && A && out, "bad arguments");
+  SHB_REQUIRE(row_begin >= 0 && row_count >= 0 && row_begin + row_count <= A->n_rows, "row range out of bounds");
+  SHB_CUDA(cudaSetDevice(c->device));
+  int32_t be[2] = {0, 0};
+  SHB_CUDA(cudaMemcpyAsync(&be[0], A->row_ptr + row_begin, 4, cudaMemcpyDeviceToHost, c->stream));
+  SHB_CUDA(cudaMemcpyAsync(&be[1], A->row_ptr + row_begin + row_count, 4, cudaMemcpyDeviceToHost, c->stream));
+  SHB_CUDA(cudaStreamSynchronize(c->stream));
+  const int64_t nnz = (int64_t)be[1] - (int64_t)be[0];
+  shb_csr *S = nullptr;
+  SHB_TRY(shb_csr_alloc(c, row_count, A->n_cols, nnz, A->val != nullptr, &S));
+  rebase_rows32_kernel<<<(unsigned)std::min<int64_t>((row_count + 256) / 256, 148 * 8), 256, 0, c->stream>>>(
+      A->row_ptr, row_begin, row_count, S->row_ptr);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && nnz)
+    e = cudaMemcpyAsync(S->col, A->col + be[0], (size_t)nnz * 4, cudaMemcpyDeviceToDevice, c->stream);
+  if (e == cudaSuccess && nnz && A->val)
+    e = cudaMemcpyAsync(S->val, (const int32_t *)A->val + be[0], (size_t)nnz * 4, cudaMemcpyDeviceToDevice, c->stream);
+  if (e != cudaSuccess) {
+    shb_csr_destroy(S);
+    shb_set_error("slicing rows failed: %s (code: %d)", cudaGetErrorString(e), (int)e);
+    return SHB_ERR_CUDA;
+  }
+  int st = shb_csr_analyse(c, S);
+  if (st != SHB_OK) {
+    shb_csr_destroy(S);
+    return st;
+  }
+  *out = S;
+  return SHB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // kernel selection + launch  (<- Harness::executeKernel, inc/harness.h:149-195)
 // ------------------------------------------------------------------------------------------------
@@ -557,7 +626,7 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
   const bool hints = !(d.flags & SHB_F_NO_CACHE_HINTS);
   int block = d.block_threads;
   if (block != 64 && block != 128 && block != 256) block = 256;  // Run.local1 outside this set: default
-  a.use_y = (d.flags & SHB_F_INTERNAL_Y_ONE) ? 2 : (d.flags & SHB_F_NO_Y_SKIP) ? 1 : (S::needs_y(a.beta) ? 1 : 0);
+  a.use_y = (d.flags & (SHB_F_INTERNAL_Y_ONE | SHB_F_Y_IS_ONE)) ? 2 : (d.flags & SHB_F_NO_Y_SKIP) ? 1 : (S::needs_y(a.beta) ? 1 : 0);
   a.reversed = (d.flags & SHB_F_REVERSED_ORDER) ? 1 : 0;
   const bool has_val = A->val != nullptr;
   if (A->n_rows == 0) return SHB_OK;

@@ -545,7 +545,8 @@ SHB_API int shb_ipc_close(shb_buf *b) { return shb_buf_destroy(b); }
 
 SHB_API int shb_spmv_scatter(shb_ctx *c, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const shb_buf *x,
                              const shb_buf *y, const void *alpha, const void *beta, shb_buf *const *dst, int n_dst,
-                             int64_t row_offset, double delta, int term_mode, shb_buf *changed_flag, uint64_t *kernel_ns) {
+                             int64_t row_offset, double delta, int term_mode, shb_buf *changed_flag,
+                             const shb_buf *prev_changed, uint64_t *kernel_ns) {
   SHB_REQUIRE(c && A && x && alpha && beta && dst, "bad arguments");
   SHB_REQUIRE(n_dst >= 1 && n_dst <= 8, "1..8 destinations");
   SHB_REQUIRE(row_offset >= 0, "negative row offset");
@@ -559,11 +560,12 @@ SHB_API int shb_spmv_scatter(shb_ctx *c, const shb_csr *A, int semiring, const s
   SHB_REQUIRE(!y || y->bytes >= (uint64_t)(row_offset + A->n_rows) * 4, "y too short");
   SHB_REQUIRE(!changed_flag || (uint64_t)(row_offset + A->n_rows) * 4 <= x->bytes, "convergence test needs x[row_offset + r]");
   SHB_CUDA(cudaSetDevice(c->device));
-  IterCtl ctl = {nullptr, changed_flag ? (uint32_t *)changed_flag->ptr : nullptr, delta, term_mode};
+  IterCtl ctl = {prev_changed ? (const uint32_t *)prev_changed->ptr : nullptr,
+                 changed_flag ? (uint32_t *)changed_flag->ptr : nullptr, delta, term_mode};
   shb_launch_cfg lcfg = {};
   if (cfg) lcfg = *cfg;
   if (!y) {
-    // y omitted: legal only when the epilogue ignores it (checked by the semiring at launch: use_y = 0)
+    // y omitted: y is x, the iterative apps' re-bound y (app/sssp.cpp:150), unless SHB_F_Y_IS_ONE
     lcfg.flags &= ~SHB_F_NO_Y_SKIP;
   }
   ScopedTimer t(c, kernel_ns);

@@ -1,0 +1,83 @@
+"""GPU tests of the row-partitioned iteration (sparseharness_b200/multi.py): all row blocks emulated on one
+device (always), and the real one-process-per-GPU path over NCCL / CUDA IPC when the box has >= 2 GPUs."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import sparseharness_b200 as shb
+    c = shb.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("parts", [1, 2, 5])
+def test_emulated_row_partition_pagerank_matches_oracle(ctx, orc, parts):
+    import sparseharness_b200 as shb
+    from sparseharness_b200 import multi
+    rp, col = orc.gen_rmat(12, 8, seed=orc.SEED_C5, symmetrise=False)
+    n = len(rp) - 1
+    val = orc.pagerank_values(rp, col)
+    A = ctx.csr(n, n, rp, col, val)
+    bounds = A.balance_rows(parts)
+    assert np.array_equal(bounds, multi.balanced_bounds(rp, parts))
+    blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(parts)]
+    for k, B in enumerate(blocks):  # the slice is the same operator rows, rebased, global column ids
+        lo, hi = int(bounds[k]), int(bounds[k + 1])
+        brp, bcol, bval = B.download()
+        assert np.array_equal(brp, rp[lo:hi + 1] - rp[lo]) and np.array_equal(bcol, col[rp[lo]:rp[hi]])
+        assert np.array_equal(bval, val[rp[lo]:rp[hi]])
+    beta = (np.float32(1.0) - np.float32(0.85)) / np.float32(n)
+    be = multi.EmulatedRowPartition(ctx, blocks, bounds, shb.PLUS_TIMES, 1.0, float(beta), y_mode="one", delta=1e-7,
+                                    term=shb.TERM_ABSDIFF, cfg=shb.launch_cfg(variant=shb.VARIANT_SCALAR), max_iters=400)
+    be.x[0].fill_u32(int(np.array([np.float32(1.0) / np.float32(n)], np.float32).view(np.uint32)[0]), n)
+    iters, conv, idx = multi.run_fixed_point(be, 400, 7)
+    want, wit = orc.pagerank(rp, col, val, delta=1e-7, max_iters=400)
+    assert conv and iters == wit
+    assert np.array_equal(be.result(idx).view(np.int32), want.view(np.int32))  # scalar schedule = CPU loop order
+
+
+def test_emulated_row_partition_faithful_min_plus(ctx, orc):
+    """The reference's sssp recurrence (y re-bound to x) on 3 row blocks == the single-process oracle."""
+    import sparseharness_b200 as shb
+    from sparseharness_b200 import multi
+    rp, col, val = orc.gen_grid2d(40, 30)
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, val)
+    bounds = A.balance_rows(3)
+    blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(3)]
+    x0 = np.where(np.arange(n) == 0, 0, orc.FLT_MAX).astype(np.float32)
+    y0 = ctx.array(x0)
+    be = multi.EmulatedRowPartition(ctx, blocks, bounds, shb.MIN_PLUS, 0.0, 0.0, y_mode="rebind", y0=y0, delta=1e-4,
+                                    term=shb.TERM_ABSDIFF, max_iters=400)
+    be.x[0].upload(x0)
+    iters, conv, idx = multi.run_fixed_point(be, 400, 16)
+    want, launches = orc.iterate(orc.MIN_PLUS, rp, col, val, x0, x0, 0.0, 0.0, delta=1e-4)
+    assert conv and iters == launches and np.array_equal(be.result(idx), want)
+    assert np.array_equal(want, orc.sssp(rp, col, val, 0))
+
+
+@pytest.mark.parametrize("mode", ["nccl", "fused"])
+def test_two_gpu_pagerank_matches_oracle(mode):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = 29600 + os.getpid() % 300
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tools", "multi_pagerank.py"), "--scale", "16",
+           "--iters", "200", "--delta", "1e-7", "--mode", mode, "--check", "--check-every", "8"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert out["parity_ok"] and out["converged"] and out["n_gpus"] == 2
+    assert abs(out["iterations"] - out["oracle_iterations"]) <= 1

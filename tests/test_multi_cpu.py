@@ -1,0 +1,101 @@
+"""world_size-2 (and 3) gloo tests, on CPU, of the multi-GPU host logic in sparseharness_b200/multi.py: the
+nnz-balanced row partition, the per-iteration exchange + flag all-reduce protocol and run_fixed_point's launch
+accounting.  The local SpMV of each rank is the CPU oracle standing in for the CUDA kernel (the oracle is the
+checker here: the product path is GpuRowPartition, exercised by the -m gpu tests)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _worker(rank, world, port, out_dir, case):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle as orc
+    from sparseharness_b200 import multi
+
+    n = 3000
+    rp, col = orc.gen_rmat(11, 8, symmetrise=False)
+    n = len(rp) - 1
+    val = orc.pagerank_values(rp, col)
+    bounds = multi.balanced_bounds(rp, world)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    lrp, lcol, lval = rp[lo:hi + 1] - rp[lo], col[rp[lo]:rp[hi]], val[rp[lo]:rp[hi]]
+    delta = 1e-7
+    beta = (np.float32(1.0) - np.float32(0.85)) / np.float32(n)
+
+    class NumpyBackend(multi.Backend):
+        def __init__(self):
+            self.x = [np.full(n, np.float32(1.0) / np.float32(n), np.float32), np.zeros(n, np.float32)]
+            self.flags = torch.zeros(4096, dtype=torch.int32)
+            self.launches = 0
+
+        def step(self, it, src, dst):
+            if it > 0 and self.flags[it - 1] == 0:
+                return  # what the kernel's prev_changed early-out does
+            out = orc.spmv(orc.PLUS_TIMES, lrp, lcol, lval, self.x[src], np.ones(hi - lo, np.float32), 1.0, beta)
+            d = (self.x[src][lo:hi] - out).astype(np.float32)
+            self.flags[it] = int(not (np.abs(d.astype(np.float64)) < delta).all())
+            self.x[dst][lo:hi] = out
+            self.launches += 1
+
+        def exchange(self, it, dst):
+            t = torch.from_numpy(self.x[dst])
+            views = [t[int(bounds[r]):int(bounds[r + 1])] for r in range(world)]
+            parts = [torch.empty_like(v) for v in views]
+            dist.all_gather(parts, views[rank].clone()) if len({len(v) for v in views}) == 1 else \
+                [dist.broadcast(parts[r] if r != rank else parts[r].copy_(views[r]), src=r) for r in range(world)]
+            for v, p in zip(views, parts):
+                v.copy_(p)
+
+        def reduce_flag(self, it):
+            dist.all_reduce(self.flags[it:it + 1], op=dist.ReduceOp.MAX)
+
+        def read_flags(self, a, b):
+            return self.flags[a:b].numpy()
+
+    be = NumpyBackend()
+    iters, converged, idx = multi.run_fixed_point(be, case["max_iters"], case["check_every"])
+    np.save(os.path.join(out_dir, f"x_{rank}.npy"), be.x[idx])
+    np.save(os.path.join(out_dir, f"meta_{rank}.npy"), np.array([iters, int(converged), be.launches, lo, hi]))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,check_every,max_iters", [(2, 8, 400), (2, 1, 400), (3, 5, 400), (2, 4, 6)])
+def test_partitioned_pagerank_over_gloo_matches_single_process_oracle(tmp_path, orc, world, check_every, max_iters):
+    port = 29500 + (os.getpid() + world * 7 + check_every) % 2000
+    mp.spawn(_worker, args=(world, port, str(tmp_path), {"check_every": check_every, "max_iters": max_iters}),
+             nprocs=world, join=True)
+    rp, col = orc.gen_rmat(11, 8, symmetrise=False)
+    val = orc.pagerank_values(rp, col)
+    want, want_iters = orc.pagerank(rp, col, val, delta=1e-7, max_iters=max_iters)
+    xs = [np.load(tmp_path / f"x_{r}.npy") for r in range(world)]
+    metas = [np.load(tmp_path / f"meta_{r}.npy") for r in range(world)]
+    for r in range(world):
+        assert np.array_equal(xs[r].view(np.int32), want.view(np.int32)), r  # same order per row -> same bits
+        assert metas[r][0] == want_iters and metas[r][2] == want_iters
+        assert bool(metas[r][1]) == (want_iters < max_iters or max_iters == 400)
+    assert metas[0][3] == 0 and metas[-1][4] == len(rp) - 1
+    assert all(metas[r][4] == metas[r + 1][3] for r in range(world - 1))
+
+
+def test_balanced_bounds_rule():
+    from sparseharness_b200 import multi
+    rp = np.array([0, 0, 10, 10, 11, 30, 30, 64], np.int64)
+    assert list(multi.balanced_bounds(rp, 1)) == [0, 7]
+    b = multi.balanced_bounds(rp, 4)  # targets 0,16,32,48 -> first row whose prefix reaches the target
+    assert list(b) == [0, 5, 7, 7, 7] or list(b) == [0, 5, 6, 7, 7] or b[0] == 0 and b[-1] == 7 and (np.diff(b) >= 0).all()
+    for parts in (2, 3, 8):
+        b = multi.balanced_bounds(rp, parts)
+        assert b[0] == 0 and b[-1] == 7 and (np.diff(b) >= 0).all()
+        for k in range(1, parts):
+            t = (64 * k) // parts
+            assert rp[b[k]] >= t and (b[k] == 0 or rp[b[k] - 1] < t)

@@ -265,18 +265,36 @@ SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t roo
 }
 
 // =================================================================================================
-// SSSP: worklist Bellman-Ford under min-plus in ONE persistent cooperative kernel.
+// SSSP: near-far (delta-stepping) label correcting under min-plus in ONE persistent cooperative kernel.
 // d[v] <- min(d[v], |d[u]| + |w(u,v)|) is applied with atomicMin on the float bits (all values are
 // non-negative, so integer order == float order).  fl(a + w) is monotone in a, hence any relaxation
-// schedule reaches the same fixed point as the reference's dense sweeps, bit for bit.
+// schedule reaches the same least fixed point as the reference's dense sweeps (app/sssp.cpp:112-153),
+// bit for bit; the schedule only decides how much work that takes:
+//   * tentative distances below the bucket bound T go to the NEAR list as (vertex, distance) pairs; an
+//     entry is live only while dist[vertex] still equals its distance, so a vertex improved twice is
+//     relaxed once (the stale entry is skipped on pop);
+//   * everything else waits in the FAR pile until the near list runs dry; the pile is then split
+//     against the next bound T' = min(far) + delta.  A vertex enters the pile exactly once, on its first
+//     touch (old distance == ZERO) with a distance >= T: a reached vertex whose distance is still >= T
+//     is in the pile by induction, so later improvements need no second entry and no flag array;
+//   * inside a bucket every CTA keeps relaxing what it discovers out of two shared-memory lists, with
+//     no grid barrier between those local rounds (the dependent chain of a wave front costs L2 round
+//     trips, not barriers); lists that overflow spill to the global near list of the next phase.
+// delta = C * mean|w| / mean degree (near-far heuristic of Davidson et al.; C = 128 measured best on B200).
 // =================================================================================================
 struct SsspState {
-  uint32_t q_size[3];
+  uint32_t near_size[3];  // global near lists; slot = phase % 3
+  uint32_t far_size[3];   // far piles; slot = generation % 3
+  uint32_t far_min[3];    // smallest distance (bits) recorded for that pile
   uint32_t bar_count;
   uint32_t bar_gen;
-  uint32_t rounds;
+  uint32_t phases;
+  uint32_t buckets;
   uint32_t done;
-  uint32_t pad;
+  uint32_t overflow;
+  float delta;
+  double w_sum;
+  unsigned long long w_cnt;
 };
 
 __device__ __forceinline__ void grid_barrier(SsspState *st, uint32_t n_blocks) {
@@ -290,78 +308,281 @@ __device__ __forceinline__ void grid_barrier(SsspState *st, uint32_t n_blocks) {
       __threadfence();
       *gen = g + 1;
     } else {
-      while (*gen == g) __nanosleep(32);
+      while (*gen == g) __nanosleep(20);
     }
     __threadfence();
   }
   __syncthreads();
 }
 
-#define SSSP_THREADS 256
-#define SSSP_LOCAL_Q 2048
+#define SSSP_THREADS 512
+#define SSSP_CAP 2048     // entries per shared-memory near list (two lists)
+#define SSSP_FSTAGE 2048  // far pushes staged per CTA between flushes
+#define SSSP_BIG_ROW 32   // rows at least this long are relaxed by the whole warp
 
-template <bool HAS_VAL>
-__global__ void __launch_bounds__(SSSP_THREADS)
-    sssp_persistent_kernel(SsspState *st, const int32_t *__restrict__ at_row_ptr, const int32_t *__restrict__ at_col,
-                           const float *__restrict__ at_val, uint32_t *dist, int32_t *q0, int32_t *q1, uint32_t *stamp,
-                           uint32_t max_rounds) {
-  __shared__ int32_t local_q[SSSP_LOCAL_Q];
-  __shared__ uint32_t local_n, global_base;
-  const uint32_t n_blocks = gridDim.x;
-  const int64_t n_threads = (int64_t)gridDim.x * blockDim.x;
-  uint32_t round = 0;
-  while (true) {
-    const uint32_t qs = *(volatile uint32_t *)&st->q_size[round % 3];
-    if (qs == 0 || round >= max_rounds) break;
-    const int32_t *cur = (round & 1) ? q1 : q0;
-    int32_t *next = (round & 1) ? q0 : q1;
-    uint32_t *next_size = &st->q_size[(round + 1) % 3];
-    if (blockIdx.x == 0 && threadIdx.x == 0) st->q_size[(round + 2) % 3] = 0;  // dead since the last barrier
-    if (threadIdx.x == 0) local_n = 0;
-    __syncthreads();
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < (int64_t)qs; i += n_threads) {
-      const int32_t u = __ldcg(cur + i);
-      const float du = __uint_as_float(__ldcg(dist + u));
-      const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
-      for (int k = s; k < e; ++k) {
-        const int32_t v = at_col[k];
-        const float w = HAS_VAL ? at_val[k] : 1.0f;
-        const uint32_t cb = __float_as_uint(MinPlusF32::mult(du, w));
-        if (cb < __ldcg(dist + v)) {
-          const uint32_t old = atomicMin(dist + v, cb);
-          if (cb < old && atomicExch(stamp + v, round + 1) != round + 1) {
-            const uint32_t slot = atomicAdd(&local_n, 1u);
-            if (slot < SSSP_LOCAL_Q) local_q[slot] = v;
-            else next[atomicAdd(next_size, 1u)] = v;  // block-local staging full: straight to HBM
-          }
-        }
-      }
+struct SsspShared {
+  uint2 lst[2][SSSP_CAP];
+  int32_t fstage[SSSP_FSTAGE];
+  uint32_t lcount[2];
+  uint32_t fcount, fbase, fmin;
+};
+
+struct SsspArgs {
+  SsspState *st;
+  const int32_t *at_row_ptr;
+  const int32_t *at_col;
+  const float *at_val;
+  uint32_t *dist;
+  uint2 *near_q[2];
+  int32_t *far_q[2];
+  uint32_t n;
+  uint32_t near_cap;
+  uint32_t max_phases;
+};
+
+// one successful relaxation: dist[v] just dropped to cb
+__device__ __forceinline__ void sssp_improved(const SsspArgs &a, SsspShared &sh, int32_t v, uint32_t cb, uint32_t old,
+                                              uint32_t t_hi,
+                                              int nxt, uint2 *near_next, uint32_t *near_next_size, int32_t *far_cur,
+                                              uint32_t *far_cur_size, uint32_t &fmin) {
+  if (cb < t_hi) {
+    // v is popped a round from now: have its row bounds in L2 by then
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.at_row_ptr + v));
+    const uint32_t slot = atomicAdd(&sh.lcount[nxt], 1u);
+    if (slot < SSSP_CAP) {
+      sh.lst[nxt][slot] = make_uint2((uint32_t)v, cb);
+    } else {
+      const uint32_t g = atomicAdd(near_next_size, 1u);
+      if (g < a.near_cap) near_next[g] = make_uint2((uint32_t)v, cb);
+      else a.st->overflow = 1u;
     }
-    __syncthreads();
-    const uint32_t ln = min(local_n, (uint32_t)SSSP_LOCAL_Q);
-    if (threadIdx.x == 0 && ln) global_base = atomicAdd(next_size, ln);
-    __syncthreads();
-    for (uint32_t j = threadIdx.x; j < ln; j += blockDim.x) next[global_base + j] = local_q[j];
-    grid_barrier(st, n_blocks);
-    ++round;
-  }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    st->rounds = round;
-    st->done = (*(volatile uint32_t *)&st->q_size[round % 3] == 0) ? 1u : 0u;
+  } else {
+    fmin = min(fmin, cb);
+    if (old == 0x7f7fffffu) {  // first touch: the vertex's one and only far entry
+      const uint32_t slot = atomicAdd(&sh.fcount, 1u);
+      if (slot < SSSP_FSTAGE) sh.fstage[slot] = v;
+      else far_cur[atomicAdd(far_cur_size, 1u)] = v;  // staging full: straight to HBM (one entry per vertex: fits)
+    }
   }
 }
 
-__global__ void sssp_init_kernel(SsspState *st, uint32_t *dist, int32_t *q0, uint32_t *stamp, int64_t source) {
+__device__ __forceinline__ void sssp_flush_far(SsspShared &sh, int32_t *far_cur, uint32_t *far_cur_size) {
+  // called by all threads of the CTA between two __syncthreads-separated rounds
+  const uint32_t cnt = min(sh.fcount, (uint32_t)SSSP_FSTAGE);
+  if (cnt == 0) return;  // uniform: fcount is stable here
+  if (threadIdx.x == 0) sh.fbase = atomicAdd(far_cur_size, cnt);
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < cnt; j += blockDim.x) far_cur[sh.fbase + j] = sh.fstage[j];
+  __syncthreads();
+  if (threadIdx.x == 0) sh.fcount = 0;
+}
+
+template <bool HAS_VAL>
+__global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_nearfar_kernel(const __grid_constant__ SsspArgs a) {
+  __shared__ SsspShared sh;
+  SsspState *st = a.st;
+  const uint32_t n_blocks = gridDim.x;
+  const int lane = threadIdx.x & 31;
+  const uint32_t n_threads = gridDim.x * blockDim.x;
+  const float delta = *(volatile float *)&st->delta;
+  uint32_t phase = 0, fgen = 0, buckets = 1;
+  uint32_t t_hi = __float_as_uint(delta);  // bucket bound (exclusive) of the near list
+  bool finished = false;
+  if (threadIdx.x == 0) {
+    sh.lcount[0] = sh.lcount[1] = 0;
+    sh.fcount = 0;
+    sh.fmin = 0xffffffffu;
+  }
+  __syncthreads();
+  while (phase < a.max_phases) {
+    const uint32_t ns = *(volatile uint32_t *)&st->near_size[phase % 3];
+    const uint2 *near_cur = a.near_q[phase & 1];
+    uint2 *near_next = a.near_q[(phase + 1) & 1];
+    uint32_t *near_next_size = &st->near_size[(phase + 1) % 3];
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->near_size[(phase + 2) % 3] = 0;  // dead since the last barrier
+    uint32_t fmin = 0xffffffffu;
+    if (ns > 0) {
+      // ---- near phase: relax the global near list, then whatever this CTA discovers, to exhaustion
+      int32_t *far_cur = a.far_q[fgen & 1];
+      uint32_t *far_cur_size = &st->far_size[fgen % 3];
+      const uint32_t ch = max(32u, min((uint32_t)SSSP_CAP, (ns + n_blocks - 1) / n_blocks));
+      for (uint32_t base = blockIdx.x * ch; base < ns; base += n_blocks * ch) {
+        const uint32_t cnt = min(ch, ns - base);
+        for (uint32_t j = threadIdx.x; j < cnt; j += blockDim.x) sh.lst[0][j] = near_cur[base + j];
+        if (threadIdx.x == 0) sh.lcount[0] = cnt;
+        int cur = 0;
+        while (true) {
+          __syncthreads();
+          const uint32_t cn = sh.lcount[cur];
+          if (cn == 0) break;
+          const int nxt = cur ^ 1;
+          for (uint32_t i = threadIdx.x; i < ((cn + 31u) & ~31u); i += blockDim.x) {
+            int s = 0, e = 0;
+            uint32_t du_bits = 0;
+            if (i < cn) {
+              const uint2 ent = sh.lst[cur][i];
+              const uint32_t d_now = __ldcg(a.dist + ent.x);  // the three loads go out together
+              const int s0 = __ldg(a.at_row_ptr + ent.x), e0 = __ldg(a.at_row_ptr + ent.x + 1);
+              if (d_now == ent.y) {  // still the vertex's distance: live entry
+                s = s0;
+                e = e0;
+                du_bits = ent.y;
+              }
+            }
+            const float du = __uint_as_float(du_bits);
+            const bool big = (e - s) >= SSSP_BIG_ROW;
+            if (!big) {
+              for (int k = s; k < e; k += 4) {
+                int32_t vv[4];
+                uint32_t cb[4], old[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  vv[j] = (k + j < e) ? __ldg(a.at_col + k + j) : -1;
+                  const float w = (HAS_VAL && k + j < e) ? __ldg(a.at_val + k + j) : 1.0f;
+                  cb[j] = __float_as_uint(MinPlusF32::mult(du, w));
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) old[j] = ((uint32_t)vv[j] < a.n) ? atomicMin(a.dist + vv[j], cb[j]) : 0u;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (cb[j] < old[j])
+                    sssp_improved(a, sh, vv[j], cb[j], old[j], t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
+              }
+            }
+            uint32_t bigs = __ballot_sync(0xffffffffu, big);
+            while (bigs) {
+              const int src = __ffs(bigs) - 1;
+              bigs &= bigs - 1;
+              const int bs = __shfl_sync(0xffffffffu, s, src), be = __shfl_sync(0xffffffffu, e, src);
+              const float bd = __uint_as_float(__shfl_sync(0xffffffffu, du_bits, src));
+              for (int k = bs + lane; k < be; k += 32) {
+                const int32_t v = __ldg(a.at_col + k);
+                const float w = HAS_VAL ? __ldg(a.at_val + k) : 1.0f;
+                const uint32_t c1 = __float_as_uint(MinPlusF32::mult(bd, w));
+                if ((uint32_t)v < a.n && c1 < __ldcg(a.dist + v)) {
+                  const uint32_t o1 = atomicMin(a.dist + v, c1);
+                  if (c1 < o1) sssp_improved(a, sh, v, c1, o1, t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
+                }
+              }
+            }
+          }
+          __syncthreads();
+          if (threadIdx.x == 0) {
+            sh.lcount[cur] = 0;
+            sh.lcount[nxt] = min(sh.lcount[nxt], (uint32_t)SSSP_CAP);  // the excess went to the global list
+          }
+          if (sh.fcount >= SSSP_FSTAGE / 2) sssp_flush_far(sh, far_cur, far_cur_size);
+          cur = nxt;
+        }
+      }
+      __syncthreads();
+      sssp_flush_far(sh, far_cur, far_cur_size);
+      for (int off = 16; off > 0; off >>= 1) fmin = min(fmin, __shfl_xor_sync(0xffffffffu, fmin, off));
+      if (lane == 0 && fmin != 0xffffffffu) atomicMin(&sh.fmin, fmin);
+      __syncthreads();
+      if (threadIdx.x == 0 && sh.fmin != 0xffffffffu) {
+        atomicMin(&st->far_min[fgen % 3], sh.fmin);
+        sh.fmin = 0xffffffffu;
+      }
+    } else {
+      // ---- the near list ran dry: split the far pile against the next bucket bound
+      const uint32_t fs = *(volatile uint32_t *)&st->far_size[fgen % 3];
+      if (fs == 0) {
+        finished = true;
+        break;
+      }
+      const uint32_t t_old = t_hi;
+      t_hi = __float_as_uint(__fadd_rn(__uint_as_float(*(volatile uint32_t *)&st->far_min[fgen % 3]), delta));
+      ++buckets;
+      const int32_t *far_cur = a.far_q[fgen & 1];
+      int32_t *far_next = a.far_q[(fgen + 1) & 1];
+      uint32_t *far_next_size = &st->far_size[(fgen + 1) % 3];
+      if (blockIdx.x == 0 && threadIdx.x == 0) {
+        st->far_size[(fgen + 2) % 3] = 0;  // the pile split one bucket ago
+        st->far_min[(fgen + 2) % 3] = 0xffffffffu;
+      }
+      for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((fs + 31u) & ~31u); i += n_threads) {
+        int kind = 0;
+        int32_t v = 0;
+        uint32_t d = 0;
+        if (i < fs) {
+          v = far_cur[i];
+          d = __ldcg(a.dist + v);
+          if (d < t_old) {
+            // went through the near list in an earlier bucket: stale, dropped
+          } else if (d < t_hi) {
+            kind = 1;
+          } else {
+            kind = 2;
+            fmin = min(fmin, d);
+          }
+        }
+        const uint32_t m1 = __ballot_sync(0xffffffffu, kind == 1), m2 = __ballot_sync(0xffffffffu, kind == 2);
+        uint32_t b1 = 0, b2 = 0;
+        if (lane == 0) {
+          if (m1) b1 = atomicAdd(near_next_size, __popc(m1));
+          if (m2) b2 = atomicAdd(far_next_size, __popc(m2));
+        }
+        b1 = __shfl_sync(0xffffffffu, b1, 0);
+        b2 = __shfl_sync(0xffffffffu, b2, 0);
+        const uint32_t below = (1u << lane) - 1u;
+        if (kind == 1) {
+          const uint32_t g = b1 + __popc(m1 & below);
+          if (g < a.near_cap) near_next[g] = make_uint2((uint32_t)v, d);
+          else st->overflow = 1u;
+        } else if (kind == 2) {
+          far_next[b2 + __popc(m2 & below)] = v;
+        }
+      }
+      for (int off = 16; off > 0; off >>= 1) fmin = min(fmin, __shfl_xor_sync(0xffffffffu, fmin, off));
+      if (lane == 0 && fmin != 0xffffffffu) atomicMin(&st->far_min[(fgen + 1) % 3], fmin);
+      ++fgen;
+    }
+    grid_barrier(st, n_blocks);
+    ++phase;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st->phases = phase;
+    st->buckets = buckets;
+    st->done = (finished && st->overflow == 0) ? 1u : 0u;
+  }
+}
+
+// mean |weight| over a strided sample of the stored values (the bucket width heuristic needs a scale)
+__global__ void sssp_weight_stats_kernel(SsspState *st, const float *val, int64_t nnz, int64_t stride) {
+  double s = 0.0;
+  unsigned long long c = 0;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * stride; i < nnz; i += (int64_t)gridDim.x * blockDim.x * stride) {
+    s += (double)fabsf(val[i]);
+    ++c;
+  }
+  for (int off = 16; off > 0; off >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, off);
+    c += __shfl_xor_sync(0xffffffffu, c, off);
+  }
+  if ((threadIdx.x & 31) == 0 && c) {
+    atomicAdd(&st->w_sum, s);
+    atomicAdd(&st->w_cnt, c);
+  }
+}
+
+__global__ void sssp_init_kernel(SsspState *st, uint32_t *dist, uint2 *near0, int64_t source, double mean_degree,
+                                 float c_scale, float delta_override) {
   dist[source] = 0u;  // bits of 0.0f
-  q0[0] = (int32_t)source;
-  stamp[source] = 0u;
-  st->q_size[0] = 1;
-  st->q_size[1] = 0;
-  st->q_size[2] = 0;
-  st->bar_count = 0;
-  st->bar_gen = 0;
-  st->rounds = 0;
-  st->done = 0;
+  near0[0] = make_uint2((uint32_t)source, 0u);
+  st->near_size[0] = 1;
+  st->near_size[1] = st->near_size[2] = 0;
+  for (int i = 0; i < 3; ++i) {
+    st->far_size[i] = 0;
+    st->far_min[i] = 0xffffffffu;
+  }
+  st->bar_count = st->bar_gen = 0;
+  st->phases = st->buckets = st->done = st->overflow = 0;
+  const double mean_w = st->w_cnt ? st->w_sum / (double)st->w_cnt : 1.0;
+  float delta = (float)(c_scale * mean_w / (mean_degree > 1.0 ? mean_degree : 1.0));
+  if (delta_override > 0.f) delta = delta_override;
+  if (!(delta > 0.f) || delta > 1.0e37f) delta = 1.0f;
+  st->delta = delta;
 }
 
 // reached vertices and the TEPS numerator (sum of in-degrees of reached vertices)
@@ -399,8 +620,8 @@ SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t
     AT = AT_own;
   }
   SsspState *st = nullptr;
-  int32_t *q = nullptr;
-  uint32_t *stamp = nullptr;
+  uint2 *near_q = nullptr;
+  int32_t *far_q = nullptr;
   unsigned long long *d_out = nullptr;
   int status = SHB_OK;
   SsspState h;
@@ -417,40 +638,59 @@ SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t
     }                                                                                                     \
   } while (0)
   {
+    // bucket width: C * mean|w| / mean degree; SHB_SSSP_C and SHB_SSSP_DELTA are tuning overrides
+    float c_scale = 128.0f, delta_override = 0.0f;
+    if (const char *e = getenv("SHB_SSSP_C")) c_scale = (float)atof(e);
+    if (const char *e = getenv("SHB_SSSP_DELTA")) delta_override = (float)atof(e);
+    int per_sm_cap = 1;
+    if (const char *e = getenv("SHB_SSSP_CTAS_PER_SM")) per_sm_cap = std::max(1, atoi(e));
+    const uint64_t near_cap = (uint64_t)n + 1024;
     SS_CUDA(cudaMalloc(&st, sizeof(SsspState)));
-    SS_CUDA(cudaMalloc(&q, (size_t)n * 8));
-    SS_CUDA(cudaMalloc(&stamp, (size_t)n * 4));
+    SS_CUDA(cudaMalloc(&near_q, (size_t)near_cap * 2 * sizeof(uint2)));
+    SS_CUDA(cudaMalloc(&far_q, (size_t)n * 2 * sizeof(int32_t)));
     SS_CUDA(cudaMalloc(&d_out, 16));
     SS_CUDA(cudaMemsetAsync(d_out, 0, 16, c->stream));
-    int32_t *q0 = q, *q1 = q + n;
     int per_sm = 0;
     const bool has_val = AT->val != nullptr;
-    if (has_val) SS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_persistent_kernel<true>, SSSP_THREADS, 0));
-    else SS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_persistent_kernel<false>, SSSP_THREADS, 0));
-    per_sm = std::max(1, std::min(per_sm, 4));
+    if (has_val) SS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_nearfar_kernel<true>, SSSP_THREADS, 0));
+    else SS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_nearfar_kernel<false>, SSSP_THREADS, 0));
+    per_sm = std::max(1, std::min(per_sm, per_sm_cap));
     const int blocks = per_sm * c->prop.multiProcessorCount;
     SS_CUDA(cudaEventRecord(c->ev0, c->stream));
-    // dist = ZERO of min-plus everywhere (3.4028235E38f = 0x7f7fffff), stamp = never
+    // dist = ZERO of min-plus everywhere (3.4028235E38f = 0x7f7fffff)
     {
-      const uint32_t fmax_bits = 0x7f7fffffu;
-      // fill with a kernel-free trick is not possible for this pattern; use the u32 fill kernel via API
       shb_buf tmp;
       tmp.ctx = c; tmp.ptr = dist->ptr; tmp.bytes = dist->bytes; tmp.owned = false;
-      status = shb_buf_fill_u32(c, &tmp, 0, (uint64_t)n, fmax_bits);
+      status = shb_buf_fill_u32(c, &tmp, 0, (uint64_t)n, 0x7f7fffffu);
       if (status != SHB_OK) goto done;
     }
-    SS_CUDA(cudaMemsetAsync(stamp, 0xff, (size_t)n * 4, c->stream));
-    sssp_init_kernel<<<1, 1, 0, c->stream>>>(st, (uint32_t *)dist->ptr, q0, stamp, source);
+    SS_CUDA(cudaMemsetAsync(st, 0, sizeof(SsspState), c->stream));
+    if (has_val && AT->nnz > 0) {
+      const int64_t stride = std::max<int64_t>(1, AT->nnz / (1 << 22));
+      sssp_weight_stats_kernel<<<148, 256, 0, c->stream>>>(st, (const float *)AT->val, AT->nnz, stride);
+    }
+    sssp_init_kernel<<<1, 1, 0, c->stream>>>(st, (uint32_t *)dist->ptr, near_q, source,
+                                             n > 0 ? (double)AT->nnz / (double)n : 1.0, c_scale, delta_override);
     SS_CUDA(cudaGetLastError());
     {
-      const int32_t *a0 = AT->row_ptr, *a1 = AT->col;
-      const float *a2 = (const float *)AT->val;
-      uint32_t *a3 = (uint32_t *)dist->ptr;
-      void *args[] = {&st, &a0, &a1, &a2, &a3, &q0, &q1, &stamp, &max_rounds};
+      SsspArgs a;
+      a.st = st;
+      a.at_row_ptr = AT->row_ptr;
+      a.at_col = AT->col;
+      a.at_val = (const float *)AT->val;
+      a.dist = (uint32_t *)dist->ptr;
+      a.near_q[0] = near_q;
+      a.near_q[1] = near_q + near_cap;
+      a.far_q[0] = far_q;
+      a.far_q[1] = far_q + n;
+      a.n = (uint32_t)n;
+      a.near_cap = (uint32_t)near_cap;
+      a.max_phases = max_rounds;
+      void *args[] = {&a};
       if (has_val)
-        SS_CUDA(cudaLaunchCooperativeKernel((void *)sssp_persistent_kernel<true>, dim3(blocks), dim3(SSSP_THREADS), args, 0, c->stream));
+        SS_CUDA(cudaLaunchCooperativeKernel((void *)sssp_nearfar_kernel<true>, dim3(blocks), dim3(SSSP_THREADS), args, 0, c->stream));
       else
-        SS_CUDA(cudaLaunchCooperativeKernel((void *)sssp_persistent_kernel<false>, dim3(blocks), dim3(SSSP_THREADS), args, 0, c->stream));
+        SS_CUDA(cudaLaunchCooperativeKernel((void *)sssp_nearfar_kernel<false>, dim3(blocks), dim3(SSSP_THREADS), args, 0, c->stream));
     }
     reached_stats_kernel<<<grid_for(n), 256, 0, c->stream>>>((const uint32_t *)dist->ptr, 0x7f7fffffu, A->row_ptr, n, d_out);
     SS_CUDA(cudaEventRecord(c->ev1, c->stream));
@@ -458,23 +698,28 @@ SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t
     SS_CUDA(cudaMemcpyAsync(h_out, d_out, 16, cudaMemcpyDeviceToHost, c->stream));
     SS_CUDA(cudaStreamSynchronize(c->stream));
     SS_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    if (!h.done) {
-      shb_set_error("round cap of %u reached before the worklist emptied", max_rounds);
+    if (h.overflow) {
+      shb_set_error("near list overflow (capacity %llu entries)", (unsigned long long)near_cap);
+      status = SHB_ERR_CUDA;
+    } else if (!h.done) {
+      shb_set_error("phase cap of %u reached before the worklists emptied", max_rounds);
       status = SHB_ERR_NOT_CONVERGED;
     }
+    if (getenv("SHB_SSSP_VERBOSE"))
+      fprintf(stderr, "shb_sssp: delta %g, %u buckets, %u phases, %d CTAs, %.3f ms\n", (double)h.delta, h.buckets, h.phases, blocks, (double)ms);
   }
 done:
   if (stats) {
-    stats->iterations = h.rounds;
+    stats->iterations = h.phases;
     stats->converged = h.done;
     stats->reached = (int64_t)h_out[0];
     stats->edges_traversed = (int64_t)h_out[1];
     stats->total_ns = (uint64_t)((double)ms * 1e6 + 0.5);
-    stats->launches = 4;
+    stats->launches = 5;
   }
   cudaFree(st);
-  cudaFree(q);
-  cudaFree(stamp);
+  cudaFree(near_q);
+  cudaFree(far_q);
   cudaFree(d_out);
   if (AT_own) shb_csr_destroy(AT_own);
   return status;

@@ -135,6 +135,39 @@ def test_sssp_grid_and_directed(ctx, orc):
     assert np.array_equal(dist.download(np.float32, 4000).view(np.int32), orc.sssp(rp, col, val, 5).view(np.int32))
 
 
+@pytest.mark.parametrize("env", [{}, {"SHB_SSSP_DELTA": "0.01"}, {"SHB_SSSP_DELTA": "1e30"}, {"SHB_SSSP_C": "2"},
+                                 {"SHB_SSSP_CTAS_PER_SM": "2"}])
+def test_sssp_near_far_schedules_reach_the_same_fixed_point(ctx, orc, env, monkeypatch):
+    """Near-far SSSP on a power-law graph with hub rows (warp-cooperative relaxation, shared-memory list
+    spills) and non-integer float weights; any bucket width -- one bucket per distinct distance, a single
+    bucket (plain label correcting), the heuristic -- gives the oracle's distances bit for bit."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    A = ctx.synth_rmat(14, 16, seed=orc.SEED_C3, symmetrise=True, value_mode=1)
+    rp, col, val = A.download()
+    n = len(rp) - 1
+    root = int(np.argmax(np.diff(rp) > 0))
+    want = orc.sssp(rp, col, val, root)
+    dist, st = ctx.sssp(A, root)  # values are not symmetric: the library builds the transpose
+    assert st.converged
+    assert np.array_equal(dist.download(np.float32, n).view(np.int32), want.view(np.int32))
+    assert st.reached == int((want < orc.FLT_MAX).sum())
+    # pattern operator: every edge weighs 1 -> distances are BFS levels
+    P = ctx.synth_rmat(12, 8, seed=orc.SEED_C3, symmetrise=True)
+    prp, pcol, _ = P.download()
+    proot = int(np.argmax(np.diff(prp) > 0))
+    lv, _, _ = orc.bfs_levels(prp, pcol, None, proot)
+    dist, st = ctx.sssp(P, proot, AT=P)
+    d = dist.download(np.float32, len(prp) - 1)
+    assert st.converged and np.array_equal(d[lv >= 0], lv[lv >= 0].astype(np.float32)) and (d[lv < 0] == orc.FLT_MAX).all()
+
+
+def test_sssp_phase_cap_reports_not_converged(ctx, orc):
+    G = ctx.synth_grid2d(64, 64)
+    with pytest.raises(shb.ShbError):
+        ctx.sssp(G, 0, AT=G, max_rounds=3)
+
+
 def test_pagerank_canonical(ctx, orc):
     A = ctx.synth_rmat(12, 16, seed=orc.SEED_C5, symmetrise=False, value_mode=1)
     rp, col, val = A.download()

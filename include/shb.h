@@ -60,7 +60,9 @@ typedef enum {
   SHB_VARIANT_AUTO = 0,   /* chosen from row-length statistics                                            */
   SHB_VARIANT_SCALAR = 1, /* thread per row, forward order (glb-sdp / glb-sdp-rsa, kernel5/6.json)        */
   SHB_VARIANT_VECTOR = 2, /* sub-warp of `lanes` threads per row, 128-bit loads, shuffle reduction        */
-  SHB_VARIANT_STREAM = 3  /* nnz-split load-balanced tiles staged through shared memory (power-law rows)   */
+  SHB_VARIANT_STREAM = 3, /* nnz-split load-balanced tiles staged through shared memory (power-law rows)   */
+  SHB_VARIANT_BLOCKED = 4 /* propagation blocking for gather-bound operators: x slices staged in shared
+                             memory, products streamed to the row owners (needs shb_csr_build_blocked)     */
 } shb_variant;
 
 enum { SHB_F_NO_CACHE_HINTS = 1u, /* plain ld.global for every stream (A/B experiments)          */
@@ -137,6 +139,14 @@ int shb_csr_transpose(shb_ctx *ctx, const shb_csr *csr, shb_csr **transposed); /
 /* 1-D row partition: row_bounds[0..parts] with row_bounds[k] = first row whose prefix nnz
  * reaches k*nnz/parts (contiguous blocks balanced by non-zeros); slice_rows copies one block, on the
  * device, into an operator of its own that keeps GLOBAL column ids. */
+/* Builds the column-slice-major copy of the operator that SHB_VARIANT_BLOCKED runs on (the analogue of the
+ * reference re-encoding a matrix for its kernel, SparseMatrix::cl_encode, src/sparse_matrix.cpp:122-399).
+ * rows_per_consumer: rows of a panel one CTA reduces out of shared memory (0 = sized so that a consumer
+ * unit fills about 44 KB).  make_default != 0 makes SHB_VARIANT_AUTO resolve to the blocked schedule for
+ * this operator.  SHB_ERR_UNSUPPORTED when a consumer unit cannot fit shared memory (skewed operators). */
+int shb_csr_build_blocked(shb_ctx *ctx, shb_csr *csr, int rows_per_consumer, int make_default);
+int shb_csr_blocked_info(const shb_csr *csr, int32_t *geom /* 8: n_prod, n_pass, n_panel, W, RS, cbuf, slot_cap, depth */, int64_t *entries,
+                         uint64_t *device_bytes);
 int shb_csr_balance_rows(shb_ctx *ctx, const shb_csr *csr, int parts, int64_t *row_bounds);
 int shb_csr_slice_rows(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int64_t row_count, shb_csr **slice);
 

@@ -12,7 +12,7 @@ from . import _capi
 from ._capi import CsrInfo, GraphStats, LaunchCfg, lib
 
 PLUS_TIMES, MIN_PLUS, OR_AND, MAX_MIN = 0, 1, 2, 3
-VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_STREAM = 0, 1, 2, 3
+VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_STREAM, VARIANT_BLOCKED = 0, 1, 2, 3, 4
 TERM_ABSDIFF, TERM_EQUAL = 0, 1
 F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER, F_Y_IS_ONE = 1, 2, 4, 8
 _DTYPE = {PLUS_TIMES: np.float32, MIN_PLUS: np.float32, OR_AND: np.int32, MAX_MIN: np.int32}
@@ -130,6 +130,15 @@ class Csr:
         h = C.c_void_p()
         _ck(lib.shb_csr_slice_rows(self.ctx.h, self.h, row_begin, row_count, C.byref(h)))
         return Csr(self.ctx, h)
+
+    def build_blocked(self, rows_per_consumer: int = 0, make_default: bool = True) -> dict:
+        """Build the propagation-blocked copy that VARIANT_BLOCKED runs on (pb.cuh); returns its geometry."""
+        _ck(lib.shb_csr_build_blocked(self.ctx.h, self.h, rows_per_consumer, int(make_default)))
+        geom = (C.c_int32 * 8)()
+        entries, nbytes = C.c_int64(), C.c_uint64()
+        _ck(lib.shb_csr_blocked_info(self.h, geom, C.byref(entries), C.byref(nbytes)))
+        return {"n_prod": geom[0], "n_pass": geom[1], "n_panel": geom[2], "W": geom[3], "RS": geom[4],
+                "cbuf_cap": geom[5], "slot_cap": geom[6], "depth": geom[7], "entries": entries.value, "device_bytes": nbytes.value}
 
     def free(self):
         if self.h:

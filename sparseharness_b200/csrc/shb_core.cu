@@ -5,6 +5,7 @@
 
 #include <algorithm>
 
+#include "pb.cuh"
 #include "spmv.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -329,6 +330,7 @@ SHB_API int shb_csr_destroy(shb_csr *A) {
   cudaFree(A->tile_row);
   cudaFree(A->carry_tail);
   cudaFree(A->carry_head);
+  shb_pb_free(A->pb);
   delete A;
   return SHB_OK;
 }
@@ -615,6 +617,57 @@ static int default_rpg(int lanes) {
   }
 }
 
+// BLOCKED: one persistent cooperative kernel, a CTA per SM, producer and consumer warps (pb.cuh).
+// SHB_PB_SPLIT=1 runs the two roles as two launches over a full-size ring (debug aid).
+template <class S, bool HAS_VAL>
+static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> &a) {
+  typedef typename S::T T;
+  const int n_groups = pb->g.n_pass * pb->g.n_panel;
+  PbArgs<T> pa;
+  pa.g = pb->g;
+  pa.lcol = pb->lcol;
+  pa.val = (const T *)pb->val;
+  pa.slot = pb->slot;
+  pa.unit_ptr = pb->unit_ptr;
+  pa.cons_desc = pb->cons_desc;
+  pa.crp = pb->crp;
+  pa.partial = (T *)pb->partial;
+  pa.ready = pb->sync;
+  pa.consumed = pb->sync + n_groups;
+  pa.exit_count = pb->sync + 2 * n_groups;
+  static const bool split = getenv("SHB_PB_SPLIT") != nullptr;
+  if (split) {
+    SHB_TRY(shb_pb_reserve_ring(c, pb, n_groups));
+    pa.g.depth = n_groups;
+  }
+  pa.ring = (T *)pb->ring;
+  const size_t smem = shb_pb_smem_bytes(pb);
+  SHB_CUDA(cudaFuncSetAttribute(pb_fused_kernel<S, HAS_VAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SpmvArgs<T> aa = a;
+  void *args[] = {&pa, &aa};
+  const dim3 grid((unsigned)pb->g.n_prod), block(PB_THREADS);
+  if (!split) {
+    pa.roles = PB_ROLE_PRODUCE | PB_ROLE_CONSUME;
+    pa.reset_sync = 1;
+    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+  } else {
+    pa.roles = PB_ROLE_PRODUCE;
+    pa.reset_sync = 0;
+    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+    pa.roles = PB_ROLE_CONSUME;
+    pa.reset_sync = 1;
+    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+  }
+  return SHB_OK;
+}
+
+template <class S>
+static int run_blocked(shb_ctx *c, const shb_csr *A, const SpmvArgs<typename S::T> &a) {
+  SHB_REQUIRE(A->pb != nullptr, "SHB_VARIANT_BLOCKED needs shb_csr_build_blocked on this operator first");
+  SHB_REQUIRE(A->pb->g.n_prod == c->prop.multiProcessorCount, "blocked layout was built for another device");
+  return A->pb->val ? launch_blocked<S, true>(c, A->pb, a) : launch_blocked<S, false>(c, A->pb, a);
+}
+
 template <class S>
 static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, SpmvArgs<typename S::T> &a) {
   typedef typename S::T T;
@@ -665,6 +718,8 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
       }
       return SHB_OK;
     }
+    case SHB_VARIANT_BLOCKED:
+      return run_blocked<S>(c, A, a);
     default:
       shb_set_error("unknown kernel variant %d", variant);
       return SHB_ERR_UNSUPPORTED;

@@ -65,6 +65,9 @@ struct shb_buf {
 // Stream-kernel tile: nnz per CTA tile
 static const int SHB_TILE_NNZ = 4096;
 
+struct shb_pb;  // blocked copy of the operator (pb.cuh)
+void shb_pb_free(shb_pb *pb);
+
 struct shb_csr {
   shb_ctx *ctx = nullptr;
   int64_t n_rows = 0, n_cols = 0, nnz = 0;
@@ -82,6 +85,7 @@ struct shb_csr {
   // carry buffers for rows straddling stream tiles (element-typed, n_tiles each)
   void *carry_tail = nullptr;
   void *carry_head = nullptr;
+  shb_pb *pb = nullptr;  // built on request (shb_csr_build_blocked)
 };
 
 struct ScopedTimer {

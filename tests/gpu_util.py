@@ -12,11 +12,18 @@ ALL_CFGS = [("scalar", dict(variant=shb.VARIANT_SCALAR)), ("stream", dict(varian
            [("vector4r1", dict(variant=shb.VARIANT_VECTOR, lanes=4, rows_per_group=1)),
             ("vector8r4", dict(variant=shb.VARIANT_VECTOR, lanes=8, rows_per_group=4)),
             ("vector4nohint", dict(variant=shb.VARIANT_VECTOR, lanes=4, flags=shb.F_NO_CACHE_HINTS)),
-            ("stream_nohint", dict(variant=shb.VARIANT_STREAM, flags=shb.F_NO_CACHE_HINTS))]
+            ("stream_nohint", dict(variant=shb.VARIANT_STREAM, flags=shb.F_NO_CACHE_HINTS)),
+            ("blocked", dict(variant=shb.VARIANT_BLOCKED)),          # one row panel on the small fixtures
+            ("blocked_rs5", dict(variant=shb.VARIANT_BLOCKED, pb_rows=5))]  # many row panels, tiny pieces
 
 
 def run_spmv(ctx, A, semiring, x, y, alpha, beta, n_rows, **cfg):
     dt = DT[semiring]
+    cfg = dict(cfg)
+    pb_rows = cfg.pop("pb_rows", 0)
+    if cfg.get("variant") == shb.VARIANT_BLOCKED and A.info.nnz > 0 and getattr(A, "_pb_rows", None) != pb_rows:
+        A.build_blocked(pb_rows, make_default=False)  # the operator's blocked copy (pb.cuh), rebuilt per geometry
+        A._pb_rows = pb_rows
     xb = ctx.array(np.asarray(x, dt))
     yb = ctx.array(np.asarray(y, dt)) if y is not None else None
     out = ctx.empty(max(n_rows, 1) * 4)

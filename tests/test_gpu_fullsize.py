@@ -26,8 +26,11 @@ def test_config2_full_size_spmv(ctx, orc):
         x = ctx.synth_vector(N2, mode=xmode)
         xh = x.download(np.float32, N2)
         results = {}
+        geom = A.build_blocked(make_default=False)  # config 2 at full size: 3 column passes of 148 slices
+        assert geom["n_pass"] == 3 and geom["W"] <= 40960 and geom["entries"] >= info.nnz
         for label, cfg in (("auto", {}), ("scalar", dict(variant=shb.VARIANT_SCALAR)),
-                           ("stream", dict(variant=shb.VARIANT_STREAM)), ("vector8", dict(variant=shb.VARIANT_VECTOR, lanes=8))):
+                           ("stream", dict(variant=shb.VARIANT_STREAM)), ("vector8", dict(variant=shb.VARIANT_VECTOR, lanes=8)),
+                           ("blocked", dict(variant=shb.VARIANT_BLOCKED))):
             out.fill_u32(0xDEADBEEF)
             ctx.spmv(A, shb.PLUS_TIMES, x, None, 1.0, 0.0, out, shb.launch_cfg(**cfg))
             results[label] = out.download(np.float32, N2)
@@ -47,11 +50,13 @@ def test_config2_full_size_spmv(ctx, orc):
         assert np.array_equal(results["scalar"], results["stream"])
         if val_mode == 1:
             assert np.array_equal(results["auto"], results["scalar"]) and np.array_equal(results["vector8"], results["scalar"])
+            assert np.array_equal(results["blocked"], results["scalar"])
             assert results["scalar"].astype(np.float64).sum() == results["auto"].astype(np.float64).sum()
         else:
             s = np.abs(results["scalar"]).max()
             assert np.abs(results["auto"] - results["scalar"]).max() <= 1e-5 * s
             assert np.abs(results["vector8"] - results["scalar"]).max() <= 1e-5 * s
+            assert np.abs(results["blocked"] - results["scalar"]).max() <= 1e-5 * s
         A.free(); x.free()
 
 

@@ -90,6 +90,10 @@ __device__ __forceinline__ uint32_t pb_ld_acquire(const uint32_t *p) {
 __device__ __forceinline__ void pb_red_release(uint32_t *p) {
   asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
 }
+__device__ __forceinline__ void pb_prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void pb_bulk_prefetch_l2(const void *p, uint32_t bytes) {  // 16-byte aligned, multiple of 16
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ uint32_t pb_ld_cg_b32(const void *p) {
   uint32_t v;
   asm volatile("ld.global.cg.b32 %0, [%1];" : "=r"(v) : "l"(p));
@@ -155,6 +159,18 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
       for (int i = b + tid * 8; i < e; i += PB_PROD_THREADS * 16) {
         const int i2 = i + PB_PROD_THREADS * 8;
         const bool p2 = i2 < e;
+        if ((tid & 31) == 0) {  // pull this warp's part of the stream, two steps ahead, into L2
+          const int ip = i + PB_PROD_THREADS * 32;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int ib = ip + h * PB_PROD_THREADS * 8;
+            const int n = min(256, e - ib);  // entries of this warp's 16-byte groups (multiple of 8)
+            if (n > 0) {
+              pb_bulk_prefetch_l2(c.lcol + ib, (uint32_t)n * 2u);
+              if (HAS_VAL) pb_bulk_prefetch_l2(c.val + ib, (uint32_t)n * 4u);
+            }
+          }
+        }
         const uint4 lcA = shb_ld_stream_v4<true>(c.lcol + i, true, 0u, pol_stream);
         const uint4 lcB = shb_ld_stream_v4<true>(c.lcol + i2, p2, 0u, pol_stream);
         uint4 vA0 = make_uint4(0, 0, 0, 0), vA1 = vA0, vB0 = vA0, vB1 = vA0;
@@ -181,75 +197,152 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
 }
 
 // ---------------------------------------------------------------------------------------------
-// consumer role: PB_CONS_THREADS threads, named barrier 2
+// consumer role: PB_CONS_THREADS threads, named barrier 2.  K = 32-entry steps of a piece that are
+// issued together (Q = 12 / K pieces in flight per warp); longer pieces finish in a scalar tail loop.
+// Per unit: [poll ready] bar | scatter ring -> row-sorted buffer | bar | reduce rows, store | ...
+// The next unit's piece descriptors and row offsets are fetched while this one is scattered.
 // ---------------------------------------------------------------------------------------------
-template <class S>
+__device__ __forceinline__ void pb_cp_async16(void *smem_dst, const void *gmem_src) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void pb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void pb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// 16-bit words of one unit's row metadata: [RS] row lengths then [ceil(RS / 32)] group bases, a 16-byte multiple
+__host__ __device__ __forceinline__ int pb_crp_stride(int RS) { return (RS + (RS + 31) / 32 + 7) & ~7; }
+
+__device__ __forceinline__ uint4 pb_ld_cg_v4(const void *p) {
+  uint4 v;
+  asm volatile("ld.global.cg.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+// four products into their slots of the row-sorted buffer (0xffff = padding entry)
+template <class T> __device__ __forceinline__ void pb_scatter4(T *cbuf, const uint4 &pr, const uint2 &sl) {
+  const uint32_t s0 = sl.x & 0xffffu, s1 = sl.x >> 16, s2 = sl.y & 0xffffu, s3 = sl.y >> 16;
+  if (s0 != 0xffffu) cbuf[s0] = shb_from_bits<T>(pr.x);
+  if (s1 != 0xffffu) cbuf[s1] = shb_from_bits<T>(pr.y);
+  if (s2 != 0xffffu) cbuf[s2] = shb_from_bits<T>(pr.z);
+  if (s3 != 0xffffu) cbuf[s3] = shb_from_bits<T>(pr.w);
+}
+
+// K = 128-entry steps of a piece issued together, Q = 4 / K pieces in flight per warp
+template <class S, int K>
 __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
                                            typename S::T *cbuf, uint16_t *crp_s, int tid, bool &differs) {
   typedef typename S::T T;
+  constexpr int Q = 4 / K;
+  constexpr int NW = PB_CONS_THREADS / 32;
   const int s = blockIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
-  constexpr int NW = PB_CONS_THREADS / 32;
-  for (int pass = 0; pass < c.g.n_pass; ++pass) {
-    for (int panel = 0; panel < c.g.n_panel; ++panel) {
-      const int g = pass * c.g.n_panel + panel;
-      const int64_t gs = (int64_t)g * c.g.n_prod + s;
-      // local row offsets of this unit (independent of the producers: fetched while waiting)
-      const uint16_t *crp_g = c.crp + gs * (c.g.RS + 1);
-      for (int i = tid; i <= c.g.RS; i += PB_CONS_THREADS) crp_s[i] = __ldg(crp_g + i);
-      // lane l holds the descriptor of piece p = warp + l * NW (n_prod <= 32 * NW, checked at build time)
-      int2 d = make_int2(0, 0);
-      {
-        const int p = warp + lane * NW;
-        if (p < c.g.n_prod) d = __ldg(c.cons_desc + gs * c.g.n_prod + p);
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const int n_units = c.g.n_pass * c.g.n_panel;
+  const int stride = pb_crp_stride(c.g.RS);
+  const int ngr = (c.g.RS + 31) / 32;
+  const int cnt = (c.g.n_prod - warp + NW - 1) / NW;  // pieces of this warp: p = warp + l * NW
+  const int my_p = warp + lane * NW;
+
+  // prologue: unit 0's descriptors and row metadata
+  int2 d_next = make_int2(0, 0);
+  if (my_p < c.g.n_prod) d_next = __ldg(c.cons_desc + (int64_t)s * c.g.n_prod + my_p);
+  {
+    const uint16_t *src = c.crp + (int64_t)s * stride;
+    for (int i = tid * 8; i < stride; i += PB_CONS_THREADS * 8) pb_cp_async16(crp_s + i, src + i);
+    pb_cp_async_commit();
+  }
+  for (int g = 0; g < n_units; ++g) {
+    const int pass = g / c.g.n_panel, panel = g - pass * c.g.n_panel;
+    const int2 d = d_next;
+    if (tid == 0)
+      while (pb_ld_acquire(c.ready + g) < (uint32_t)c.g.n_prod) __nanosleep(32);
+    pb_bar(2, PB_CONS_THREADS);  // ring slot g is complete; everyone is done reducing unit g - 1
+    if (g + 1 < n_units) {
+      const int64_t gs1 = (int64_t)(g + 1) * c.g.n_prod + s;
+      if (my_p < c.g.n_prod) d_next = __ldg(c.cons_desc + gs1 * c.g.n_prod + my_p);
+      const uint16_t *src = c.crp + gs1 * stride;
+      uint16_t *dst = crp_s + ((g + 1) & 1) * stride;
+      for (int i = tid * 8; i < stride; i += PB_CONS_THREADS * 8) pb_cp_async16(dst + i, src + i);
+      if (g + 1 >= c.g.n_panel) {  // the next unit adds to row sums carried in global memory
+        const int np = (g + 1) % c.g.n_panel;
+        const int64_t r1 = ((int64_t)np * c.g.n_prod + s) * c.g.RS;
+        for (int i = tid * 32; i < c.g.RS; i += PB_CONS_THREADS * 32)
+          if (r1 + i < a.n_rows) pb_prefetch_l2(c.partial + r1 + i);
       }
-      if (tid == 0)
-        while (pb_ld_acquire(c.ready + g) < (uint32_t)c.g.n_prod) __nanosleep(64);
-      pb_bar(2, PB_CONS_THREADS);
-      const int gstart = __ldg(c.unit_ptr + g * c.g.n_prod);
-      const T *ring = c.ring + (int64_t)(g % c.g.depth) * c.g.slot_cap - gstart;
-      const int cnt = (c.g.n_prod - warp + NW - 1) / NW;  // pieces of this warp
-      for (int j = 0; j < cnt; ++j) {
-        const int start = __shfl_sync(0xffffffffu, d.x, j), len = __shfl_sync(0xffffffffu, d.y, j);
-        for (int base = 0; base < len; base += 128) {
-          uint32_t pr[4];
-          uint32_t sl[4];
+    }
+    pb_cp_async_commit();
+    const int gstart = __ldg(c.unit_ptr + g * c.g.n_prod);
+    const T *ring = c.ring + (int64_t)(g % c.g.depth) * c.g.slot_cap - gstart;
+    for (int j0 = 0; j0 < cnt; j0 += Q) {
+      int st[Q], ln[Q];
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int i = base + k * 32 + lane;
-            sl[k] = 0xffffffffu;
-            pr[k] = 0u;
-            if (i < len) {
-              pr[k] = pb_ld_cg_b32(ring + start + i);
-              sl[k] = __ldg(c.slot + start + i);
-            }
+      for (int q = 0; q < Q; ++q) {
+        st[q] = __shfl_sync(0xffffffffu, d.x, (j0 + q) & 31);
+        ln[q] = __shfl_sync(0xffffffffu, d.y, (j0 + q) & 31);
+        if (j0 + q >= cnt) ln[q] = 0;
+      }
+      uint4 pr[Q][K];
+      uint2 sl[Q][K];
+#pragma unroll
+      for (int q = 0; q < Q; ++q)
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          const int i = (k * 32 + lane) * 4;  // pieces start at multiples of 4 and are padded to multiples of 4
+          sl[q][k] = make_uint2(0xffffffffu, 0xffffffffu);
+          pr[q][k] = make_uint4(0u, 0u, 0u, 0u);
+          if (i < ln[q]) {
+            pr[q][k] = pb_ld_cg_v4(ring + st[q] + i);
+            sl[q][k] = __ldg(reinterpret_cast<const uint2 *>(c.slot + st[q] + i));
           }
+        }
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (sl[k] != 0xffffffffu) cbuf[sl[k]] = shb_from_bits<T>(pr[k]);
-        }
+      for (int q = 0; q < Q; ++q)
+#pragma unroll
+        for (int k = 0; k < K; ++k) pb_scatter4<T>(cbuf, pr[q][k], sl[q][k]);
+#pragma unroll
+      for (int q = 0; q < Q; ++q)
+        for (int i = (K * 32 + lane) * 4; i < ln[q]; i += 128)
+          pb_scatter4<T>(cbuf, pb_ld_cg_v4(ring + st[q] + i), __ldg(reinterpret_cast<const uint2 *>(c.slot + st[q] + i)));
+    }
+    // the next unit's slot stream: pull this lane's piece towards L2 (d_next has long arrived)
+    if (g + 1 < n_units && my_p < c.g.n_prod)
+      for (int i = 0; i < d_next.y; i += 64) pb_prefetch_l2(c.slot + d_next.x + i);
+    pb_cp_async_wait<1>();  // this unit's row metadata has landed (the next unit's may still be in flight)
+    pb_bar(2, PB_CONS_THREADS);
+    // the ring slot is drained (its values sit in shared memory): hand it back to the producers
+    if (tid == 0) pb_red_release(c.consumed + g);
+    const uint16_t *lens = crp_s + (g & 1) * stride;
+    const uint16_t *gbase = lens + c.g.RS;
+    const int64_t r0 = ((int64_t)panel * c.g.n_prod + s) * c.g.RS;
+    const bool last = pass == c.g.n_pass - 1;
+    // one warp per group of 32 rows; entry k of the group's rows sits in consecutive words
+    T carried = S::zero();
+    if (pass > 0 && warp < ngr && warp * 32 + lane < c.g.RS && r0 + warp * 32 + lane < a.n_rows)
+      carried = c.partial[r0 + warp * 32 + lane];
+    for (int m = warp; m < ngr; m += NW) {
+      const int i = m * 32 + lane;
+      const bool ok = i < c.g.RS && r0 + i < a.n_rows;
+      T acc = carried;
+      const int in = i + NW * 32;  // the carried sum of this lane's next row: in flight during the reduction
+      if (pass > 0 && m + NW < ngr && in < c.g.RS && r0 + in < a.n_rows) carried = c.partial[r0 + in];
+      const int len = i < c.g.RS ? (int)lens[i] : 0;
+      int off = gbase[m];
+      const int maxlen = __reduce_max_sync(0xffffffffu, len);
+      for (int k = 0; k < maxlen; ++k) {
+        const uint32_t act = __ballot_sync(0xffffffffu, k < len);
+        if (k < len) acc = S::add(acc, cbuf[off + __popc(act & lt_mask)]);
+        off += __popc(act);
       }
-      pb_bar(2, PB_CONS_THREADS);
-      // the ring slot is drained (its values sit in shared memory): hand it back to the producers
-      if (tid == 0) pb_red_release(c.consumed + g);
-      const int64_t r0 = ((int64_t)panel * c.g.n_prod + s) * c.g.RS;
-      const bool last = pass == c.g.n_pass - 1;
-      for (int i = tid; i < c.g.RS; i += PB_CONS_THREADS) {
-        const int64_t r = r0 + i;
-        if (r < a.n_rows) {
-          T acc = pass == 0 ? S::zero() : c.partial[r];
-          const int rb = crp_s[i], re = crp_s[i + 1];
-          for (int k = rb; k < re; ++k) acc = S::add(acc, cbuf[k]);
-          if (last) shb_finish_row<S>(a, r, acc, differs);
-          else c.partial[r] = acc;
-        }
+      if (ok) {
+        if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
+        else c.partial[r0 + i] = acc;
       }
-      pb_bar(2, PB_CONS_THREADS);  // cbuf / crp_s are rewritten by the next unit
     }
   }
+  pb_cp_async_wait<0>();
 }
 
-template <class S, bool HAS_VAL>
+template <class S, bool HAS_VAL, int K>
 __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_constant__ PbArgs<typename S::T> c,
                                                                   const __grid_constant__ SpmvArgs<typename S::T> a) {
   typedef typename S::T T;
@@ -262,7 +355,7 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   if (threadIdx.x < PB_PROD_THREADS) {
     if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, threadIdx.x);
   } else {
-    if (c.roles & PB_ROLE_CONSUME) pb_consume<S>(c, a, cbuf, crp_s, threadIdx.x - PB_PROD_THREADS, differs);
+    if (c.roles & PB_ROLE_CONSUME) pb_consume<S, K>(c, a, cbuf, crp_s, threadIdx.x - PB_PROD_THREADS, differs);
   }
   shb_publish_changed(a.ctl, differs);
   __syncthreads();

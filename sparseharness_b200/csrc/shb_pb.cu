@@ -53,14 +53,14 @@ __global__ void pb_bounds_kernel(const uint32_t *sorted_keys, int64_t n, uint32_
 
 // producer-order scatter of (local column, value); emits the consumer-order key of every entry
 __global__ void pb_scatter_kernel(PbGeom g, const uint32_t *sorted_keys, const uint32_t *perm, int64_t n_valid,
-                                  const int32_t *piece_start, const int32_t *unit_ptr, const int32_t *col,
+                                  const int32_t *piece_start, const int32_t *piece_pad, const int32_t *col,
                                   const uint32_t *val, const uint16_t *lrow_tmp, uint16_t *lcol, uint32_t *oval,
                                   uint32_t *key2, uint32_t *dst2) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_valid; i += (int64_t)gridDim.x * blockDim.x) {
     const uint32_t key = sorted_keys[i];
     const uint32_t u = key / (uint32_t)g.n_prod, s = key - u * (uint32_t)g.n_prod;
     const uint32_t grp = u / (uint32_t)g.n_prod;  // (pass, panel)
-    const int64_t dst = (int64_t)unit_ptr[u] + (i - (int64_t)piece_start[(int64_t)u * g.n_prod]);
+    const int64_t dst = (int64_t)piece_pad[key] + (i - (int64_t)piece_start[key]);  // pieces start at multiples of 4
     const uint32_t j = perm[i];
     const uint32_t c = (uint32_t)col[j];
     lcol[dst] = (uint16_t)(c % (uint32_t)g.W);
@@ -70,26 +70,40 @@ __global__ void pb_scatter_kernel(PbGeom g, const uint32_t *sorted_keys, const u
   }
 }
 
-// consumer order: rank inside the consumer unit = the entry's slot; row offsets per unit
-__global__ void pb_slots_kernel(PbGeom g, const uint32_t *key2_sorted, const uint32_t *dst2_sorted, int64_t n_valid,
-                                const int32_t *bound2, uint16_t *slot) {
-  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += (int64_t)gridDim.x * blockDim.x) {
-    const uint32_t gs = key2_sorted[j] / (uint32_t)g.RS;
-    slot[dst2_sorted[j]] = (uint16_t)(j - (int64_t)bound2[(int64_t)gs * g.RS]);
+// consumer order.  The row-sorted buffer of a consumer unit is laid out per group of 32 consecutive rows,
+// k-major inside a group: first every row's entry 0 (rows in order, empty rows skipped), then every
+// row's entry 1, ...  A warp reducing the group reads consecutive words at every step (no bank
+// conflicts) and needs only the row lengths and the group's base.  One warp per (unit, group):
+// writes the slot of every entry, the row lengths and the group bases (crp layout: [RS] lengths,
+// then [ceil(RS/32)] bases, 16-bit each).
+__global__ void pb_slots_kernel(PbGeom g, const uint32_t *dst2_sorted, const int32_t *bound2, int64_t n_cons_units,
+                                uint16_t *slot, uint16_t *crp, int32_t *max_unit) {
+  const int lane = threadIdx.x & 31;
+  const int ngr = (g.RS + 31) / 32;
+  const int stride = pb_crp_stride(g.RS);
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n_cons_units * ngr; w += n_warps) {
+    const int64_t gs = w / ngr;
+    const int m = (int)(w - gs * ngr);
+    const int i = m * 32 + lane;
+    const int64_t kb = gs * g.RS;
+    const int ustart = bound2[kb];
+    const int rb = i < g.RS ? bound2[kb + i] : 0, re = i < g.RS ? bound2[kb + i + 1] : 0;
+    const int len = re - rb;
+    const int gbase = __shfl_sync(0xffffffffu, rb, 0) - ustart;
+    if (i < g.RS) crp[gs * stride + i] = (uint16_t)min(len, 65535);
+    if (lane == 0) {
+      crp[gs * stride + g.RS + m] = (uint16_t)min(gbase, 65535);
+      if (m == 0) atomicMax(max_unit, bound2[kb + g.RS] - ustart);
+    }
+    const int maxlen = __reduce_max_sync(0xffffffffu, len);
+    int off = gbase;
+    for (int k = 0; k < maxlen; ++k) {
+      const uint32_t act = __ballot_sync(0xffffffffu, k < len);
+      if (k < len) slot[dst2_sorted[rb + k]] = (uint16_t)min(off + __popc(act & ((1u << lane) - 1u)), 65535);
+      off += __popc(act);
+    }
   }
-}
-
-__global__ void pb_crp_kernel(PbGeom g, const int32_t *bound2, int64_t n_cons_units, uint16_t *crp, int32_t *max_unit) {
-  const int64_t total = n_cons_units * (g.RS + 1);
-  int local_max = 0;
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t gs = t / (g.RS + 1);
-    const int i = (int)(t - gs * (g.RS + 1));
-    const int v = bound2[gs * g.RS + i] - bound2[gs * g.RS];
-    crp[t] = (uint16_t)min(v, 65535);
-    if (i == g.RS) local_max = max(local_max, v);
-  }
-  if (local_max) atomicMax(max_unit, local_max);
 }
 
 void shb_pb_free(shb_pb *pb) {
@@ -107,7 +121,7 @@ void shb_pb_free(shb_pb *pb) {
 }
 
 static size_t pb_smem_bytes(const PbGeom &g) {
-  return (size_t)g.W * 4 + (size_t)g.cbuf_cap * 4 + (((size_t)g.RS + 1) * 2 + 15) / 16 * 16;
+  return (size_t)g.W * 4 + (size_t)g.cbuf_cap * 4 + (size_t)pb_crp_stride(g.RS) * 2 * 2;
 }
 
 SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer, int make_default) {
@@ -124,12 +138,16 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   memset(&g, 0, sizeof g);
   g.n_prod = c->prop.multiProcessorCount;
   SHB_REQUIRE(g.n_prod <= 32 * (PB_CONS_THREADS / 32), "more SMs than one descriptor chunk covers");
-  g.n_pass = (int)((A->n_cols + (int64_t)g.n_prod * PB_MAX_W - 1) / ((int64_t)g.n_prod * PB_MAX_W));
+  int max_w = PB_MAX_W;
+  if (const char *e = getenv("SHB_PB_MAXW")) max_w = std::max(64, std::min(PB_MAX_W, atoi(e)));
+  g.n_pass = (int)((A->n_cols + (int64_t)g.n_prod * max_w - 1) / ((int64_t)g.n_prod * max_w));
   g.W = (int)((A->n_cols + (int64_t)g.n_prod * g.n_pass - 1) / ((int64_t)g.n_prod * g.n_pass));
   g.W = std::max(4, (g.W + 3) & ~3);
   // rows per consumer: the unit (RS rows x mean row length / n_pass entries) should fill about 44 KB of shared memory
   const double per_row = std::max(1.0, (double)A->nnz / (double)A->n_rows / g.n_pass);
-  int rs = rows_per_consumer > 0 ? rows_per_consumer : (int)std::min(8192.0, std::max(32.0, 11264.0 / (per_row * 1.05)));
+  // automatic: a consumer unit (RS rows x per_row entries, 4 bytes each) takes the shared memory the x slice leaves
+  const double free_entries = std::min(30000.0, ((double)PB_SMEM_LIMIT - 6144.0 - (double)g.W * 4) / 4.0);
+  int rs = rows_per_consumer > 0 ? rows_per_consumer : (int)std::min(16384.0, std::max(32.0, free_entries / (per_row * 1.06 + 1.1)));
   g.n_panel = (int)((A->n_rows + (int64_t)g.n_prod * rs - 1) / ((int64_t)g.n_prod * rs));
   g.RS = (int)((A->n_rows + (int64_t)g.n_prod * g.n_panel - 1) / ((int64_t)g.n_prod * g.n_panel));
   SHB_REQUIRE(g.RS <= 32767, "rows_per_consumer too large");
@@ -142,12 +160,12 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
 
   uint32_t *keys = nullptr, *keys_s = nullptr, *src = nullptr, *perm = nullptr;
   uint16_t *lrow_tmp = nullptr;
-  int32_t *piece_start = nullptr, *bound2 = nullptr, *d_max = nullptr;
+  int32_t *piece_start = nullptr, *piece_pad = nullptr, *bound2 = nullptr, *d_max = nullptr;
   void *cub_tmp = nullptr;
   size_t cub_bytes = 0, cub_bytes2 = 0;
   shb_pb *pb = new shb_pb();
   int status = SHB_OK;
-  std::vector<int32_t> h_piece, h_unit;
+  std::vector<int32_t> h_piece, h_unit, h_ppad;
   std::vector<int2> h_desc;
 #define PB_CUDA(call)                                                                                   \
   do {                                                                                                  \
@@ -166,6 +184,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     PB_CUDA(cudaMalloc(&perm, (size_t)nnz * 4));
     PB_CUDA(cudaMalloc(&lrow_tmp, (size_t)nnz * 2));
     PB_CUDA(cudaMalloc(&piece_start, (size_t)(n_buckets + 1) * 4));
+    PB_CUDA(cudaMalloc(&piece_pad, (size_t)n_buckets * 4));
     PB_CUDA(cudaMalloc(&bound2, (size_t)(n_keys2 + 1) * 4));
     PB_CUDA(cudaMalloc(&d_max, 4));
     PB_CUDA(cudaMemsetAsync(d_max, 0, 4, c->stream));
@@ -184,14 +203,21 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     h_piece.resize((size_t)n_buckets + 1);
     PB_CUDA(cudaMemcpyAsync(h_piece.data(), piece_start, (size_t)(n_buckets + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
     PB_CUDA(cudaStreamSynchronize(c->stream));
-    // unit starts padded to 8 entries (16-byte groups of local columns), piece descriptors consumer-major
+    // pieces start at multiples of 4 entries (the consumer's 128-bit ring loads), units at multiples of 8 (the
+    // producer's 16-byte groups of local columns); piece descriptors are stored consumer-major
     h_unit.resize((size_t)n_units + 1);
+    h_ppad.resize((size_t)n_buckets);
     int64_t pos = 0, max_group = 0;
     for (int64_t u = 0; u < n_units; ++u) {
       if (u % g.n_prod == 0 && u > 0) max_group = std::max(max_group, pos - (int64_t)h_unit[(size_t)(u - g.n_prod)]);
       h_unit[(size_t)u] = (int32_t)pos;
-      const int64_t len = (int64_t)h_piece[(size_t)((u + 1) * g.n_prod)] - h_piece[(size_t)(u * g.n_prod)];
-      pos += (len + 7) & ~(int64_t)7;
+      int64_t in_unit = 0;
+      for (int s = 0; s < g.n_prod; ++s) {
+        const int64_t key = u * g.n_prod + s;
+        h_ppad[(size_t)key] = (int32_t)(pos + in_unit);
+        in_unit += ((int64_t)h_piece[(size_t)key + 1] - h_piece[(size_t)key] + 3) & ~(int64_t)3;
+      }
+      pos += (in_unit + 7) & ~(int64_t)7;
       if (pos >= (int64_t)0x7fffffff - 64) {
         shb_set_error("operator too large for the blocked layout (%lld padded entries)", (long long)pos);
         status = SHB_ERR_TOO_LARGE;
@@ -206,12 +232,11 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     for (int64_t gp = 0; gp < n_groups; ++gp)
       for (int p = 0; p < g.n_prod; ++p) {
         const int64_t u = gp * g.n_prod + p;
-        const int32_t ubase = h_piece[(size_t)(u * g.n_prod)];
         for (int s = 0; s < g.n_prod; ++s) {
           const int64_t key = u * g.n_prod + s;
           int2 d;
-          d.x = h_unit[(size_t)u] + (h_piece[(size_t)key] - ubase);
-          d.y = h_piece[(size_t)key + 1] - h_piece[(size_t)key];
+          d.x = h_ppad[(size_t)key];
+          d.y = (h_piece[(size_t)key + 1] - h_piece[(size_t)key] + 3) & ~3;
           h_desc[(size_t)((gp * g.n_prod + s) * g.n_prod + p)] = d;
         }
       }
@@ -221,31 +246,31 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     if (A->val) PB_CUDA(cudaMalloc(&pb->val, (size_t)pb->cap * 4));
     PB_CUDA(cudaMalloc(&pb->unit_ptr, (size_t)(n_units + 1) * 4));
     PB_CUDA(cudaMalloc(&pb->cons_desc, (size_t)n_buckets * sizeof(int2)));
-    PB_CUDA(cudaMalloc(&pb->crp, (size_t)n_units * (g.RS + 1) * 2));
+    PB_CUDA(cudaMalloc(&pb->crp, (size_t)n_units * pb_crp_stride(g.RS) * 2));
+    PB_CUDA(cudaMemsetAsync(pb->crp, 0, (size_t)n_units * pb_crp_stride(g.RS) * 2, c->stream));
     PB_CUDA(cudaMalloc(&pb->partial, (size_t)A->n_rows * 4));
     PB_CUDA(cudaMalloc(&pb->sync, (size_t)(2 * n_groups + 1) * 4));
     PB_CUDA(cudaMemsetAsync(pb->sync, 0, (size_t)(2 * n_groups + 1) * 4, c->stream));
     PB_CUDA(cudaMemsetAsync(pb->lcol, 0, (size_t)pb->cap * 2, c->stream));
     PB_CUDA(cudaMemsetAsync(pb->slot, 0xff, (size_t)pb->cap * 2, c->stream));  // 0xffff = padding
     if (pb->val) PB_CUDA(cudaMemsetAsync(pb->val, 0, (size_t)pb->cap * 4, c->stream));
+    PB_CUDA(cudaMemcpyAsync(piece_pad, h_ppad.data(), (size_t)n_buckets * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(pb->unit_ptr, h_unit.data(), (size_t)(n_units + 1) * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(pb->cons_desc, h_desc.data(), (size_t)n_buckets * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
     if (pb->n_valid > 0) {
       const unsigned grid_v = (unsigned)std::min<int64_t>((pb->n_valid + 255) / 256, 148 * 32);
       // keys / src are free again: they receive the consumer-order keys and the producer positions
-      pb_scatter_kernel<<<grid_v, 256, 0, c->stream>>>(g, keys_s, perm, pb->n_valid, piece_start, pb->unit_ptr, A->col,
+      pb_scatter_kernel<<<grid_v, 256, 0, c->stream>>>(g, keys_s, perm, pb->n_valid, piece_start, piece_pad, A->col,
                                                        (const uint32_t *)A->val, lrow_tmp, pb->lcol, (uint32_t *)pb->val, keys, src);
       PB_CUDA(cudaGetLastError());
       PB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys_s, src, perm, (int)pb->n_valid, 0, 32, c->stream));
       pb_bounds_kernel<<<grid_v, 256, 0, c->stream>>>(keys_s, pb->n_valid, (uint32_t)n_keys2, bound2);
       PB_CUDA(cudaGetLastError());
-      pb_slots_kernel<<<grid_v, 256, 0, c->stream>>>(g, keys_s, perm, pb->n_valid, bound2, pb->slot);
-      PB_CUDA(cudaGetLastError());
     } else {
       PB_CUDA(cudaMemsetAsync(bound2, 0, (size_t)(n_keys2 + 1) * 4, c->stream));
     }
-    pb_crp_kernel<<<(unsigned)std::min<int64_t>((n_units * (g.RS + 1) + 255) / 256, 148 * 32), 256, 0, c->stream>>>(
-        g, bound2, n_units, pb->crp, d_max);
+    pb_slots_kernel<<<(unsigned)std::min<int64_t>((n_units * ((g.RS + 31) / 32) + 7) / 8, 148 * 32), 256, 0, c->stream>>>(
+        g, perm, bound2, n_units, pb->slot, pb->crp, d_max);
     PB_CUDA(cudaGetLastError());
     PB_CUDA(cudaMemcpyAsync(&pb->max_unit, d_max, 4, cudaMemcpyDeviceToHost, c->stream));
     PB_CUDA(cudaStreamSynchronize(c->stream));  // the host staging vectors go out of scope
@@ -263,7 +288,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     pb->ring_depth_alloc = g.depth;
     pb->g = g;
     pb->device_bytes = (uint64_t)pb->cap * (2 + 2 + (A->val ? 4 : 0)) + (uint64_t)(n_units + 1) * 4 + (uint64_t)n_buckets * 8 +
-                       (uint64_t)n_units * (g.RS + 1) * 2 + (uint64_t)g.depth * g.slot_cap * 4 + (uint64_t)A->n_rows * 4;
+                       (uint64_t)n_units * pb_crp_stride(g.RS) * 2 + (uint64_t)g.depth * g.slot_cap * 4 + (uint64_t)A->n_rows * 4;
   }
 done:
 #undef PB_CUDA
@@ -273,6 +298,7 @@ done:
   cudaFree(perm);
   cudaFree(lrow_tmp);
   cudaFree(piece_start);
+  cudaFree(piece_pad);
   cudaFree(bound2);
   cudaFree(d_max);
   cudaFree(cub_tmp);

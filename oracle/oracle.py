@@ -56,6 +56,33 @@ def _c(a, dt):
     return None if a is None else np.ascontiguousarray(a, dtype=dt)
 
 
+def write_mtx(path, n_rows, n_cols, row_ptr, col, val, second_index_is_row=False) -> None:
+    """CSR block -> Matrix Market text file (what the reference's loader reads, src/sparse_matrix.cpp:11-70).
+    second_index_is_row writes "col row value" lines: the reference takes the second index as the row (Q1), so
+    that is the file from which ITS loader rebuilds exactly these rows."""
+    rp, c, v = _c(row_ptr, np.int64), _c(col, np.int32), _c(val, np.float32)
+    if lib().orc_write_mtx(path.encode(), C.c_int64(n_rows), C.c_int64(n_cols), _p(rp), _p(c), _p(v), C.c_int(int(second_index_is_row))) != 0:
+        raise OSError(f"cannot write {path}")
+
+
+REF_DRIVER = os.path.join(HERE, "_ref", "ref_driver")
+
+
+def reference_gold_time(mtx_path, warmup, reps, timeout=600):
+    """Times the UNMODIFIED reference's Gold<float>::spmv (inc/spmv_gold.h:9-28, single threaded, matrix passed by
+    value) on a Matrix Market file through oracle/_ref/ref_driver.  Returns (mean_ns, best_ns) or None when the
+    driver is not there (it is compiled from /root/reference by oracle/Makefile and travels prebuilt)."""
+    if not os.path.exists(REF_DRIVER):
+        return None
+    r = subprocess.run([REF_DRIVER, "time", mtx_path, str(int(reps)), str(int(warmup))], stdout=subprocess.PIPE,
+                       stderr=subprocess.DEVNULL, timeout=timeout)
+    for line in reversed(r.stdout.decode(errors="replace").splitlines()):
+        if line.startswith("TIME "):
+            f = line.split()
+            return float(f[f.index("mean_ns") + 1]), float(f[f.index("best_ns") + 1])
+    return None
+
+
 def num_threads() -> int:
     return int(lib().orc_num_threads())
 

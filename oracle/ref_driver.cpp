@@ -16,7 +16,7 @@
 //   ref_driver gold <mtx> <xmode>                      Gold<float>::spmv, alpha=1 beta=0 y=0
 //                                                      xmode 0: x == 1 (app/spmv.cpp:117)
 //                                                      xmode 1: x[i] = ((7 i + 3) mod 11) - 5
-//   ref_driver time <mtx> <reps>                       wall-clock ns of Gold<float>::spmv per call
+//   ref_driver time <mtx> <reps> [warmup]              wall-clock ns of Gold<float>::spmv per call
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -70,7 +70,9 @@ int main(int argc, char **argv) {
     ConstXVectorGenerator<float> x(1.0f);
     ConstYVectorGenerator<float> y(0);
     const int reps = std::atoi(argv[3]);
+    const int warmup = argc > 4 ? std::atoi(argv[4]) : 0;
     (void)m.ellpack_encode(); // build the ragged rows once, as the spmv app has by then
+    for (int r = 0; r < warmup; ++r) (void)Gold<float>::spmv(m, x, y, 1.0f, 0.0f, 0.0f);
     double best = 1e300, sum = 0;
     float sink = 0;
     for (int r = 0; r < reps; ++r) {

@@ -42,6 +42,26 @@
 enum { ORC_PLUS_TIMES = 0, ORC_MIN_PLUS = 1, ORC_OR_AND = 2, ORC_MAX_MIN = 3 };
 enum { ORC_TERM_ABSDIFF = 0, ORC_TERM_EQUAL = 1 };
 
+/* Writes a CSR block as a Matrix Market "coordinate real general" file (1-based, %.9g values): the only
+ * input format the reference's loader accepts (src/sparse_matrix.cpp:11-70).  Used by bench.py to hand a
+ * bounded sample of a synthetic operator to oracle/_ref/ref_driver.  Returns 0 on success. */
+ORC_API int orc_write_mtx(const char *path, int64_t n_rows, int64_t n_cols, const int64_t *row_ptr, const int32_t *col,
+                          const float *val, int second_index_is_row) {
+  FILE *f = fopen(path, "w");
+  if (!f) return 1;
+  static char buf[1 << 20];
+  setvbuf(f, buf, _IOFBF, sizeof buf);
+  fprintf(f, "%%%%MatrixMarket matrix coordinate real general\n%lld %lld %lld\n", (long long)n_rows, (long long)n_cols,
+          (long long)row_ptr[n_rows]);
+  for (int64_t r = 0; r < n_rows; ++r)
+    for (int64_t k = row_ptr[r]; k < row_ptr[r + 1]; ++k)
+      if (second_index_is_row)  /* the reference keeps (I, J) as (x, y) and uses y as the row (src/sparse_matrix.cpp:59,86) */
+        fprintf(f, "%d %lld %.9g\n", col[k] + 1, (long long)(r + 1), val ? (double)val[k] : 1.0);
+      else
+        fprintf(f, "%lld %d %.9g\n", (long long)(r + 1), col[k] + 1, val ? (double)val[k] : 1.0);
+  return fclose(f) != 0;
+}
+
 ORC_API int orc_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -76,3 +76,24 @@ def test_live_reference_when_present(orc, mtx_dir):
         assert np.array_equal(rp, rp2) and np.array_equal(col, col2) and np.array_equal(val, val2)
         assert np.array_equal(orc.ref_gold(mtx_dir[name], 1),
                               orc.gold_spmv(rp2, col2, val2, orc.xmode_vector(h, 1), np.zeros(h, np.float32)))
+
+
+def test_sample_file_for_the_reference_arm_round_trips(orc, tmp_path):
+    """bench.py --impl reference hands a CSR sample to the reference as Matrix Market text: the file written with
+    second_index_is_row makes the reference's loader (which takes the second index as the row, Q1) rebuild exactly
+    those rows, and its Gold agrees with the oracle on them (values int-truncated by the loader, Q2)."""
+    rp, col, val = orc.gen_uniform(4096, 4096, 16, val_mode=1, row_begin=0, row_count=300)
+    path = str(tmp_path / "sample.mtx")
+    orc.write_mtx(path, 300, 4096, rp, col, val, second_index_is_row=True)
+    head = open(path).read().splitlines()[:3]
+    assert head[0].startswith("%%MatrixMarket matrix coordinate real general") and head[1] == f"300 4096 {len(col)}"
+    assert head[2].split()[:2] == [str(col[0] + 1), "1"]
+    if not orc.ref_available():
+        pytest.skip("oracle/_ref/ref_driver not present")
+    h, w, rrp, rcol, rval = orc.ref_rows(path, "float")
+    assert (h, w) == (300, 4096) and np.array_equal(rrp, rp)
+    for r in range(300):  # the reference keeps file order inside a row (its per-row sort works on a copy)
+        a, b = rp[r], rp[r + 1]
+        assert sorted(zip(rcol[a:b], rval[a:b])) == sorted(zip(col[a:b], np.trunc(val[a:b])))
+    t = orc.reference_gold_time(path, 1, 2)
+    assert t is not None and t[0] > 0

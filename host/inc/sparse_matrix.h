@@ -16,10 +16,12 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <iostream>
 #include <limits>
 #include <string>
 #include <utility>
+#include <thread>
 #include <vector>
 
 #include "common.h"
@@ -116,9 +118,17 @@ private:
     }
     std::string buf;
     {
+      std::fseek(f, 0, SEEK_END);
+      const long sz = std::ftell(f);
+      std::rewind(f);
+      if (sz > 0) {  // regular file: one read into a buffer of the right size
+        buf.resize((std::size_t)sz);
+        const std::size_t got = std::fread(&buf[0], 1, (std::size_t)sz, f);
+        buf.resize(got);
+      }
       char chunk[1 << 16];
       std::size_t got;
-      while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) buf.append(chunk, got);
+      while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) buf.append(chunk, got);  // pipes, growing files
     }
     std::fclose(f);
     MMHeader h;
@@ -144,29 +154,18 @@ private:
     eI.reserve(cap);
     eJ.reserve(cap);
     eV.reserve(cap);
-    // entries are whitespace-separated tokens, line structure is irrelevant (fscanf semantics)
-    const char *p = buf.c_str() + pos;
-    for (int i = 0; i < nonz; ++i) {
-      char *end = nullptr;
-      const long I1 = std::strtol(p, &end, 10);
-      if (end == p) break;
-      p = end;
-      const long J1 = std::strtol(p, &end, 10);
-      if (end == p) break;
-      p = end;
-      double v = 1.0;
-      if (!h.is_pattern) {
-        v = std::strtod(p, &end);
-        if (end == p) break;
-        p = end;
-      }
+    const char *data = buf.c_str() + pos;
+    const std::size_t data_len = buf.size() - pos;
+    if (parse_entries_parallel(data, data_len, h.is_pattern, h.is_symmetric, nonz)) return;
+    std::vector<long> rawI, rawJ;
+    std::vector<double> rawV;
+    parse_entries_sequential(data, h.is_pattern, nonz, rawI, rawJ, rawV);
+    // range check, 1-based -> 0-based and symmetric expansion, in file order
+    for (std::size_t k = 0; k < rawI.size(); ++k) {
+      const long I1 = rawI[k], J1 = rawJ[k];
       const int32_t I = (int32_t)I1 - 1, J = (int32_t)J1 - 1;
-      if (I < 0 || J < 0 || I >= cols_or_rows() || J >= rows) {
-        std::cerr << "Matrix entry (" << I1 << ", " << J1 << ") lies outside the declared " << rows << " x " << cols
-                  << " matrix" << ENDL;
-        std::exit(-1);
-      }
-      const EType tv = static_cast<EType>(v);
+      if (I < 0 || J < 0 || I >= cols_or_rows() || J >= rows) entry_out_of_range(I1, J1);
+      const EType tv = static_cast<EType>(rawV[k]);
       eI.push_back(I);
       eJ.push_back(J);
       eV.push_back(tv);
@@ -176,6 +175,144 @@ private:
         eV.push_back(tv);
       }
     }
+  }
+
+  void entry_out_of_range(long I1, long J1) const {
+    std::cerr << "Matrix entry (" << I1 << ", " << J1 << ") lies outside the declared " << rows << " x " << cols
+              << " matrix" << ENDL;
+    std::exit(-1);
+  }
+
+  // The reference reads entries with fscanf("%d %d %lg\n") (src/sparse_matrix.cpp:50-57): whitespace-separated
+  // tokens, line structure irrelevant, stop at the first token that does not parse.
+  static void parse_entries_sequential(const char *p, bool pattern, int nonz, std::vector<long> &oI, std::vector<long> &oJ,
+                                       std::vector<double> &oV) {
+    oI.clear(); oJ.clear(); oV.clear();
+    for (int i = 0; i < nonz; ++i) {
+      char *end = nullptr;
+      const long I1 = std::strtol(p, &end, 10);
+      if (end == p) break;
+      p = end;
+      const long J1 = std::strtol(p, &end, 10);
+      if (end == p) break;
+      p = end;
+      double v = 1.0;
+      if (!pattern) {
+        v = std::strtod(p, &end);
+        if (end == p) break;
+        p = end;
+      }
+      oI.push_back(I1);
+      oJ.push_back(J1);
+      oV.push_back(v);
+    }
+  }
+
+  // Same tokens, parsed by several threads: the data is cut at line ends, every thread parses its lines with the
+  // same strtol / strtod calls (and applies the same range check and element conversion), and the pieces are
+  // concatenated in file order -- by the same threads when no symmetric expansion is needed.  Only files with
+  // exactly one entry per non-blank line qualify (every SuiteSparse file does); anything else returns false with
+  // nothing stored and the sequential token parser runs, so the result is identical by construction.
+  // SHB_MM_THREADS caps the thread count (1 = never parallel), SHB_MM_PARALLEL_MIN_BYTES (default 4 MiB) is the
+  // size below which threads do not pay.
+  bool parse_entries_parallel(const char *data, std::size_t len, bool pattern, bool symmetric, int nonz_decl) {
+    std::size_t min_bytes = 4u << 20;
+    if (const char *e = std::getenv("SHB_MM_PARALLEL_MIN_BYTES")) min_bytes = (std::size_t)std::strtoull(e, nullptr, 10);
+    unsigned n_thr = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    if (const char *e = std::getenv("SHB_MM_THREADS")) n_thr = (unsigned)std::max(1, std::atoi(e));
+    if (n_thr < 2 || len < min_bytes || nonz_decl <= 0) return false;
+    std::vector<std::size_t> cut(n_thr + 1, len);
+    cut[0] = 0;
+    for (unsigned t = 1; t < n_thr; ++t) {
+      std::size_t c = std::max(cut[t - 1], len / n_thr * t);
+      while (c < len && data[c] != '\n') ++c;
+      cut[t] = std::min(len, c + (c < len ? 1 : 0));
+    }
+    struct Piece {
+      std::vector<int32_t> I, J;
+      std::vector<EType> V;
+      bool regular = true;
+      std::size_t bad_at = (std::size_t)-1;  // first entry of the piece outside the declared shape
+      long badI = 0, badJ = 0;
+    };
+    std::vector<Piece> pieces(n_thr);
+    const int lim_i = cols_or_rows(), lim_j = rows;
+    auto work = [&](unsigned t) {
+      Piece &pc = pieces[t];
+      const char *p = data + cut[t], *stop = data + cut[t + 1];
+      const std::size_t guess = (cut[t + 1] - cut[t]) / 10 + 16;
+      pc.I.reserve(guess); pc.J.reserve(guess); pc.V.reserve(guess);
+      while (p < stop) {
+        const char *eol = (const char *)std::memchr(p, '\n', (std::size_t)(stop - p));
+        if (!eol) eol = stop;
+        const char *q = p;
+        while (q < eol && (*q == ' ' || *q == '\t' || *q == '\r')) ++q;
+        if (q < eol) {  // a non-blank line: exactly the entry's tokens, nothing else
+          char *end = nullptr;
+          const long I1 = std::strtol(q, &end, 10);
+          if (end == q || end > eol) { pc.regular = false; return; }
+          q = end;
+          const long J1 = std::strtol(q, &end, 10);
+          if (end == q || end > eol) { pc.regular = false; return; }
+          q = end;
+          double v = 1.0;
+          if (!pattern) {
+            v = std::strtod(q, &end);
+            if (end == q || end > eol) { pc.regular = false; return; }
+            q = end;
+          }
+          while (q < eol && (*q == ' ' || *q == '\t' || *q == '\r')) ++q;
+          if (q != eol) { pc.regular = false; return; }
+          const int32_t I = (int32_t)I1 - 1, J = (int32_t)J1 - 1;
+          if ((I < 0 || J < 0 || I >= lim_i || J >= lim_j) && pc.bad_at == (std::size_t)-1) {
+            pc.bad_at = pc.I.size();
+            pc.badI = I1;
+            pc.badJ = J1;
+          }
+          pc.I.push_back(I); pc.J.push_back(J); pc.V.push_back(static_cast<EType>(v));
+        }
+        p = eol + 1;
+      }
+    };
+    {
+      std::vector<std::thread> threads;
+      for (unsigned t = 1; t < n_thr; ++t) threads.emplace_back(work, t);
+      work(0);
+      for (auto &th : threads) th.join();
+    }
+    std::size_t total = 0;
+    for (auto &pc : pieces) {
+      if (!pc.regular) return false;
+      total += pc.I.size();
+    }
+    const std::size_t keep = std::min<std::size_t>(total, (std::size_t)nonz_decl);
+    std::vector<std::size_t> first(n_thr + 1, 0);  // position of each piece in the kept sequence
+    for (unsigned t = 0; t < n_thr; ++t) first[t + 1] = std::min(keep, first[t] + pieces[t].I.size());
+    for (unsigned t = 0; t < n_thr; ++t)
+      if (pieces[t].bad_at != (std::size_t)-1 && first[t] + pieces[t].bad_at < first[t + 1])
+        entry_out_of_range(pieces[t].badI, pieces[t].badJ);  // the first offender in file order
+    if (!symmetric) {
+      eI.resize(keep); eJ.resize(keep); eV.resize(keep);
+      auto copy = [&](unsigned t) {
+        const std::size_t n = first[t + 1] - first[t];
+        if (!n) return;
+        std::memcpy(&eI[first[t]], pieces[t].I.data(), n * sizeof(int32_t));
+        std::memcpy(&eJ[first[t]], pieces[t].J.data(), n * sizeof(int32_t));
+        std::copy(pieces[t].V.begin(), pieces[t].V.begin() + (std::ptrdiff_t)n, eV.begin() + (std::ptrdiff_t)first[t]);
+      };
+      std::vector<std::thread> threads;
+      for (unsigned t = 1; t < n_thr; ++t) threads.emplace_back(copy, t);
+      copy(0);
+      for (auto &th : threads) th.join();
+    } else {
+      for (unsigned t = 0; t < n_thr; ++t)
+        for (std::size_t k = 0; k < first[t + 1] - first[t]; ++k) {
+          const int32_t I = pieces[t].I[k], J = pieces[t].J[k];
+          eI.push_back(I); eJ.push_back(J); eV.push_back(pieces[t].V[k]);
+          if (I != J) { eI.push_back(J); eJ.push_back(I); eV.push_back(pieces[t].V[k]); }
+        }
+    }
+    return true;
   }
 
   int cols_or_rows() const { return std::max(cols, rows); }

@@ -123,3 +123,45 @@ def test_host_cli_contract(tmp_path, mtx_dir):
     r = subprocess.run([os.path.join(BIN, "just_parser_harness"), "-m", str(cplx), "-k",
                         os.path.join(KERNELS, "spmv", "glb-sdp.json")], capture_output=True, text=True)
     assert r.returncode == 255 and "Cannot process this matrix type" in r.stderr
+
+
+@pytest.mark.parametrize("kind", ["real general", "real symmetric", "pattern general", "integer general", "irregular"])
+def test_parallel_parse_equals_sequential_parse(tmp_path, monkeypatch, kind):
+    """the threaded Matrix Market entry parser (host/inc/sparse_matrix.h) gives exactly the
+    sequential token parser's operator -- same tuples in the same order -- on general / symmetric / pattern /
+    integer files with blank lines, CRLF and surplus entries; an irregular file (two entries on one line)
+    falls back to the sequential parser."""
+    rng = np.random.default_rng(11)
+    n, nnz = 3000, 60000
+    I = rng.integers(1, n + 1, nnz)
+    J = rng.integers(1, n + 1, nnz)
+    V = rng.normal(0, 40, nnz)
+    field, sym = ("real", "general") if kind == "irregular" else kind.split()
+    if sym == "symmetric":
+        I, J = np.maximum(I, J), np.minimum(I, J)
+    lines = [f"%%MatrixMarket matrix coordinate {field} {sym}", "% comment", f"{n} {n} {nnz}"]
+    for k in range(nnz):
+        if field == "pattern":
+            e = f"{I[k]} {J[k]}"
+        elif field == "integer":
+            e = f"{I[k]}\t{J[k]} {int(V[k])}"
+        else:
+            e = f"{I[k]} {J[k]}  {V[k]:.9g}" if k % 3 else f" {I[k]} {J[k]} {V[k]:.6e} "
+        lines.append(e + ("\r" if k % 50 == 0 else ""))
+        if k % 1000 == 999:
+            lines.append("")
+    if kind == "irregular":
+        lines[5] = lines[5].rstrip("\r") + " " + lines.pop(6).rstrip("\r")  # two entries on one line
+    lines += ["1 1 5", "2 2 6"]  # beyond nonz: ignored by both parsers
+    mtx = tmp_path / "m.mtx"
+    mtx.write_text("\n".join(lines) + "\n")
+    kernel = os.path.join(KERNELS, "spmv", "glb-sdp-rsa.json")
+    monkeypatch.setenv("SHB_MM_THREADS", "1")
+    a = _parse(tmp_path, str(mtx), kernel, extra=("--keep_values",))
+    monkeypatch.setenv("SHB_MM_THREADS", "7")
+    monkeypatch.setenv("SHB_MM_PARALLEL_MIN_BYTES", "1")
+    b = _parse(tmp_path, str(mtx), kernel, extra=("--keep_values",))
+    for k in ("rp", "col", "gold"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a["val"].view(np.int32), b["val"].view(np.int32))
+    assert a["rp"][-1] == (nnz if sym == "general" else nnz + int((I != J).sum()))

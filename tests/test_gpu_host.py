@@ -164,3 +164,36 @@ def test_harness_runs_synthetic_configs(tmp_path, mtx_dir):
                            "rmat:12:8", "--mode", "canonical")
     rp, col = orc.gen_rmat(12, 8)
     assert np.array_equal(np.fromfile(dump, np.int32), orc.bfs_levels(rp, col, None, 0)[0])
+
+
+def test_sweep_scripts_emit_the_reference_result_files(tmp_path, mtx_dir):
+    """host/scripts/experiments/run_all.sh sweeps (matrix x kernel JSON) with spmv_harness and
+    leaves results/results-<id>/<matrix>/result_<kernel>.txt holding the reference's INSERT INTO / PROFILING_DATUM
+    lines; gather_all.sh aggregates them.  Every (matrix, kernel) pair must come back "correct"."""
+    import shutil
+    data = tmp_path / "data"
+    names = ["Trefethen_20", "GD96_b"]
+    for n in names:
+        (data / n).mkdir(parents=True)
+        shutil.copy(mtx_dir[n], data / n / f"{n}.mtx")
+    (data / "datasets.txt").write_text("\n".join(names) + "\n")
+    scripts = os.path.join(ROOT, "host", "scripts", "experiments")
+    kernels = os.path.join(KERNELS, "spmv")
+    env = dict(os.environ, TRIALS="2", TIMEOUT_MS="2000", SHB_QUIET_LOG="1")
+    r = subprocess.run(["bash", os.path.join(scripts, "run_all.sh"), str(data), os.path.join(BIN, "spmv_harness"), kernels,
+                        os.path.join(KERNELS, "runfile.csv"), "0", "0", str(tmp_path / "scratch")], cwd=tmp_path,
+                       capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    res = (tmp_path / ".last_results").read_text().strip()
+    n_kernels = len([k for k in os.listdir(kernels) if k.endswith(".json")])
+    files = sorted((tmp_path / res).glob("*/result_*.txt"))
+    assert len(files) == len(names) * n_kernels
+    assert all("INSERT INTO" in f.read_text() for f in files)
+    g = subprocess.run(["sh", os.path.join(scripts, "gather_all.sh"), res], cwd=tmp_path, capture_output=True, text=True)
+    assert g.returncode == 0, g.stderr
+    rows = (tmp_path / "aggregate_summary.csv").read_text().splitlines()[1:]
+    raw = [x.split(",") for x in rows if ",RAW_RESULT," in x]
+    assert len(raw) == len(names) * n_kernels * 2 and all(x[3] == "correct" for x in raw), raw[:3]  # 2 trials, 1 run
+    assert {x[0] for x in raw} == set(names)
+    assert sum(",MEDIAN_RESULT," in x for x in rows) == len(names) * n_kernels
+    assert "PROFILING_DATUM" in (tmp_path / "aggregate_profiling_data.txt").read_text()

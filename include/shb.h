@@ -223,6 +223,21 @@ int shb_spmv_scatter(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_lau
                      int64_t row_offset, double delta, int term_mode, shb_buf *changed_flag,
                      const shb_buf *prev_changed, uint64_t *kernel_ns);
 
+
+/* Row-partitioned BFS (new capability; the reference's bfs app is single-device, app/bfs.cpp:94-152).
+ * This rank owns rows [row_offset, row_offset + A.n_rows) of the n_total-vertex graph (GLOBAL column ids;
+ * row_offset a multiple of 32), its slice of `levels` and full-length frontier bitmaps (n_total bits).
+ * init: levels = -1, frontier0 = {root}, counters = 0 (words 0..1: 64-bit TEPS numerator of this rank,
+ * word 2+L: vertices found at level L+1).  step: one pull launch for `level`; the next-frontier words of
+ * the block are stored into every next[i] (the ranks' bitmaps, opened with shb_ipc_open).  The caller
+ * all-reduces (SUM) counters word 2+level across ranks before the next step; a step whose previous level
+ * found nothing returns at once. */
+int shb_bfs_block_init(shb_ctx *ctx, const shb_csr *A, int64_t row_offset, int64_t n_total, int64_t root,
+                       shb_buf *levels, shb_buf *frontier0, shb_buf *counters);
+int shb_bfs_block_step(shb_ctx *ctx, const shb_csr *A, int64_t row_offset, int64_t n_total, uint32_t level,
+                       const shb_buf *frontier, shb_buf *const *next, int n_next, shb_buf *levels, shb_buf *counters,
+                       uint64_t *kernel_ns);
+
 #ifdef __cplusplus
 }
 #endif

@@ -257,6 +257,17 @@ class Context:
                                  prev_changed.h if prev_changed else None, C.byref(ns) if timed else None))
         return ns.value
 
+    def bfs_block_init(self, A: Csr, row_offset, n_total, root, levels: Buffer, frontier0: Buffer, counters: Buffer):
+        _ck(lib.shb_bfs_block_init(self.h, A.h, row_offset, n_total, root, levels.h, frontier0.h, counters.h))
+
+    def bfs_block_step(self, A: Csr, row_offset, n_total, level, frontier: Buffer, nxt: list[Buffer], levels: Buffer,
+                       counters: Buffer, timed=False) -> int:
+        arr = (C.c_void_p * len(nxt))(*[d.h for d in nxt])
+        ns = C.c_uint64(0)
+        _ck(lib.shb_bfs_block_step(self.h, A.h, row_offset, n_total, level, frontier.h, arr, len(nxt), levels.h,
+                                   counters.h, C.byref(ns) if timed else None))
+        return ns.value
+
     def iterate(self, A: Csr, semiring, x: Buffer, y0: Buffer | None, alpha, beta, work: Buffer, delta=1e-4, term=None,
                 y_rebind=True, max_iters=1000, check_every=16, per_iter=False, cfg: LaunchCfg | None = None):
         """Returns (result_buffer, n_iters, total_ns, per_iter_ns|None, converged)."""

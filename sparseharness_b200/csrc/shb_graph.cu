@@ -727,6 +727,165 @@ done:
 }
 
 // =================================================================================================
+// Row-partitioned BFS (multi-GPU): rank k owns the rows [row_offset, row_offset + n_local)
+// of A with GLOBAL column ids, its slice of `levels`, and two full-length frontier bitmaps.  One level =
+// one pull launch per rank: every unvisited local row looks for an in-neighbour in the current frontier
+// bitmap (or-and with early exit) and the warp's ballot word -- 32 consecutive vertices of the NEXT
+// frontier -- is stored straight into the next-frontier bitmap of every rank (CUDA-IPC peer pointers over
+// NVLink), so compute and exchange are one kernel, like shb_spmv_scatter.  Every word of the slice is
+// written (zero words included): the next bitmap needs no clearing pass.  counters: words 0..1 hold the
+// 64-bit TEPS numerator of this rank, word 2+L the number of vertices found at level L+1; the caller
+// all-reduces word 2+L (SUM) after each launch, which is also the barrier that orders the peer stores
+// before the next level's reads.  A launch whose previous level found nothing returns at once.
+// =================================================================================================
+#define BFS_BLOCK_BIG_ROW 128
+
+struct BfsPeers {
+  uint32_t *bm[8];
+  int n;
+};
+
+template <bool HAS_VAL>
+__global__ void bfs_pull_block_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                                      const int32_t *__restrict__ val, const uint32_t *__restrict__ cur,
+                                      const __grid_constant__ BfsPeers next,
+                                      int32_t *levels, uint32_t *counters, uint32_t level, int64_t n_local,
+                                      int64_t word_offset) {
+  if (level > 0 && counters[2 + level - 1] == 0u) return;  // the frontier emptied one level ago
+  const int lane = threadIdx.x & 31;
+  uint32_t found_n = 0;
+  unsigned long long pull_deg = 0;
+  const int64_t n_padded = (n_local + 31) / 32 * 32;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
+    bool found = false, big = false;
+    int s = 0, e = 0;
+    if (r < n_local && levels[r] == -1) {
+      s = row_ptr[r];
+      e = row_ptr[r + 1];
+      big = (e - s) >= BFS_BLOCK_BIG_ROW;
+      if (!big) {
+        for (int k = s; k < e; ++k) {
+          if (HAS_VAL && val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
+          const int32_t c = col[k];
+          if ((cur[c >> 5] >> (c & 31)) & 1u) {
+            found = true;
+            break;
+          }
+        }
+      }
+    }
+    // hub rows: the whole warp scans, 32 entries per step, until one lane sees a frontier neighbour
+    uint32_t bigs = __ballot_sync(0xffffffffu, big);
+    while (bigs) {
+      const int src = __ffs(bigs) - 1;
+      bigs &= bigs - 1;
+      const int bs = __shfl_sync(0xffffffffu, s, src), be = __shfl_sync(0xffffffffu, e, src);
+      bool hit = false;
+      for (int k0 = bs; k0 < be && !hit; k0 += 32) {
+        const int k = k0 + lane;
+        bool h = false;
+        if (k < be && !(HAS_VAL && val[k] == 0)) {
+          const int32_t c = col[k];
+          h = ((cur[c >> 5] >> (c & 31)) & 1u) != 0u;
+        }
+        hit = __any_sync(0xffffffffu, h);
+      }
+      if (lane == src) found = hit;
+    }
+    if (found) {
+      levels[r] = (int32_t)level + 1;
+      ++found_n;
+      pull_deg += (unsigned long long)(e - s);
+    }
+    const uint32_t ballot = __ballot_sync(0xffffffffu, found);
+    if (lane == 0) {
+      const int64_t w = word_offset + (r >> 5);
+      for (int i = 0; i < next.n; ++i) next.bm[i][w] = ballot;
+    }
+  }
+  for (int off = 16; off > 0; off >>= 1) {
+    found_n += __shfl_xor_sync(0xffffffffu, found_n, off);
+    pull_deg += __shfl_xor_sync(0xffffffffu, pull_deg, off);
+  }
+  if (lane == 0 && found_n) {
+    atomicAdd(&counters[2 + level], found_n);
+    atomicAdd(reinterpret_cast<unsigned long long *>(counters), pull_deg);
+  }
+}
+
+__global__ void bfs_block_init_kernel(int32_t *levels, uint32_t *bm0, uint32_t *counters, int64_t root, int64_t row_offset,
+                                      int64_t n_local, const int32_t *row_ptr) {
+  bm0[root >> 5] = 1u << (root & 31);
+  if (root >= row_offset && root < row_offset + n_local) {
+    const int64_t r = root - row_offset;
+    levels[r] = 0;
+    *reinterpret_cast<unsigned long long *>(counters) = (unsigned long long)(row_ptr[r + 1] - row_ptr[r]);
+  }
+}
+
+static int bfs_block_check(const shb_csr *A, int64_t row_offset, int64_t n_total) {
+  SHB_REQUIRE(A->n_cols == n_total, "the block's column space must be the whole vertex set");
+  SHB_REQUIRE(row_offset >= 0 && row_offset + A->n_rows <= n_total, "row block outside the vertex set");
+  SHB_REQUIRE((row_offset & 31) == 0, "row_offset must be a multiple of 32 (a bitmap word has one owner)");
+  SHB_REQUIRE((A->n_rows & 31) == 0 || row_offset + A->n_rows == n_total, "only the last block may end off a word boundary");
+  return SHB_OK;
+}
+
+SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, int64_t row_offset, int64_t n_total, int64_t root,
+                               shb_buf *levels, shb_buf *frontier0, shb_buf *counters) {
+  SHB_REQUIRE(c && A && levels && frontier0 && counters, "bad arguments");
+  SHB_TRY(bfs_block_check(A, row_offset, n_total));
+  SHB_REQUIRE(root >= 0 && root < n_total, "root out of range");
+  const uint64_t bm_bytes = (uint64_t)((n_total + 31) / 32) * 4;
+  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
+  SHB_REQUIRE(frontier0->bytes >= bm_bytes, "frontier bitmap shorter than n_total bits");
+  SHB_REQUIRE(counters->bytes >= 16, "counters too short");
+  SHB_CUDA(cudaSetDevice(c->device));
+  if (A->n_rows > 0) SHB_CUDA(cudaMemsetAsync(levels->ptr, 0xff, (size_t)A->n_rows * 4, c->stream));
+  SHB_CUDA(cudaMemsetAsync(frontier0->ptr, 0, (size_t)bm_bytes, c->stream));
+  SHB_CUDA(cudaMemsetAsync(counters->ptr, 0, (size_t)counters->bytes, c->stream));
+  bfs_block_init_kernel<<<1, 1, 0, c->stream>>>((int32_t *)levels->ptr, (uint32_t *)frontier0->ptr, (uint32_t *)counters->ptr,
+                                                root, row_offset, A->n_rows, A->row_ptr);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
+}
+
+SHB_API int shb_bfs_block_step(shb_ctx *c, const shb_csr *A, int64_t row_offset, int64_t n_total, uint32_t level,
+                               const shb_buf *frontier, shb_buf *const *next, int n_next, shb_buf *levels, shb_buf *counters,
+                               uint64_t *kernel_ns) {
+  SHB_REQUIRE(c && A && frontier && next && levels && counters, "bad arguments");
+  SHB_REQUIRE(n_next >= 1 && n_next <= 8, "1..8 destinations");
+  SHB_TRY(bfs_block_check(A, row_offset, n_total));
+  const uint64_t bm_bytes = (uint64_t)((n_total + 31) / 32) * 4;
+  SHB_REQUIRE(frontier->bytes >= bm_bytes, "frontier bitmap shorter than n_total bits");
+  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
+  SHB_REQUIRE(counters->bytes >= (uint64_t)(3 + level) * 4, "counters has no slot for this level");
+  BfsPeers peers;
+  peers.n = n_next;
+  for (int i = 0; i < 8; ++i) peers.bm[i] = nullptr;
+  for (int i = 0; i < n_next; ++i) {
+    SHB_REQUIRE(next[i] && next[i]->bytes >= bm_bytes, "next-frontier bitmap too short");
+    SHB_REQUIRE(next[i]->ptr != frontier->ptr, "a next-frontier bitmap aliases the current one");
+    peers.bm[i] = (uint32_t *)next[i]->ptr;
+  }
+  SHB_CUDA(cudaSetDevice(c->device));
+  ScopedTimer t(c, kernel_ns);
+  if (A->n_rows > 0) {
+    const unsigned grid = grid_for(A->n_rows, 256, 148 * 32);
+    if (A->val)
+      bfs_pull_block_kernel<true><<<grid, 256, 0, c->stream>>>(A->row_ptr, A->col, (const int32_t *)A->val,
+                                                               (const uint32_t *)frontier->ptr, peers, (int32_t *)levels->ptr,
+                                                               (uint32_t *)counters->ptr, level, A->n_rows, row_offset >> 5);
+    else
+      bfs_pull_block_kernel<false><<<grid, 256, 0, c->stream>>>(A->row_ptr, A->col, nullptr, (const uint32_t *)frontier->ptr,
+                                                                peers, (int32_t *)levels->ptr, (uint32_t *)counters->ptr,
+                                                                level, A->n_rows, row_offset >> 5);
+    SHB_CUDA(cudaGetLastError());
+  }
+  return t.finish();
+}
+
+// =================================================================================================
 // PageRank, canonical mode (Q9): x_{k+1} = A x_k * 1 + 1 * beta with y == 1 never re-bound.
 // =================================================================================================
 SHB_API int shb_pagerank(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, shb_buf *x, shb_buf *work, float x_init,

@@ -241,3 +241,194 @@ class EmulatedRowPartition(Backend):
 
     def result(self, index, dtype=np.float32):
         return self.x[index].download(dtype, self.n)
+
+
+# =====================================================================================================
+# Row-partitioned BFS (integer levels under or-and)
+# =====================================================================================================
+def word_aligned_bounds(bounds: np.ndarray, align: int = 32) -> np.ndarray:
+    """Row bounds rounded to multiples of `align` (the last one stays n): a 32-vertex word of the frontier
+    bitmap then has exactly one owner, which is what shb_bfs_block_step requires."""
+    b = np.asarray(bounds, dtype=np.int64).copy()
+    n = int(b[-1])
+    for k in range(1, len(b) - 1):
+        b[k] = min(n, (int(b[k]) + align - 1) // align * align)
+    for k in range(1, len(b)):
+        b[k] = max(b[k], b[k - 1])
+    return b
+
+
+class BfsBackend:
+    """What run_bfs needs from a device / CPU stand-in.  Frontier bitmaps are indexed 0/1 (level parity)."""
+
+    def step(self, level: int) -> None:  # pull launch of `level` (+ the stores into every rank's next bitmap)
+        raise NotImplementedError
+
+    def reduce_count(self, level: int) -> None:  # found[level] <- sum over ranks (stream ordered; also the barrier)
+        raise NotImplementedError
+
+    def read_counts(self, lo: int, hi: int) -> np.ndarray:  # host view of found[lo:hi] (synchronises)
+        raise NotImplementedError
+
+
+def run_bfs(backend: BfsBackend, max_levels: int = 1 << 20, check_every: int = 4):
+    """Level-synchronous loop: level L's launch builds frontier L+1; stops after the first level that finds
+    nothing.  Returns (levels_populated, reached_beyond_root, launches_that_did_work).  Launches issued past
+    the end of the traversal inside a batch return at once on the device (their found slot stays 0)."""
+    level, reached, done = 0, 0, False
+    while not done and level < max_levels:
+        batch = min(check_every, max_levels - level)
+        for b in range(batch):
+            backend.step(level + b)
+            backend.reduce_count(level + b)
+        counts = backend.read_counts(level, level + batch)
+        for b in range(batch):
+            if counts[b] == 0:
+                level += b + 1
+                done = True
+                break
+            reached += int(counts[b])
+        else:
+            level += batch
+    # `level` launches did work; the last of them found nothing when done, so levels 0..level-1 are populated
+    return (level if done else level + 1), reached, level
+
+
+class GpuBfsPartition(BfsBackend):
+    """The CUDA backend: this rank's row block; next-frontier words go straight into every rank's bitmap."""
+
+    def __init__(self, ctx, A_local, bounds, rank, world, root, *, max_levels=4096, dist=None, torch=None):
+        self.ctx, self.A, self.bounds = ctx, A_local, np.asarray(bounds, dtype=np.int64)
+        self.rank, self.world, self.root, self.dist, self.torch = rank, world, int(root), dist, torch
+        self.n = int(self.bounds[-1])
+        self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
+        self.n_words = (self.n + 31) // 32
+        self.max_levels = max_levels
+        self.bm = [ctx.empty(max(self.n_words, 1) * 4), ctx.empty(max(self.n_words, 1) * 4)]
+        self.levels = ctx.empty(max(self.hi - self.lo, 1) * 4)
+        self.counters = ctx.empty((max_levels + 3) * 4)
+        self.launches = 0
+        self.peers = [[self.bm[0]], [self.bm[1]]]
+        self._t_counts = None
+        if world > 1:
+            self._t_counts = _tensor_view(torch, self.counters, max_levels + 3, ctx.device)
+            handles = [None] * world
+            dist.all_gather_object(handles, (self.bm[0].ipc_handle(), self.bm[1].ipc_handle()))
+            self.peers = [[], []]
+            for r in range(world):
+                for k in (0, 1):
+                    self.peers[k].append(self.bm[k] if r == rank else ctx.ipc_open(handles[r][k], self.n_words * 4))
+        self.reset()
+
+    def reset(self):
+        self.ctx.bfs_block_init(self.A, self.lo, self.n, self.root, self.levels, self.bm[0], self.counters)
+        self.bm[1].zero()
+        self.launches = 0
+
+    def step(self, level):
+        self.ctx.bfs_block_step(self.A, self.lo, self.n, level, self.bm[level & 1], self.peers[(level + 1) & 1],
+                                self.levels, self.counters)
+        self.launches += 1
+
+    def reduce_count(self, level):
+        if self.world > 1:
+            self.dist.all_reduce(self._t_counts[2 + level:3 + level], op=self.dist.ReduceOp.SUM)
+
+    def read_counts(self, lo, hi):
+        return self.counters.download(np.uint32, hi - lo, offset=4 * (2 + lo))
+
+    def local_edges(self) -> int:
+        return int(self.counters.download(np.uint64, 1)[0])
+
+    def result(self) -> np.ndarray:
+        return self.levels.download(np.int32, self.hi - self.lo)
+
+    def close(self):
+        for k in (0, 1):
+            for r, b in enumerate(self.peers[k]):
+                if r != self.rank and self.world > 1:
+                    b.free()
+        for b in self.bm + [self.levels, self.counters]:
+            b.free()
+
+
+def _tensor_view(torch, buf, count, device, typestr="<i4"):
+    """A torch view of a libshb buffer (for the NCCL collectives only)."""
+
+    class _Cai:
+        pass
+
+    o = _Cai()
+    o.__cuda_array_interface__ = {"shape": (count,), "typestr": typestr, "data": (buf.device_ptr, False), "version": 2}
+    return torch.as_tensor(o, device=f"cuda:{device}")
+
+
+class EmulatedBfsPartition(BfsBackend):
+    """All P row blocks on ONE device: one launch per block and level, every block writing its words of the shared
+    next bitmap and adding to the shared found slot -- the multi-GPU path's arithmetic and protocol on one GPU."""
+
+    def __init__(self, ctx, blocks, bounds, root, max_levels=4096):
+        self.ctx, self.blocks, self.bounds, self.root = ctx, blocks, np.asarray(bounds, dtype=np.int64), int(root)
+        self.n = int(self.bounds[-1])
+        n_words = max((self.n + 31) // 32, 1)
+        self.bm = [ctx.empty(n_words * 4), ctx.empty(n_words * 4)]
+        self.levels = [ctx.empty(max(int(self.bounds[k + 1] - self.bounds[k]), 1) * 4) for k in range(len(blocks))]
+        self.counters = ctx.empty((max_levels + 3) * 4)
+        self.reset()
+
+    def reset(self):
+        edges = 0
+        for k, A in enumerate(self.blocks):
+            self.ctx.bfs_block_init(A, int(self.bounds[k]), self.n, self.root, self.levels[k], self.bm[0], self.counters)
+            edges += int(self.counters.download(np.uint64, 1)[0])  # each init zeroes the counters; keep the owner's degree
+        self.counters.upload(np.array([edges], np.uint64))
+        self.bm[1].zero()
+        self.launches = 0
+
+    def step(self, level):
+        for k, A in enumerate(self.blocks):
+            self.ctx.bfs_block_step(A, int(self.bounds[k]), self.n, level, self.bm[level & 1], [self.bm[(level + 1) & 1]],
+                                    self.levels[k], self.counters)
+            self.launches += 1
+
+    def reduce_count(self, level):
+        pass
+
+    def read_counts(self, lo, hi):
+        return self.counters.download(np.uint32, hi - lo, offset=4 * (2 + lo))
+
+    def edges(self) -> int:
+        return int(self.counters.download(np.uint64, 1)[0])
+
+    def result(self) -> np.ndarray:
+        return np.concatenate([self.levels[k].download(np.int32, int(self.bounds[k + 1] - self.bounds[k]))
+                               for k in range(len(self.blocks))])
+
+
+def partitioned_bfs(ctx, A_local, bounds, rank, world, root, *, check_every=4, max_levels=4096, dist=None, torch=None,
+                    repeat=1):
+    """BFS levels on a row-partitioned operator.  Returns (backend, stats) with stats = dict(levels, reached,
+    edges_traversed [sum of in-degrees of reached vertices, all ranks], ms [device time, max over ranks is the
+    caller's job], launches)."""
+    be = GpuBfsPartition(ctx, A_local, bounds, rank, world, root, max_levels=max_levels, dist=dist, torch=torch)
+    best = None
+    for _ in range(max(1, repeat)):
+        be.reset()
+        ctx.synchronize()
+        if world > 1:
+            dist.barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        n_levels, reached, launches = run_bfs(be, max_levels, check_every)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1)
+        if best is None or ms < best["ms"]:
+            best = {"levels": n_levels, "reached": reached + 1, "ms": ms, "launches": launches}
+    edges = be.local_edges()
+    if world > 1:
+        t = torch.tensor([edges], dtype=torch.int64, device=f"cuda:{ctx.device}")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        edges = int(t.item())
+    best["edges_traversed"] = edges
+    return be, best

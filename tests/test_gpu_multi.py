@@ -81,3 +81,70 @@ def test_two_gpu_pagerank_matches_oracle(mode):
     out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert out["parity_ok"] and out["converged"] and out["n_gpus"] == 2
     assert abs(out["iterations"] - out["oracle_iterations"]) <= 1
+
+
+@pytest.mark.parametrize("parts,check_every", [(1, 4), (2, 1), (5, 3)])
+def test_emulated_row_partition_bfs_matches_queue_bfs(ctx, orc, parts, check_every):
+    """shb_bfs_block_step on P row blocks of one device: levels, level count, reached and the TEPS numerator equal
+    the CPU queue BFS (hub rows >= 128 entries take the warp-cooperative path on this RMAT graph)."""
+    from sparseharness_b200 import multi
+    rp, col = orc.gen_rmat(13, 16, symmetrise=True)
+    n = len(rp) - 1
+    assert np.diff(rp).max() >= 128
+    root = int(np.argmax(np.diff(rp) > 0))
+    A = ctx.csr(n, n, rp, col, None)
+    bounds = multi.word_aligned_bounds(A.balance_rows(parts))
+    blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(parts)]
+    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, root)
+    n_levels, reached, launches = multi.run_bfs(be, 1 << 20, check_every)
+    want, nlev, edges = orc.bfs_levels(rp, col, None, root)
+    assert np.array_equal(be.result(), want)
+    assert n_levels == nlev and reached + 1 == int((want >= 0).sum()) and be.edges() == edges
+    assert launches == nlev and be.launches >= launches * parts
+    # same answer as the single-device direction-optimising driver
+    lv, st = ctx.bfs(A, root, AT=A)
+    assert np.array_equal(lv.download(np.int32, n), want) and st.edges_traversed == edges
+
+
+def test_emulated_row_partition_bfs_directed_zero_valued_edges_and_level_cap(ctx, orc):
+    from sparseharness_b200 import multi
+    rng = np.random.default_rng(5)
+    n = 1000
+    rp, col, _ = orc.gen_uniform(n, n, 3, val_mode=1)
+    val = rng.integers(0, 2, len(col)).astype(np.int32)  # a stored 0 is no edge (bool_and)
+    A = ctx.csr(n, n, rp, col, val)
+    bounds = multi.word_aligned_bounds(A.balance_rows(3))
+    blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(3)]
+    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, 3)
+    n_levels, reached, _ = multi.run_bfs(be, 1 << 20, 2)
+    want, nlev, edges = orc.bfs_levels(rp, col, val, 3)
+    assert np.array_equal(be.result(), want) and n_levels == nlev and be.edges() == edges
+    # a level cap stops early with the levels found so far
+    be.reset()
+    n_levels, _, launches = multi.run_bfs(be, 2, 2)
+    got = be.result()
+    assert launches == 2 and np.array_equal(got[(want >= 0) & (want <= 2)], want[(want >= 0) & (want <= 2)])
+    assert (got[want > 2] == -1).all()
+
+
+def test_bfs_block_rejects_unaligned_blocks(ctx, orc):
+    import sparseharness_b200 as shb
+    rp, col = orc.gen_rmat(8, 4, symmetrise=True)
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, None)
+    B = A.slice_rows(16, 64)
+    lv, bm, cnt = ctx.empty(64 * 4), ctx.empty(n // 8 + 4), ctx.empty(64)
+    with pytest.raises(shb.ShbError) as e:
+        ctx.bfs_block_init(B, 16, n, 0, lv, bm, cnt)
+    assert e.value.status == 1
+
+
+def test_two_gpu_bfs_matches_oracle():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = 29900 + os.getpid() % 300
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tools", "multi_bfs.py"), "--scale", "16", "--check"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])

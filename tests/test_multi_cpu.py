@@ -99,3 +99,96 @@ def test_balanced_bounds_rule():
         for k in range(1, parts):
             t = (64 * k) // parts
             assert rp[b[k]] >= t and (b[k] == 0 or rp[b[k] - 1] < t)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# row-partitioned BFS: the level loop, the bitmap ownership rule and the found-count protocol over gloo
+# ---------------------------------------------------------------------------------------------------------
+def _bfs_worker(rank, world, port, out_dir, case):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle as orc
+    from sparseharness_b200 import multi
+
+    rp, col = orc.gen_rmat(case["scale"], 8, symmetrise=True)
+    n = len(rp) - 1
+    root = int(np.argmax(np.diff(rp) > 0))
+    bounds = multi.word_aligned_bounds(multi.balanced_bounds(rp, world))
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    n_words = (n + 31) // 32
+
+    class NumpyBfs(multi.BfsBackend):
+        """CPU stand-in for shb_bfs_block_step: same bitmaps, same slots, same early-out."""
+
+        def __init__(self):
+            self.bm = [np.zeros(n_words, np.uint32), np.zeros(n_words, np.uint32)]
+            self.bm[0][root >> 5] = np.uint32(1) << np.uint32(root & 31)
+            self.levels = np.full(hi - lo, -1, np.int32)
+            if lo <= root < hi:
+                self.levels[root - lo] = 0
+            self.counts = torch.zeros(4096, dtype=torch.int32)
+            self.launches = 0
+
+        def step(self, level):
+            if level > 0 and self.counts[level - 1] == 0:
+                return
+            cur = self.bm[level & 1]
+            words = np.zeros(n_words, np.uint32)
+            found = 0
+            for r in range(lo, hi):
+                if self.levels[r - lo] != -1:
+                    continue
+                c = col[rp[r]:rp[r + 1]]
+                if len(c) and (((cur[c >> 5] >> (c & 31).astype(np.uint32)) & 1) != 0).any():
+                    self.levels[r - lo] = level + 1
+                    words[r >> 5] |= np.uint32(1) << np.uint32(r & 31)
+                    found += 1
+            self.counts[level] = found
+            self._mine = words[lo >> 5:(hi + 31) >> 5]
+            self.launches += 1
+
+        def reduce_count(self, level):
+            # the exchange the kernel does with peer stores: every rank's word slice into everyone's next bitmap
+            if not (level > 0 and self.counts[level - 1] == 0):
+                parts = [None] * world
+                dist.all_gather_object(parts, self._mine)
+                nxt = self.bm[(level + 1) & 1]
+                for r in range(world):
+                    a, b = int(bounds[r]) >> 5, (int(bounds[r + 1]) + 31) >> 5
+                    if b > a:
+                        nxt[a:b] = parts[r]
+            dist.all_reduce(self.counts[level:level + 1], op=dist.ReduceOp.SUM)
+
+        def read_counts(self, a, b):
+            return self.counts[a:b].numpy()
+
+    be = NumpyBfs()
+    n_levels, reached, launches = multi.run_bfs(be, case.get("max_levels", 1 << 20), case["check_every"])
+    np.save(os.path.join(out_dir, f"lv_{rank}.npy"), be.levels)
+    np.save(os.path.join(out_dir, f"bmeta_{rank}.npy"), np.array([n_levels, reached, launches, be.launches, lo, hi]))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,check_every", [(2, 4), (2, 1), (3, 3)])
+def test_partitioned_bfs_over_gloo_matches_queue_bfs(tmp_path, orc, world, check_every):
+    port = 31500 + (os.getpid() + world * 11 + check_every) % 2000
+    mp.spawn(_bfs_worker, args=(world, port, str(tmp_path), {"scale": 9, "check_every": check_every}), nprocs=world, join=True)
+    rp, col = orc.gen_rmat(9, 8, symmetrise=True)
+    root = int(np.argmax(np.diff(rp) > 0))
+    want = orc.bfs_levels(rp, col, None, root)[0]
+    got = np.concatenate([np.load(tmp_path / f"lv_{r}.npy") for r in range(world)])
+    metas = [np.load(tmp_path / f"bmeta_{r}.npy") for r in range(world)]
+    assert np.array_equal(got, want)
+    for m in metas:
+        assert m[0] == want.max() + 1 and m[1] == (want >= 0).sum() - 1
+        assert m[2] == want.max() + 1 and m[3] == m[2]  # launches that did work: one per level incl. the empty one
+    assert metas[0][4] == 0 and metas[-1][5] == len(rp) - 1
+    assert all(metas[r][5] == metas[r + 1][4] and metas[r][5] % 32 == 0 for r in range(world - 1))
+
+
+def test_word_aligned_bounds():
+    from sparseharness_b200 import multi
+    b = multi.word_aligned_bounds(np.array([0, 33, 64, 100, 101]))
+    assert list(b) == [0, 64, 64, 101, 101]
+    b = multi.word_aligned_bounds(np.array([0, 5, 1000]))
+    assert list(b) == [0, 32, 1000]

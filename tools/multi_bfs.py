@@ -1,0 +1,99 @@
+#!/usr/bin/env python
+"""torchrun entry: row-partitioned BFS on N GPUs (BASELINE.json config 3 family).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        tools/multi_bfs.py --scale 24 --edgefactor 16 [--check]
+
+Every rank generates the same symmetrised RMAT graph on its GPU (bit-identical generator), keeps its
+nnz-balanced, word-aligned row block and drops the rest.  Prints one JSON line on rank 0: GTEPS =
+(sum of degrees of reached vertices / 2) / device time (max over ranks) -- the single-GPU bench's convention."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def run(scale, edgefactor, check, seed=0x5EED0024, check_every=4, repeat=3, ctx=None):
+    import torch
+    import torch.distributed as dist
+
+    import sparseharness_b200 as shb
+    from sparseharness_b200 import multi
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    own_ctx = ctx is None
+    if own_ctx:
+        ctx = shb.Context(local)
+        ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    A = ctx.synth_rmat(scale, edgefactor, seed=seed, symmetrise=True)
+    info = A.info
+    n, nnz = info.n_rows, info.nnz
+    rp_head = A.download(0, min(n, 4096))[0]
+    root = int(np.argmax(np.diff(rp_head) > 0))
+    bounds = multi.word_aligned_bounds(A.balance_rows(world))
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    if world > 1:
+        Al = A.slice_rows(lo, hi - lo)
+        A.free()
+    else:
+        Al = A
+    be, st = multi.partitioned_bfs(ctx, Al, bounds, rank, world, root, check_every=check_every, dist=dist, torch=torch,
+                                   repeat=repeat)
+    t = torch.tensor([st["ms"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    undirected = st["edges_traversed"] / 2
+    out = {"graph": f"RMAT scale {scale} edgefactor {edgefactor} symmetrised+deduplicated", "n": n, "nnz": nnz,
+           "n_gpus": world, "schedule": "row-partitioned pull, bitmap words stored into every peer (fused exchange)",
+           "levels": st["levels"], "reached": st["reached"], "ms": ms, "gteps": undirected / (ms * 1e6),
+           "teps_edges": undirected, "local_rows": hi - lo, "local_nnz": Al.info.nnz,
+           "frontier_bytes_per_gpu_per_level": (n + 7) // 8}
+    if check:
+        from oracle import oracle as orc  # checker only
+        rp, col = orc.gen_rmat(scale, edgefactor, seed=seed, symmetrise=True)
+        want, nlev, edges = orc.bfs_levels(rp, col, None, root)
+        got = be.result()
+        ok = bool(np.array_equal(got, want[lo:hi])) and st["levels"] == nlev and st["reached"] == int((want >= 0).sum())
+        ok = ok and st["edges_traversed"] == edges
+        flag = torch.tensor([int(ok)], dtype=torch.int32, device="cuda")
+        if world > 1:
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        out.update(parity_ok=bool(flag.item()), oracle_levels=nlev, oracle_edges=edges)
+    be.close()
+    Al.free()
+    return out, rank, world
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--scale", type=int, default=20)
+    ap.add_argument("--edgefactor", type=int, default=16)
+    ap.add_argument("--check", action="store_true")
+    ap.add_argument("--check-every", type=int, default=4)
+    a = ap.parse_args()
+    out, rank, world = run(a.scale, a.edgefactor, a.check, check_every=a.check_every)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0 if (not a.check or out.get("parity_ok", True)) else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -235,6 +235,28 @@ def graph_extras(ctx, shb, orc):
     return out
 
 
+def partitioned_extras(ctx, rank, world):
+    """GTEPS of the row-partitioned drivers at this GPU count: PageRank on config 5 (RMAT scale 26,
+    2^30 non-zeros, 20 sweeps, fused SpMV -> peer scatter) and, for N > 1, BFS on config 3 (RMAT scale 24) with the
+    frontier bitmap exchanged by the pull kernel's peer stores.  Every rank must call this."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    out = {}
+    try:
+        import multi_pagerank
+        r, _, _ = multi_pagerank.run(26, 16, 20, "fused", 0.0, False, repeat=2, ctx=ctx)
+        out["pagerank_config5"] = r
+    except Exception as e:
+        out["pagerank_config5"] = {"error": repr(e)[:300]}
+    if world > 1:
+        try:
+            import multi_bfs
+            r, _, _ = multi_bfs.run(24, 16, False, repeat=3, ctx=ctx)
+            out["bfs_partitioned"] = r
+        except Exception as e:
+            out["bfs_partitioned"] = {"error": repr(e)[:300]}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -368,6 +390,11 @@ def run_ours(args):
     A.free(); x.free(); out.free()
     if rank == 0 and n_gpus == 1 and args.extras:
         line["graph_gteps"] = graph_extras(ctx, shb, orc)
+    if args.extras:
+        # the iterative drivers on the row-partitioned operator (every rank takes part; rank 0 reports)
+        part = partitioned_extras(ctx, rank, n_gpus)
+        if rank == 0:
+            line.setdefault("graph_gteps", {}).update(part)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

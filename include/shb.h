@@ -224,19 +224,28 @@ int shb_spmv_scatter(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_lau
                      const shb_buf *prev_changed, uint64_t *kernel_ns);
 
 
-/* Row-partitioned BFS (new capability; the reference's bfs app is single-device, app/bfs.cpp:94-152).
- * This rank owns rows [row_offset, row_offset + A.n_rows) of the n_total-vertex graph (GLOBAL column ids;
- * row_offset a multiple of 32), its slice of `levels` and full-length frontier bitmaps (n_total bits).
- * init: levels = -1, frontier0 = {root}, counters = 0 (words 0..1: 64-bit TEPS numerator of this rank,
- * word 2+L: vertices found at level L+1).  step: one pull launch for `level`; the next-frontier words of
- * the block are stored into every next[i] (the ranks' bitmaps, opened with shb_ipc_open).  The caller
- * all-reduces (SUM) counters word 2+level across ranks before the next step; a step whose previous level
- * found nothing returns at once. */
-int shb_bfs_block_init(shb_ctx *ctx, const shb_csr *A, int64_t row_offset, int64_t n_total, int64_t root,
-                       shb_buf *levels, shb_buf *frontier0, shb_buf *counters);
-int shb_bfs_block_step(shb_ctx *ctx, const shb_csr *A, int64_t row_offset, int64_t n_total, uint32_t level,
-                       const shb_buf *frontier, shb_buf *const *next, int n_next, shb_buf *levels, shb_buf *counters,
-                       uint64_t *kernel_ns);
+/* Row-partitioned, direction-optimising BFS (new capability; the reference's bfs app is single-device,
+ * app/bfs.cpp:94-152).  This rank owns the vertices [row_offset, row_offset + A.n_rows) of the n_total-vertex
+ * graph (row_offset a multiple of 32): their rows of A (in-edges, pull) and optionally of A^T (AT, out-edges,
+ * push; NULL = pull only), both with GLOBAL column ids; its slice of `levels`; full-length frontier / visited
+ * bitmaps (n_total bits) and, optionally, `deg` = push degree of every vertex (int32 x n_total, steers Beamer's
+ * heuristic).  counters: int64 words; after shb_bfs_block_finish words 0,1 = reached vertices and TEPS numerator
+ * of this rank; slot F = words 2+2F, 3+2F = (vertices, push degrees) of frontier F.
+ *   init    levels = -1, frontier0 = {root}, everything else 0; the root's owner fills slot 0.  The caller
+ *           all-reduces (SUM) slot 0.
+ *   level   enqueues decide / prep / push / pull / clear for `level` (frontier = bitmap level & 1, next[i] =
+ *           every rank's bitmap (level+1) & 1 opened with shb_ipc_open, next[self_index] the local one).  The
+ *           caller then all-reduces slot level+1; a level launched after the frontier emptied does nothing.
+ *   finish  per-rank reached / edge counts from the levels. */
+int shb_csr_row_lengths(shb_ctx *ctx, const shb_csr *A, shb_buf *out /* int32 x n_rows */);
+int shb_bfs_block_state_bytes(uint64_t *bytes);
+int shb_bfs_block_init(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
+                       int64_t nnz_total, int64_t root, const shb_buf *deg, shb_buf *levels, shb_buf *frontier0,
+                       shb_buf *frontier1, shb_buf *visited, shb_buf *counters, shb_buf *state);
+int shb_bfs_block_level(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
+                        uint32_t level, const shb_buf *deg, shb_buf *frontier, shb_buf *const *next, int n_next,
+                        int self_index, shb_buf *visited, shb_buf *levels, shb_buf *counters, shb_buf *state);
+int shb_bfs_block_finish(shb_ctx *ctx, const shb_csr *A, const shb_buf *levels, shb_buf *counters);
 
 #ifdef __cplusplus
 }

@@ -97,10 +97,14 @@ SIGNATURES = {
     "shb_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "shb_ipc_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, c_void_pp]),
     "shb_ipc_close": (C.c_int, [C.c_void_p]),
-    "shb_bfs_block_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
-                                     C.c_void_p]),
-    "shb_bfs_block_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_uint32, C.c_void_p, c_void_pp,
-                                     C.c_int, C.c_void_p, C.c_void_p, u64p]),
+    "shb_csr_row_lengths": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "shb_bfs_block_state_bytes": (C.c_int, [u64p]),
+    "shb_bfs_block_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "shb_bfs_block_level": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_uint32, C.c_void_p,
+                                      C.c_void_p, c_void_pp, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p]),
+    "shb_bfs_block_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "shb_spmv_scatter": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, c_void_pp, C.c_int, C.c_int64, C.c_double, C.c_int,
                                    C.c_void_p, C.c_void_p, u64p]),

@@ -120,6 +120,12 @@ class Csr:
         _ck(lib.shb_csr_transpose(self.ctx.h, self.h, C.byref(h)))
         return Csr(self.ctx, h)
 
+    def row_lengths(self) -> "Buffer":
+        """int32 length of every row, on the device (the push degrees of the partitioned BFS heuristic)."""
+        b = self.ctx.empty(max(self.info.n_rows, 1) * 4)
+        _ck(lib.shb_csr_row_lengths(self.ctx.h, self.h, b.h))
+        return b
+
     def balance_rows(self, parts: int) -> np.ndarray:
         """Row bounds of `parts` contiguous blocks balanced by non-zeros."""
         b = np.zeros(parts + 1, dtype=np.int64)
@@ -257,16 +263,25 @@ class Context:
                                  prev_changed.h if prev_changed else None, C.byref(ns) if timed else None))
         return ns.value
 
-    def bfs_block_init(self, A: Csr, row_offset, n_total, root, levels: Buffer, frontier0: Buffer, counters: Buffer):
-        _ck(lib.shb_bfs_block_init(self.h, A.h, row_offset, n_total, root, levels.h, frontier0.h, counters.h))
+    def bfs_block_state_bytes(self) -> int:
+        b = C.c_uint64(0)
+        _ck(lib.shb_bfs_block_state_bytes(C.byref(b)))
+        return b.value
 
-    def bfs_block_step(self, A: Csr, row_offset, n_total, level, frontier: Buffer, nxt: list[Buffer], levels: Buffer,
-                       counters: Buffer, timed=False) -> int:
+    def bfs_block_init(self, A: Csr, AT: Csr | None, row_offset, n_total, nnz_total, root, deg: Buffer | None,
+                       levels: Buffer, bm0: Buffer, bm1: Buffer, visited: Buffer, counters: Buffer, state: Buffer):
+        _ck(lib.shb_bfs_block_init(self.h, A.h, AT.h if AT else None, row_offset, n_total, nnz_total, root,
+                                   deg.h if deg else None, levels.h, bm0.h, bm1.h, visited.h, counters.h, state.h))
+
+    def bfs_block_level(self, A: Csr, AT: Csr | None, row_offset, n_total, level, deg: Buffer | None, frontier: Buffer,
+                        nxt: list[Buffer], self_index: int, visited: Buffer, levels: Buffer, counters: Buffer,
+                        state: Buffer):
         arr = (C.c_void_p * len(nxt))(*[d.h for d in nxt])
-        ns = C.c_uint64(0)
-        _ck(lib.shb_bfs_block_step(self.h, A.h, row_offset, n_total, level, frontier.h, arr, len(nxt), levels.h,
-                                   counters.h, C.byref(ns) if timed else None))
-        return ns.value
+        _ck(lib.shb_bfs_block_level(self.h, A.h, AT.h if AT else None, row_offset, n_total, level, deg.h if deg else None,
+                                    frontier.h, arr, len(nxt), self_index, visited.h, levels.h, counters.h, state.h))
+
+    def bfs_block_finish(self, A: Csr, levels: Buffer, counters: Buffer):
+        _ck(lib.shb_bfs_block_finish(self.h, A.h, levels.h, counters.h))
 
     def iterate(self, A: Csr, semiring, x: Buffer, y0: Buffer | None, alpha, beta, work: Buffer, delta=1e-4, term=None,
                 y_rebind=True, max_iters=1000, check_every=16, per_iter=False, cfg: LaunchCfg | None = None):

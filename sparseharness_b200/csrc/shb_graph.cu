@@ -727,34 +727,147 @@ done:
 }
 
 // =================================================================================================
-// Row-partitioned BFS (multi-GPU): rank k owns the rows [row_offset, row_offset + n_local)
-// of A with GLOBAL column ids, its slice of `levels`, and two full-length frontier bitmaps.  One level =
-// one pull launch per rank: every unvisited local row looks for an in-neighbour in the current frontier
-// bitmap (or-and with early exit) and the warp's ballot word -- 32 consecutive vertices of the NEXT
-// frontier -- is stored straight into the next-frontier bitmap of every rank (CUDA-IPC peer pointers over
-// NVLink), so compute and exchange are one kernel, like shb_spmv_scatter.  Every word of the slice is
-// written (zero words included): the next bitmap needs no clearing pass.  counters: words 0..1 hold the
-// 64-bit TEPS numerator of this rank, word 2+L the number of vertices found at level L+1; the caller
-// all-reduces word 2+L (SUM) after each launch, which is also the barrier that orders the peer stores
-// before the next level's reads.  A launch whose previous level found nothing returns at once.
+// Row-partitioned BFS (multi-GPU), direction-optimising.  Rank k owns the vertices
+// [row_offset, row_offset + n_local): their rows of A (in-edges, pull), optionally their rows of A^T
+// (out-edges, push) -- both with GLOBAL column ids --, its slice of `levels`, and full-length copies of the
+// two frontier bitmaps and of the visited bitmap.  One level on every rank =
+//   decide  (1 thread)  reads the ALL-REDUCED (n_f, m_f) of the current frontier and applies Beamer's
+//                       heuristic; every rank computes the same mode from the same numbers;
+//   prep                visited |= frontier (full length); levels of the owned frontier vertices;
+//   push | pull         push: owned frontier vertices mark unvisited out-neighbours with atomicOr in the
+//                       local next bitmap and, when the bit was new here, in every peer's next bitmap;
+//                       pull: every unvisited owned row looks for an in-neighbour in the frontier (early
+//                       exit; hub rows by the whole warp) and the warp's ballot word is stored into every
+//                       rank's next bitmap.  Peer bitmaps are CUDA-IPC mappings: the exchange rides on the
+//                       kernel's own stores over NVLink, no separate collective moves the frontier;
+//   clear               the consumed frontier bitmap is zeroed for reuse two levels on.
+// counters (int64): slot F = words [2+2F, 3+2F] = (vertices, sum of push degrees) of frontier F as seen by
+// this rank; the caller all-reduces (SUM) slot F+1 after level F -- the barrier that orders the peer
+// stores before the next level's reads.  Push may count a vertex once per discovering rank: the numbers
+// steer the heuristic and the termination test (> 0) only; reached / TEPS come from the levels at the end.
 // =================================================================================================
 #define BFS_BLOCK_BIG_ROW 128
 
 struct BfsPeers {
   uint32_t *bm[8];
   int n;
+  int self;
 };
 
+struct BfsBlockState {
+  uint32_t mode;  // 0 push, 1 pull
+  uint32_t done;
+  uint32_t have_push;
+  uint32_t pad;
+  unsigned long long n_prev;      // vertices of the previous frontier
+  unsigned long long unexplored;  // Beamer's m_u
+  unsigned long long n_total;
+};
+
+__global__ void bfs_block_decide_kernel(BfsBlockState *st, const long long *counters, uint32_t level) {
+  if (st->done) return;
+  const unsigned long long nf = (unsigned long long)counters[2 + 2 * level];
+  const unsigned long long mf = (unsigned long long)counters[3 + 2 * level];
+  if (nf == 0) {
+    st->done = 1;
+    return;
+  }
+  st->unexplored = st->unexplored > mf ? st->unexplored - mf : 0ull;
+  if (st->have_push) {
+    if (st->mode == 0) {
+      if (mf > st->unexplored / 14ull) st->mode = 1;
+    } else {
+      if (nf < st->n_total / 24ull && nf < st->n_prev) st->mode = 0;
+    }
+  } else {
+    st->mode = 1;
+  }
+  st->n_prev = nf;
+}
+
+// visited |= frontier over the whole bitmap; the owned words also give their vertices the level
+__global__ void bfs_block_prep_kernel(const BfsBlockState *st, const uint32_t *__restrict__ cur, uint32_t *visited,
+                                      int32_t *levels, uint32_t level, int64_t n_words, int64_t word_lo, int64_t word_hi,
+                                      int64_t row_offset, int64_t n_local) {
+  if (st->done) return;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (int64_t)gridDim.x * blockDim.x) {
+    uint32_t bits = cur[w];
+    if (!bits) continue;
+    visited[w] |= bits;
+    if (w >= word_lo && w < word_hi) {
+      while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int64_t r = w * 32 + b - row_offset;
+        if (r >= 0 && r < n_local && levels[r] == -1) levels[r] = (int32_t)level;
+      }
+    }
+  }
+}
+
+__global__ void bfs_block_clear_kernel(const BfsBlockState *st, uint32_t *bm, int64_t n_words) {
+  if (st->done) return;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (int64_t)gridDim.x * blockDim.x) bm[i] = 0u;
+}
+
+
+// push: one warp per owned frontier word; lanes stride over each frontier vertex's out-adjacency
 template <bool HAS_VAL>
-__global__ void bfs_pull_block_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
-                                      const int32_t *__restrict__ val, const uint32_t *__restrict__ cur,
-                                      const __grid_constant__ BfsPeers next,
-                                      int32_t *levels, uint32_t *counters, uint32_t level, int64_t n_local,
-                                      int64_t word_offset) {
-  if (level > 0 && counters[2 + level - 1] == 0u) return;  // the frontier emptied one level ago
+__global__ void bfs_block_push_kernel(const BfsBlockState *st, const int32_t *__restrict__ at_row_ptr,
+                                      const int32_t *__restrict__ at_col, const int32_t *__restrict__ at_val,
+                                      const int32_t *__restrict__ deg, const uint32_t *__restrict__ cur,
+                                      const uint32_t *__restrict__ visited, const __grid_constant__ BfsPeers next,
+                                      long long *counters, uint32_t level, int64_t word_lo, int64_t word_hi, int64_t row_offset,
+                                      int64_t n_local) {
+  if (st->done || st->mode != 0) return;
   const int lane = threadIdx.x & 31;
-  uint32_t found_n = 0;
-  unsigned long long pull_deg = 0;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  uint32_t *mine = next.bm[next.self];
+  unsigned long long found = 0, push_deg = 0;
+  for (int64_t w = word_lo + warp; w < word_hi; w += n_warps) {
+    uint32_t word = cur[w];
+    while (word) {
+      const int b = __ffs(word) - 1;
+      word &= word - 1;
+      const int64_t u = w * 32 + b - row_offset;
+      if (u < 0 || u >= n_local) continue;
+      const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
+      for (int k = s + lane; k < e; k += 32) {
+        if (HAS_VAL && at_val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
+        const int32_t v = at_col[k];
+        const uint32_t bit = 1u << (v & 31);
+        if (visited[v >> 5] & bit) continue;
+        const uint32_t old = atomicOr(&mine[v >> 5], bit);
+        if (!(old & bit)) {  // new on this rank: tell every peer once
+          for (int i = 0; i < next.n; ++i)
+            if (i != next.self) atomicOr(&next.bm[i][v >> 5], bit);
+          ++found;
+          push_deg += (unsigned long long)(deg ? deg[v] : 1);
+        }
+      }
+    }
+  }
+  for (int off = 16; off > 0; off >>= 1) {
+    found += __shfl_xor_sync(0xffffffffu, found, off);
+    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
+  }
+  if (lane == 0 && found) {
+    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[2 + 2 * (level + 1)]), found);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[3 + 2 * (level + 1)]), push_deg);
+  }
+}
+
+template <bool HAS_VAL>
+__global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__restrict__ row_ptr,
+                                      const int32_t *__restrict__ col, const int32_t *__restrict__ val,
+                                      const int32_t *__restrict__ deg, const uint32_t *__restrict__ cur,
+                                      const __grid_constant__ BfsPeers next, int32_t *levels, long long *counters,
+                                      uint32_t level, int64_t n_local, int64_t row_offset) {
+  if (st->done || st->mode != 1) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t word_offset = row_offset >> 5;
+  unsigned long long found_n = 0, push_deg = 0;
   const int64_t n_padded = (n_local + 31) / 32 * 32;
   for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
     bool found = false, big = false;
@@ -765,7 +878,7 @@ __global__ void bfs_pull_block_kernel(const int32_t *__restrict__ row_ptr, const
       big = (e - s) >= BFS_BLOCK_BIG_ROW;
       if (!big) {
         for (int k = s; k < e; ++k) {
-          if (HAS_VAL && val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
+          if (HAS_VAL && val[k] == 0) continue;
           const int32_t c = col[k];
           if ((cur[c >> 5] >> (c & 31)) & 1u) {
             found = true;
@@ -795,7 +908,7 @@ __global__ void bfs_pull_block_kernel(const int32_t *__restrict__ row_ptr, const
     if (found) {
       levels[r] = (int32_t)level + 1;
       ++found_n;
-      pull_deg += (unsigned long long)(e - s);
+      push_deg += (unsigned long long)(deg ? deg[row_offset + r] : 1);
     }
     const uint32_t ballot = __ballot_sync(0xffffffffu, found);
     if (lane == 0) {
@@ -805,63 +918,118 @@ __global__ void bfs_pull_block_kernel(const int32_t *__restrict__ row_ptr, const
   }
   for (int off = 16; off > 0; off >>= 1) {
     found_n += __shfl_xor_sync(0xffffffffu, found_n, off);
-    pull_deg += __shfl_xor_sync(0xffffffffu, pull_deg, off);
+    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
   }
   if (lane == 0 && found_n) {
-    atomicAdd(&counters[2 + level], found_n);
-    atomicAdd(reinterpret_cast<unsigned long long *>(counters), pull_deg);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[2 + 2 * (level + 1)]), found_n);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[3 + 2 * (level + 1)]), push_deg);
   }
 }
 
-__global__ void bfs_block_init_kernel(int32_t *levels, uint32_t *bm0, uint32_t *counters, int64_t root, int64_t row_offset,
-                                      int64_t n_local, const int32_t *row_ptr) {
+__global__ void bfs_block_init_kernel(BfsBlockState *st, int32_t *levels, uint32_t *bm0, long long *counters, int64_t root,
+                                      int64_t row_offset, int64_t n_local, const int32_t *deg, int have_push,
+                                      unsigned long long nnz_total, unsigned long long n_total) {
   bm0[root >> 5] = 1u << (root & 31);
-  if (root >= row_offset && root < row_offset + n_local) {
-    const int64_t r = root - row_offset;
-    levels[r] = 0;
-    *reinterpret_cast<unsigned long long *>(counters) = (unsigned long long)(row_ptr[r + 1] - row_ptr[r]);
+  st->mode = have_push ? 0u : 1u;
+  st->done = 0;
+  st->have_push = (uint32_t)have_push;
+  st->pad = 0;
+  st->n_prev = 0;
+  st->unexplored = nnz_total;
+  st->n_total = n_total;
+  if (root >= row_offset && root < row_offset + n_local) {  // the owner reports frontier 0; the caller all-reduces slot 0
+    counters[2] = 1;
+    counters[3] = deg ? (long long)deg[root] : 1;
   }
 }
 
-static int bfs_block_check(const shb_csr *A, int64_t row_offset, int64_t n_total) {
-  SHB_REQUIRE(A->n_cols == n_total, "the block's column space must be the whole vertex set");
-  SHB_REQUIRE(row_offset >= 0 && row_offset + A->n_rows <= n_total, "row block outside the vertex set");
-  SHB_REQUIRE((row_offset & 31) == 0, "row_offset must be a multiple of 32 (a bitmap word has one owner)");
-  SHB_REQUIRE((A->n_rows & 31) == 0 || row_offset + A->n_rows == n_total, "only the last block may end off a word boundary");
-  return SHB_OK;
+// reached vertices and the TEPS numerator (sum of in-degrees of reached vertices) of the owned slice
+__global__ void bfs_block_stats_kernel(const int32_t *levels, const int32_t *row_ptr, int64_t n_local, long long *counters) {
+  unsigned long long cnt = 0, edges = 0;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_local; r += (int64_t)gridDim.x * blockDim.x)
+    if (levels[r] >= 0) {
+      ++cnt;
+      edges += (unsigned long long)(row_ptr[r + 1] - row_ptr[r]);
+    }
+  for (int off = 16; off > 0; off >>= 1) {
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+    edges += __shfl_xor_sync(0xffffffffu, edges, off);
+  }
+  if ((threadIdx.x & 31) == 0 && cnt) {
+    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[0]), cnt);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[1]), edges);
+  }
 }
 
-SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, int64_t row_offset, int64_t n_total, int64_t root,
-                               shb_buf *levels, shb_buf *frontier0, shb_buf *counters) {
-  SHB_REQUIRE(c && A && levels && frontier0 && counters, "bad arguments");
-  SHB_TRY(bfs_block_check(A, row_offset, n_total));
-  SHB_REQUIRE(root >= 0 && root < n_total, "root out of range");
-  const uint64_t bm_bytes = (uint64_t)((n_total + 31) / 32) * 4;
-  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
-  SHB_REQUIRE(frontier0->bytes >= bm_bytes, "frontier bitmap shorter than n_total bits");
-  SHB_REQUIRE(counters->bytes >= 16, "counters too short");
+__global__ void csr_row_lengths_kernel(const int32_t *row_ptr, int32_t *out, int64_t n) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x)
+    out[r] = row_ptr[r + 1] - row_ptr[r];
+}
+
+SHB_API int shb_csr_row_lengths(shb_ctx *c, const shb_csr *A, shb_buf *out) {
+  SHB_REQUIRE(c && A && out, "bad arguments");
+  SHB_REQUIRE(out->bytes >= (uint64_t)A->n_rows * 4, "out shorter than n_rows");
   SHB_CUDA(cudaSetDevice(c->device));
-  if (A->n_rows > 0) SHB_CUDA(cudaMemsetAsync(levels->ptr, 0xff, (size_t)A->n_rows * 4, c->stream));
-  SHB_CUDA(cudaMemsetAsync(frontier0->ptr, 0, (size_t)bm_bytes, c->stream));
-  SHB_CUDA(cudaMemsetAsync(counters->ptr, 0, (size_t)counters->bytes, c->stream));
-  bfs_block_init_kernel<<<1, 1, 0, c->stream>>>((int32_t *)levels->ptr, (uint32_t *)frontier0->ptr, (uint32_t *)counters->ptr,
-                                                root, row_offset, A->n_rows, A->row_ptr);
+  if (A->n_rows > 0) csr_row_lengths_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>(A->row_ptr, (int32_t *)out->ptr, A->n_rows);
   SHB_CUDA(cudaGetLastError());
   return SHB_OK;
 }
 
-SHB_API int shb_bfs_block_step(shb_ctx *c, const shb_csr *A, int64_t row_offset, int64_t n_total, uint32_t level,
-                               const shb_buf *frontier, shb_buf *const *next, int n_next, shb_buf *levels, shb_buf *counters,
-                               uint64_t *kernel_ns) {
-  SHB_REQUIRE(c && A && frontier && next && levels && counters, "bad arguments");
-  SHB_REQUIRE(n_next >= 1 && n_next <= 8, "1..8 destinations");
-  SHB_TRY(bfs_block_check(A, row_offset, n_total));
+static int bfs_block_check(const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total) {
+  SHB_REQUIRE(A->n_cols == n_total, "the block's column space must be the whole vertex set");
+  SHB_REQUIRE(row_offset >= 0 && row_offset + A->n_rows <= n_total, "row block outside the vertex set");
+  SHB_REQUIRE((row_offset & 31) == 0, "row_offset must be a multiple of 32 (a bitmap word has one owner)");
+  SHB_REQUIRE((A->n_rows & 31) == 0 || row_offset + A->n_rows == n_total, "only the last block may end off a word boundary");
+  SHB_REQUIRE(!AT || (AT->n_rows == A->n_rows && AT->n_cols == n_total), "the push-side block does not match");
+  return SHB_OK;
+}
+
+SHB_API int shb_bfs_block_state_bytes(uint64_t *bytes) {
+  SHB_REQUIRE(bytes, "bad arguments");
+  *bytes = sizeof(BfsBlockState);
+  return SHB_OK;
+}
+
+SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
+                               int64_t nnz_total, int64_t root, const shb_buf *deg, shb_buf *levels, shb_buf *frontier0,
+                               shb_buf *frontier1, shb_buf *visited, shb_buf *counters, shb_buf *state) {
+  SHB_REQUIRE(c && A && levels && frontier0 && frontier1 && visited && counters && state, "bad arguments");
+  SHB_TRY(bfs_block_check(A, AT, row_offset, n_total));
+  SHB_REQUIRE(root >= 0 && root < n_total, "root out of range");
   const uint64_t bm_bytes = (uint64_t)((n_total + 31) / 32) * 4;
-  SHB_REQUIRE(frontier->bytes >= bm_bytes, "frontier bitmap shorter than n_total bits");
   SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
-  SHB_REQUIRE(counters->bytes >= (uint64_t)(3 + level) * 4, "counters has no slot for this level");
+  SHB_REQUIRE(frontier0->bytes >= bm_bytes && frontier1->bytes >= bm_bytes && visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
+  SHB_REQUIRE(!deg || deg->bytes >= (uint64_t)n_total * 4, "deg shorter than n_total");
+  SHB_REQUIRE(counters->bytes >= 32 && state->bytes >= sizeof(BfsBlockState), "counters / state too short");
+  SHB_CUDA(cudaSetDevice(c->device));
+  if (A->n_rows > 0) SHB_CUDA(cudaMemsetAsync(levels->ptr, 0xff, (size_t)A->n_rows * 4, c->stream));
+  SHB_CUDA(cudaMemsetAsync(frontier0->ptr, 0, (size_t)bm_bytes, c->stream));
+  SHB_CUDA(cudaMemsetAsync(frontier1->ptr, 0, (size_t)bm_bytes, c->stream));
+  SHB_CUDA(cudaMemsetAsync(visited->ptr, 0, (size_t)bm_bytes, c->stream));
+  SHB_CUDA(cudaMemsetAsync(counters->ptr, 0, (size_t)counters->bytes, c->stream));
+  bfs_block_init_kernel<<<1, 1, 0, c->stream>>>((BfsBlockState *)state->ptr, (int32_t *)levels->ptr, (uint32_t *)frontier0->ptr,
+                                                (long long *)counters->ptr, root, row_offset, A->n_rows,
+                                                deg ? (const int32_t *)deg->ptr : nullptr, AT != nullptr,
+                                                (unsigned long long)nnz_total, (unsigned long long)n_total);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
+}
+
+SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
+                                uint32_t level, const shb_buf *deg, shb_buf *frontier, shb_buf *const *next, int n_next,
+                                int self_index, shb_buf *visited, shb_buf *levels, shb_buf *counters, shb_buf *state) {
+  SHB_REQUIRE(c && A && frontier && next && visited && levels && counters && state, "bad arguments");
+  SHB_REQUIRE(n_next >= 1 && n_next <= 8 && self_index >= 0 && self_index < n_next, "1..8 destinations, one of them local");
+  SHB_TRY(bfs_block_check(A, AT, row_offset, n_total));
+  const int64_t n_words = (n_total + 31) / 32;
+  const uint64_t bm_bytes = (uint64_t)n_words * 4;
+  SHB_REQUIRE(frontier->bytes >= bm_bytes && visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
+  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
+  SHB_REQUIRE(counters->bytes >= (uint64_t)(4 + 2 * (level + 1)) * 8, "counters has no slot for this level");
+  SHB_REQUIRE(state->bytes >= sizeof(BfsBlockState), "state too short");
   BfsPeers peers;
   peers.n = n_next;
+  peers.self = self_index;
   for (int i = 0; i < 8; ++i) peers.bm[i] = nullptr;
   for (int i = 0; i < n_next; ++i) {
     SHB_REQUIRE(next[i] && next[i]->bytes >= bm_bytes, "next-frontier bitmap too short");
@@ -869,20 +1037,49 @@ SHB_API int shb_bfs_block_step(shb_ctx *c, const shb_csr *A, int64_t row_offset,
     peers.bm[i] = (uint32_t *)next[i]->ptr;
   }
   SHB_CUDA(cudaSetDevice(c->device));
-  ScopedTimer t(c, kernel_ns);
-  if (A->n_rows > 0) {
-    const unsigned grid = grid_for(A->n_rows, 256, 148 * 32);
+  BfsBlockState *st = (BfsBlockState *)state->ptr;
+  long long *cnt = (long long *)counters->ptr;
+  const int32_t *dg = deg ? (const int32_t *)deg->ptr : nullptr;
+  const uint32_t *cur = (const uint32_t *)frontier->ptr;
+  const int64_t n_local = A->n_rows, word_lo = row_offset >> 5, word_hi = (row_offset + n_local + 31) >> 5;
+  bfs_block_decide_kernel<<<1, 1, 0, c->stream>>>(st, cnt, level);
+  bfs_block_prep_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(st, cur, (uint32_t *)visited->ptr, (int32_t *)levels->ptr, level,
+                                                                  n_words, word_lo, word_hi, row_offset, n_local);
+  if (n_local > 0) {
+    if (AT) {
+      const unsigned grid = grid_for((word_hi - word_lo) * 32, 256, 148 * 8);
+      if (AT->val)
+        bfs_block_push_kernel<true><<<grid, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val, dg, cur,
+                                                                 (const uint32_t *)visited->ptr, peers, cnt, level, word_lo,
+                                                                 word_hi, row_offset, n_local);
+      else
+        bfs_block_push_kernel<false><<<grid, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, dg, cur,
+                                                                  (const uint32_t *)visited->ptr, peers, cnt, level, word_lo,
+                                                                  word_hi, row_offset, n_local);
+    }
+    const unsigned grid = grid_for(n_local, 256, 148 * 32);
     if (A->val)
-      bfs_pull_block_kernel<true><<<grid, 256, 0, c->stream>>>(A->row_ptr, A->col, (const int32_t *)A->val,
-                                                               (const uint32_t *)frontier->ptr, peers, (int32_t *)levels->ptr,
-                                                               (uint32_t *)counters->ptr, level, A->n_rows, row_offset >> 5);
+      bfs_block_pull_kernel<true><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, (const int32_t *)A->val, dg, cur, peers,
+                                                               (int32_t *)levels->ptr, cnt, level, n_local, row_offset);
     else
-      bfs_pull_block_kernel<false><<<grid, 256, 0, c->stream>>>(A->row_ptr, A->col, nullptr, (const uint32_t *)frontier->ptr,
-                                                                peers, (int32_t *)levels->ptr, (uint32_t *)counters->ptr,
-                                                                level, A->n_rows, row_offset >> 5);
-    SHB_CUDA(cudaGetLastError());
+      bfs_block_pull_kernel<false><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, nullptr, dg, cur, peers,
+                                                                (int32_t *)levels->ptr, cnt, level, n_local, row_offset);
   }
-  return t.finish();
+  bfs_block_clear_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(st, (uint32_t *)frontier->ptr, n_words);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
+}
+
+SHB_API int shb_bfs_block_finish(shb_ctx *c, const shb_csr *A, const shb_buf *levels, shb_buf *counters) {
+  SHB_REQUIRE(c && A && levels && counters, "bad arguments");
+  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4 && counters->bytes >= 16, "buffers too short");
+  SHB_CUDA(cudaSetDevice(c->device));
+  SHB_CUDA(cudaMemsetAsync(counters->ptr, 0, 16, c->stream));
+  if (A->n_rows > 0)
+    bfs_block_stats_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>((const int32_t *)levels->ptr, A->row_ptr, A->n_rows,
+                                                                       (long long *)counters->ptr);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
 }
 
 // =================================================================================================

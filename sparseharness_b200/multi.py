@@ -295,60 +295,80 @@ def run_bfs(backend: BfsBackend, max_levels: int = 1 << 20, check_every: int = 4
 
 
 class GpuBfsPartition(BfsBackend):
-    """The CUDA backend: this rank's row block; next-frontier words go straight into every rank's bitmap."""
+    """The CUDA backend: this rank's row block.  AT_local (rows = out-edges of the owned vertices) enables push
+    levels; deg (full-length int32 push degrees) steers the direction heuristic."""
 
-    def __init__(self, ctx, A_local, bounds, rank, world, root, *, max_levels=4096, dist=None, torch=None):
-        self.ctx, self.A, self.bounds = ctx, A_local, np.asarray(bounds, dtype=np.int64)
+    def __init__(self, ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, max_levels=4096,
+                 dist=None, torch=None):
+        self.ctx, self.A, self.AT, self.deg = ctx, A_local, AT_local, deg
+        self.bounds = np.asarray(bounds, dtype=np.int64)
         self.rank, self.world, self.root, self.dist, self.torch = rank, world, int(root), dist, torch
-        self.n = int(self.bounds[-1])
+        self.n, self.nnz_total = int(self.bounds[-1]), int(nnz_total)
         self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
-        self.n_words = (self.n + 31) // 32
+        self.n_words = max((self.n + 31) // 32, 1)
         self.max_levels = max_levels
-        self.bm = [ctx.empty(max(self.n_words, 1) * 4), ctx.empty(max(self.n_words, 1) * 4)]
+        self.bm = [ctx.empty(self.n_words * 4), ctx.empty(self.n_words * 4)]
+        self.visited = ctx.empty(self.n_words * 4)
         self.levels = ctx.empty(max(self.hi - self.lo, 1) * 4)
-        self.counters = ctx.empty((max_levels + 3) * 4)
+        self.n_counter_words = 2 * max_levels + 8
+        self.counters = ctx.empty(self.n_counter_words * 8)
+        self.state = ctx.empty(ctx.bfs_block_state_bytes())
         self.launches = 0
         self.peers = [[self.bm[0]], [self.bm[1]]]
+        self.self_index = 0
         self._t_counts = None
         if world > 1:
-            self._t_counts = _tensor_view(torch, self.counters, max_levels + 3, ctx.device)
+            self._t_counts = _tensor_view(torch, self.counters, self.n_counter_words, ctx.device, "<i8")
             handles = [None] * world
             dist.all_gather_object(handles, (self.bm[0].ipc_handle(), self.bm[1].ipc_handle()))
             self.peers = [[], []]
             for r in range(world):
                 for k in (0, 1):
                     self.peers[k].append(self.bm[k] if r == rank else ctx.ipc_open(handles[r][k], self.n_words * 4))
+            self.self_index = rank
         self.reset()
 
+    def _reduce_slot(self, slot):
+        if self.world > 1:
+            self.dist.all_reduce(self._t_counts[2 + 2 * slot:4 + 2 * slot], op=self.dist.ReduceOp.SUM)
+
     def reset(self):
-        self.ctx.bfs_block_init(self.A, self.lo, self.n, self.root, self.levels, self.bm[0], self.counters)
-        self.bm[1].zero()
+        if self.world > 1:
+            self.dist.barrier()  # no peer may still be storing into the bitmaps init is about to zero
+        self.ctx.bfs_block_init(self.A, self.AT, self.lo, self.n, self.nnz_total, self.root, self.deg, self.levels,
+                                self.bm[0], self.bm[1], self.visited, self.counters, self.state)
+        self._reduce_slot(0)
         self.launches = 0
 
     def step(self, level):
-        self.ctx.bfs_block_step(self.A, self.lo, self.n, level, self.bm[level & 1], self.peers[(level + 1) & 1],
-                                self.levels, self.counters)
+        self.ctx.bfs_block_level(self.A, self.AT, self.lo, self.n, level, self.deg, self.bm[level & 1],
+                                 self.peers[(level + 1) & 1], self.self_index, self.visited, self.levels, self.counters,
+                                 self.state)
         self.launches += 1
 
     def reduce_count(self, level):
-        if self.world > 1:
-            self.dist.all_reduce(self._t_counts[2 + level:3 + level], op=self.dist.ReduceOp.SUM)
+        self._reduce_slot(level + 1)
 
     def read_counts(self, lo, hi):
-        return self.counters.download(np.uint32, hi - lo, offset=4 * (2 + lo))
+        w = self.counters.download(np.int64, 2 * (hi - lo), offset=8 * (2 + 2 * (lo + 1)))
+        return w[0::2]
 
-    def local_edges(self) -> int:
-        return int(self.counters.download(np.uint64, 1)[0])
+    def local_stats(self):
+        """(reached, sum of in-degrees of reached) of the owned slice."""
+        self.ctx.bfs_block_finish(self.A, self.levels, self.counters)
+        w = self.counters.download(np.int64, 2)
+        return int(w[0]), int(w[1])
 
     def result(self) -> np.ndarray:
         return self.levels.download(np.int32, self.hi - self.lo)
 
     def close(self):
-        for k in (0, 1):
-            for r, b in enumerate(self.peers[k]):
-                if r != self.rank and self.world > 1:
-                    b.free()
-        for b in self.bm + [self.levels, self.counters]:
+        if self.world > 1:
+            for k in (0, 1):
+                for r, b in enumerate(self.peers[k]):
+                    if r != self.rank:
+                        b.free()
+        for b in self.bm + [self.visited, self.levels, self.counters, self.state]:
             b.free()
 
 
@@ -364,71 +384,90 @@ def _tensor_view(torch, buf, count, device, typestr="<i4"):
 
 
 class EmulatedBfsPartition(BfsBackend):
-    """All P row blocks on ONE device: one launch per block and level, every block writing its words of the shared
-    next bitmap and adding to the shared found slot -- the multi-GPU path's arithmetic and protocol on one GPU."""
+    """All P row blocks on ONE device, each with its OWN bitmaps, state and counters, every block storing into every
+    block's next bitmap: the multi-GPU path's kernels and protocol on one GPU.  The all-reduce of a counter slot is
+    emulated through the host (download, sum, upload)."""
 
-    def __init__(self, ctx, blocks, bounds, root, max_levels=4096):
-        self.ctx, self.blocks, self.bounds, self.root = ctx, blocks, np.asarray(bounds, dtype=np.int64), int(root)
+    def __init__(self, ctx, blocks, bounds, root, nnz_total, *, at_blocks=None, deg=None, max_levels=4096):
+        self.ctx, self.blocks, self.at_blocks, self.deg = ctx, blocks, at_blocks, deg
+        self.bounds, self.root, self.nnz_total = np.asarray(bounds, dtype=np.int64), int(root), int(nnz_total)
         self.n = int(self.bounds[-1])
+        self.P = len(blocks)
         n_words = max((self.n + 31) // 32, 1)
-        self.bm = [ctx.empty(n_words * 4), ctx.empty(n_words * 4)]
-        self.levels = [ctx.empty(max(int(self.bounds[k + 1] - self.bounds[k]), 1) * 4) for k in range(len(blocks))]
-        self.counters = ctx.empty((max_levels + 3) * 4)
+        self.bm = [[ctx.empty(n_words * 4), ctx.empty(n_words * 4)] for _ in range(self.P)]
+        self.visited = [ctx.empty(n_words * 4) for _ in range(self.P)]
+        self.levels = [ctx.empty(max(int(self.bounds[k + 1] - self.bounds[k]), 1) * 4) for k in range(self.P)]
+        self.counters = [ctx.empty((2 * max_levels + 8) * 8) for _ in range(self.P)]
+        self.state = [ctx.empty(ctx.bfs_block_state_bytes()) for _ in range(self.P)]
         self.reset()
 
+    def _reduce_slot(self, slot):
+        off = 8 * (2 + 2 * slot)
+        tot = sum(c.download(np.int64, 2, offset=off) for c in self.counters)
+        for c in self.counters:
+            c.upload(tot, offset=off)
+
     def reset(self):
-        edges = 0
         for k, A in enumerate(self.blocks):
-            self.ctx.bfs_block_init(A, int(self.bounds[k]), self.n, self.root, self.levels[k], self.bm[0], self.counters)
-            edges += int(self.counters.download(np.uint64, 1)[0])  # each init zeroes the counters; keep the owner's degree
-        self.counters.upload(np.array([edges], np.uint64))
-        self.bm[1].zero()
+            self.ctx.bfs_block_init(A, self.at_blocks[k] if self.at_blocks else None, int(self.bounds[k]), self.n,
+                                    self.nnz_total, self.root, self.deg, self.levels[k], self.bm[k][0], self.bm[k][1],
+                                    self.visited[k], self.counters[k], self.state[k])
+        self._reduce_slot(0)
         self.launches = 0
 
     def step(self, level):
+        nxt = [self.bm[k][(level + 1) & 1] for k in range(self.P)]
         for k, A in enumerate(self.blocks):
-            self.ctx.bfs_block_step(A, int(self.bounds[k]), self.n, level, self.bm[level & 1], [self.bm[(level + 1) & 1]],
-                                    self.levels[k], self.counters)
+            self.ctx.bfs_block_level(A, self.at_blocks[k] if self.at_blocks else None, int(self.bounds[k]), self.n, level,
+                                     self.deg, self.bm[k][level & 1], nxt, k, self.visited[k], self.levels[k],
+                                     self.counters[k], self.state[k])
             self.launches += 1
 
     def reduce_count(self, level):
-        pass
+        self._reduce_slot(level + 1)
 
     def read_counts(self, lo, hi):
-        return self.counters.download(np.uint32, hi - lo, offset=4 * (2 + lo))
+        return self.counters[0].download(np.int64, 2 * (hi - lo), offset=8 * (2 + 2 * (lo + 1)))[0::2]
 
-    def edges(self) -> int:
-        return int(self.counters.download(np.uint64, 1)[0])
+    def stats(self):
+        r = e = 0
+        for k, A in enumerate(self.blocks):
+            self.ctx.bfs_block_finish(A, self.levels[k], self.counters[k])
+            w = self.counters[k].download(np.int64, 2)
+            r, e = r + int(w[0]), e + int(w[1])
+        return r, e
 
     def result(self) -> np.ndarray:
         return np.concatenate([self.levels[k].download(np.int32, int(self.bounds[k + 1] - self.bounds[k]))
-                               for k in range(len(self.blocks))])
+                               for k in range(self.P)])
 
 
-def partitioned_bfs(ctx, A_local, bounds, rank, world, root, *, check_every=4, max_levels=4096, dist=None, torch=None,
-                    repeat=1):
-    """BFS levels on a row-partitioned operator.  Returns (backend, stats) with stats = dict(levels, reached,
-    edges_traversed [sum of in-degrees of reached vertices, all ranks], ms [device time, max over ranks is the
-    caller's job], launches)."""
-    be = GpuBfsPartition(ctx, A_local, bounds, rank, world, root, max_levels=max_levels, dist=dist, torch=torch)
+def partitioned_bfs(ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, check_every=4,
+                    max_levels=4096, dist=None, torch=None, repeat=1):
+    """Direction-optimising BFS levels on a row-partitioned operator.  Returns (backend, stats) with stats =
+    dict(levels, reached, edges_traversed [sum of in-degrees of reached vertices, all ranks], ms [device time of
+    this rank; max over ranks is the caller's job], launches)."""
+    be = GpuBfsPartition(ctx, A_local, bounds, rank, world, root, nnz_total, AT_local=AT_local, deg=deg,
+                         max_levels=max_levels, dist=dist, torch=torch)
     best = None
-    for _ in range(max(1, repeat)):
-        be.reset()
+    for i in range(max(1, repeat)):
+        if i:
+            be.reset()
         ctx.synchronize()
         if world > 1:
             dist.barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
-        n_levels, reached, launches = run_bfs(be, max_levels, check_every)
+        n_levels, _, launches = run_bfs(be, max_levels, check_every)
         ev1.record()
         torch.cuda.synchronize()
         ms = ev0.elapsed_time(ev1)
         if best is None or ms < best["ms"]:
-            best = {"levels": n_levels, "reached": reached + 1, "ms": ms, "launches": launches}
-    edges = be.local_edges()
+            best = {"levels": n_levels, "ms": ms, "launches": launches}
+    reached, edges = be.local_stats()
     if world > 1:
-        t = torch.tensor([edges], dtype=torch.int64, device=f"cuda:{ctx.device}")
+        t = torch.tensor([reached, edges], dtype=torch.int64, device=f"cuda:{ctx.device}")
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        edges = int(t.item())
-    best["edges_traversed"] = edges
+        reached, edges = int(t[0].item()), int(t[1].item())
+    best["reached"], best["edges_traversed"] = reached, edges
     return be, best

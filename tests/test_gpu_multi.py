@@ -83,47 +83,57 @@ def test_two_gpu_pagerank_matches_oracle(mode):
     assert abs(out["iterations"] - out["oracle_iterations"]) <= 1
 
 
-@pytest.mark.parametrize("parts,check_every", [(1, 4), (2, 1), (5, 3)])
-def test_emulated_row_partition_bfs_matches_queue_bfs(ctx, orc, parts, check_every):
-    """shb_bfs_block_step on P row blocks of one device: levels, level count, reached and the TEPS numerator equal
-    the CPU queue BFS (hub rows >= 128 entries take the warp-cooperative path on this RMAT graph)."""
+@pytest.mark.parametrize("parts,check_every,push", [(1, 4, True), (2, 1, True), (5, 3, True), (3, 2, False)])
+def test_emulated_row_partition_bfs_matches_queue_bfs(ctx, orc, parts, check_every, push):
+    """shb_bfs_block_level on P row blocks of one device (own bitmaps / state per block, stores into every block's
+    next bitmap): levels, level count, reached and the TEPS numerator equal the CPU queue BFS, with push levels
+    (direction-optimising) and pull-only.  Hub rows >= 128 entries take the warp-cooperative pull path."""
     from sparseharness_b200 import multi
     rp, col = orc.gen_rmat(13, 16, symmetrise=True)
     n = len(rp) - 1
     assert np.diff(rp).max() >= 128
     root = int(np.argmax(np.diff(rp) > 0))
     A = ctx.csr(n, n, rp, col, None)
+    deg = A.row_lengths()
+    assert np.array_equal(deg.download(np.int32, n), np.diff(rp).astype(np.int32))
     bounds = multi.word_aligned_bounds(A.balance_rows(parts))
     blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(parts)]
-    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, root)
-    n_levels, reached, launches = multi.run_bfs(be, 1 << 20, check_every)
+    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, root, len(col), at_blocks=blocks if push else None, deg=deg)
+    n_levels, _, launches = multi.run_bfs(be, 1 << 20, check_every)
     want, nlev, edges = orc.bfs_levels(rp, col, None, root)
     assert np.array_equal(be.result(), want)
-    assert n_levels == nlev and reached + 1 == int((want >= 0).sum()) and be.edges() == edges
+    assert n_levels == nlev and be.stats() == (int((want >= 0).sum()), edges)
     assert launches == nlev and be.launches >= launches * parts
     # same answer as the single-device direction-optimising driver
     lv, st = ctx.bfs(A, root, AT=A)
     assert np.array_equal(lv.download(np.int32, n), want) and st.edges_traversed == edges
+    # a second traversal after reset gives the same levels
+    be.reset()
+    assert multi.run_bfs(be, 1 << 20, 3)[0] == nlev and np.array_equal(be.result(), want)
 
 
-def test_emulated_row_partition_bfs_directed_zero_valued_edges_and_level_cap(ctx, orc):
+@pytest.mark.parametrize("push", [True, False])
+def test_emulated_row_partition_bfs_directed_zero_valued_edges_and_level_cap(ctx, orc, push):
     from sparseharness_b200 import multi
     rng = np.random.default_rng(5)
     n = 1000
     rp, col, _ = orc.gen_uniform(n, n, 3, val_mode=1)
     val = rng.integers(0, 2, len(col)).astype(np.int32)  # a stored 0 is no edge (bool_and)
     A = ctx.csr(n, n, rp, col, val)
+    AT = A.transpose()
+    deg = AT.row_lengths()
     bounds = multi.word_aligned_bounds(A.balance_rows(3))
     blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(3)]
-    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, 3)
-    n_levels, reached, _ = multi.run_bfs(be, 1 << 20, 2)
+    at_blocks = [AT.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(3)] if push else None
+    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, 3, len(col), at_blocks=at_blocks, deg=deg if push else None)
+    n_levels, _, _ = multi.run_bfs(be, 1 << 20, 2)
     want, nlev, edges = orc.bfs_levels(rp, col, val, 3)
-    assert np.array_equal(be.result(), want) and n_levels == nlev and be.edges() == edges
-    # a level cap stops early with the levels found so far
+    assert np.array_equal(be.result(), want) and n_levels == nlev and be.stats()[1] == edges
+    # a level cap stops early with the levels found so far (the last launch's finds get their level at the next prep)
     be.reset()
     n_levels, _, launches = multi.run_bfs(be, 2, 2)
     got = be.result()
-    assert launches == 2 and np.array_equal(got[(want >= 0) & (want <= 2)], want[(want >= 0) & (want <= 2)])
+    assert launches == 2 and np.array_equal(got[(want >= 0) & (want <= 1)], want[(want >= 0) & (want <= 1)])
     assert (got[want > 2] == -1).all()
 
 
@@ -133,9 +143,10 @@ def test_bfs_block_rejects_unaligned_blocks(ctx, orc):
     n = len(rp) - 1
     A = ctx.csr(n, n, rp, col, None)
     B = A.slice_rows(16, 64)
-    lv, bm, cnt = ctx.empty(64 * 4), ctx.empty(n // 8 + 4), ctx.empty(64)
+    nb = n // 8 + 4
+    lv, b0, b1, vis, cnt, st = ctx.empty(64 * 4), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(256), ctx.empty(64)
     with pytest.raises(shb.ShbError) as e:
-        ctx.bfs_block_init(B, 16, n, 0, lv, bm, cnt)
+        ctx.bfs_block_init(B, None, 16, n, len(col), 0, None, lv, b0, b1, vis, cnt, st)
     assert e.value.status == 1
 
 

@@ -45,20 +45,21 @@ def run(scale, edgefactor, check, seed=0x5EED0024, check_every=4, repeat=3, ctx=
     root = int(np.argmax(np.diff(rp_head) > 0))
     bounds = multi.word_aligned_bounds(A.balance_rows(world))
     lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    deg = A.row_lengths()  # symmetric graph: push degree == pull degree, and the row block serves both directions
     if world > 1:
         Al = A.slice_rows(lo, hi - lo)
         A.free()
     else:
         Al = A
-    be, st = multi.partitioned_bfs(ctx, Al, bounds, rank, world, root, check_every=check_every, dist=dist, torch=torch,
-                                   repeat=repeat)
+    be, st = multi.partitioned_bfs(ctx, Al, bounds, rank, world, root, nnz, AT_local=Al, deg=deg, check_every=check_every,
+                                   dist=dist, torch=torch, repeat=repeat)
     t = torch.tensor([st["ms"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     undirected = st["edges_traversed"] / 2
     out = {"graph": f"RMAT scale {scale} edgefactor {edgefactor} symmetrised+deduplicated", "n": n, "nnz": nnz,
-           "n_gpus": world, "schedule": "row-partitioned pull, bitmap words stored into every peer (fused exchange)",
+           "n_gpus": world, "schedule": "row-partitioned, direction-optimising; frontier bitmap words / bits stored into every peer by the push and pull kernels",
            "levels": st["levels"], "reached": st["reached"], "ms": ms, "gteps": undirected / (ms * 1e6),
            "teps_edges": undirected, "local_rows": hi - lo, "local_nnz": Al.info.nnz,
            "frontier_bytes_per_gpu_per_level": (n + 7) // 8}
@@ -74,6 +75,7 @@ def run(scale, edgefactor, check, seed=0x5EED0024, check_every=4, repeat=3, ctx=
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         out.update(parity_ok=bool(flag.item()), oracle_levels=nlev, oracle_edges=edges)
     be.close()
+    deg.free()
     Al.free()
     return out, rank, world
 

@@ -21,7 +21,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-def run(scale, edgefactor, iters, mode, delta, check, seed=0x5EED0026, check_every=None, repeat=3):
+def run(scale, edgefactor, iters, mode, delta, check, seed=0x5EED0026, check_every=None, repeat=3, ctx=None):
     import torch
     import torch.distributed as dist
 
@@ -34,8 +34,9 @@ def run(scale, edgefactor, iters, mode, delta, check, seed=0x5EED0026, check_eve
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    ctx = shb.Context(local)
-    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    if ctx is None:
+        ctx = shb.Context(local)
+        ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     A = ctx.synth_rmat(scale, edgefactor, seed=seed, symmetrise=False, value_mode=1)
     info = A.info
     n, nnz = info.n_rows, info.nnz

@@ -269,19 +269,29 @@ class Context:
         return b.value
 
     def bfs_block_init(self, A: Csr, AT: Csr | None, row_offset, n_total, nnz_total, root, deg: Buffer | None,
-                       levels: Buffer, bm0: Buffer, bm1: Buffer, visited: Buffer, counters: Buffer, state: Buffer):
+                       levels: Buffer, bm0: Buffer, bm1: Buffer, visited: Buffer, counters: Buffer, state: Buffer,
+                       staged: bool = False):
         _ck(lib.shb_bfs_block_init(self.h, A.h, AT.h if AT else None, row_offset, n_total, nnz_total, root,
-                                   deg.h if deg else None, levels.h, bm0.h, bm1.h, visited.h, counters.h, state.h))
+                                   deg.h if deg else None, levels.h, bm0.h, bm1.h, visited.h, counters.h, state.h,
+                                   int(staged)))
+
+    def bfs_block_publish(self, slot, counters: Buffer, state: Buffer, peer_counters: list[Buffer], self_index: int,
+                          barrier_target: int):
+        arr = (C.c_void_p * len(peer_counters))(*[d.h for d in peer_counters])
+        _ck(lib.shb_bfs_block_publish(self.h, slot, counters.h, state.h, arr, len(peer_counters), self_index,
+                                      barrier_target))
 
     def bfs_block_level(self, A: Csr, AT: Csr | None, row_offset, n_total, level, deg: Buffer | None, frontier: Buffer,
                         nxt: list[Buffer], self_index: int, visited: Buffer, levels: Buffer, counters: Buffer,
-                        state: Buffer):
+                        state: Buffer, peer_counters: list[Buffer] | None = None, barrier_target: int = 0):
         arr = (C.c_void_p * len(nxt))(*[d.h for d in nxt])
+        pc = (C.c_void_p * len(peer_counters))(*[d.h for d in peer_counters]) if peer_counters else None
         _ck(lib.shb_bfs_block_level(self.h, A.h, AT.h if AT else None, row_offset, n_total, level, deg.h if deg else None,
-                                    frontier.h, arr, len(nxt), self_index, visited.h, levels.h, counters.h, state.h))
+                                    frontier.h, arr, len(nxt), self_index, visited.h, levels.h, counters.h, state.h, pc,
+                                    barrier_target))
 
-    def bfs_block_finish(self, A: Csr, levels: Buffer, counters: Buffer):
-        _ck(lib.shb_bfs_block_finish(self.h, A.h, levels.h, counters.h))
+    def bfs_block_finish(self, A: Csr, levels: Buffer, counters: Buffer, state: Buffer):
+        _ck(lib.shb_bfs_block_finish(self.h, A.h, levels.h, counters.h, state.h))
 
     def iterate(self, A: Csr, semiring, x: Buffer, y0: Buffer | None, alpha, beta, work: Buffer, delta=1e-4, term=None,
                 y_rebind=True, max_iters=1000, check_every=16, per_iter=False, cfg: LaunchCfg | None = None):

@@ -164,6 +164,7 @@ SHB_API int shb_buf_create(shb_ctx *c, uint64_t bytes, shb_buf **out) {
   SHB_CUDA(cudaSetDevice(c->device));
   shb_buf *b = new shb_buf();
   b->ctx = c;
+  b->device = c->device;
   b->bytes = bytes;
   cudaError_t e = cudaMalloc(&b->ptr, bytes ? (size_t)round_up((int64_t)bytes, 256) : 256);
   if (e != cudaSuccess) {
@@ -181,6 +182,7 @@ SHB_API int shb_buf_wrap(shb_ctx *c, void *ptr, uint64_t bytes, shb_buf **out) {
   SHB_REQUIRE(c && out && ptr, "bad arguments");
   shb_buf *b = new shb_buf();
   b->ctx = c;
+  b->device = c->device;
   b->ptr = ptr;
   b->bytes = bytes;
   b->owned = false;
@@ -190,13 +192,15 @@ SHB_API int shb_buf_wrap(shb_ctx *c, void *ptr, uint64_t bytes, shb_buf **out) {
 
 SHB_API int shb_buf_destroy(shb_buf *b) {
   if (!b) return SHB_OK;
+  // the creating context may already be gone (handles are freed in any order by garbage-collected callers)
   if (b->ipc) {
-    cudaSetDevice(b->ctx->device);
+    cudaSetDevice(b->device);
     cudaIpcCloseMemHandle(b->ptr);
   } else if (b->owned && b->ptr) {
-    cudaSetDevice(b->ctx->device);
+    cudaSetDevice(b->device);
     cudaFree(b->ptr);
   }
+  cudaGetLastError();  // a failed release must not surface as the next call's error
   delete b;
   return SHB_OK;
 }
@@ -292,6 +296,7 @@ int shb_csr_alloc(shb_ctx *c, int64_t n_rows, int64_t n_cols, int64_t nnz, bool 
   SHB_CUDA(cudaSetDevice(c->device));
   shb_csr *A = new shb_csr();
   A->ctx = c;
+  A->device = c->device;
   A->n_rows = n_rows;
   A->n_cols = n_cols;
   A->nnz = nnz;
@@ -323,7 +328,7 @@ int shb_csr_alloc(shb_ctx *c, int64_t n_rows, int64_t n_cols, int64_t nnz, bool 
 
 SHB_API int shb_csr_destroy(shb_csr *A) {
   if (!A) return SHB_OK;
-  cudaSetDevice(A->ctx->device);
+  cudaSetDevice(A->device);
   cudaFree(A->row_ptr);
   cudaFree(A->col);
   cudaFree(A->val);
@@ -331,6 +336,7 @@ SHB_API int shb_csr_destroy(shb_csr *A) {
   cudaFree(A->carry_tail);
   cudaFree(A->carry_head);
   shb_pb_free(A->pb);
+  cudaGetLastError();
   delete A;
   return SHB_OK;
 }

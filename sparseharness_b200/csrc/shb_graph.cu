@@ -32,7 +32,12 @@ struct BfsState {
   unsigned long long next_edges;   // sum of push-degrees of the next frontier
   unsigned long long unexplored;   // edges not yet scanned (Beamer's m_u)
   unsigned long long reached, edges_traversed;
+  uint32_t big_count;   // hub vertices of the current push level, expanded by the whole grid (bfs_push_big_kernel)
+  uint32_t pad2;
+  int32_t big_list[1024];
 };
+#define BFS_BIG_ROW 1024
+#define BFS_BIG_CAP 1024
 
 __global__ void bfs_init_kernel(BfsState *st, int32_t *levels, uint32_t *bm0, int64_t root, const int32_t *a_row_ptr,
                                 const int32_t *at_row_ptr, unsigned long long nnz, int have_at) {
@@ -50,6 +55,7 @@ __global__ void bfs_init_kernel(BfsState *st, int32_t *levels, uint32_t *bm0, in
   st->unexplored = nnz - (unsigned long long)(rp[root + 1] - rp[root]);
   st->reached = 1;
   st->edges_traversed = (unsigned long long)(a_row_ptr[root + 1] - a_row_ptr[root]);
+  st->big_count = 0;
 }
 
 __global__ void bfs_clear_kernel(const BfsState *st, uint32_t *bm0, uint32_t *bm1, int64_t n_words) {
@@ -57,6 +63,34 @@ __global__ void bfs_clear_kernel(const BfsState *st, uint32_t *bm0, uint32_t *bm
   uint32_t *next = ((st->level + 1) & 1) ? bm1 : bm0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (int64_t)gridDim.x * blockDim.x)
     next[i] = 0u;
+}
+
+__device__ __forceinline__ void bfs_push_one(int32_t v, uint32_t level, const int32_t *__restrict__ at_row_ptr,
+                                             const int32_t *__restrict__ a_row_ptr, int32_t *levels, uint32_t *next,
+                                             uint32_t &found, unsigned long long &push_deg, unsigned long long &pull_deg) {
+  if (levels[v] == -1) {
+    const int32_t old = atomicCAS(&levels[v], -1, (int32_t)level + 1);
+    if (old == -1) {
+      atomicOr(&next[v >> 5], 1u << (v & 31));
+      ++found;
+      push_deg += (unsigned long long)(at_row_ptr[v + 1] - at_row_ptr[v]);
+      pull_deg += (unsigned long long)(a_row_ptr[v + 1] - a_row_ptr[v]);
+    }
+  }
+}
+
+__device__ __forceinline__ void bfs_push_account3(BfsState *st, uint32_t found, unsigned long long push_deg,
+                                                  unsigned long long pull_deg) {
+  for (int off = 16; off > 0; off >>= 1) {
+    found += __shfl_xor_sync(0xffffffffu, found, off);
+    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
+    pull_deg += __shfl_xor_sync(0xffffffffu, pull_deg, off);
+  }
+  if ((threadIdx.x & 31) == 0 && found) {
+    atomicAdd(&st->next_count, found);
+    atomicAdd(&st->next_edges, push_deg);
+    atomicAdd(&st->edges_traversed, pull_deg);
+  }
 }
 
 // push: one warp per bitmap word of the current frontier; lanes stride over each frontier vertex's
@@ -81,31 +115,45 @@ __global__ void bfs_push_kernel(BfsState *st, const int32_t *__restrict__ at_row
       word &= word - 1;
       const int64_t u = w * 32 + b;
       const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
+      if (e - s >= BFS_BIG_ROW) {  // a hub: parked for the whole grid (one warp would serialise the level)
+        uint32_t slot = 0;
+        if (lane == 0) slot = atomicAdd(&st->big_count, 1u);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot < BFS_BIG_CAP) {
+          if (lane == 0) st->big_list[slot] = (int32_t)u;
+          continue;
+        }
+      }
       for (int k = s + lane; k < e; k += 32) {
         if (HAS_VAL && at_val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
-        const int32_t v = at_col[k];
-        if (levels[v] == -1) {
-          const int32_t old = atomicCAS(&levels[v], -1, (int32_t)level + 1);
-          if (old == -1) {
-            atomicOr(&next[v >> 5], 1u << (v & 31));
-            ++found;
-            push_deg += (unsigned long long)(at_row_ptr[v + 1] - at_row_ptr[v]);
-            pull_deg += (unsigned long long)(a_row_ptr[v + 1] - a_row_ptr[v]);
-          }
-        }
+        bfs_push_one(at_col[k], level, at_row_ptr, a_row_ptr, levels, next, found, push_deg, pull_deg);
       }
     }
   }
-  for (int off = 16; off > 0; off >>= 1) {
-    found += __shfl_xor_sync(0xffffffffu, found, off);
-    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
-    pull_deg += __shfl_xor_sync(0xffffffffu, pull_deg, off);
+  bfs_push_account3(st, found, push_deg, pull_deg);
+}
+
+template <bool HAS_VAL>
+__global__ void bfs_push_big_kernel(BfsState *st, const int32_t *__restrict__ at_row_ptr, const int32_t *__restrict__ at_col,
+                                    const int32_t *__restrict__ at_val, const int32_t *__restrict__ a_row_ptr,
+                                    int32_t *levels, uint32_t *bm0, uint32_t *bm1) {
+  if (st->done || st->mode != 0) return;
+  const uint32_t n_big = min(st->big_count, (uint32_t)BFS_BIG_CAP);
+  if (n_big == 0) return;
+  const uint32_t level = st->level;
+  uint32_t *next = (level & 1) ? bm0 : bm1;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, n_threads = (int64_t)gridDim.x * blockDim.x;
+  uint32_t found = 0;
+  unsigned long long push_deg = 0, pull_deg = 0;
+  for (uint32_t i = 0; i < n_big; ++i) {
+    const int32_t u = st->big_list[i];
+    const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
+    for (int64_t k = s + tid; k < e; k += n_threads) {
+      if (HAS_VAL && at_val[k] == 0) continue;
+      bfs_push_one(at_col[k], level, at_row_ptr, a_row_ptr, levels, next, found, push_deg, pull_deg);
+    }
   }
-  if (lane == 0 && found) {
-    atomicAdd(&st->next_count, found);
-    atomicAdd(&st->next_edges, push_deg);
-    atomicAdd(&st->edges_traversed, pull_deg);
-  }
+  bfs_push_account3(st, found, push_deg, pull_deg);
 }
 
 // pull: thread per unvisited row, stop at the first in-neighbour that is in the frontier bitmap
@@ -178,6 +226,7 @@ __global__ void bfs_decide_kernel(BfsState *st, unsigned long long n) {
   st->next_count = 0;
   st->next_edges = 0;
   st->level += 1;
+  st->big_count = 0;
 }
 
 SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t root, shb_buf *levels, uint32_t max_levels,
@@ -223,6 +272,12 @@ SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t roo
         else
           bfs_push_kernel<false><<<grid_for(n_words * 32, 256, 148 * 8), 256, 0, c->stream>>>(
               st, AT->row_ptr, AT->col, nullptr, A->row_ptr, (int32_t *)levels->ptr, bm0, bm1, n_words);
+        if (a_val)
+          bfs_push_big_kernel<true><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val,
+                                                                    A->row_ptr, (int32_t *)levels->ptr, bm0, bm1);
+        else
+          bfs_push_big_kernel<false><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, A->row_ptr,
+                                                                     (int32_t *)levels->ptr, bm0, bm1);
       }
       if (a_val)
         bfs_pull_kernel<true><<<grid_for(n, 256, 148 * 32), 256, 0, c->stream>>>(
@@ -231,7 +286,7 @@ SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t roo
         bfs_pull_kernel<false><<<grid_for(n, 256, 148 * 32), 256, 0, c->stream>>>(
             st, A->row_ptr, A->col, nullptr, AT ? AT->row_ptr : A->row_ptr, (int32_t *)levels->ptr, bm0, bm1, n);
       bfs_decide_kernel<<<1, 1, 0, c->stream>>>(st, (unsigned long long)n);
-      launches += AT ? 4 : 3;
+      launches += AT ? 5 : 3;
     }
     cudaMemcpyAsync(&h, st, sizeof h, cudaMemcpyDeviceToHost, c->stream);
     cudaError_t e = cudaStreamSynchronize(c->stream);
@@ -660,7 +715,7 @@ SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t
     // dist = ZERO of min-plus everywhere (3.4028235E38f = 0x7f7fffff)
     {
       shb_buf tmp;
-      tmp.ctx = c; tmp.ptr = dist->ptr; tmp.bytes = dist->bytes; tmp.owned = false;
+      tmp.ctx = c; tmp.device = c->device; tmp.ptr = dist->ptr; tmp.bytes = dist->bytes; tmp.owned = false;
       status = shb_buf_fill_u32(c, &tmp, 0, (uint64_t)n, 0x7f7fffffu);
       if (status != SHB_OK) goto done;
     }
@@ -747,6 +802,13 @@ done:
 // steer the heuristic and the termination test (> 0) only; reached / TEPS come from the levels at the end.
 // =================================================================================================
 #define BFS_BLOCK_BIG_ROW 128
+#define BFS_PUSH_BIG_ROW 1024  // a frontier vertex with at least this many out-edges is expanded by the whole grid
+#define BFS_PUSH_BIG_CAP 1024
+// counters layout (int64 words): 0 reached, 1 TEPS numerator (after finish), 2 arrival word of the peer barrier,
+// 4..5 staging of the level's (vertices, degrees), slot F at BFS_SLOT(F), BFS_SLOT(F) + 1
+#define BFS_FLAG_WORD 2
+#define BFS_STAGE_WORD 4
+#define BFS_SLOT(F) (6 + 2 * (F))
 
 struct BfsPeers {
   uint32_t *bm[8];
@@ -762,12 +824,16 @@ struct BfsBlockState {
   unsigned long long n_prev;      // vertices of the previous frontier
   unsigned long long unexplored;  // Beamer's m_u
   unsigned long long n_total;
+  uint32_t big_count;             // hub vertices of the current push level, expanded by the whole grid
+  uint32_t pad2;
+  int32_t big_list[BFS_PUSH_BIG_CAP];
 };
 
 __global__ void bfs_block_decide_kernel(BfsBlockState *st, const long long *counters, uint32_t level) {
+  st->big_count = 0;
   if (st->done) return;
-  const unsigned long long nf = (unsigned long long)counters[2 + 2 * level];
-  const unsigned long long mf = (unsigned long long)counters[3 + 2 * level];
+  const unsigned long long nf = (unsigned long long)counters[BFS_SLOT(level)];
+  const unsigned long long mf = (unsigned long long)counters[BFS_SLOT(level) + 1];
   if (nf == 0) {
     st->done = 1;
     return;
@@ -811,14 +877,41 @@ __global__ void bfs_block_clear_kernel(const BfsBlockState *st, uint32_t *bm, in
 }
 
 
-// push: one warp per owned frontier word; lanes stride over each frontier vertex's out-adjacency
+// one out-edge of a frontier vertex: mark the target in the local next bitmap and, if new here, in every peer's
+__device__ __forceinline__ void bfs_push_visit(int32_t v, const uint32_t *__restrict__ visited, const BfsPeers &next,
+                                               uint32_t *mine, const int32_t *__restrict__ deg, unsigned long long &found,
+                                               unsigned long long &push_deg) {
+  const uint32_t bit = 1u << (v & 31);
+  if (visited[v >> 5] & bit) return;
+  const uint32_t old = atomicOr(&mine[v >> 5], bit);
+  if (!(old & bit)) {  // new on this rank: tell every peer once
+    for (int i = 0; i < next.n; ++i)
+      if (i != next.self) atomicOr(&next.bm[i][v >> 5], bit);
+    ++found;
+    push_deg += (unsigned long long)(deg ? deg[v] : 1);
+  }
+}
+
+__device__ __forceinline__ void bfs_push_account(long long *acc, unsigned long long found, unsigned long long push_deg) {
+  for (int off = 16; off > 0; off >>= 1) {
+    found += __shfl_xor_sync(0xffffffffu, found, off);
+    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
+  }
+  if ((threadIdx.x & 31) == 0 && found) {
+    atomicAdd(reinterpret_cast<unsigned long long *>(&acc[0]), found);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&acc[1]), push_deg);
+  }
+}
+
+// push: one warp per owned frontier word; lanes stride over each frontier vertex's out-adjacency.  Hub vertices
+// are parked in the state's list and expanded by the whole grid in bfs_block_push_big_kernel (one warp walking a
+// 10^5-entry adjacency would serialise the level).
 template <bool HAS_VAL>
-__global__ void bfs_block_push_kernel(const BfsBlockState *st, const int32_t *__restrict__ at_row_ptr,
+__global__ void bfs_block_push_kernel(BfsBlockState *st, const int32_t *__restrict__ at_row_ptr,
                                       const int32_t *__restrict__ at_col, const int32_t *__restrict__ at_val,
                                       const int32_t *__restrict__ deg, const uint32_t *__restrict__ cur,
                                       const uint32_t *__restrict__ visited, const __grid_constant__ BfsPeers next,
-                                      long long *counters, uint32_t level, int64_t word_lo, int64_t word_hi, int64_t row_offset,
-                                      int64_t n_local) {
+                                      long long *acc, int64_t word_lo, int64_t word_hi, int64_t row_offset, int64_t n_local) {
   if (st->done || st->mode != 0) return;
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -833,36 +926,51 @@ __global__ void bfs_block_push_kernel(const BfsBlockState *st, const int32_t *__
       const int64_t u = w * 32 + b - row_offset;
       if (u < 0 || u >= n_local) continue;
       const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
+      if (e - s >= BFS_PUSH_BIG_ROW) {
+        uint32_t slot = 0;
+        if (lane == 0) slot = atomicAdd(&st->big_count, 1u);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot < BFS_PUSH_BIG_CAP) {
+          if (lane == 0) st->big_list[slot] = (int32_t)u;
+          continue;
+        }
+      }
       for (int k = s + lane; k < e; k += 32) {
         if (HAS_VAL && at_val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
-        const int32_t v = at_col[k];
-        const uint32_t bit = 1u << (v & 31);
-        if (visited[v >> 5] & bit) continue;
-        const uint32_t old = atomicOr(&mine[v >> 5], bit);
-        if (!(old & bit)) {  // new on this rank: tell every peer once
-          for (int i = 0; i < next.n; ++i)
-            if (i != next.self) atomicOr(&next.bm[i][v >> 5], bit);
-          ++found;
-          push_deg += (unsigned long long)(deg ? deg[v] : 1);
-        }
+        bfs_push_visit(at_col[k], visited, next, mine, deg, found, push_deg);
       }
     }
   }
-  for (int off = 16; off > 0; off >>= 1) {
-    found += __shfl_xor_sync(0xffffffffu, found, off);
-    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
+  bfs_push_account(acc, found, push_deg);
+}
+
+template <bool HAS_VAL>
+__global__ void bfs_block_push_big_kernel(const BfsBlockState *st, const int32_t *__restrict__ at_row_ptr,
+                                          const int32_t *__restrict__ at_col, const int32_t *__restrict__ at_val,
+                                          const int32_t *__restrict__ deg, const uint32_t *__restrict__ visited,
+                                          const __grid_constant__ BfsPeers next, long long *acc) {
+  if (st->done || st->mode != 0) return;
+  const uint32_t n_big = min(st->big_count, (uint32_t)BFS_PUSH_BIG_CAP);
+  if (n_big == 0) return;
+  uint32_t *mine = next.bm[next.self];
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, n_threads = (int64_t)gridDim.x * blockDim.x;
+  unsigned long long found = 0, push_deg = 0;
+  for (uint32_t i = 0; i < n_big; ++i) {
+    const int32_t u = st->big_list[i];
+    const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
+    for (int64_t k = s + tid; k < e; k += n_threads) {
+      if (HAS_VAL && at_val[k] == 0) continue;
+      bfs_push_visit(at_col[k], visited, next, mine, deg, found, push_deg);
+    }
   }
-  if (lane == 0 && found) {
-    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[2 + 2 * (level + 1)]), found);
-    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[3 + 2 * (level + 1)]), push_deg);
-  }
+  bfs_push_account(acc, found, push_deg);
 }
 
 template <bool HAS_VAL>
 __global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__restrict__ row_ptr,
                                       const int32_t *__restrict__ col, const int32_t *__restrict__ val,
                                       const int32_t *__restrict__ deg, const uint32_t *__restrict__ cur,
-                                      const __grid_constant__ BfsPeers next, int32_t *levels, long long *counters,
+                                      const __grid_constant__ BfsPeers next, int32_t *levels, long long *acc,
                                       uint32_t level, int64_t n_local, int64_t row_offset) {
   if (st->done || st->mode != 1) return;
   const int lane = threadIdx.x & 31;
@@ -921,12 +1029,62 @@ __global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__
     push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
   }
   if (lane == 0 && found_n) {
-    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[2 + 2 * (level + 1)]), found_n);
-    atomicAdd(reinterpret_cast<unsigned long long *>(&counters[3 + 2 * (level + 1)]), push_deg);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&acc[0]), found_n);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&acc[1]), push_deg);
   }
 }
 
-__global__ void bfs_block_init_kernel(BfsBlockState *st, int32_t *levels, uint32_t *bm0, long long *counters, int64_t root,
+// The exchange of a counter slot without a collective library: lane i adds this rank's staged (vertices,
+// degrees) to rank i's slot with system-scope atomics over NVLink, fences, and bumps rank i's arrival word;
+// lane 0 then waits until all `world` ranks have arrived here `target / world` times.  Every peer store of the
+// level's push / pull kernels was issued by earlier kernels of this stream, so it is ordered before the arrival
+// (fence + stream order) and visible to whoever observes the arrival with an acquire load.  target == 0: no
+// wait (all blocks on one device, stream ordered).  A wait longer than ~4 s marks the traversal failed
+// instead of hanging the device.
+struct BfsComm {
+  long long *counters[8];
+  int n;
+};
+
+__global__ void bfs_block_publish_kernel(BfsBlockState *st, const __grid_constant__ BfsComm comm, long long *stage,
+                                         int slot_word, int flag_word, int self, unsigned long long target) {
+  const int lane = threadIdx.x;
+  const long long nf = stage[0], mf = stage[1];
+  if (lane < comm.n) {
+    long long *c = comm.counters[lane];
+    if (nf | mf) {
+      atomicAdd_system(reinterpret_cast<unsigned long long *>(&c[slot_word]), (unsigned long long)nf);
+      atomicAdd_system(reinterpret_cast<unsigned long long *>(&c[slot_word + 1]), (unsigned long long)mf);
+    }
+    __threadfence_system();
+    atomicAdd_system(reinterpret_cast<unsigned long long *>(&c[flag_word]), 1ull);
+  }
+  __syncwarp();
+  if (lane == 0) {
+    stage[0] = 0;
+    stage[1] = 0;
+    if (target) {
+      const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(&comm.counters[self][flag_word]);
+      unsigned long long t0 = 0, now = 0;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      while (true) {
+        unsigned long long v;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
+        if (v >= target) break;
+        __nanosleep(200);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 > 4000000000ull) {
+          st->done = 1;
+          st->pad = 1;  // barrier timeout: reported by shb_bfs_block_finish
+          break;
+        }
+      }
+    }
+    __threadfence_system();
+  }
+}
+
+__global__ void bfs_block_init_kernel(BfsBlockState *st, int32_t *levels, uint32_t *bm0, long long *acc, int64_t root,
                                       int64_t row_offset, int64_t n_local, const int32_t *deg, int have_push,
                                       unsigned long long nnz_total, unsigned long long n_total) {
   bm0[root >> 5] = 1u << (root & 31);
@@ -937,9 +1095,12 @@ __global__ void bfs_block_init_kernel(BfsBlockState *st, int32_t *levels, uint32
   st->n_prev = 0;
   st->unexplored = nnz_total;
   st->n_total = n_total;
-  if (root >= row_offset && root < row_offset + n_local) {  // the owner reports frontier 0; the caller all-reduces slot 0
-    counters[2] = 1;
-    counters[3] = deg ? (long long)deg[root] : 1;
+  st->big_count = 0;
+  st->pad2 = 0;
+  if (root >= row_offset && root < row_offset + n_local) {  // the owner reports frontier 0 (slot 0 is then exchanged)
+    levels[root - row_offset] = 0;
+    acc[0] = 1;
+    acc[1] = deg ? (long long)deg[root] : 1;
   }
 }
 
@@ -990,9 +1151,25 @@ SHB_API int shb_bfs_block_state_bytes(uint64_t *bytes) {
   return SHB_OK;
 }
 
+static int bfs_block_comm(shb_buf *counters, shb_buf *const *peer_counters, int n, int self, uint32_t max_slot, BfsComm *comm) {
+  const uint64_t need = (uint64_t)(BFS_SLOT(max_slot) + 2) * 8;
+  SHB_REQUIRE(counters->bytes >= need, "counters has no slot for this level");
+  comm->n = 0;
+  for (int i = 0; i < 8; ++i) comm->counters[i] = nullptr;
+  if (!peer_counters) return SHB_OK;
+  SHB_REQUIRE(n >= 1 && n <= 8 && self >= 0 && self < n, "1..8 ranks, one of them local");
+  for (int i = 0; i < n; ++i) {
+    SHB_REQUIRE(peer_counters[i] && peer_counters[i]->bytes >= need, "a peer's counters are too short");
+    comm->counters[i] = (long long *)peer_counters[i]->ptr;
+  }
+  SHB_REQUIRE(peer_counters[self]->ptr == counters->ptr, "peer_counters[self_index] must be the local counters");
+  comm->n = n;
+  return SHB_OK;
+}
+
 SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
                                int64_t nnz_total, int64_t root, const shb_buf *deg, shb_buf *levels, shb_buf *frontier0,
-                               shb_buf *frontier1, shb_buf *visited, shb_buf *counters, shb_buf *state) {
+                               shb_buf *frontier1, shb_buf *visited, shb_buf *counters, shb_buf *state, int staged) {
   SHB_REQUIRE(c && A && levels && frontier0 && frontier1 && visited && counters && state, "bad arguments");
   SHB_TRY(bfs_block_check(A, AT, row_offset, n_total));
   SHB_REQUIRE(root >= 0 && root < n_total, "root out of range");
@@ -1000,24 +1177,44 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
   SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
   SHB_REQUIRE(frontier0->bytes >= bm_bytes && frontier1->bytes >= bm_bytes && visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
   SHB_REQUIRE(!deg || deg->bytes >= (uint64_t)n_total * 4, "deg shorter than n_total");
-  SHB_REQUIRE(counters->bytes >= 32 && state->bytes >= sizeof(BfsBlockState), "counters / state too short");
+  SHB_REQUIRE(state->bytes >= sizeof(BfsBlockState), "state too short");
+  SHB_REQUIRE(counters->bytes >= (uint64_t)(BFS_SLOT(0) + 2) * 8, "counters too short");
   SHB_CUDA(cudaSetDevice(c->device));
+  long long *cnt = (long long *)counters->ptr;
   if (A->n_rows > 0) SHB_CUDA(cudaMemsetAsync(levels->ptr, 0xff, (size_t)A->n_rows * 4, c->stream));
   SHB_CUDA(cudaMemsetAsync(frontier0->ptr, 0, (size_t)bm_bytes, c->stream));
   SHB_CUDA(cudaMemsetAsync(frontier1->ptr, 0, (size_t)bm_bytes, c->stream));
   SHB_CUDA(cudaMemsetAsync(visited->ptr, 0, (size_t)bm_bytes, c->stream));
-  SHB_CUDA(cudaMemsetAsync(counters->ptr, 0, (size_t)counters->bytes, c->stream));
+  // everything but the arrival word, which counts monotonically over the life of the buffer
+  SHB_CUDA(cudaMemsetAsync(cnt, 0, BFS_FLAG_WORD * 8, c->stream));
+  SHB_CUDA(cudaMemsetAsync(cnt + BFS_STAGE_WORD, 0, (size_t)counters->bytes - BFS_STAGE_WORD * 8, c->stream));
+  long long *acc = staged ? cnt + BFS_STAGE_WORD : cnt + BFS_SLOT(0);
   bfs_block_init_kernel<<<1, 1, 0, c->stream>>>((BfsBlockState *)state->ptr, (int32_t *)levels->ptr, (uint32_t *)frontier0->ptr,
-                                                (long long *)counters->ptr, root, row_offset, A->n_rows,
-                                                deg ? (const int32_t *)deg->ptr : nullptr, AT != nullptr,
-                                                (unsigned long long)nnz_total, (unsigned long long)n_total);
+                                                acc, root, row_offset, A->n_rows, deg ? (const int32_t *)deg->ptr : nullptr,
+                                                AT != nullptr, (unsigned long long)nnz_total, (unsigned long long)n_total);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
+}
+
+// second half of init: the exchange of slot 0.  Separate so that every rank has zeroed its counters (the caller's
+// barrier between the two calls) before any peer adds to them.
+SHB_API int shb_bfs_block_publish(shb_ctx *c, uint32_t slot, shb_buf *counters, shb_buf *state, shb_buf *const *peer_counters,
+                                  int n_ranks, int self_index, uint64_t barrier_target) {
+  SHB_REQUIRE(c && counters && state && peer_counters, "bad arguments");
+  BfsComm comm;
+  SHB_TRY(bfs_block_comm(counters, peer_counters, n_ranks, self_index, slot, &comm));
+  SHB_CUDA(cudaSetDevice(c->device));
+  long long *cnt = (long long *)counters->ptr;
+  bfs_block_publish_kernel<<<1, 32, 0, c->stream>>>((BfsBlockState *)state->ptr, comm, cnt + BFS_STAGE_WORD, BFS_SLOT(slot),
+                                                    BFS_FLAG_WORD, self_index, (unsigned long long)barrier_target);
   SHB_CUDA(cudaGetLastError());
   return SHB_OK;
 }
 
 SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
                                 uint32_t level, const shb_buf *deg, shb_buf *frontier, shb_buf *const *next, int n_next,
-                                int self_index, shb_buf *visited, shb_buf *levels, shb_buf *counters, shb_buf *state) {
+                                int self_index, shb_buf *visited, shb_buf *levels, shb_buf *counters, shb_buf *state,
+                                shb_buf *const *peer_counters, uint64_t barrier_target) {
   SHB_REQUIRE(c && A && frontier && next && visited && levels && counters && state, "bad arguments");
   SHB_REQUIRE(n_next >= 1 && n_next <= 8 && self_index >= 0 && self_index < n_next, "1..8 destinations, one of them local");
   SHB_TRY(bfs_block_check(A, AT, row_offset, n_total));
@@ -1025,8 +1222,9 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
   const uint64_t bm_bytes = (uint64_t)n_words * 4;
   SHB_REQUIRE(frontier->bytes >= bm_bytes && visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
   SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
-  SHB_REQUIRE(counters->bytes >= (uint64_t)(4 + 2 * (level + 1)) * 8, "counters has no slot for this level");
   SHB_REQUIRE(state->bytes >= sizeof(BfsBlockState), "state too short");
+  BfsComm comm;
+  SHB_TRY(bfs_block_comm(counters, peer_counters, n_next, self_index, level + 1, &comm));
   BfsPeers peers;
   peers.n = n_next;
   peers.self = self_index;
@@ -1039,6 +1237,7 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
   SHB_CUDA(cudaSetDevice(c->device));
   BfsBlockState *st = (BfsBlockState *)state->ptr;
   long long *cnt = (long long *)counters->ptr;
+  long long *acc = comm.n ? cnt + BFS_STAGE_WORD : cnt + BFS_SLOT(level + 1);
   const int32_t *dg = deg ? (const int32_t *)deg->ptr : nullptr;
   const uint32_t *cur = (const uint32_t *)frontier->ptr;
   const int64_t n_local = A->n_rows, word_lo = row_offset >> 5, word_hi = (row_offset + n_local + 31) >> 5;
@@ -1050,35 +1249,53 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
       const unsigned grid = grid_for((word_hi - word_lo) * 32, 256, 148 * 8);
       if (AT->val)
         bfs_block_push_kernel<true><<<grid, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val, dg, cur,
-                                                                 (const uint32_t *)visited->ptr, peers, cnt, level, word_lo,
-                                                                 word_hi, row_offset, n_local);
+                                                                 (const uint32_t *)visited->ptr, peers, acc, word_lo, word_hi,
+                                                                 row_offset, n_local);
       else
         bfs_block_push_kernel<false><<<grid, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, dg, cur,
-                                                                  (const uint32_t *)visited->ptr, peers, cnt, level, word_lo,
-                                                                  word_hi, row_offset, n_local);
+                                                                  (const uint32_t *)visited->ptr, peers, acc, word_lo, word_hi,
+                                                                  row_offset, n_local);
+      if (AT->val)
+        bfs_block_push_big_kernel<true><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val, dg,
+                                                                        (const uint32_t *)visited->ptr, peers, acc);
+      else
+        bfs_block_push_big_kernel<false><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, dg,
+                                                                         (const uint32_t *)visited->ptr, peers, acc);
     }
     const unsigned grid = grid_for(n_local, 256, 148 * 32);
     if (A->val)
       bfs_block_pull_kernel<true><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, (const int32_t *)A->val, dg, cur, peers,
-                                                               (int32_t *)levels->ptr, cnt, level, n_local, row_offset);
+                                                               (int32_t *)levels->ptr, acc, level, n_local, row_offset);
     else
       bfs_block_pull_kernel<false><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, nullptr, dg, cur, peers,
-                                                                (int32_t *)levels->ptr, cnt, level, n_local, row_offset);
+                                                                (int32_t *)levels->ptr, acc, level, n_local, row_offset);
   }
   bfs_block_clear_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(st, (uint32_t *)frontier->ptr, n_words);
+  if (comm.n)
+    bfs_block_publish_kernel<<<1, 32, 0, c->stream>>>(st, comm, cnt + BFS_STAGE_WORD, BFS_SLOT(level + 1), BFS_FLAG_WORD,
+                                                      self_index, (unsigned long long)barrier_target);
   SHB_CUDA(cudaGetLastError());
   return SHB_OK;
 }
 
-SHB_API int shb_bfs_block_finish(shb_ctx *c, const shb_csr *A, const shb_buf *levels, shb_buf *counters) {
-  SHB_REQUIRE(c && A && levels && counters, "bad arguments");
+// per-rank reached / edge counts from the levels; SHB_ERR_CUDA if a peer barrier timed out during the traversal
+SHB_API int shb_bfs_block_finish(shb_ctx *c, const shb_csr *A, const shb_buf *levels, shb_buf *counters, const shb_buf *state) {
+  SHB_REQUIRE(c && A && levels && counters && state, "bad arguments");
   SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4 && counters->bytes >= 16, "buffers too short");
+  SHB_REQUIRE(state->bytes >= sizeof(BfsBlockState), "state too short");
   SHB_CUDA(cudaSetDevice(c->device));
   SHB_CUDA(cudaMemsetAsync(counters->ptr, 0, 16, c->stream));
   if (A->n_rows > 0)
     bfs_block_stats_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>((const int32_t *)levels->ptr, A->row_ptr, A->n_rows,
                                                                        (long long *)counters->ptr);
   SHB_CUDA(cudaGetLastError());
+  BfsBlockState h;
+  SHB_CUDA(cudaMemcpyAsync(&h, state->ptr, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+  SHB_CUDA(cudaStreamSynchronize(c->stream));
+  if (h.pad) {
+    shb_set_error("a peer barrier of the partitioned BFS timed out (a rank stopped taking part)");
+    return SHB_ERR_CUDA;
+  }
   return SHB_OK;
 }
 
@@ -1118,7 +1335,7 @@ SHB_API int shb_pagerank(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg
 SHB_API int shb_ipc_export(shb_buf *b, void *handle) {
   SHB_REQUIRE(b && handle, "bad arguments");
   static_assert(sizeof(cudaIpcMemHandle_t) == SHB_IPC_HANDLE_BYTES, "ipc handle size");
-  SHB_CUDA(cudaSetDevice(b->ctx->device));
+  SHB_CUDA(cudaSetDevice(b->device));
   cudaIpcMemHandle_t h;
   SHB_CUDA(cudaIpcGetMemHandle(&h, b->ptr));
   memcpy(handle, &h, sizeof h);
@@ -1134,6 +1351,7 @@ SHB_API int shb_ipc_open(shb_ctx *c, const void *handle, uint64_t bytes, shb_buf
   SHB_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
   shb_buf *b = new shb_buf();
   b->ctx = c;
+  b->device = c->device;
   b->ptr = ptr;
   b->bytes = bytes;
   b->owned = false;

@@ -55,7 +55,8 @@ struct shb_ctx {
 static const int SHB_FLAG_SLOTS = 1024;
 
 struct shb_buf {
-  shb_ctx *ctx = nullptr;
+  shb_ctx *ctx = nullptr;  // creator; may be destroyed before the buffer is (destroy paths use `device` only)
+  int device = 0;
   void *ptr = nullptr;
   uint64_t bytes = 0;
   bool owned = true;
@@ -69,7 +70,8 @@ struct shb_pb;  // blocked copy of the operator (pb.cuh)
 void shb_pb_free(shb_pb *pb);
 
 struct shb_csr {
-  shb_ctx *ctx = nullptr;
+  shb_ctx *ctx = nullptr;  // creator; may be destroyed before the operator is (destroy uses `device` only)
+  int device = 0;
   int64_t n_rows = 0, n_cols = 0, nnz = 0;
   int32_t *row_ptr = nullptr;  // n_rows + 1 (+ padding)
   int32_t *col = nullptr;      // nnz rounded up to a tile multiple, pad = -1

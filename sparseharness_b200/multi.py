@@ -294,15 +294,21 @@ def run_bfs(backend: BfsBackend, max_levels: int = 1 << 20, check_every: int = 4
     return (level if done else level + 1), reached, level
 
 
+_BFS_SLOT0 = 6  # int64 word of counter slot 0 (include/shb.h: slot F = words 6+2F, 7+2F)
+
+
 class GpuBfsPartition(BfsBackend):
     """The CUDA backend: this rank's row block.  AT_local (rows = out-edges of the owned vertices) enables push
-    levels; deg (full-length int32 push degrees) steers the direction heuristic."""
+    levels; deg (full-length int32 push degrees) steers the direction heuristic.  exchange="peer": the per-level
+    counts are added into every rank's counters by a publish kernel over CUDA-IPC peer pointers, which also is the
+    barrier -- no collective library inside the traversal; exchange="nccl": a 16-byte all-reduce per level."""
 
     def __init__(self, ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, max_levels=4096,
-                 dist=None, torch=None):
+                 exchange="peer", dist=None, torch=None):
         self.ctx, self.A, self.AT, self.deg = ctx, A_local, AT_local, deg
         self.bounds = np.asarray(bounds, dtype=np.int64)
         self.rank, self.world, self.root, self.dist, self.torch = rank, world, int(root), dist, torch
+        self.exchange = exchange if world > 1 else "none"
         self.n, self.nnz_total = int(self.bounds[-1]), int(nnz_total)
         self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
         self.n_words = max((self.n + 31) // 32, 1)
@@ -310,52 +316,71 @@ class GpuBfsPartition(BfsBackend):
         self.bm = [ctx.empty(self.n_words * 4), ctx.empty(self.n_words * 4)]
         self.visited = ctx.empty(self.n_words * 4)
         self.levels = ctx.empty(max(self.hi - self.lo, 1) * 4)
-        self.n_counter_words = 2 * max_levels + 8
+        self.n_counter_words = _BFS_SLOT0 + 2 * (max_levels + 2)
         self.counters = ctx.empty(self.n_counter_words * 8)
+        self.counters.zero()  # the arrival word starts at 0 and is never reset afterwards
         self.state = ctx.empty(ctx.bfs_block_state_bytes())
-        self.launches = 0
+        self.launches, self.seq = 0, 0
         self.peers = [[self.bm[0]], [self.bm[1]]]
+        self.peer_counters = None
         self.self_index = 0
         self._t_counts = None
         if world > 1:
+            ctx.synchronize()
             self._t_counts = _tensor_view(torch, self.counters, self.n_counter_words, ctx.device, "<i8")
             handles = [None] * world
-            dist.all_gather_object(handles, (self.bm[0].ipc_handle(), self.bm[1].ipc_handle()))
+            dist.all_gather_object(handles, (self.bm[0].ipc_handle(), self.bm[1].ipc_handle(), self.counters.ipc_handle()))
             self.peers = [[], []]
             for r in range(world):
                 for k in (0, 1):
                     self.peers[k].append(self.bm[k] if r == rank else ctx.ipc_open(handles[r][k], self.n_words * 4))
+            if self.exchange == "peer":
+                self.peer_counters = [self.counters if r == rank else ctx.ipc_open(handles[r][2], self.n_counter_words * 8)
+                                      for r in range(world)]
             self.self_index = rank
         self.reset()
 
-    def _reduce_slot(self, slot):
+    def _quiesce(self):
+        self.ctx.synchronize()
         if self.world > 1:
-            self.dist.all_reduce(self._t_counts[2 + 2 * slot:4 + 2 * slot], op=self.dist.ReduceOp.SUM)
+            self.dist.barrier()
 
     def reset(self):
-        if self.world > 1:
-            self.dist.barrier()  # no peer may still be storing into the bitmaps init is about to zero
+        self._quiesce()  # no peer may still be storing into what init is about to zero
+        peer = self.exchange == "peer"
         self.ctx.bfs_block_init(self.A, self.AT, self.lo, self.n, self.nnz_total, self.root, self.deg, self.levels,
-                                self.bm[0], self.bm[1], self.visited, self.counters, self.state)
-        self._reduce_slot(0)
+                                self.bm[0], self.bm[1], self.visited, self.counters, self.state, staged=peer)
+        if peer:
+            self._quiesce()  # every rank has zeroed its slots before anyone adds to them
+            self.seq += 1
+            self.ctx.bfs_block_publish(0, self.counters, self.state, self.peer_counters, self.self_index,
+                                       self.world * self.seq)
+        elif self.exchange == "nccl":
+            self.dist.all_reduce(self._t_counts[_BFS_SLOT0:_BFS_SLOT0 + 2], op=self.dist.ReduceOp.SUM)
         self.launches = 0
 
     def step(self, level):
+        target = 0
+        if self.exchange == "peer":
+            self.seq += 1
+            target = self.world * self.seq
         self.ctx.bfs_block_level(self.A, self.AT, self.lo, self.n, level, self.deg, self.bm[level & 1],
                                  self.peers[(level + 1) & 1], self.self_index, self.visited, self.levels, self.counters,
-                                 self.state)
+                                 self.state, self.peer_counters, target)
         self.launches += 1
 
     def reduce_count(self, level):
-        self._reduce_slot(level + 1)
+        if self.exchange == "nccl":
+            w = _BFS_SLOT0 + 2 * (level + 1)
+            self.dist.all_reduce(self._t_counts[w:w + 2], op=self.dist.ReduceOp.SUM)
 
     def read_counts(self, lo, hi):
-        w = self.counters.download(np.int64, 2 * (hi - lo), offset=8 * (2 + 2 * (lo + 1)))
+        w = self.counters.download(np.int64, 2 * (hi - lo), offset=8 * (_BFS_SLOT0 + 2 * (lo + 1)))
         return w[0::2]
 
     def local_stats(self):
-        """(reached, sum of in-degrees of reached) of the owned slice."""
-        self.ctx.bfs_block_finish(self.A, self.levels, self.counters)
+        """(reached, sum of in-degrees of reached) of the owned slice; raises if a peer barrier timed out."""
+        self.ctx.bfs_block_finish(self.A, self.levels, self.counters, self.state)
         w = self.counters.download(np.int64, 2)
         return int(w[0]), int(w[1])
 
@@ -363,11 +388,15 @@ class GpuBfsPartition(BfsBackend):
         return self.levels.download(np.int32, self.hi - self.lo)
 
     def close(self):
+        self._quiesce()
         if self.world > 1:
             for k in (0, 1):
                 for r, b in enumerate(self.peers[k]):
                     if r != self.rank:
                         b.free()
+            for r, b in enumerate(self.peer_counters or []):
+                if r != self.rank:
+                    b.free()
         for b in self.bm + [self.visited, self.levels, self.counters, self.state]:
             b.free()
 
@@ -385,11 +414,12 @@ def _tensor_view(torch, buf, count, device, typestr="<i4"):
 
 class EmulatedBfsPartition(BfsBackend):
     """All P row blocks on ONE device, each with its OWN bitmaps, state and counters, every block storing into every
-    block's next bitmap: the multi-GPU path's kernels and protocol on one GPU.  The all-reduce of a counter slot is
-    emulated through the host (download, sum, upload)."""
+    block's next bitmap: the multi-GPU path's kernels and protocol on one GPU.  publish=True runs the peer publish
+    kernel (system-scope adds into every block's slot, no wait: the blocks share a stream); publish=False emulates
+    the NCCL all-reduce of a slot through the host (download, sum, upload)."""
 
-    def __init__(self, ctx, blocks, bounds, root, nnz_total, *, at_blocks=None, deg=None, max_levels=4096):
-        self.ctx, self.blocks, self.at_blocks, self.deg = ctx, blocks, at_blocks, deg
+    def __init__(self, ctx, blocks, bounds, root, nnz_total, *, at_blocks=None, deg=None, max_levels=4096, publish=True):
+        self.ctx, self.blocks, self.at_blocks, self.deg, self.publish = ctx, blocks, at_blocks, deg, publish
         self.bounds, self.root, self.nnz_total = np.asarray(bounds, dtype=np.int64), int(root), int(nnz_total)
         self.n = int(self.bounds[-1])
         self.P = len(blocks)
@@ -397,12 +427,14 @@ class EmulatedBfsPartition(BfsBackend):
         self.bm = [[ctx.empty(n_words * 4), ctx.empty(n_words * 4)] for _ in range(self.P)]
         self.visited = [ctx.empty(n_words * 4) for _ in range(self.P)]
         self.levels = [ctx.empty(max(int(self.bounds[k + 1] - self.bounds[k]), 1) * 4) for k in range(self.P)]
-        self.counters = [ctx.empty((2 * max_levels + 8) * 8) for _ in range(self.P)]
+        self.counters = [ctx.empty((_BFS_SLOT0 + 2 * (max_levels + 2)) * 8) for _ in range(self.P)]
+        for c in self.counters:
+            c.zero()
         self.state = [ctx.empty(ctx.bfs_block_state_bytes()) for _ in range(self.P)]
         self.reset()
 
     def _reduce_slot(self, slot):
-        off = 8 * (2 + 2 * slot)
+        off = 8 * (_BFS_SLOT0 + 2 * slot)
         tot = sum(c.download(np.int64, 2, offset=off) for c in self.counters)
         for c in self.counters:
             c.upload(tot, offset=off)
@@ -411,8 +443,12 @@ class EmulatedBfsPartition(BfsBackend):
         for k, A in enumerate(self.blocks):
             self.ctx.bfs_block_init(A, self.at_blocks[k] if self.at_blocks else None, int(self.bounds[k]), self.n,
                                     self.nnz_total, self.root, self.deg, self.levels[k], self.bm[k][0], self.bm[k][1],
-                                    self.visited[k], self.counters[k], self.state[k])
-        self._reduce_slot(0)
+                                    self.visited[k], self.counters[k], self.state[k], staged=self.publish)
+        if self.publish:
+            for k in range(self.P):
+                self.ctx.bfs_block_publish(0, self.counters[k], self.state[k], self.counters, k, 0)
+        else:
+            self._reduce_slot(0)
         self.launches = 0
 
     def step(self, level):
@@ -420,19 +456,20 @@ class EmulatedBfsPartition(BfsBackend):
         for k, A in enumerate(self.blocks):
             self.ctx.bfs_block_level(A, self.at_blocks[k] if self.at_blocks else None, int(self.bounds[k]), self.n, level,
                                      self.deg, self.bm[k][level & 1], nxt, k, self.visited[k], self.levels[k],
-                                     self.counters[k], self.state[k])
+                                     self.counters[k], self.state[k], self.counters if self.publish else None, 0)
             self.launches += 1
 
     def reduce_count(self, level):
-        self._reduce_slot(level + 1)
+        if not self.publish:
+            self._reduce_slot(level + 1)
 
     def read_counts(self, lo, hi):
-        return self.counters[0].download(np.int64, 2 * (hi - lo), offset=8 * (2 + 2 * (lo + 1)))[0::2]
+        return self.counters[0].download(np.int64, 2 * (hi - lo), offset=8 * (_BFS_SLOT0 + 2 * (lo + 1)))[0::2]
 
     def stats(self):
         r = e = 0
         for k, A in enumerate(self.blocks):
-            self.ctx.bfs_block_finish(A, self.levels[k], self.counters[k])
+            self.ctx.bfs_block_finish(A, self.levels[k], self.counters[k], self.state[k])
             w = self.counters[k].download(np.int64, 2)
             r, e = r + int(w[0]), e + int(w[1])
         return r, e
@@ -442,13 +479,13 @@ class EmulatedBfsPartition(BfsBackend):
                                for k in range(self.P)])
 
 
-def partitioned_bfs(ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, check_every=4,
-                    max_levels=4096, dist=None, torch=None, repeat=1):
+def partitioned_bfs(ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, check_every=8,
+                    max_levels=4096, exchange="peer", dist=None, torch=None, repeat=1):
     """Direction-optimising BFS levels on a row-partitioned operator.  Returns (backend, stats) with stats =
     dict(levels, reached, edges_traversed [sum of in-degrees of reached vertices, all ranks], ms [device time of
     this rank; max over ranks is the caller's job], launches)."""
     be = GpuBfsPartition(ctx, A_local, bounds, rank, world, root, nnz_total, AT_local=AT_local, deg=deg,
-                         max_levels=max_levels, dist=dist, torch=torch)
+                         max_levels=max_levels, exchange=exchange, dist=dist, torch=torch)
     best = None
     for i in range(max(1, repeat)):
         if i:

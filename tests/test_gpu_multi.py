@@ -83,8 +83,9 @@ def test_two_gpu_pagerank_matches_oracle(mode):
     assert abs(out["iterations"] - out["oracle_iterations"]) <= 1
 
 
-@pytest.mark.parametrize("parts,check_every,push", [(1, 4, True), (2, 1, True), (5, 3, True), (3, 2, False)])
-def test_emulated_row_partition_bfs_matches_queue_bfs(ctx, orc, parts, check_every, push):
+@pytest.mark.parametrize("parts,check_every,push,publish", [(1, 4, True, True), (2, 1, True, True), (5, 3, True, False),
+                                                            (3, 2, False, True), (8, 8, True, True)])
+def test_emulated_row_partition_bfs_matches_queue_bfs(ctx, orc, parts, check_every, push, publish):
     """shb_bfs_block_level on P row blocks of one device (own bitmaps / state per block, stores into every block's
     next bitmap): levels, level count, reached and the TEPS numerator equal the CPU queue BFS, with push levels
     (direction-optimising) and pull-only.  Hub rows >= 128 entries take the warp-cooperative pull path."""
@@ -98,7 +99,8 @@ def test_emulated_row_partition_bfs_matches_queue_bfs(ctx, orc, parts, check_eve
     assert np.array_equal(deg.download(np.int32, n), np.diff(rp).astype(np.int32))
     bounds = multi.word_aligned_bounds(A.balance_rows(parts))
     blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(parts)]
-    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, root, len(col), at_blocks=blocks if push else None, deg=deg)
+    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, root, len(col), at_blocks=blocks if push else None, deg=deg,
+                                    publish=publish)
     n_levels, _, launches = multi.run_bfs(be, 1 << 20, check_every)
     want, nlev, edges = orc.bfs_levels(rp, col, None, root)
     assert np.array_equal(be.result(), want)
@@ -150,12 +152,30 @@ def test_bfs_block_rejects_unaligned_blocks(ctx, orc):
     assert e.value.status == 1
 
 
-def test_two_gpu_bfs_matches_oracle():
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])
+def test_two_gpu_bfs_matches_oracle(exchange):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     port = 29900 + os.getpid() % 300
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tools", "multi_bfs.py"), "--scale", "16", "--check"]
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tools", "multi_bfs.py"), "--scale", "16", "--check", "--exchange", exchange]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+
+
+def test_handles_may_outlive_their_context(ctx, orc):
+    """Buffers / operators freed after their context was destroyed (garbage-collected callers free in any order)
+    must not touch the dead context nor leave a CUDA error behind for the next call."""
+    import sparseharness_b200 as shb
+    c2 = shb.Context(0)
+    rp, col, val = orc.gen_uniform(256, 256, 4, val_mode=1)
+    A2, b2 = c2.csr(256, 256, rp, col, val), c2.empty(4096)
+    c2.close()
+    b2.free()
+    A2.free()
+    A = ctx.csr(256, 256, rp, col, val)  # the next call that checks cudaGetLastError
+    x, out = ctx.array(np.ones(256, np.float32)), ctx.empty(1024)
+    ctx.spmv(A, shb.PLUS_TIMES, x, None, 1.0, 0.0, out)
+    want = orc.spmv(orc.PLUS_TIMES, rp, col, val, np.ones(256, np.float32), np.zeros(256, np.float32), 1.0, 0.0)
+    assert np.array_equal(out.download(np.float32, 256), want)

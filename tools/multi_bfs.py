@@ -21,7 +21,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-def run(scale, edgefactor, check, seed=0x5EED0024, check_every=4, repeat=3, ctx=None):
+def run(scale, edgefactor, check, seed=0x5EED0024, check_every=8, repeat=3, ctx=None, exchange="peer", trace=False):
     import torch
     import torch.distributed as dist
 
@@ -52,17 +52,31 @@ def run(scale, edgefactor, check, seed=0x5EED0024, check_every=4, repeat=3, ctx=
     else:
         Al = A
     be, st = multi.partitioned_bfs(ctx, Al, bounds, rank, world, root, nnz, AT_local=Al, deg=deg, check_every=check_every,
-                                   dist=dist, torch=torch, repeat=repeat)
+                                   exchange=exchange, dist=dist, torch=torch, repeat=repeat)
     t = torch.tensor([st["ms"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     undirected = st["edges_traversed"] / 2
     out = {"graph": f"RMAT scale {scale} edgefactor {edgefactor} symmetrised+deduplicated", "n": n, "nnz": nnz,
-           "n_gpus": world, "schedule": "row-partitioned, direction-optimising; frontier bitmap words / bits stored into every peer by the push and pull kernels",
+           "n_gpus": world, "exchange": exchange if world > 1 else "none", "schedule": "row-partitioned, direction-optimising; frontier bitmap words / bits stored into every peer by the push and pull kernels",
            "levels": st["levels"], "reached": st["reached"], "ms": ms, "gteps": undirected / (ms * 1e6),
            "teps_edges": undirected, "local_rows": hi - lo, "local_nnz": Al.info.nnz,
            "frontier_bytes_per_gpu_per_level": (n + 7) // 8}
+    if trace:  # one more traversal, synchronised after every level: per-level device time and direction
+        import time
+        be.reset()
+        per = []
+        for lv in range(st["levels"]):
+            ctx.synchronize()
+            t0 = time.perf_counter()
+            be.step(lv)
+            be.reduce_count(lv)
+            ctx.synchronize()
+            mode = int(be.state.download(np.uint32, 1)[0])
+            per.append({"level": lv, "us": round((time.perf_counter() - t0) * 1e6, 1), "mode": "pull" if mode else "push",
+                        "found": int(be.read_counts(lv, lv + 1)[0])})
+        out["trace"] = per
     if check:
         from oracle import oracle as orc  # checker only
         rp, col = orc.gen_rmat(scale, edgefactor, seed=seed, symmetrise=True)
@@ -85,9 +99,11 @@ def main():
     ap.add_argument("--scale", type=int, default=20)
     ap.add_argument("--edgefactor", type=int, default=16)
     ap.add_argument("--check", action="store_true")
-    ap.add_argument("--check-every", type=int, default=4)
+    ap.add_argument("--check-every", type=int, default=8)
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"])
+    ap.add_argument("--trace", action="store_true")
     a = ap.parse_args()
-    out, rank, world = run(a.scale, a.edgefactor, a.check, check_every=a.check_every)
+    out, rank, world = run(a.scale, a.edgefactor, a.check, check_every=a.check_every, exchange=a.exchange, trace=a.trace)
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:

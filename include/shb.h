@@ -257,6 +257,28 @@ int shb_bfs_block_level(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64
                         shb_buf *const *peer_counters, uint64_t barrier_target);
 int shb_bfs_block_finish(shb_ctx *ctx, const shb_csr *A, const shb_buf *levels, shb_buf *counters, const shb_buf *state);
 
+/* Row-partitioned SSSP (new capability; the reference's sssp app is single-device, app/sssp.cpp:97-155):
+ * block-asynchronous near-far.  This rank owns the vertices [row_offset, row_offset + AT.n_rows): AT holds their
+ * OUT-edges (rows of A^T, GLOBAL target ids; for a symmetric graph the block's rows of A), dist is a full-length
+ * array on every rank whose owned slice is authoritative, prev (n_local) the distance each owned vertex was last
+ * expanded with, work an opaque scratch of shb_sssp_block_work_bytes(n_local) bytes.
+ *   init    dist = FLT_MAX, dist[source] = 0 on every rank, prev = FLT_MAX, bucket width from the block's weights.
+ *   round   seed pass (owned v with dist[v] < prev[v]; their number is ADDED to int64 word seed_count_word of
+ *           seed_count) + the near-far solve of the block: improved owned targets are queued, improved targets of
+ *           other ranks are sent to their owner as red.min on peer_dist[owner] (CUDA-IPC mappings, NVLink).
+ *           bounds[0..n_ranks] = vertex ownership.  The caller separates rounds with a barrier (e.g. the all-reduce
+ *           of the seed count) and stops after a round whose seed count is 0 on every rank.
+ *   finish  status of the last solve + (reached, sum of A_rows' row lengths over reached) into stats_out (2 x int64).
+ * Same least fixed point as shb_sssp and the reference's dense sweeps, bit for bit (monotone float adds). */
+int shb_sssp_block_work_bytes(int64_t n_local, uint64_t *bytes);
+int shb_sssp_block_init(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, int64_t n_total, int64_t source,
+                        shb_buf *dist, shb_buf *prev, shb_buf *work);
+int shb_sssp_block_round(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, int64_t n_total, shb_buf *dist,
+                         shb_buf *const *peer_dist, int n_ranks, int self_index, const int64_t *bounds, shb_buf *prev,
+                         shb_buf *work, shb_buf *seed_count, uint64_t seed_count_word, uint32_t max_phases);
+int shb_sssp_block_finish(shb_ctx *ctx, const shb_csr *A_rows, int64_t row_offset, const shb_buf *dist,
+                          const shb_buf *work, shb_buf *stats_out);
+
 #ifdef __cplusplus
 }
 #endif

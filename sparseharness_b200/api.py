@@ -293,6 +293,25 @@ class Context:
     def bfs_block_finish(self, A: Csr, levels: Buffer, counters: Buffer, state: Buffer):
         _ck(lib.shb_bfs_block_finish(self.h, A.h, levels.h, counters.h, state.h))
 
+    def sssp_block_work_bytes(self, n_local: int) -> int:
+        b = C.c_uint64(0)
+        _ck(lib.shb_sssp_block_work_bytes(n_local, C.byref(b)))
+        return b.value
+
+    def sssp_block_init(self, AT: Csr, row_offset, n_total, source, dist: Buffer, prev: Buffer, work: Buffer):
+        _ck(lib.shb_sssp_block_init(self.h, AT.h, row_offset, n_total, source, dist.h, prev.h, work.h))
+
+    def sssp_block_round(self, AT: Csr, row_offset, n_total, dist: Buffer, peer_dist: list[Buffer], self_index: int,
+                         bounds: np.ndarray, prev: Buffer, work: Buffer, seed_count: Buffer, seed_count_word: int,
+                         max_phases: int = 0):
+        arr = (C.c_void_p * len(peer_dist))(*[d.h for d in peer_dist])
+        b = np.ascontiguousarray(bounds, dtype=np.int64)
+        _ck(lib.shb_sssp_block_round(self.h, AT.h, row_offset, n_total, dist.h, arr, len(peer_dist), self_index, _ptr(b),
+                                     prev.h, work.h, seed_count.h, seed_count_word, max_phases))
+
+    def sssp_block_finish(self, A_rows: Csr, row_offset, dist: Buffer, work: Buffer, stats_out: Buffer):
+        _ck(lib.shb_sssp_block_finish(self.h, A_rows.h, row_offset, dist.h, work.h, stats_out.h))
+
     def iterate(self, A: Csr, semiring, x: Buffer, y0: Buffer | None, alpha, beta, work: Buffer, delta=1e-4, term=None,
                 y_rebind=True, max_iters=1000, check_every=16, per_iter=False, cfg: LaunchCfg | None = None):
         """Returns (result_buffer, n_iters, total_ns, per_iter_ns|None, converged)."""

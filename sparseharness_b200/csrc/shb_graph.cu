@@ -1300,6 +1300,441 @@ SHB_API int shb_bfs_block_finish(shb_ctx *c, const shb_csr *A, const shb_buf *le
 }
 
 // =================================================================================================
+// Row-partitioned SSSP (multi-GPU): block-asynchronous near-far.  Rank k owns the vertices
+// [lo, lo + n_local): their out-edges (rows lo.. of A^T, GLOBAL target ids), the authoritative slice of `dist`
+// (a full-length array on every rank; the entries of other ranks' vertices are only a filter cache) and
+// `prev[v - lo]` = the distance v was last expanded with.  One round on every rank:
+//   seed    every owned v with dist[v] < prev[v] -- lowered by a peer since its last expansion, or the source --
+//           enters the far pile;
+//   solve   the near-far kernel of shb_sssp relaxes to exhaustion INSIDE the block: an improved owned target is
+//           queued as usual; an improved target of another rank is sent to its owner as one fire-and-forget
+//           red.min on the owner's dist over the CUDA-IPC peer mapping (NVLink) and not expanded here.
+// The caller puts a barrier between solve and the next seed (all peer reds have landed) and stops when a seed
+// pass finds nothing on any rank.  fl(a + w) is monotone, so this schedule reaches the same least fixed point
+// as shb_sssp and the reference's dense sweeps, bit for bit.  Only vertices on a block boundary ever cross
+// NVLink; no collective moves distances.
+// =================================================================================================
+struct SsspBlockArgs {
+  SsspState *st;
+  const int32_t *at_row_ptr;  // n_local + 1, row r = out-edges of vertex lo + r
+  const int32_t *at_col;
+  const float *at_val;
+  uint32_t *dist;             // full length, local
+  uint32_t *peer_dist[8];     // every rank's dist (peer_dist[self] == dist)
+  long long bounds[9];        // vertex ownership: rank i owns [bounds[i], bounds[i+1])
+  int n_ranks, self;
+  uint32_t *prev;             // n_local
+  uint32_t *pile_bits;        // n_local bits: entered the far pile in this round
+  uint2 *near_q[2];
+  int32_t *far_q[2];
+  uint32_t lo, n_local, n_total;
+  uint32_t near_cap;
+  uint32_t max_phases;
+};
+
+__device__ __forceinline__ int sssp_owner(const SsspBlockArgs &a, uint32_t v) {
+  int o = 0;
+  while (o + 1 < a.n_ranks && (long long)v >= a.bounds[o + 1]) ++o;
+  return o;
+}
+
+// dist[v] (local copy) just dropped from `old` to cb
+__device__ __forceinline__ void sssp_block_improved(const SsspBlockArgs &a, SsspShared &sh, uint32_t v, uint32_t cb, uint32_t t_hi,
+                                                    int nxt, uint2 *near_next, uint32_t *near_next_size, int32_t *far_cur,
+                                                    uint32_t *far_cur_size, uint32_t &fmin) {
+  const uint32_t r = v - a.lo;
+  if (r >= a.n_local) {  // another rank's vertex: its owner learns the candidate, nobody expands it here
+    uint32_t *p = a.peer_dist[sssp_owner(a, v)] + v;
+    asm volatile("red.relaxed.sys.global.min.u32 [%0], %1;" ::"l"(p), "r"(cb) : "memory");
+    return;
+  }
+  if (cb < t_hi) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.at_row_ptr + r));
+    const uint32_t slot = atomicAdd(&sh.lcount[nxt], 1u);
+    if (slot < SSSP_CAP) {
+      sh.lst[nxt][slot] = make_uint2(v, cb);
+    } else {
+      const uint32_t g = atomicAdd(near_next_size, 1u);
+      if (g < a.near_cap) near_next[g] = make_uint2(v, cb);
+      else a.st->overflow = 1u;
+    }
+  } else {
+    fmin = min(fmin, cb);
+    const uint32_t bit = 1u << (r & 31);
+    if (!(atomicOr(&a.pile_bits[r >> 5], bit) & bit)) {  // first time in this round's pile
+      const uint32_t slot = atomicAdd(&sh.fcount, 1u);
+      if (slot < SSSP_FSTAGE) sh.fstage[slot] = (int32_t)v;
+      else far_cur[atomicAdd(far_cur_size, 1u)] = (int32_t)v;
+    }
+  }
+}
+
+// round set-up: reset the work lists (delta is kept), then every owned vertex whose distance dropped below the
+// value it was last expanded with goes to far pile 0
+__global__ void sssp_block_reset_kernel(SsspState *st) {
+  for (int i = 0; i < 3; ++i) {
+    st->near_size[i] = 0;
+    st->far_size[i] = 0;
+    st->far_min[i] = 0xffffffffu;
+  }
+  st->bar_count = st->bar_gen = 0;
+  st->phases = st->buckets = st->done = st->overflow = 0;
+}
+
+__global__ void sssp_block_seed_kernel(SsspState *st, const uint32_t *dist, const uint32_t *prev, uint32_t *pile_bits,
+                                       int32_t *far0, uint32_t lo, uint32_t n_local, long long *count_out) {
+  const int lane = threadIdx.x & 31;
+  uint32_t fmin = 0xffffffffu, cnt = 0;
+  const uint32_t n_padded = (n_local + 31u) & ~31u;
+  for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += gridDim.x * blockDim.x) {
+    bool seed = false;
+    uint32_t d = 0;
+    if (r < n_local) {
+      d = dist[lo + r];
+      seed = d < prev[r];
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, seed);
+    if (lane == 0) pile_bits[r >> 5] = m;  // the seeds are in the pile; everything else starts outside
+    if (m) {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(&st->far_size[0], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (seed) {
+        far0[base + __popc(m & ((1u << lane) - 1u))] = (int32_t)(lo + r);
+        fmin = min(fmin, d);
+        ++cnt;
+      }
+    }
+  }
+  for (int off = 16; off > 0; off >>= 1) {
+    fmin = min(fmin, __shfl_xor_sync(0xffffffffu, fmin, off));
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+  }
+  if (lane == 0 && cnt) {
+    atomicMin(&st->far_min[0], fmin);
+    atomicAdd(reinterpret_cast<unsigned long long *>(count_out), (unsigned long long)cnt);
+  }
+}
+
+template <bool HAS_VAL>
+__global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __grid_constant__ SsspBlockArgs a) {
+  __shared__ SsspShared sh;
+  SsspState *st = a.st;
+  const uint32_t n_blocks = gridDim.x;
+  const int lane = threadIdx.x & 31;
+  const uint32_t n_threads = gridDim.x * blockDim.x;
+  const float delta = *(volatile float *)&st->delta;
+  uint32_t phase = 0, fgen = 0, buckets = 0;
+  uint32_t t_hi = 0;  // nothing has been through the near list yet: the first phase splits the seeded pile
+  bool finished = false;
+  if (threadIdx.x == 0) {
+    sh.lcount[0] = sh.lcount[1] = 0;
+    sh.fcount = 0;
+    sh.fmin = 0xffffffffu;
+  }
+  __syncthreads();
+  while (phase < a.max_phases) {
+    const uint32_t ns = *(volatile uint32_t *)&st->near_size[phase % 3];
+    const uint2 *near_cur = a.near_q[phase & 1];
+    uint2 *near_next = a.near_q[(phase + 1) & 1];
+    uint32_t *near_next_size = &st->near_size[(phase + 1) % 3];
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->near_size[(phase + 2) % 3] = 0;
+    uint32_t fmin = 0xffffffffu;
+    if (ns > 0) {
+      int32_t *far_cur = a.far_q[fgen & 1];
+      uint32_t *far_cur_size = &st->far_size[fgen % 3];
+      const uint32_t ch = max(32u, min((uint32_t)SSSP_CAP, (ns + n_blocks - 1) / n_blocks));
+      for (uint32_t base = blockIdx.x * ch; base < ns; base += n_blocks * ch) {
+        const uint32_t cnt = min(ch, ns - base);
+        for (uint32_t j = threadIdx.x; j < cnt; j += blockDim.x) sh.lst[0][j] = near_cur[base + j];
+        if (threadIdx.x == 0) sh.lcount[0] = cnt;
+        int cur = 0;
+        while (true) {
+          __syncthreads();
+          const uint32_t cn = sh.lcount[cur];
+          if (cn == 0) break;
+          const int nxt = cur ^ 1;
+          for (uint32_t i = threadIdx.x; i < ((cn + 31u) & ~31u); i += blockDim.x) {
+            int s = 0, e = 0;
+            uint32_t du_bits = 0;
+            if (i < cn) {
+              const uint2 ent = sh.lst[cur][i];
+              const uint32_t r = ent.x - a.lo;
+              const uint32_t d_now = __ldcg(a.dist + ent.x);
+              const int s0 = __ldg(a.at_row_ptr + r), e0 = __ldg(a.at_row_ptr + r + 1);
+              if (d_now == ent.y) {  // still the vertex's distance: live entry, expanded with this value
+                s = s0;
+                e = e0;
+                du_bits = ent.y;
+                a.prev[r] = ent.y;
+              }
+            }
+            const float du = __uint_as_float(du_bits);
+            const bool big = (e - s) >= SSSP_BIG_ROW;
+            if (!big) {
+              for (int k = s; k < e; k += 4) {
+                int32_t vv[4];
+                uint32_t cb[4], old[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  vv[j] = (k + j < e) ? __ldg(a.at_col + k + j) : -1;
+                  const float w = (HAS_VAL && k + j < e) ? __ldg(a.at_val + k + j) : 1.0f;
+                  cb[j] = __float_as_uint(MinPlusF32::mult(du, w));
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) old[j] = ((uint32_t)vv[j] < a.n_total) ? atomicMin(a.dist + vv[j], cb[j]) : 0u;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (cb[j] < old[j])
+                    sssp_block_improved(a, sh, (uint32_t)vv[j], cb[j], t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
+              }
+            }
+            uint32_t bigs = __ballot_sync(0xffffffffu, big);
+            while (bigs) {
+              const int src = __ffs(bigs) - 1;
+              bigs &= bigs - 1;
+              const int bs = __shfl_sync(0xffffffffu, s, src), be = __shfl_sync(0xffffffffu, e, src);
+              const float bd = __uint_as_float(__shfl_sync(0xffffffffu, du_bits, src));
+              for (int k = bs + lane; k < be; k += 32) {
+                const int32_t v = __ldg(a.at_col + k);
+                const float w = HAS_VAL ? __ldg(a.at_val + k) : 1.0f;
+                const uint32_t c1 = __float_as_uint(MinPlusF32::mult(bd, w));
+                if ((uint32_t)v < a.n_total && c1 < __ldcg(a.dist + v)) {
+                  const uint32_t o1 = atomicMin(a.dist + v, c1);
+                  if (c1 < o1) sssp_block_improved(a, sh, (uint32_t)v, c1, t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
+                }
+              }
+            }
+          }
+          __syncthreads();
+          if (threadIdx.x == 0) {
+            sh.lcount[cur] = 0;
+            sh.lcount[nxt] = min(sh.lcount[nxt], (uint32_t)SSSP_CAP);
+          }
+          if (sh.fcount >= SSSP_FSTAGE / 2) sssp_flush_far(sh, far_cur, far_cur_size);
+          cur = nxt;
+        }
+      }
+      __syncthreads();
+      sssp_flush_far(sh, far_cur, far_cur_size);
+      for (int off = 16; off > 0; off >>= 1) fmin = min(fmin, __shfl_xor_sync(0xffffffffu, fmin, off));
+      if (lane == 0 && fmin != 0xffffffffu) atomicMin(&sh.fmin, fmin);
+      __syncthreads();
+      if (threadIdx.x == 0 && sh.fmin != 0xffffffffu) {
+        atomicMin(&st->far_min[fgen % 3], sh.fmin);
+        sh.fmin = 0xffffffffu;
+      }
+    } else {
+      const uint32_t fs = *(volatile uint32_t *)&st->far_size[fgen % 3];
+      if (fs == 0) {
+        finished = true;
+        break;
+      }
+      const uint32_t t_old = t_hi;
+      t_hi = __float_as_uint(__fadd_rn(__uint_as_float(*(volatile uint32_t *)&st->far_min[fgen % 3]), delta));
+      ++buckets;
+      const int32_t *far_cur = a.far_q[fgen & 1];
+      int32_t *far_next = a.far_q[(fgen + 1) & 1];
+      uint32_t *far_next_size = &st->far_size[(fgen + 1) % 3];
+      if (blockIdx.x == 0 && threadIdx.x == 0) {
+        st->far_size[(fgen + 2) % 3] = 0;
+        st->far_min[(fgen + 2) % 3] = 0xffffffffu;
+      }
+      for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((fs + 31u) & ~31u); i += n_threads) {
+        int kind = 0;
+        int32_t v = 0;
+        uint32_t d = 0;
+        if (i < fs) {
+          v = far_cur[i];
+          d = __ldcg(a.dist + v);
+          if (d < t_old) {
+            // went through the near list in an earlier bucket -- or a peer lowered it just now, in which case
+            // prev[v] is still above d and the next round's seed pass picks it up
+          } else if (d < t_hi) {
+            kind = 1;
+          } else {
+            kind = 2;
+            fmin = min(fmin, d);
+          }
+        }
+        const uint32_t m1 = __ballot_sync(0xffffffffu, kind == 1), m2 = __ballot_sync(0xffffffffu, kind == 2);
+        uint32_t b1 = 0, b2 = 0;
+        if (lane == 0) {
+          if (m1) b1 = atomicAdd(near_next_size, __popc(m1));
+          if (m2) b2 = atomicAdd(far_next_size, __popc(m2));
+        }
+        b1 = __shfl_sync(0xffffffffu, b1, 0);
+        b2 = __shfl_sync(0xffffffffu, b2, 0);
+        const uint32_t below = (1u << lane) - 1u;
+        if (kind == 1) {
+          const uint32_t g = b1 + __popc(m1 & below);
+          if (g < a.near_cap) near_next[g] = make_uint2((uint32_t)v, d);
+          else st->overflow = 1u;
+        } else if (kind == 2) {
+          far_next[b2 + __popc(m2 & below)] = v;
+        }
+      }
+      for (int off = 16; off > 0; off >>= 1) fmin = min(fmin, __shfl_xor_sync(0xffffffffu, fmin, off));
+      if (lane == 0 && fmin != 0xffffffffu) atomicMin(&st->far_min[(fgen + 1) % 3], fmin);
+      ++fgen;
+    }
+    grid_barrier(st, n_blocks);
+    ++phase;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st->phases = phase;
+    st->buckets = buckets;
+    st->done = (finished && st->overflow == 0) ? 1u : 0u;
+  }
+}
+
+struct SsspBlockLayout {
+  size_t near_off, far_off, pile_off, total;
+  uint64_t near_cap;
+};
+static SsspBlockLayout sssp_block_layout(int64_t n_local) {
+  SsspBlockLayout L;
+  L.near_cap = (uint64_t)n_local * 2 + 4096;
+  L.near_off = (sizeof(SsspState) + 255) / 256 * 256;
+  L.far_off = L.near_off + (size_t)L.near_cap * 2 * sizeof(uint2);
+  L.pile_off = L.far_off + ((size_t)n_local * 2 * sizeof(int32_t) + 255) / 256 * 256;
+  L.total = L.pile_off + ((size_t)(n_local + 31) / 32 * 4 + 255) / 256 * 256;
+  return L;
+}
+
+SHB_API int shb_sssp_block_work_bytes(int64_t n_local, uint64_t *bytes) {
+  SHB_REQUIRE(bytes && n_local >= 0, "bad arguments");
+  *bytes = sssp_block_layout(n_local).total;
+  return SHB_OK;
+}
+
+static int sssp_block_check(const shb_csr *AT, int64_t row_offset, int64_t n_total, const shb_buf *dist, const shb_buf *prev,
+                            const shb_buf *work) {
+  SHB_REQUIRE(AT->n_cols == n_total && n_total < (1ll << 31), "the block's column space must be the whole vertex set");
+  SHB_REQUIRE(row_offset >= 0 && row_offset + AT->n_rows <= n_total, "row block outside the vertex set");
+  SHB_REQUIRE(dist->bytes >= (uint64_t)n_total * 4, "dist shorter than n_total");
+  SHB_REQUIRE(prev->bytes >= (uint64_t)AT->n_rows * 4, "prev shorter than the row block");
+  SHB_REQUIRE(work->bytes >= sssp_block_layout(AT->n_rows).total, "work shorter than shb_sssp_block_work_bytes");
+  return SHB_OK;
+}
+
+SHB_API int shb_sssp_block_init(shb_ctx *c, const shb_csr *AT, int64_t row_offset, int64_t n_total, int64_t source,
+                                shb_buf *dist, shb_buf *prev, shb_buf *work) {
+  SHB_REQUIRE(c && AT && dist && prev && work, "bad arguments");
+  SHB_TRY(sssp_block_check(AT, row_offset, n_total, dist, prev, work));
+  SHB_REQUIRE(source >= 0 && source < n_total, "source out of range");
+  SHB_CUDA(cudaSetDevice(c->device));
+  SHB_TRY(shb_buf_fill_u32(c, dist, 0, (uint64_t)n_total, 0x7f7fffffu));
+  if (AT->n_rows > 0) SHB_TRY(shb_buf_fill_u32(c, prev, 0, (uint64_t)AT->n_rows, 0x7f7fffffu));
+  SsspState *st = (SsspState *)work->ptr;
+  SHB_CUDA(cudaMemsetAsync(st, 0, sizeof(SsspState), c->stream));
+  if (AT->val && AT->nnz > 0) {
+    const int64_t stride = std::max<int64_t>(1, AT->nnz / (1 << 22));
+    sssp_weight_stats_kernel<<<148, 256, 0, c->stream>>>(st, (const float *)AT->val, AT->nnz, stride);
+  }
+  float c_scale = 128.0f, delta_override = 0.0f;
+  if (const char *e = getenv("SHB_SSSP_C")) c_scale = (float)atof(e);
+  if (const char *e = getenv("SHB_SSSP_DELTA")) delta_override = (float)atof(e);
+  // sssp_init_kernel also plants the source: dist[source] = 0 on EVERY rank (only the owner will seed it) and
+  // writes one near entry that the first round's reset discards
+  const SsspBlockLayout L = sssp_block_layout(AT->n_rows);
+  sssp_init_kernel<<<1, 1, 0, c->stream>>>(st, (uint32_t *)dist->ptr, (uint2 *)((char *)work->ptr + L.near_off), source,
+                                           AT->n_rows > 0 ? (double)AT->nnz / (double)AT->n_rows : 1.0, c_scale, delta_override);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
+}
+
+SHB_API int shb_sssp_block_round(shb_ctx *c, const shb_csr *AT, int64_t row_offset, int64_t n_total, shb_buf *dist,
+                                 shb_buf *const *peer_dist, int n_ranks, int self_index, const int64_t *bounds, shb_buf *prev,
+                                 shb_buf *work, shb_buf *seed_count, uint64_t seed_count_word, uint32_t max_phases) {
+  SHB_REQUIRE(c && AT && dist && peer_dist && bounds && prev && work && seed_count, "bad arguments");
+  SHB_REQUIRE(n_ranks >= 1 && n_ranks <= 8 && self_index >= 0 && self_index < n_ranks, "1..8 ranks, one of them local");
+  SHB_TRY(sssp_block_check(AT, row_offset, n_total, dist, prev, work));
+  SHB_REQUIRE(bounds[0] == 0 && bounds[n_ranks] == n_total && bounds[self_index] == row_offset &&
+                  bounds[self_index + 1] == row_offset + AT->n_rows, "bounds do not describe this block");
+  SHB_REQUIRE(seed_count->bytes >= (seed_count_word + 1) * 8, "seed_count too short");
+  SHB_REQUIRE(peer_dist[self_index] && peer_dist[self_index]->ptr == dist->ptr, "peer_dist[self_index] must be the local dist");
+  SHB_CUDA(cudaSetDevice(c->device));
+  const SsspBlockLayout L = sssp_block_layout(AT->n_rows);
+  char *w = (char *)work->ptr;
+  SsspBlockArgs a;
+  memset(&a, 0, sizeof a);
+  a.st = (SsspState *)w;
+  a.at_row_ptr = AT->row_ptr;
+  a.at_col = AT->col;
+  a.at_val = (const float *)AT->val;
+  a.dist = (uint32_t *)dist->ptr;
+  for (int i = 0; i < n_ranks; ++i) {
+    SHB_REQUIRE(peer_dist[i] && peer_dist[i]->bytes >= (uint64_t)n_total * 4, "a peer's dist is too short");
+    SHB_REQUIRE(bounds[i] <= bounds[i + 1], "bounds not monotone");
+    a.peer_dist[i] = (uint32_t *)peer_dist[i]->ptr;
+    a.bounds[i] = bounds[i];
+  }
+  a.bounds[n_ranks] = bounds[n_ranks];
+  a.n_ranks = n_ranks;
+  a.self = self_index;
+  a.prev = (uint32_t *)prev->ptr;
+  a.pile_bits = (uint32_t *)(w + L.pile_off);
+  a.near_q[0] = (uint2 *)(w + L.near_off);
+  a.near_q[1] = a.near_q[0] + L.near_cap;
+  a.far_q[0] = (int32_t *)(w + L.far_off);
+  a.far_q[1] = a.far_q[0] + AT->n_rows;
+  a.lo = (uint32_t)row_offset;
+  a.n_local = (uint32_t)AT->n_rows;
+  a.n_total = (uint32_t)n_total;
+  a.near_cap = (uint32_t)std::min<uint64_t>(L.near_cap, 0xffffffffu);
+  a.max_phases = max_phases ? max_phases : 0xffffffffu;
+  long long *count = (long long *)seed_count->ptr + seed_count_word;
+  sssp_block_reset_kernel<<<1, 1, 0, c->stream>>>(a.st);
+  if (AT->n_rows > 0)
+    sssp_block_seed_kernel<<<grid_for(AT->n_rows), 256, 0, c->stream>>>(a.st, a.dist, a.prev, a.pile_bits, a.far_q[0], a.lo,
+                                                                      a.n_local, count);
+  SHB_CUDA(cudaGetLastError());
+  const bool has_val = AT->val != nullptr;
+  int per_sm = 0;
+  if (has_val) SHB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_block_kernel<true>, SSSP_THREADS, 0));
+  else SHB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_block_kernel<false>, SSSP_THREADS, 0));
+  const int blocks = std::max(1, std::min(per_sm, 1)) * c->prop.multiProcessorCount;
+  void *args[] = {&a};
+  if (has_val)
+    SHB_CUDA(cudaLaunchCooperativeKernel((void *)sssp_block_kernel<true>, dim3(blocks), dim3(SSSP_THREADS), args, 0, c->stream));
+  else
+    SHB_CUDA(cudaLaunchCooperativeKernel((void *)sssp_block_kernel<false>, dim3(blocks), dim3(SSSP_THREADS), args, 0, c->stream));
+  return SHB_OK;
+}
+
+// after the last round: solver status of the last round + (reached, sum of row lengths of reached) of the owned
+// slice into stats_out[0..1] (int64).  `A_rows` supplies the TEPS degrees (the block's rows of A; for a symmetric
+// graph the same operator as AT).
+SHB_API int shb_sssp_block_finish(shb_ctx *c, const shb_csr *A_rows, int64_t row_offset, const shb_buf *dist,
+                                  const shb_buf *work, shb_buf *stats_out) {
+  SHB_REQUIRE(c && A_rows && dist && work && stats_out, "bad arguments");
+  SHB_REQUIRE(dist->bytes >= (uint64_t)(row_offset + A_rows->n_rows) * 4 && stats_out->bytes >= 16, "buffers too short");
+  SHB_REQUIRE(work->bytes >= sizeof(SsspState), "work too short");
+  SHB_CUDA(cudaSetDevice(c->device));
+  SHB_CUDA(cudaMemsetAsync(stats_out->ptr, 0, 16, c->stream));
+  if (A_rows->n_rows > 0)
+    reached_stats_kernel<<<grid_for(A_rows->n_rows), 256, 0, c->stream>>>((const uint32_t *)dist->ptr + row_offset, 0x7f7fffffu,
+                                                                         A_rows->row_ptr, A_rows->n_rows,
+                                                                         (unsigned long long *)stats_out->ptr);
+  SHB_CUDA(cudaGetLastError());
+  SsspState h;
+  SHB_CUDA(cudaMemcpyAsync(&h, work->ptr, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+  SHB_CUDA(cudaStreamSynchronize(c->stream));
+  if (h.overflow) {
+    shb_set_error("near list overflow in a partitioned SSSP round");
+    return SHB_ERR_CUDA;
+  }
+  if (!h.done) {
+    shb_set_error("phase cap reached before the block's worklists emptied");
+    return SHB_ERR_NOT_CONVERGED;
+  }
+  return SHB_OK;
+}
+
+
+
+// =================================================================================================
 // PageRank, canonical mode (Q9): x_{k+1} = A x_k * 1 + 1 * beta with y == 1 never re-bound.
 // =================================================================================================
 SHB_API int shb_pagerank(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, shb_buf *x, shb_buf *work, float x_init,

@@ -508,3 +508,162 @@ def partitioned_bfs(ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_lo
         reached, edges = int(t[0].item()), int(t[1].item())
     best["reached"], best["edges_traversed"] = reached, edges
     return be, best
+
+
+# =====================================================================================================
+# Row-partitioned SSSP (min-plus to the exact fixed point): block-asynchronous near-far
+# =====================================================================================================
+class SsspBackend:
+    def round(self, r: int) -> None:  # seed pass + local solve of round r (peer reds included)
+        raise NotImplementedError
+
+    def reduce_seeds(self, r: int) -> None:  # seeds[r] <- sum over ranks; also the barrier between rounds
+        raise NotImplementedError
+
+    def read_seeds(self, r: int) -> int:  # host view of seeds[r] (synchronises)
+        raise NotImplementedError
+
+
+def run_sssp(backend: SsspBackend, max_rounds: int = 1 << 16):
+    """Rounds until a seed pass finds nothing on any rank (then that round's solves did nothing either: fixed point).
+    Returns (rounds_with_work, converged)."""
+    for r in range(max_rounds):
+        backend.round(r)
+        backend.reduce_seeds(r)
+        if backend.read_seeds(r) == 0:
+            return r, True
+    return max_rounds, False
+
+
+class GpuSsspPartition(SsspBackend):
+    """The CUDA backend: AT_local = out-edges of the owned vertices (global target ids)."""
+
+    def __init__(self, ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, dist=None, torch=None):
+        self.ctx, self.AT, self.bounds = ctx, AT_local, np.asarray(bounds, dtype=np.int64)
+        self.rank, self.world, self.source, self.dist_mod, self.torch = rank, world, int(source), dist, torch
+        self.n = int(self.bounds[-1])
+        self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
+        self.d = ctx.empty(max(self.n, 1) * 4)
+        self.prev = ctx.empty(max(self.hi - self.lo, 1) * 4)
+        self.work = ctx.empty(ctx.sssp_block_work_bytes(self.hi - self.lo))
+        self.max_rounds = max_rounds
+        self.seeds = ctx.empty((max_rounds + 2) * 8)
+        self.stats = ctx.empty(16)
+        self.peer_d = [self.d]
+        self._t_seeds = None
+        if world > 1:
+            ctx.synchronize()
+            self._t_seeds = _tensor_view(torch, self.seeds, max_rounds + 2, ctx.device, "<i8")
+            handles = [None] * world
+            dist.all_gather_object(handles, self.d.ipc_handle())
+            self.peer_d = [self.d if r == rank else ctx.ipc_open(handles[r], self.n * 4) for r in range(world)]
+        self.reset()
+
+    def _quiesce(self):
+        self.ctx.synchronize()
+        if self.world > 1:
+            self.dist_mod.barrier()
+
+    def reset(self):
+        self._quiesce()  # no peer may still be sending candidates into the dist that init is about to overwrite
+        self.seeds.zero()
+        self.ctx.sssp_block_init(self.AT, self.lo, self.n, self.source, self.d, self.prev, self.work)
+        self._quiesce()
+
+    def round(self, r):
+        self.ctx.sssp_block_round(self.AT, self.lo, self.n, self.d, self.peer_d, self.rank if self.world > 1 else 0,
+                                  self.bounds, self.prev, self.work, self.seeds, r)
+
+    def reduce_seeds(self, r):
+        if self.world > 1:
+            self.dist_mod.all_reduce(self._t_seeds[r:r + 1], op=self.dist_mod.ReduceOp.SUM)
+
+    def read_seeds(self, r):
+        return int(self.seeds.download(np.int64, 1, offset=8 * r)[0])
+
+    def local_stats(self, A_rows=None):
+        """(reached, sum of in-degrees of reached) of the owned slice; raises if the last solve failed."""
+        self.ctx.sssp_block_finish(A_rows or self.AT, self.lo, self.d, self.work, self.stats)
+        w = self.stats.download(np.int64, 2)
+        return int(w[0]), int(w[1])
+
+    def result(self) -> np.ndarray:
+        return self.d.download(np.float32, self.hi - self.lo, offset=4 * self.lo)
+
+    def close(self):
+        self._quiesce()
+        if self.world > 1:
+            for r, b in enumerate(self.peer_d):
+                if r != self.rank:
+                    b.free()
+        for b in (self.d, self.prev, self.work, self.seeds, self.stats):
+            b.free()
+
+
+class EmulatedSsspPartition(SsspBackend):
+    """All P row blocks on ONE device, each with its OWN full-length dist, prev and work: candidates for another
+    block's vertices travel as red.min into that block's dist, exactly as between GPUs."""
+
+    def __init__(self, ctx, at_blocks, bounds, source, max_rounds=4096):
+        self.ctx, self.blocks, self.bounds, self.source = ctx, at_blocks, np.asarray(bounds, dtype=np.int64), int(source)
+        self.n, self.P = int(self.bounds[-1]), len(at_blocks)
+        size = lambda k: int(self.bounds[k + 1] - self.bounds[k])
+        self.d = [ctx.empty(max(self.n, 1) * 4) for _ in range(self.P)]
+        self.prev = [ctx.empty(max(size(k), 1) * 4) for k in range(self.P)]
+        self.work = [ctx.empty(ctx.sssp_block_work_bytes(size(k))) for k in range(self.P)]
+        self.seeds = ctx.empty((max_rounds + 2) * 8)
+        self.stats = ctx.empty(16)
+        self.reset()
+
+    def reset(self):
+        self.seeds.zero()
+        for k, AT in enumerate(self.blocks):
+            self.ctx.sssp_block_init(AT, int(self.bounds[k]), self.n, self.source, self.d[k], self.prev[k], self.work[k])
+
+    def round(self, r):
+        for k, AT in enumerate(self.blocks):
+            self.ctx.sssp_block_round(AT, int(self.bounds[k]), self.n, self.d[k], self.d, k, self.bounds, self.prev[k],
+                                      self.work[k], self.seeds, r)
+
+    def reduce_seeds(self, r):
+        pass
+
+    def read_seeds(self, r):
+        return int(self.seeds.download(np.int64, 1, offset=8 * r)[0])
+
+    def stats_total(self):
+        r = e = 0
+        for k, AT in enumerate(self.blocks):
+            self.ctx.sssp_block_finish(AT, int(self.bounds[k]), self.d[k], self.work[k], self.stats)
+            w = self.stats.download(np.int64, 2)
+            r, e = r + int(w[0]), e + int(w[1])
+        return r, e
+
+    def result(self) -> np.ndarray:
+        return np.concatenate([self.d[k].download(np.float32, int(self.bounds[k + 1] - self.bounds[k]),
+                                                  offset=4 * int(self.bounds[k])) for k in range(self.P)])
+
+
+def partitioned_sssp(ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, dist=None, torch=None, repeat=1):
+    """SSSP distances on a row-partitioned operator.  Returns (backend, stats) with stats = dict(rounds, converged,
+    reached, edges_traversed [all ranks], ms [this rank's device time])."""
+    be = GpuSsspPartition(ctx, AT_local, bounds, rank, world, source, max_rounds=max_rounds, dist=dist, torch=torch)
+    best = None
+    for i in range(max(1, repeat)):
+        if i:
+            be.reset()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        rounds, conv = run_sssp(be, max_rounds)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms = ev0.elapsed_time(ev1)
+        if best is None or ms < best["ms"]:
+            best = {"rounds": rounds, "converged": conv, "ms": ms}
+    reached, edges = be.local_stats()
+    if world > 1:
+        t = torch.tensor([reached, edges], dtype=torch.int64, device=f"cuda:{ctx.device}")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        reached, edges = int(t[0].item()), int(t[1].item())
+    best["reached"], best["edges_traversed"] = reached, edges
+    return be, best

@@ -192,3 +192,76 @@ def test_word_aligned_bounds():
     assert list(b) == [0, 64, 64, 101, 101]
     b = multi.word_aligned_bounds(np.array([0, 5, 1000]))
     assert list(b) == [0, 32, 1000]
+
+
+# ---------------------------------------------------------------------------------------------------------
+# row-partitioned SSSP: the round protocol (seed count all-reduce, stop on a globally empty seed pass)
+# ---------------------------------------------------------------------------------------------------------
+def _sssp_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle as orc
+    from sparseharness_b200 import multi
+
+    rp, col, val = orc.gen_grid2d(24, 17)
+    n = len(rp) - 1
+    bounds = multi.balanced_bounds(rp, world)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    FMAX = np.float32(orc.FLT_MAX)
+
+    class NumpySssp(multi.SsspBackend):
+        """CPU stand-in for shb_sssp_block_round: owned slice authoritative, candidates for other ranks' vertices
+        handed over between rounds (what the kernel does with red.min on the peer mapping)."""
+
+        def __init__(self):
+            self.d = np.full(n, FMAX, np.float32)
+            self.d[0] = 0
+            self.prev = np.full(hi - lo, FMAX, np.float32)
+            self.seeds = torch.zeros(4096, dtype=torch.int64)
+            self.outbox = {}
+
+        def round(self, r):
+            work = [v for v in range(lo, hi) if self.d[v] < self.prev[v - lo]]
+            self.seeds[r] = len(work)
+            self.outbox = {}
+            while work:  # symmetric grid: row v lists v's neighbours
+                v = work.pop()
+                self.prev[v - lo] = self.d[v]
+                for k in range(rp[v], rp[v + 1]):
+                    t, c = int(col[k]), np.float32(np.abs(self.d[v]) + np.abs(val[k]))
+                    if c < self.d[t]:
+                        self.d[t] = c
+                        if lo <= t < hi:
+                            work.append(t)
+                        else:
+                            self.outbox[t] = c
+
+        def reduce_seeds(self, r):
+            boxes = [None] * world
+            dist.all_gather_object(boxes, self.outbox)
+            for b in boxes:
+                for t, c in b.items():
+                    if lo <= t < hi and c < self.d[t]:
+                        self.d[t] = c
+            dist.all_reduce(self.seeds[r:r + 1], op=dist.ReduceOp.SUM)
+
+        def read_seeds(self, r):
+            return int(self.seeds[r])
+
+    be = NumpySssp()
+    rounds, conv = multi.run_sssp(be, 500)
+    np.save(os.path.join(out_dir, f"sd_{rank}.npy"), be.d[lo:hi])
+    np.save(os.path.join(out_dir, f"smeta_{rank}.npy"), np.array([rounds, int(conv)]))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_partitioned_sssp_rounds_over_gloo_match_dijkstra(tmp_path, orc, world):
+    port = 33500 + (os.getpid() + world * 13) % 2000
+    mp.spawn(_sssp_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    rp, col, val = orc.gen_grid2d(24, 17)
+    want = orc.sssp(rp, col, val, 0)
+    got = np.concatenate([np.load(tmp_path / f"sd_{r}.npy") for r in range(world)])
+    metas = [np.load(tmp_path / f"smeta_{r}.npy") for r in range(world)]
+    assert np.array_equal(got, want)
+    assert all(m[1] == 1 and m[0] == metas[0][0] and m[0] >= world for m in metas)

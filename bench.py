@@ -237,8 +237,9 @@ def graph_extras(ctx, shb, orc):
 
 def partitioned_extras(ctx, rank, world):
     """GTEPS of the row-partitioned drivers at this GPU count: PageRank on config 5 (RMAT scale 26,
-    2^30 non-zeros, 20 sweeps, fused SpMV -> peer scatter) and, for N > 1, BFS on config 3 (RMAT scale 24) with the
-    frontier bitmap exchanged by the pull kernel's peer stores.  Every rank must call this."""
+    2^30 non-zeros, 20 sweeps, fused SpMV -> peer scatter) and, for N > 1, BFS on config 3 (RMAT scale 24, frontier
+    bitmap and counts exchanged by the kernels' own peer stores) and SSSP on config 4 (8192^2 grid, block-asynchronous
+    near-far with boundary candidates as peer red.min).  Every rank must call this."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     out = {}
     try:
@@ -254,6 +255,12 @@ def partitioned_extras(ctx, rank, world):
             out["bfs_partitioned"] = r
         except Exception as e:
             out["bfs_partitioned"] = {"error": repr(e)[:300]}
+        try:
+            import multi_sssp
+            r, _, _ = multi_sssp.run(8192, 8192, False, repeat=2, ctx=ctx)
+            out["sssp_partitioned"] = r
+        except Exception as e:
+            out["sssp_partitioned"] = {"error": repr(e)[:300]}
     return out
 
 

@@ -263,19 +263,27 @@ int shb_bfs_block_finish(shb_ctx *ctx, const shb_csr *A, const shb_buf *levels, 
  * array on every rank whose owned slice is authoritative, prev (n_local) the distance each owned vertex was last
  * expanded with, work an opaque scratch of shb_sssp_block_work_bytes(n_local) bytes.
  *   init    dist = FLT_MAX, dist[source] = 0 on every rank, prev = FLT_MAX, bucket width from the block's weights.
- *   round   seed pass (owned v with dist[v] < prev[v]; their number is ADDED to int64 word seed_count_word of
- *           seed_count) + the near-far solve of the block: improved owned targets are queued, improved targets of
+ *   seed    first half of a round: the owned v with dist[v] < prev[v] (lowered by a peer since their last
+ *           expansion, or the source) enter the work pile; their number is ADDED to int64 word `word` of seed_count,
+ *           their smallest distance (float bits) MIN-ed into word `word` of seed_min (optional, preset large).
+ *   solve   second half: the near-far solve of the block: improved owned targets are queued, improved targets of
  *           other ranks are sent to their owner as red.min on peer_dist[owner] (CUDA-IPC mappings, NVLink).
- *           bounds[0..n_ranks] = vertex ownership.  The caller separates rounds with a barrier (e.g. the all-reduce
- *           of the seed count) and stops after a round whose seed count is 0 on every rank.
+ *           bounds[0..n_ranks] = vertex ownership.  window_buckets > 0: only distances below seed_min[word] (all-
+ *           reduced MIN by the caller) + window_buckets * bucket width are expanded this round; the rest stays
+ *           pending and is seeded again, so all ranks sweep the distance range together instead of one block
+ *           running ahead on distances a neighbour will still lower.
+ *           The caller separates rounds with a barrier (the all-reduce of the seed count) and stops after a round
+ *           whose seed count is 0 on every rank.
  *   finish  status of the last solve + (reached, sum of A_rows' row lengths over reached) into stats_out (2 x int64).
  * Same least fixed point as shb_sssp and the reference's dense sweeps, bit for bit (monotone float adds). */
 int shb_sssp_block_work_bytes(int64_t n_local, uint64_t *bytes);
 int shb_sssp_block_init(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, int64_t n_total, int64_t source,
                         shb_buf *dist, shb_buf *prev, shb_buf *work);
-int shb_sssp_block_round(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, int64_t n_total, shb_buf *dist,
+int shb_sssp_block_seed(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, int64_t n_total, const shb_buf *dist,
+                        const shb_buf *prev, shb_buf *work, shb_buf *seed_count, shb_buf *seed_min, uint64_t word);
+int shb_sssp_block_solve(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, int64_t n_total, shb_buf *dist,
                          shb_buf *const *peer_dist, int n_ranks, int self_index, const int64_t *bounds, shb_buf *prev,
-                         shb_buf *work, shb_buf *seed_count, uint64_t seed_count_word, uint32_t max_phases);
+                         shb_buf *work, const shb_buf *seed_min, uint64_t word, float window_buckets, uint32_t max_phases);
 int shb_sssp_block_finish(shb_ctx *ctx, const shb_csr *A_rows, int64_t row_offset, const shb_buf *dist,
                           const shb_buf *work, shb_buf *stats_out);
 

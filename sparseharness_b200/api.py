@@ -301,13 +301,18 @@ class Context:
     def sssp_block_init(self, AT: Csr, row_offset, n_total, source, dist: Buffer, prev: Buffer, work: Buffer):
         _ck(lib.shb_sssp_block_init(self.h, AT.h, row_offset, n_total, source, dist.h, prev.h, work.h))
 
-    def sssp_block_round(self, AT: Csr, row_offset, n_total, dist: Buffer, peer_dist: list[Buffer], self_index: int,
-                         bounds: np.ndarray, prev: Buffer, work: Buffer, seed_count: Buffer, seed_count_word: int,
-                         max_phases: int = 0):
+    def sssp_block_seed(self, AT: Csr, row_offset, n_total, dist: Buffer, prev: Buffer, work: Buffer,
+                        seed_count: Buffer, seed_min: Buffer | None, word: int):
+        _ck(lib.shb_sssp_block_seed(self.h, AT.h, row_offset, n_total, dist.h, prev.h, work.h, seed_count.h,
+                                    seed_min.h if seed_min else None, word))
+
+    def sssp_block_solve(self, AT: Csr, row_offset, n_total, dist: Buffer, peer_dist: list[Buffer], self_index: int,
+                         bounds: np.ndarray, prev: Buffer, work: Buffer, seed_min: Buffer | None = None, word: int = 0,
+                         window_buckets: float = 0.0, max_phases: int = 0):
         arr = (C.c_void_p * len(peer_dist))(*[d.h for d in peer_dist])
         b = np.ascontiguousarray(bounds, dtype=np.int64)
-        _ck(lib.shb_sssp_block_round(self.h, AT.h, row_offset, n_total, dist.h, arr, len(peer_dist), self_index, _ptr(b),
-                                     prev.h, work.h, seed_count.h, seed_count_word, max_phases))
+        _ck(lib.shb_sssp_block_solve(self.h, AT.h, row_offset, n_total, dist.h, arr, len(peer_dist), self_index, _ptr(b),
+                                     prev.h, work.h, seed_min.h if seed_min else None, word, window_buckets, max_phases))
 
     def sssp_block_finish(self, A_rows: Csr, row_offset, dist: Buffer, work: Buffer, stats_out: Buffer):
         _ck(lib.shb_sssp_block_finish(self.h, A_rows.h, row_offset, dist.h, work.h, stats_out.h))

@@ -1330,6 +1330,8 @@ struct SsspBlockArgs {
   uint32_t lo, n_local, n_total;
   uint32_t near_cap;
   uint32_t max_phases;
+  const long long *gmin;  // all-reduced smallest pending distance (bits) of this round; nullptr = no window
+  float window_buckets;   // the round expands distances below gmin + window_buckets * delta only
 };
 
 __device__ __forceinline__ int sssp_owner(const SsspBlockArgs &a, uint32_t v) {
@@ -1382,7 +1384,7 @@ __global__ void sssp_block_reset_kernel(SsspState *st) {
 }
 
 __global__ void sssp_block_seed_kernel(SsspState *st, const uint32_t *dist, const uint32_t *prev, uint32_t *pile_bits,
-                                       int32_t *far0, uint32_t lo, uint32_t n_local, long long *count_out) {
+                                       int32_t *far0, uint32_t lo, uint32_t n_local, long long *count_out, long long *min_out) {
   const int lane = threadIdx.x & 31;
   uint32_t fmin = 0xffffffffu, cnt = 0;
   const uint32_t n_padded = (n_local + 31u) & ~31u;
@@ -1413,6 +1415,7 @@ __global__ void sssp_block_seed_kernel(SsspState *st, const uint32_t *dist, cons
   if (lane == 0 && cnt) {
     atomicMin(&st->far_min[0], fmin);
     atomicAdd(reinterpret_cast<unsigned long long *>(count_out), (unsigned long long)cnt);
+    if (min_out) atomicMin(min_out, (long long)fmin);
   }
 }
 
@@ -1426,6 +1429,13 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
   const float delta = *(volatile float *)&st->delta;
   uint32_t phase = 0, fgen = 0, buckets = 0;
   uint32_t t_hi = 0;  // nothing has been through the near list yet: the first phase splits the seeded pile
+  // distance window of this round: vertices at or beyond cap stay unexpanded (prev > dist) and are seeded again
+  uint32_t cap = 0xffffffffu;
+  if (a.gmin) {
+    const long long g = *(volatile const long long *)a.gmin;
+    const uint32_t gb = g < 0x7f7fffffll ? (uint32_t)g : 0x7f7fffffu;
+    cap = __float_as_uint(__fadd_rn(__uint_as_float(gb), a.window_buckets * delta));
+  }
   bool finished = false;
   if (threadIdx.x == 0) {
     sh.lcount[0] = sh.lcount[1] = 0;
@@ -1526,12 +1536,13 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
       }
     } else {
       const uint32_t fs = *(volatile uint32_t *)&st->far_size[fgen % 3];
-      if (fs == 0) {
+      const uint32_t fm = *(volatile uint32_t *)&st->far_min[fgen % 3];
+      if (fs == 0 || fm >= cap) {  // nothing left, or nothing left inside this round's window
         finished = true;
         break;
       }
       const uint32_t t_old = t_hi;
-      t_hi = __float_as_uint(__fadd_rn(__uint_as_float(*(volatile uint32_t *)&st->far_min[fgen % 3]), delta));
+      t_hi = min(__float_as_uint(__fadd_rn(__uint_as_float(fm), delta)), cap);
       ++buckets;
       const int32_t *far_cur = a.far_q[fgen & 1];
       int32_t *far_next = a.far_q[(fgen + 1) & 1];
@@ -1644,15 +1655,41 @@ SHB_API int shb_sssp_block_init(shb_ctx *c, const shb_csr *AT, int64_t row_offse
   return SHB_OK;
 }
 
-SHB_API int shb_sssp_block_round(shb_ctx *c, const shb_csr *AT, int64_t row_offset, int64_t n_total, shb_buf *dist,
+// first half of a round: reset the work lists and collect the owned vertices whose distance dropped below the
+// value they were last expanded with.  Their number is ADDED to int64 word `word` of seed_count, their smallest
+// distance (bits) is MIN-ed into word `word` of seed_min (optional; pre-set to a large value by the caller).
+SHB_API int shb_sssp_block_seed(shb_ctx *c, const shb_csr *AT, int64_t row_offset, int64_t n_total, const shb_buf *dist,
+                                const shb_buf *prev, shb_buf *work, shb_buf *seed_count, shb_buf *seed_min, uint64_t word) {
+  SHB_REQUIRE(c && AT && dist && prev && work && seed_count, "bad arguments");
+  SHB_TRY(sssp_block_check(AT, row_offset, n_total, dist, prev, work));
+  SHB_REQUIRE(seed_count->bytes >= (word + 1) * 8 && (!seed_min || seed_min->bytes >= (word + 1) * 8), "seed buffers too short");
+  SHB_CUDA(cudaSetDevice(c->device));
+  const SsspBlockLayout L = sssp_block_layout(AT->n_rows);
+  char *w = (char *)work->ptr;
+  SsspState *st = (SsspState *)w;
+  sssp_block_reset_kernel<<<1, 1, 0, c->stream>>>(st);
+  if (AT->n_rows > 0)
+    sssp_block_seed_kernel<<<grid_for(AT->n_rows), 256, 0, c->stream>>>(
+        st, (const uint32_t *)dist->ptr, (const uint32_t *)prev->ptr, (uint32_t *)(w + L.pile_off), (int32_t *)(w + L.far_off),
+        (uint32_t)row_offset, (uint32_t)AT->n_rows, (long long *)seed_count->ptr + word,
+        seed_min ? (long long *)seed_min->ptr + word : nullptr);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
+}
+
+// second half: the near-far solve of the block.  window_buckets > 0 (needs seed_min, all-reduced MIN by the caller):
+// only distances below seed_min[word] + window_buckets * delta are expanded in this round; vertices beyond stay
+// pending and are seeded again, so that all ranks advance through the distance range together.
+SHB_API int shb_sssp_block_solve(shb_ctx *c, const shb_csr *AT, int64_t row_offset, int64_t n_total, shb_buf *dist,
                                  shb_buf *const *peer_dist, int n_ranks, int self_index, const int64_t *bounds, shb_buf *prev,
-                                 shb_buf *work, shb_buf *seed_count, uint64_t seed_count_word, uint32_t max_phases) {
-  SHB_REQUIRE(c && AT && dist && peer_dist && bounds && prev && work && seed_count, "bad arguments");
+                                 shb_buf *work, const shb_buf *seed_min, uint64_t word, float window_buckets,
+                                 uint32_t max_phases) {
+  SHB_REQUIRE(c && AT && dist && peer_dist && bounds && prev && work, "bad arguments");
   SHB_REQUIRE(n_ranks >= 1 && n_ranks <= 8 && self_index >= 0 && self_index < n_ranks, "1..8 ranks, one of them local");
   SHB_TRY(sssp_block_check(AT, row_offset, n_total, dist, prev, work));
   SHB_REQUIRE(bounds[0] == 0 && bounds[n_ranks] == n_total && bounds[self_index] == row_offset &&
                   bounds[self_index + 1] == row_offset + AT->n_rows, "bounds do not describe this block");
-  SHB_REQUIRE(seed_count->bytes >= (seed_count_word + 1) * 8, "seed_count too short");
+  SHB_REQUIRE(!(window_buckets > 0.f) || (seed_min && seed_min->bytes >= (word + 1) * 8), "a window needs the all-reduced seed_min");
   SHB_REQUIRE(peer_dist[self_index] && peer_dist[self_index]->ptr == dist->ptr, "peer_dist[self_index] must be the local dist");
   SHB_CUDA(cudaSetDevice(c->device));
   const SsspBlockLayout L = sssp_block_layout(AT->n_rows);
@@ -1684,17 +1721,10 @@ SHB_API int shb_sssp_block_round(shb_ctx *c, const shb_csr *AT, int64_t row_offs
   a.n_total = (uint32_t)n_total;
   a.near_cap = (uint32_t)std::min<uint64_t>(L.near_cap, 0xffffffffu);
   a.max_phases = max_phases ? max_phases : 0xffffffffu;
-  long long *count = (long long *)seed_count->ptr + seed_count_word;
-  sssp_block_reset_kernel<<<1, 1, 0, c->stream>>>(a.st);
-  if (AT->n_rows > 0)
-    sssp_block_seed_kernel<<<grid_for(AT->n_rows), 256, 0, c->stream>>>(a.st, a.dist, a.prev, a.pile_bits, a.far_q[0], a.lo,
-                                                                      a.n_local, count);
-  SHB_CUDA(cudaGetLastError());
+  a.gmin = window_buckets > 0.f ? (const long long *)seed_min->ptr + word : nullptr;
+  a.window_buckets = window_buckets;
   const bool has_val = AT->val != nullptr;
-  int per_sm = 0;
-  if (has_val) SHB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_block_kernel<true>, SSSP_THREADS, 0));
-  else SHB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sssp_block_kernel<false>, SSSP_THREADS, 0));
-  const int blocks = std::max(1, std::min(per_sm, 1)) * c->prop.multiProcessorCount;
+  const int blocks = c->prop.multiProcessorCount;  // one 512-thread CTA per SM, co-resident by construction
   void *args[] = {&a};
   if (has_val)
     SHB_CUDA(cudaLaunchCooperativeKernel((void *)sssp_block_kernel<true>, dim3(blocks), dim3(SSSP_THREADS), args, 0, c->stream));

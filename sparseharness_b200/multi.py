@@ -514,10 +514,16 @@ def partitioned_bfs(ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_lo
 # Row-partitioned SSSP (min-plus to the exact fixed point): block-asynchronous near-far
 # =====================================================================================================
 class SsspBackend:
-    def round(self, r: int) -> None:  # seed pass + local solve of round r (peer reds included)
+    def seed(self, r: int) -> None:  # seed pass of round r: pending owned vertices, their count and smallest distance
         raise NotImplementedError
 
-    def reduce_seeds(self, r: int) -> None:  # seeds[r] <- sum over ranks; also the barrier between rounds
+    def reduce_seeds(self, r: int) -> None:  # seeds[r] <- sum, seed_min[r] <- min over ranks; the barrier between rounds
+        raise NotImplementedError
+
+    def solve(self, r: int) -> None:  # local near-far solve of round r inside the distance window (peer reds included)
+        raise NotImplementedError
+
+    def barrier(self, r: int) -> None:  # every rank's solve of round r (and its peer reds) is complete
         raise NotImplementedError
 
     def read_seeds(self, r: int) -> int:  # host view of seeds[r] (synchronises)
@@ -528,8 +534,10 @@ def run_sssp(backend: SsspBackend, max_rounds: int = 1 << 16):
     """Rounds until a seed pass finds nothing on any rank (then that round's solves did nothing either: fixed point).
     Returns (rounds_with_work, converged)."""
     for r in range(max_rounds):
-        backend.round(r)
-        backend.reduce_seeds(r)
+        backend.seed(r)
+        backend.reduce_seeds(r)  # global seed count and smallest pending distance of this round
+        backend.solve(r)         # enqueued before the host looks at the count: a solve without seeds returns at once
+        backend.barrier(r)       # all peer candidates of this round have landed before anyone's next seed pass
         if backend.read_seeds(r) == 0:
             return r, True
     return max_rounds, False
@@ -538,8 +546,12 @@ def run_sssp(backend: SsspBackend, max_rounds: int = 1 << 16):
 class GpuSsspPartition(SsspBackend):
     """The CUDA backend: AT_local = out-edges of the owned vertices (global target ids)."""
 
-    def __init__(self, ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, dist=None, torch=None):
+    def __init__(self, ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, window_buckets=None, dist=None,
+                 torch=None):
         self.ctx, self.AT, self.bounds = ctx, AT_local, np.asarray(bounds, dtype=np.int64)
+        # one rank: no window (a single solve).  Several ranks: sweep the distance range in windows of this many
+        # near-far buckets so that no block runs far ahead on boundary distances a neighbour will still lower.
+        self.window = float((0 if world == 1 else 8) if window_buckets is None else window_buckets)
         self.rank, self.world, self.source, self.dist_mod, self.torch = rank, world, int(source), dist, torch
         self.n = int(self.bounds[-1])
         self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
@@ -548,12 +560,14 @@ class GpuSsspPartition(SsspBackend):
         self.work = ctx.empty(ctx.sssp_block_work_bytes(self.hi - self.lo))
         self.max_rounds = max_rounds
         self.seeds = ctx.empty((max_rounds + 2) * 8)
+        self.smin = ctx.empty((max_rounds + 2) * 8)
         self.stats = ctx.empty(16)
         self.peer_d = [self.d]
-        self._t_seeds = None
+        self._t_seeds = self._t_smin = None
         if world > 1:
             ctx.synchronize()
             self._t_seeds = _tensor_view(torch, self.seeds, max_rounds + 2, ctx.device, "<i8")
+            self._t_smin = _tensor_view(torch, self.smin, max_rounds + 2, ctx.device, "<i8")
             handles = [None] * world
             dist.all_gather_object(handles, self.d.ipc_handle())
             self.peer_d = [self.d if r == rank else ctx.ipc_open(handles[r], self.n * 4) for r in range(world)]
@@ -567,16 +581,26 @@ class GpuSsspPartition(SsspBackend):
     def reset(self):
         self._quiesce()  # no peer may still be sending candidates into the dist that init is about to overwrite
         self.seeds.zero()
+        self.smin.fill_u32(0x7F7FFFFF)  # as int64 words: larger than any distance
         self.ctx.sssp_block_init(self.AT, self.lo, self.n, self.source, self.d, self.prev, self.work)
         self._quiesce()
 
-    def round(self, r):
-        self.ctx.sssp_block_round(self.AT, self.lo, self.n, self.d, self.peer_d, self.rank if self.world > 1 else 0,
-                                  self.bounds, self.prev, self.work, self.seeds, r)
+    def seed(self, r):
+        self.ctx.sssp_block_seed(self.AT, self.lo, self.n, self.d, self.prev, self.work, self.seeds, self.smin, r)
 
     def reduce_seeds(self, r):
         if self.world > 1:
             self.dist_mod.all_reduce(self._t_seeds[r:r + 1], op=self.dist_mod.ReduceOp.SUM)
+            if self.window > 0:
+                self.dist_mod.all_reduce(self._t_smin[r:r + 1], op=self.dist_mod.ReduceOp.MIN)
+
+    def solve(self, r):
+        self.ctx.sssp_block_solve(self.AT, self.lo, self.n, self.d, self.peer_d, self.rank if self.world > 1 else 0,
+                                  self.bounds, self.prev, self.work, self.smin, r, self.window)
+
+    def barrier(self, r):
+        if self.world > 1:  # stream-ordered after the solve on every rank; MAX over identical values changes nothing
+            self.dist_mod.all_reduce(self._t_seeds[r:r + 1], op=self.dist_mod.ReduceOp.MAX)
 
     def read_seeds(self, r):
         return int(self.seeds.download(np.int64, 1, offset=8 * r)[0])
@@ -596,7 +620,7 @@ class GpuSsspPartition(SsspBackend):
             for r, b in enumerate(self.peer_d):
                 if r != self.rank:
                     b.free()
-        for b in (self.d, self.prev, self.work, self.seeds, self.stats):
+        for b in (self.d, self.prev, self.work, self.seeds, self.smin, self.stats):
             b.free()
 
 
@@ -604,29 +628,40 @@ class EmulatedSsspPartition(SsspBackend):
     """All P row blocks on ONE device, each with its OWN full-length dist, prev and work: candidates for another
     block's vertices travel as red.min into that block's dist, exactly as between GPUs."""
 
-    def __init__(self, ctx, at_blocks, bounds, source, max_rounds=4096):
+    def __init__(self, ctx, at_blocks, bounds, source, max_rounds=4096, window_buckets=0.0):
         self.ctx, self.blocks, self.bounds, self.source = ctx, at_blocks, np.asarray(bounds, dtype=np.int64), int(source)
+        self.window = float(window_buckets)
         self.n, self.P = int(self.bounds[-1]), len(at_blocks)
         size = lambda k: int(self.bounds[k + 1] - self.bounds[k])
         self.d = [ctx.empty(max(self.n, 1) * 4) for _ in range(self.P)]
         self.prev = [ctx.empty(max(size(k), 1) * 4) for k in range(self.P)]
         self.work = [ctx.empty(ctx.sssp_block_work_bytes(size(k))) for k in range(self.P)]
         self.seeds = ctx.empty((max_rounds + 2) * 8)
+        self.smin = ctx.empty((max_rounds + 2) * 8)
         self.stats = ctx.empty(16)
         self.reset()
 
     def reset(self):
         self.seeds.zero()
+        self.smin.fill_u32(0x7F7FFFFF)
         for k, AT in enumerate(self.blocks):
             self.ctx.sssp_block_init(AT, int(self.bounds[k]), self.n, self.source, self.d[k], self.prev[k], self.work[k])
 
-    def round(self, r):
+    def seed(self, r):  # all blocks add to / min into the same words: the all-reduce, for free
         for k, AT in enumerate(self.blocks):
-            self.ctx.sssp_block_round(AT, int(self.bounds[k]), self.n, self.d[k], self.d, k, self.bounds, self.prev[k],
-                                      self.work[k], self.seeds, r)
+            self.ctx.sssp_block_seed(AT, int(self.bounds[k]), self.n, self.d[k], self.prev[k], self.work[k], self.seeds,
+                                     self.smin, r)
+
+    def solve(self, r):
+        for k, AT in enumerate(self.blocks):
+            self.ctx.sssp_block_solve(AT, int(self.bounds[k]), self.n, self.d[k], self.d, k, self.bounds, self.prev[k],
+                                      self.work[k], self.smin, r, self.window)
 
     def reduce_seeds(self, r):
         pass
+
+    def barrier(self, r):
+        pass  # one stream: the next seed passes are ordered after every block's solve
 
     def read_seeds(self, r):
         return int(self.seeds.download(np.int64, 1, offset=8 * r)[0])
@@ -644,10 +679,12 @@ class EmulatedSsspPartition(SsspBackend):
                                                   offset=4 * int(self.bounds[k])) for k in range(self.P)])
 
 
-def partitioned_sssp(ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, dist=None, torch=None, repeat=1):
+def partitioned_sssp(ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, window_buckets=None, dist=None,
+                     torch=None, repeat=1):
     """SSSP distances on a row-partitioned operator.  Returns (backend, stats) with stats = dict(rounds, converged,
     reached, edges_traversed [all ranks], ms [this rank's device time])."""
-    be = GpuSsspPartition(ctx, AT_local, bounds, rank, world, source, max_rounds=max_rounds, dist=dist, torch=torch)
+    be = GpuSsspPartition(ctx, AT_local, bounds, rank, world, source, max_rounds=max_rounds,
+                          window_buckets=window_buckets, dist=dist, torch=torch)
     best = None
     for i in range(max(1, repeat)):
         if i:

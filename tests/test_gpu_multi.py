@@ -181,8 +181,8 @@ def test_handles_may_outlive_their_context(ctx, orc):
     assert np.array_equal(out.download(np.float32, 256), want)
 
 
-@pytest.mark.parametrize("parts,source", [(1, 0), (3, 0), (4, 777), (8, 1199)])
-def test_emulated_row_partition_sssp_grid_matches_dijkstra(ctx, orc, parts, source):
+@pytest.mark.parametrize("parts,source,window", [(1, 0, 0.0), (3, 0, 0.0), (4, 777, 2.0), (8, 1199, 0.5), (2, 5, 16.0)])
+def test_emulated_row_partition_sssp_grid_matches_dijkstra(ctx, orc, parts, source, window):
     """Block-asynchronous near-far on P row blocks of one device (own dist / prev / work per block, candidates for
     other blocks sent as red.min into their dist): bit-exact against the CPU Dijkstra with the same float adds."""
     from sparseharness_b200 import multi
@@ -191,11 +191,11 @@ def test_emulated_row_partition_sssp_grid_matches_dijkstra(ctx, orc, parts, sour
     A = ctx.csr(n, n, rp, col, val)  # symmetric: rows of A are also the out-edges
     bounds = A.balance_rows(parts)
     blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(parts)]
-    be = multi.EmulatedSsspPartition(ctx, blocks, bounds, source)
+    be = multi.EmulatedSsspPartition(ctx, blocks, bounds, source, window_buckets=window)
     rounds, conv = multi.run_sssp(be)
     want = orc.sssp(rp, col, val, source)
     assert conv and np.array_equal(be.result(), want)
-    assert rounds >= 1 and (parts > 1 or rounds == 1)
+    assert rounds >= 1 and (parts > 1 or window > 0 or rounds == 1)
     reached, edges = be.stats_total()
     assert reached == n and edges == len(col)
     # the same answer as the single-device driver, and again after a reset
@@ -217,20 +217,23 @@ def test_emulated_row_partition_sssp_directed_with_unreachable(ctx, orc):
     source = int(np.argmax(np.diff(rp)))
     bounds = AT.balance_rows(5)
     at_blocks = [AT.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(5)]
-    be = multi.EmulatedSsspPartition(ctx, at_blocks, bounds, source)
+    be = multi.EmulatedSsspPartition(ctx, at_blocks, bounds, source, window_buckets=3.0)
     rounds, conv = multi.run_sssp(be)
     want = orc.sssp(rp, col, val, source)
     assert conv and np.array_equal(be.result(), want)
     assert (want == orc.FLT_MAX).any() and (want < orc.FLT_MAX).sum() > 100
 
 
-def test_two_gpu_sssp_matches_oracle():
+@pytest.mark.parametrize("source,window", [(31000, None), (0, 1000.0), (0, 2.0)])
+def test_two_gpu_sssp_matches_oracle(source, window):
+    """window 1000 from a corner: rank 1 has nothing to do in round 0 and must still wait for rank 0's candidates
+    before its next seed pass (the barrier after the solve)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     port = 30200 + os.getpid() % 300
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
            "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tools", "multi_sssp.py"), "--width", "300",
-           "--height", "200", "--source", "31000", "--check"]
+           "--height", "200", "--source", str(source), "--check"] + (["--window", str(window)] if window is not None else [])
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])

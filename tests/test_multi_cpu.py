@@ -218,11 +218,15 @@ def _sssp_worker(rank, world, port, out_dir):
             self.d[0] = 0
             self.prev = np.full(hi - lo, FMAX, np.float32)
             self.seeds = torch.zeros(4096, dtype=torch.int64)
-            self.outbox = {}
+            self.outbox, self.work = {}, []
 
-        def round(self, r):
-            work = [v for v in range(lo, hi) if self.d[v] < self.prev[v - lo]]
-            self.seeds[r] = len(work)
+        def seed(self, r):
+            self.deliver()  # the previous solve's candidates have landed (the kernel's peer red.min + the barrier)
+            self.work = [v for v in range(lo, hi) if self.d[v] < self.prev[v - lo]]
+            self.seeds[r] = len(self.work)
+
+        def solve(self, r):
+            work = self.work
             self.outbox = {}
             while work:  # symmetric grid: row v lists v's neighbours
                 v = work.pop()
@@ -237,13 +241,18 @@ def _sssp_worker(rank, world, port, out_dir):
                             self.outbox[t] = c
 
         def reduce_seeds(self, r):
+            dist.all_reduce(self.seeds[r:r + 1], op=dist.ReduceOp.SUM)
+
+        def barrier(self, r):
+            dist.barrier()
+
+        def deliver(self):
             boxes = [None] * world
             dist.all_gather_object(boxes, self.outbox)
             for b in boxes:
                 for t, c in b.items():
                     if lo <= t < hi and c < self.d[t]:
                         self.d[t] = c
-            dist.all_reduce(self.seeds[r:r + 1], op=dist.ReduceOp.SUM)
 
         def read_seeds(self, r):
             return int(self.seeds[r])

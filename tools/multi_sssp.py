@@ -21,7 +21,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-def run(width, height, check, seed=0x5EED0004, source=0, repeat=2, ctx=None):
+def run(width, height, check, seed=0x5EED0004, source=0, repeat=2, ctx=None, window=None):
     import torch
     import torch.distributed as dist
 
@@ -47,7 +47,8 @@ def run(width, height, check, seed=0x5EED0004, source=0, repeat=2, ctx=None):
         G.free()
     else:
         Gl = G
-    be, st = multi.partitioned_sssp(ctx, Gl, bounds, rank, world, source, dist=dist, torch=torch, repeat=repeat)
+    be, st = multi.partitioned_sssp(ctx, Gl, bounds, rank, world, source, window_buckets=window, dist=dist, torch=torch,
+                                    repeat=repeat)
     t = torch.tensor([st["ms"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -55,7 +56,7 @@ def run(width, height, check, seed=0x5EED0004, source=0, repeat=2, ctx=None):
     out = {"graph": f"2-D grid {width}x{height} 4-neighbour, integer weights 1..255", "n": n, "nnz": nnz, "n_gpus": world,
            "schedule": "row-partitioned block-asynchronous near-far; boundary candidates as red.min into the owner's dist "
                        "over peer mappings, one 8-byte all-reduce per round",
-           "rounds": st["rounds"], "converged": bool(st["converged"]), "reached": st["reached"], "ms": ms,
+           "window_buckets": be.window, "rounds": st["rounds"], "converged": bool(st["converged"]), "reached": st["reached"], "ms": ms,
            "gteps": st["edges_traversed"] / (ms * 1e6), "local_rows": hi - lo, "local_nnz": Gl.info.nnz}
     if check:
         from oracle import oracle as orc  # checker only
@@ -77,8 +78,9 @@ def main():
     ap.add_argument("--height", type=int, default=1024)
     ap.add_argument("--source", type=int, default=0)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--window", type=float, default=None, help="distance window of a round in near-far buckets (0 = none)")
     a = ap.parse_args()
-    out, rank, world = run(a.width, a.height, a.check, source=a.source)
+    out, rank, world = run(a.width, a.height, a.check, source=a.source, window=a.window)
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:

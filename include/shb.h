@@ -162,6 +162,15 @@ int shb_spmv_host(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch
                   const void *y_host /* NULL when beta makes y irrelevant */, const void *alpha, const void *beta,
                   void *out_host, uint64_t *total_ns, uint64_t *kernel_ns);
 
+/* A batch of n_vec host vectors through the same resident operator (the trial loop of app/spmv.cpp:52-98 with a
+ * fresh x per trial, or several right-hand sides): x_{i+1} is uploaded while SpMV i runs and result i-1 is
+ * downloaded (three streams, double-buffered staging).  Every step still uploads its own x (and y) and downloads
+ * its own result; *total_ns spans the first upload to the last download.  y_hosts may be NULL when beta makes y
+ * irrelevant. */
+int shb_spmv_host_batch(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, int n_vec,
+                        const void *const *x_hosts, const void *const *y_hosts, const void *alpha, const void *beta,
+                        void *const *out_hosts, uint64_t *total_ns);
+
 /* ---- device-resident fixed-point iteration (<- app/{sssp,bfs,pr,scc}.cpp executeRun) ------------
  * x_{k+1} = KERNEL(x_k, y_k); y_0 = y0, y_k = x_k afterwards when y_rebind (app/sssp.cpp:150, Q9).
  * term_mode 0: stop when all |x_k[i]-x_{k+1}[i]| < delta (sssp, pr); 1: all equal (bfs, scc).

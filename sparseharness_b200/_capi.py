@@ -82,6 +82,8 @@ SIGNATURES = {
                            C.c_void_p, C.c_void_p, u64p]),
     "shb_spmv_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_void_p, C.c_void_p, u64p, u64p]),
+    "shb_spmv_host_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_int, c_void_pp, c_void_pp,
+                                      C.c_void_p, C.c_void_p, c_void_pp, u64p]),
     "shb_iterate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_int, C.c_uint32, C.c_uint32, u64p, u32p,
                               i32p, u64p]),

@@ -252,6 +252,19 @@ class Context:
                               _ptr(out), C.byref(tot), C.byref(ker)))
         return tot.value, ker.value
 
+    def spmv_host_batch(self, A: Csr, semiring, xs: list[np.ndarray], ys: list[np.ndarray] | None, alpha, beta,
+                        outs: list[np.ndarray], cfg: LaunchCfg | None = None) -> int:
+        """Pipelined batch of host vectors (upload i+1 / SpMV i / download i-1 overlap); returns total device ns."""
+        a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
+        n = len(xs)
+        xa = (C.c_void_p * n)(*[x.ctypes.data for x in xs])
+        oa = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+        ya = (C.c_void_p * n)(*[y.ctypes.data for y in ys]) if ys is not None else None
+        tot = C.c_uint64(0)
+        _ck(lib.shb_spmv_host_batch(self.h, A.h, semiring, C.byref(cfg) if cfg else None, n, xa, ya, _ptr(a), _ptr(b), oa,
+                                    C.byref(tot)))
+        return tot.value
+
     def spmv_scatter(self, A: Csr, semiring, x: Buffer, y: Buffer | None, alpha, beta, dst: list[Buffer], row_offset,
                      delta=0.0, term=TERM_ABSDIFF, changed: Buffer | None = None, cfg: LaunchCfg | None = None,
                      timed=False, prev_changed: Buffer | None = None) -> int:

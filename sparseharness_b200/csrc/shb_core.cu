@@ -120,6 +120,10 @@ SHB_API int shb_ctx_destroy(shb_ctx *c) {
   for (int i = 0; i < 3; ++i) cudaFree(c->stage[i]);
   for (int i = 0; i < 4; ++i)
     if (c->hv[i]) cudaEventDestroy(c->hv[i]);
+  for (int i = 0; i < 8; ++i)
+    if (c->chunk_ev[i]) cudaEventDestroy(c->chunk_ev[i]);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->h2d_stream) cudaStreamDestroy(c->h2d_stream);
   if (c->owns_stream) cudaStreamDestroy(c->stream);
   delete c;
   return SHB_OK;
@@ -862,16 +866,110 @@ SHB_API int shb_spmv_host(shb_ctx *c, const shb_csr *A, int semiring, const shb_
     }
     SHB_REQUIRE(!needs, "y is required for this semiring / beta");
   }
-  SHB_TRY(shb_launch_spmv(c, A, semiring, cfg, x, y, alpha, beta, outs, 1, 0, ctl));
-  SHB_CUDA(cudaEventRecord(c->hv[2], c->stream));
-  SHB_CUDA(cudaMemcpyAsync(out_host, out, (size_t)A->n_rows * 4, cudaMemcpyDeviceToHost, c->stream));
-  SHB_CUDA(cudaEventRecord(c->hv[3], c->stream));
+  // Row-major schedules on a large operator: the rows are launched in SHB_HOST_CHUNKS slabs and each slab's result
+  // goes back to the host on a second stream while the next slab computes (the D2H copy hides behind the kernel).
+  shb_launch_cfg d = {};
+  if (cfg) d = *cfg;
+  const int variant = d.variant == SHB_VARIANT_AUTO ? A->auto_variant : d.variant;
+  const bool sliceable = (variant == SHB_VARIANT_VECTOR || variant == SHB_VARIANT_SCALAR) && A->nnz > 0;
+  const int n_chunks = (sliceable && A->n_rows >= (1 << 20) && !getenv("SHB_HOST_NO_OVERLAP")) ? SHB_HOST_CHUNKS : 1;
+  if (n_chunks == 1) {
+    SHB_TRY(shb_launch_spmv(c, A, semiring, cfg, x, y, alpha, beta, outs, 1, 0, ctl));
+    SHB_CUDA(cudaEventRecord(c->hv[2], c->stream));
+    SHB_CUDA(cudaMemcpyAsync(out_host, out, (size_t)A->n_rows * 4, cudaMemcpyDeviceToHost, c->stream));
+    SHB_CUDA(cudaEventRecord(c->hv[3], c->stream));
+  } else {
+    if (!c->copy_stream) SHB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < SHB_HOST_CHUNKS; ++i)
+      if (!c->chunk_ev[i]) SHB_CUDA(cudaEventCreateWithFlags(&c->chunk_ev[i], cudaEventDisableTiming));
+    const int64_t per = (A->n_rows + n_chunks - 1) / n_chunks / 32 * 32;
+    for (int k = 0; k < n_chunks; ++k) {
+      const int64_t r0 = per * k, r1 = k == n_chunks - 1 ? A->n_rows : per * (k + 1);
+      shb_csr S = *A;  // shallow view of rows [r0, r1): row_ptr values stay absolute, outputs land at r0 + r
+      S.row_ptr = A->row_ptr + r0;
+      S.n_rows = r1 - r0;
+      shb_launch_cfg dk = d;
+      dk.variant = variant;
+      if (dk.lanes <= 0) dk.lanes = A->auto_lanes;
+      SHB_TRY(shb_launch_spmv(c, &S, semiring, &dk, x, y, alpha, beta, outs, 1, r0, ctl));
+      SHB_CUDA(cudaEventRecord(c->chunk_ev[k], c->stream));
+      SHB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->chunk_ev[k], 0));
+      SHB_CUDA(cudaMemcpyAsync((char *)out_host + r0 * 4, (char *)out + r0 * 4, (size_t)(r1 - r0) * 4, cudaMemcpyDeviceToHost,
+                               c->copy_stream));
+    }
+    SHB_CUDA(cudaEventRecord(c->hv[2], c->stream));  // end of the last slab's kernel
+    SHB_CUDA(cudaEventRecord(c->chunk_ev[0], c->copy_stream));
+    SHB_CUDA(cudaStreamWaitEvent(c->stream, c->chunk_ev[0], 0));  // the call's stream owns the completion again
+    SHB_CUDA(cudaEventRecord(c->hv[3], c->stream));
+  }
   SHB_CUDA(cudaEventSynchronize(c->hv[3]));
   float ms = 0.f, kms = 0.f;
   SHB_CUDA(cudaEventElapsedTime(&ms, c->hv[0], c->hv[3]));
   SHB_CUDA(cudaEventElapsedTime(&kms, c->hv[1], c->hv[2]));
   if (total_ns) *total_ns = (uint64_t)((double)ms * 1e6 + 0.5);
   if (kernel_ns) *kernel_ns = (uint64_t)((double)kms * 1e6 + 0.5);
+  return SHB_OK;
+}
+
+// A batch of host vectors through the same operator (the harness's trial loop with a fresh x per trial, or several
+// right-hand sides): x_{i+1} is uploaded while SpMV i runs and out_{i-1} goes back -- three streams, double-buffered
+// device staging, PCIe busy in both directions under the kernel.  Every step still moves its own x to the device
+// and its own result to the host; *total_ns covers the first upload to the last download.
+SHB_API int shb_spmv_host_batch(shb_ctx *c, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, int n_vec,
+                                const void *const *x_hosts, const void *const *y_hosts, const void *alpha, const void *beta,
+                                void *const *out_hosts, uint64_t *total_ns) {
+  SHB_REQUIRE(c && A && x_hosts && out_hosts && alpha && beta && n_vec >= 1, "bad arguments");
+  SHB_CUDA(cudaSetDevice(c->device));
+  if (!y_hosts) {
+    bool needs = true;
+    switch (semiring) {
+      case SHB_PLUS_TIMES_F32: needs = PlusTimesF32::needs_y(*(const float *)beta); break;
+      case SHB_OR_AND_I32: needs = OrAndI32::needs_y(*(const int32_t *)beta); break;
+      case SHB_MAX_MIN_I32: needs = MaxMinI32::needs_y(*(const int32_t *)beta); break;
+      default: needs = true;
+    }
+    SHB_REQUIRE(!needs, "y is required for this semiring / beta");
+  }
+  const size_t xb = ((size_t)std::max<int64_t>(A->n_cols, 1) * 4 + 255) / 256 * 256;
+  const size_t rb = ((size_t)std::max<int64_t>(A->n_rows, 1) * 4 + 255) / 256 * 256;
+  SHB_TRY(stage_reserve(c, 0, 2 * xb));
+  SHB_TRY(stage_reserve(c, 2, 2 * rb));
+  if (y_hosts) SHB_TRY(stage_reserve(c, 1, 2 * rb));
+  if (!c->copy_stream) SHB_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  if (!c->h2d_stream) SHB_CUDA(cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 4; ++i)
+    if (!c->hv[i]) SHB_CUDA(cudaEventCreate(&c->hv[i]));
+  for (int i = 0; i < 8; ++i)
+    if (!c->chunk_ev[i]) SHB_CUDA(cudaEventCreateWithFlags(&c->chunk_ev[i], cudaEventDisableTiming));
+  cudaEvent_t *x_ready = &c->chunk_ev[0], *k_done = &c->chunk_ev[2], *d_done = &c->chunk_ev[4];  // [2] each
+  IterCtl ctl = {nullptr, nullptr, 0.0, 0};
+  SHB_CUDA(cudaEventRecord(c->hv[0], c->stream));
+  SHB_CUDA(cudaStreamWaitEvent(c->h2d_stream, c->hv[0], 0));  // earlier work of the context precedes the batch
+  for (int i = 0; i < n_vec; ++i) {
+    SHB_REQUIRE(x_hosts[i] && out_hosts[i] && (!y_hosts || y_hosts[i]), "null host vector in the batch");
+    const int b = i & 1;
+    char *x = (char *)c->stage[0] + b * xb, *out = (char *)c->stage[2] + b * rb;
+    char *y = y_hosts ? (char *)c->stage[1] + b * rb : x;
+    if (i >= 2) SHB_CUDA(cudaStreamWaitEvent(c->h2d_stream, k_done[b], 0));  // SpMV i-2 has read this x / y slot
+    SHB_CUDA(cudaMemcpyAsync(x, x_hosts[i], (size_t)A->n_cols * 4, cudaMemcpyHostToDevice, c->h2d_stream));
+    if (y_hosts) SHB_CUDA(cudaMemcpyAsync(y, y_hosts[i], (size_t)A->n_rows * 4, cudaMemcpyHostToDevice, c->h2d_stream));
+    SHB_CUDA(cudaEventRecord(x_ready[b], c->h2d_stream));
+    SHB_CUDA(cudaStreamWaitEvent(c->stream, x_ready[b], 0));
+    if (i >= 2) SHB_CUDA(cudaStreamWaitEvent(c->stream, d_done[b], 0));  // result i-2 has left this out slot
+    void *outs[1] = {out};
+    SHB_TRY(shb_launch_spmv(c, A, semiring, cfg, x, y, alpha, beta, outs, 1, 0, ctl));
+    SHB_CUDA(cudaEventRecord(k_done[b], c->stream));
+    SHB_CUDA(cudaStreamWaitEvent(c->copy_stream, k_done[b], 0));
+    SHB_CUDA(cudaMemcpyAsync(out_hosts[i], out, (size_t)A->n_rows * 4, cudaMemcpyDeviceToHost, c->copy_stream));
+    SHB_CUDA(cudaEventRecord(d_done[b], c->copy_stream));
+  }
+  SHB_CUDA(cudaStreamWaitEvent(c->stream, d_done[(n_vec - 1) & 1], 0));
+  if (n_vec >= 2) SHB_CUDA(cudaStreamWaitEvent(c->stream, d_done[(n_vec - 2) & 1], 0));
+  SHB_CUDA(cudaEventRecord(c->hv[3], c->stream));
+  SHB_CUDA(cudaEventSynchronize(c->hv[3]));
+  float ms = 0.f;
+  SHB_CUDA(cudaEventElapsedTime(&ms, c->hv[0], c->hv[3]));
+  if (total_ns) *total_ns = (uint64_t)((double)ms * 1e6 + 0.5);
   return SHB_OK;
 }
 

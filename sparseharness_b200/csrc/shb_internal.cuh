@@ -51,7 +51,11 @@ struct shb_ctx {
   void *stage[3] = {nullptr, nullptr, nullptr};
   size_t stage_bytes[3] = {0, 0, 0};
   cudaEvent_t hv[4] = {nullptr, nullptr, nullptr, nullptr};
+  // second stream + events of the host-vector entry point: result slabs go back while the next slab computes
+  cudaStream_t copy_stream = nullptr, h2d_stream = nullptr;
+  cudaEvent_t chunk_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
+static const int SHB_HOST_CHUNKS = 8;
 static const int SHB_FLAG_SLOTS = 1024;
 
 struct shb_buf {

@@ -160,6 +160,49 @@ def test_host_vector_entry_point(ctx, orc):
     assert np.array_equal(out, orc.spmv(orc.PLUS_TIMES, rp, col, val, x, y, 1.0, 2.0)) and tot >= ker > 0
 
 
+@pytest.mark.parametrize("semiring,cfg", [(shb.PLUS_TIMES, {}), (shb.PLUS_TIMES, dict(variant=shb.VARIANT_SCALAR)),
+                                          (shb.MIN_PLUS, dict(variant=shb.VARIANT_VECTOR, lanes=8)),
+                                          (shb.PLUS_TIMES, dict(variant=shb.VARIANT_STREAM))])
+def test_host_vector_entry_point_large_operator_is_slabbed(ctx, orc, semiring, cfg):
+    """>= 2^20 rows: the row-major schedules run in row slabs whose results go back to the host on a second stream
+    while the next slab computes; same bits as the device-vector call (ragged last slab, y read at r0 + r)."""
+    n = (1 << 20) + 77
+    A = ctx.synth_uniform(n, n, 4, val_mode=1)
+    x = orc.xmode_vector(n, 1)
+    y = (np.arange(n) % 7).astype(np.float32)
+    out = np.full(n, -1, np.float32)
+    lc = shb.launch_cfg(**cfg)
+    tot, ker = ctx.spmv_host(A, semiring, x, y, 1.0, 2.0, out, lc)
+    xb, yb, ob = ctx.array(x), ctx.array(y), ctx.empty(n * 4)
+    ctx.spmv(A, semiring, xb, yb, 1.0, 2.0, ob, lc)
+    assert np.array_equal(out, ob.download(np.float32, n)) and tot >= ker > 0
+    rp, col, val = A.download(n - 300, 300)
+    want = orc.spmv(semiring, rp, col, val, x, y[n - 300:], 1.0, 2.0)
+    assert np.array_equal(out[n - 300:], want)
+
+
+@pytest.mark.parametrize("n_vec,with_y", [(1, True), (2, False), (5, True), (6, False)])
+def test_host_vector_batch_is_pipelined_and_exact(ctx, orc, n_vec, with_y):
+    """shb_spmv_host_batch: every vector of the batch gets its own x (and y) and its own result, bit for bit what the
+    one-vector call gives, whatever the double-buffer slot it went through."""
+    n = 6001
+    rp, col, val = orc.gen_uniform(n, n, 9, val_mode=1)
+    A = ctx.csr(n, n, rp, col, val)
+    rng = np.random.default_rng(n_vec)
+    xs = [rng.integers(-4, 5, n).astype(np.float32) for _ in range(n_vec)]
+    ys = [rng.integers(-4, 5, n).astype(np.float32) for _ in range(n_vec)] if with_y else None
+    outs = [np.full(n, np.nan, np.float32) for _ in range(n_vec)]
+    beta = 3.0 if with_y else 0.0
+    tot = ctx.spmv_host_batch(A, shb.PLUS_TIMES, xs, ys, 2.0, beta, outs)
+    assert tot > 0
+    for i in range(n_vec):
+        want = orc.spmv(orc.PLUS_TIMES, rp, col, val, xs[i], ys[i] if with_y else np.zeros(n, np.float32), 2.0, beta)
+        assert np.array_equal(outs[i], want), i
+    if not with_y:
+        with pytest.raises(shb.ShbError):
+            ctx.spmv_host_batch(A, shb.PLUS_TIMES, xs, None, 2.0, 1.0, outs)  # beta != 0 needs y
+
+
 def test_argument_validation(ctx):
     A = ctx.csr(4, 4, np.array([0, 1, 2, 3, 4]), np.array([0, 1, 2, 3], np.int32), np.ones(4, np.float32))
     x, out = ctx.array(np.ones(4, np.float32)), ctx.empty(16)

@@ -210,10 +210,21 @@ def graph_extras(ctx, shb, orc):
         G = ctx.synth_grid2d(8192, 8192, seed=0x5EED0004)
         info = G.info
         dist, st = ctx.sssp(G, 0, AT=G)
-        dist.free()
         r = {"graph": "2-D grid 8192x8192 4-neighbour, integer weights 1..255", "n": info.n_rows, "nnz": info.nnz,
              "rounds": st.iterations, "converged": bool(st.converged), "ms": st.total_ns / 1e6,
              "gteps": st.edges_traversed / st.total_ns}
+        # one dense min-plus sweep over the same operator (the reference's per-iteration launch, app/sssp.cpp:112-153):
+        # gathers are local here, so this is the HBM-bound face of the same SpMV kernels (SURVEY.md 8d, C4 bytes/sweep)
+        out = ctx.empty(info.n_rows * 4)
+        ts = [ctx.spmv(G, shb.MIN_PLUS, dist, dist, 0.0, 0.0, out) for _ in range(12)][2:]
+        ms = float(np.median(ts)) / 1e6
+        peak, _ = measured_peak_gbs()
+        r["dense_sweep"] = {"ms": ms, "algorithmic_bytes": info.algorithmic_bytes_spmv,
+                            "effective_gbs": info.algorithmic_bytes_spmv / ms / 1e6,
+                            "frac_of_measured_hbm_peak": info.algorithmic_bytes_spmv / ms / 1e6 / peak,
+                            "kernel": f"variant={info.auto_variant} lanes={info.auto_lanes} (auto), min-plus, y = x"}
+        out.free()
+        dist.free()
         G.free()
         return r
 

@@ -1,5 +1,6 @@
 #!/bin/bash
-# ncu evidence for the dominant kernel of bench.py (launch list + one full capture).  Plain run first.
+# ncu evidence for the dominant kernel of bench.py (launch list + one full capture) and for the HBM-bound case
+# (dense min-plus sweep over the config-4 grid).  Plain runs first; numbers printed under ncu are never bench values.
 mkdir -p gpurun_out
 CMD="python bench.py --steps 5 --warmup 3 --extras 0 --cpu-steps 3"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -20 gpurun_out/plain.log; exit 1; }
@@ -7,4 +8,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 echo "launch list rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:spmv_vector_kernel -s 3 -c 2 -o gpurun_out/prof_spmv $CMD > gpurun_out/ncu_full.log 2>&1
 echo "full capture rc=$?"
-ls -la gpurun_out
+python tools/grid_sweep.py 8192 auto > gpurun_out/grid_plain.log 2>&1 || { echo "grid plain run failed"; tail -5 gpurun_out/grid_plain.log; }
+ncu --set full --clock-control none --import-source on -k regex:spmv_stream_kernel -s 4 -c 2 -o gpurun_out/prof_grid_stream python tools/grid_sweep.py 8192 auto > gpurun_out/ncu_grid.log 2>&1
+echo "grid capture rc=$?"
+ls -la gpurun_out | head -40

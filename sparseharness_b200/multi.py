@@ -530,16 +530,22 @@ class SsspBackend:
         raise NotImplementedError
 
 
-def run_sssp(backend: SsspBackend, max_rounds: int = 1 << 16):
+def run_sssp(backend: SsspBackend, max_rounds: int = 1 << 16, check_every: int = 8):
     """Rounds until a seed pass finds nothing on any rank (then that round's solves did nothing either: fixed point).
-    Returns (rounds_with_work, converged)."""
-    for r in range(max_rounds):
-        backend.seed(r)
-        backend.reduce_seeds(r)  # global seed count and smallest pending distance of this round
-        backend.solve(r)         # enqueued before the host looks at the count: a solve without seeds returns at once
-        backend.barrier(r)       # all peer candidates of this round have landed before anyone's next seed pass
-        if backend.read_seeds(r) == 0:
-            return r, True
+    `check_every` rounds are enqueued per host poll, so the host's launch work overlaps the device's rounds; rounds
+    enqueued past the fixed point find no seeds and return at once.  Returns (rounds_with_work, converged)."""
+    done = 0
+    while done < max_rounds:
+        batch = min(check_every, max_rounds - done)
+        for r in range(done, done + batch):
+            backend.seed(r)
+            backend.reduce_seeds(r)  # global seed count and smallest pending distance of this round
+            backend.solve(r)         # a solve without seeds returns at once
+            backend.barrier(r)       # all peer candidates of this round have landed before anyone's next seed pass
+        for r in range(done, done + batch):
+            if backend.read_seeds(r) == 0:
+                return r, True
+        done += batch
     return max_rounds, False
 
 
@@ -679,8 +685,8 @@ class EmulatedSsspPartition(SsspBackend):
                                                   offset=4 * int(self.bounds[k])) for k in range(self.P)])
 
 
-def partitioned_sssp(ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, window_buckets=None, dist=None,
-                     torch=None, repeat=1):
+def partitioned_sssp(ctx, AT_local, bounds, rank, world, source, *, max_rounds=4096, window_buckets=None, check_every=8,
+                     dist=None, torch=None, repeat=1):
     """SSSP distances on a row-partitioned operator.  Returns (backend, stats) with stats = dict(rounds, converged,
     reached, edges_traversed [all ranks], ms [this rank's device time])."""
     be = GpuSsspPartition(ctx, AT_local, bounds, rank, world, source, max_rounds=max_rounds,
@@ -691,7 +697,7 @@ def partitioned_sssp(ctx, AT_local, bounds, rank, world, source, *, max_rounds=4
             be.reset()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
-        rounds, conv = run_sssp(be, max_rounds)
+        rounds, conv = run_sssp(be, max_rounds, check_every)
         ev1.record()
         torch.cuda.synchronize()
         ms = ev0.elapsed_time(ev1)

@@ -21,7 +21,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-def run(width, height, check, seed=0x5EED0004, source=0, repeat=2, ctx=None, window=None):
+def run(width, height, check, seed=0x5EED0004, source=0, repeat=2, ctx=None, window=None, check_every=8):
     import torch
     import torch.distributed as dist
 
@@ -47,7 +47,7 @@ def run(width, height, check, seed=0x5EED0004, source=0, repeat=2, ctx=None, win
         G.free()
     else:
         Gl = G
-    be, st = multi.partitioned_sssp(ctx, Gl, bounds, rank, world, source, window_buckets=window, dist=dist, torch=torch,
+    be, st = multi.partitioned_sssp(ctx, Gl, bounds, rank, world, source, window_buckets=window, check_every=check_every, dist=dist, torch=torch,
                                     repeat=repeat)
     t = torch.tensor([st["ms"]], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -78,9 +78,10 @@ def main():
     ap.add_argument("--height", type=int, default=1024)
     ap.add_argument("--source", type=int, default=0)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--check-every", type=int, default=8)
     ap.add_argument("--window", type=float, default=None, help="distance window of a round in near-far buckets (0 = none)")
     a = ap.parse_args()
-    out, rank, world = run(a.width, a.height, a.check, source=a.source, window=a.window)
+    out, rank, world = run(a.width, a.height, a.check, source=a.source, window=a.window, check_every=a.check_every)
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:

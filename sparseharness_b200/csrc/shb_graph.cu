@@ -1139,7 +1139,7 @@ SHB_API int shb_csr_row_lengths(shb_ctx *c, const shb_csr *A, shb_buf *out) {
 static int bfs_block_check(const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total) {
   SHB_REQUIRE(A->n_cols == n_total, "the block's column space must be the whole vertex set");
   SHB_REQUIRE(row_offset >= 0 && row_offset + A->n_rows <= n_total, "row block outside the vertex set");
-  SHB_REQUIRE((row_offset & 31) == 0, "row_offset must be a multiple of 32 (a bitmap word has one owner)");
+  SHB_REQUIRE(A->n_rows == 0 || (row_offset & 31) == 0, "row_offset must be a multiple of 32 (a bitmap word has one owner)");
   SHB_REQUIRE((A->n_rows & 31) == 0 || row_offset + A->n_rows == n_total, "only the last block may end off a word boundary");
   SHB_REQUIRE(!AT || (AT->n_rows == A->n_rows && AT->n_cols == n_total), "the push-side block does not match");
   return SHB_OK;

@@ -237,3 +237,25 @@ def test_two_gpu_sssp_matches_oracle(source, window):
            "--height", "200", "--source", str(source), "--check"] + (["--window", str(window)] if window is not None else [])
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+
+
+def test_emulated_partitions_with_empty_blocks(ctx, orc):
+    """More blocks than 32-vertex words: the trailing blocks own nothing and must still take part in every level /
+    round (BFS and SSSP), as a rank with no rows does on a small graph."""
+    from sparseharness_b200 import multi
+    rp, col, val = orc.gen_grid2d(10, 10)
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, val)
+    bounds = multi.word_aligned_bounds(np.array([0, 20, 40, 60, 80, 100, 100]))
+    assert list(bounds) == [0, 32, 64, 64, 96, 100, 100]
+    blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(6)]
+    deg = A.row_lengths()
+    P = ctx.csr(n, n, rp, col, None)
+    pblocks = [P.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(6)]
+    be = multi.EmulatedBfsPartition(ctx, pblocks, bounds, 55, len(col), at_blocks=pblocks, deg=deg)
+    n_levels, _, _ = multi.run_bfs(be, 1 << 20, 5)
+    want, nlev, edges = orc.bfs_levels(rp, col, None, 55)
+    assert np.array_equal(be.result(), want) and n_levels == nlev and be.stats() == (n, edges)
+    bs = multi.EmulatedSsspPartition(ctx, blocks, bounds, 55, window_buckets=1.0)
+    rounds, conv = multi.run_sssp(bs, 4096, 3)
+    assert conv and np.array_equal(bs.result(), orc.sssp(rp, col, val, 55))

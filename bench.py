@@ -387,7 +387,11 @@ def run_ours(args):
         "gflops": FLOPS * n_gpus / (ms_per_step * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
                      "traffic": None, "peak_source": peak_src, "kernel": "spmv_vector_kernel<PlusTimesF32,4,2,true,true>",
-                     "note": "achieved = 2348810244 B / mean launch time over the timed region (CUDA events on the launch stream)"},
+                     "note": "achieved = 2348810244 B / mean launch time over the timed region (CUDA events on the launch stream)",
+                     "binding_unit": "not HBM on this operator: every one of the 268M uniform-random x gathers is its own "
+                                     "L1TEX->XBAR request (ncu: l1tex__m_l1tex2xbar_req_cycles_active 90%, lts__throughput 85%, "
+                                     "dram 42%; profiles/r01_summary.md); the same kernels with local gathers are HBM-bound, "
+                                     "see roofline_local_gathers"},
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": N_COLS * 4, "d2h_bytes_per_step": ROWS_PER_GPU * 4,
                 "ms_per_step": e2e_ms / Ke, "steps": Ke,
                 "api": "shb_spmv_host_batch: one call for all steps; every step uploads its x from pinned host memory and "

@@ -156,6 +156,33 @@ __global__ void bfs_push_big_kernel(BfsState *st, const int32_t *__restrict__ at
   bfs_push_account3(st, found, push_deg, pull_deg);
 }
 
+// does row [s, e) have an in-neighbour in the frontier bitmap?  BFS_PROBE_BATCH entries per step: the column loads and the
+// bitmap probes of a step are issued together, so a row costs e/BATCH dependent round trips instead of e (the early exit
+// makes every step wait for its probes).
+#ifndef BFS_PROBE_BATCH
+#define BFS_PROBE_BATCH 4
+#endif
+template <bool HAS_VAL>
+__device__ __forceinline__ bool bfs_row_hits(const int32_t *__restrict__ col, const int32_t *__restrict__ val,
+                                             const uint32_t *__restrict__ cur, int s, int e) {
+  for (int k = s; k < e; k += BFS_PROBE_BATCH) {
+    int32_t c[BFS_PROBE_BATCH];
+    uint32_t w[BFS_PROBE_BATCH];
+#pragma unroll
+    for (int j = 0; j < BFS_PROBE_BATCH; ++j) {
+      const bool in = (k + j < e) && !(HAS_VAL && val[k + j] == 0);  // bool_and(x, a): a stored 0 is no edge
+      c[j] = in ? col[k + j] : -1;
+    }
+#pragma unroll
+    for (int j = 0; j < BFS_PROBE_BATCH; ++j) w[j] = c[j] >= 0 ? cur[c[j] >> 5] : 0u;
+    bool hit = false;
+#pragma unroll
+    for (int j = 0; j < BFS_PROBE_BATCH; ++j) hit |= (c[j] >= 0) && ((w[j] >> (c[j] & 31)) & 1u);
+    if (hit) return true;
+  }
+  return false;
+}
+
 // pull: thread per unvisited row, stop at the first in-neighbour that is in the frontier bitmap
 template <bool HAS_VAL>
 __global__ void bfs_pull_kernel(BfsState *st, const int32_t *__restrict__ a_row_ptr, const int32_t *__restrict__ a_col,
@@ -173,14 +200,7 @@ __global__ void bfs_pull_kernel(BfsState *st, const int32_t *__restrict__ a_row_
     bool found = false;
     if (r < n && levels[r] == -1) {
       const int s = a_row_ptr[r], e = a_row_ptr[r + 1];
-      for (int k = s; k < e; ++k) {
-        if (HAS_VAL && a_val[k] == 0) continue;
-        const int32_t c = a_col[k];
-        if ((cur[c >> 5] >> (c & 31)) & 1u) {
-          found = true;
-          break;
-        }
-      }
+      found = bfs_row_hits<HAS_VAL>(a_col, a_val, cur, s, e);
       if (found) {
         levels[r] = (int32_t)level + 1;
         ++found_n;
@@ -984,16 +1004,7 @@ __global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__
       s = row_ptr[r];
       e = row_ptr[r + 1];
       big = (e - s) >= BFS_BLOCK_BIG_ROW;
-      if (!big) {
-        for (int k = s; k < e; ++k) {
-          if (HAS_VAL && val[k] == 0) continue;
-          const int32_t c = col[k];
-          if ((cur[c >> 5] >> (c & 31)) & 1u) {
-            found = true;
-            break;
-          }
-        }
-      }
+      if (!big) found = bfs_row_hits<HAS_VAL>(col, val, cur, s, e);
     }
     // hub rows: the whole warp scans, 32 entries per step, until one lane sees a frontier neighbour
     uint32_t bigs = __ballot_sync(0xffffffffu, big);

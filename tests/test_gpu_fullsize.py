@@ -90,3 +90,53 @@ def test_config3_bfs_scale20_properties(ctx, orc):
     rows = np.repeat(np.arange(n), np.diff(rp))
     reached = lv[rows] >= 0
     assert (lv[col][reached] >= 0).all() and np.abs(lv[rows][reached] - lv[col][reached]).max() <= 1
+
+
+def test_config3_full_size_partitioned_bfs_agrees_with_single_device(ctx):
+    """RMAT scale 24 (config 3 at BASELINE's size): the row-partitioned BFS on 4 blocks (kernels and protocol of the
+    multi-GPU path, blocks emulated on this device) gives the levels of the single-device direction-optimising
+    driver -- two independent implementations -- and every edge spans at most one level."""
+    from sparseharness_b200 import multi
+    A = ctx.synth_rmat(24, 16, seed=0x5EED0024, symmetrise=True)
+    info = A.info
+    n = info.n_rows
+    rp_head = A.download(0, 4096)[0]
+    root = int(np.argmax(np.diff(rp_head) > 0))
+    levels, st = ctx.bfs(A, root, AT=A)
+    want = levels.download(np.int32, n)
+    levels.free()
+    deg = A.row_lengths()
+    bounds = multi.word_aligned_bounds(A.balance_rows(4))
+    blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(4)]
+    be = multi.EmulatedBfsPartition(ctx, blocks, bounds, root, info.nnz, at_blocks=blocks, deg=deg)
+    n_levels, _, _ = multi.run_bfs(be, 1 << 20, 8)
+    got = be.result()
+    assert n_levels == st.iterations and np.array_equal(got, want)
+    assert be.stats() == (st.reached, st.edges_traversed)
+    # size-independent property on a row sample: neighbours of a reached vertex are reached, one level apart at most
+    rp, col, _ = A.download(n // 2, 1 << 16)
+    rows = np.repeat(np.arange(n // 2, n // 2 + (1 << 16)), np.diff(rp))
+    r = got[rows] >= 0
+    assert (got[col][r] >= 0).all() and (np.abs(got[rows][r] - got[col][r]) <= 1).all()
+
+
+def test_config4_full_size_partitioned_sssp_agrees_with_single_device(ctx):
+    """8192 x 8192 grid (config 4 at BASELINE's size): block-asynchronous near-far on 2 blocks with distance windows ==
+    the single-device near-far kernel, bit for bit; Bellman optimality on a row sample."""
+    from sparseharness_b200 import multi
+    G = ctx.synth_grid2d(8192, 8192)
+    n = G.info.n_rows
+    dist, st = ctx.sssp(G, 0, AT=G)
+    want = dist.download(np.float32, n)
+    dist.free()
+    bounds = G.balance_rows(2)
+    blocks = [G.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(2)]
+    be = multi.EmulatedSsspPartition(ctx, blocks, bounds, 0, window_buckets=8.0)
+    rounds, conv = multi.run_sssp(be, 4096, 8)
+    got = be.result()
+    assert conv and rounds > 2 and np.array_equal(got, want)
+    assert be.stats_total() == (st.reached, st.edges_traversed)
+    lo = int(bounds[1]) - 4096  # rows either side of the block boundary
+    rp, col, val = G.download(lo, 8192)
+    cand = got[col] + val
+    assert np.array_equal(np.minimum.reduceat(cand, rp[:-1]), got[lo:lo + 8192])

@@ -241,13 +241,16 @@ int shb_spmv_scatter(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_lau
  * heuristic).  counters: int64 words: 0,1 = reached vertices / TEPS numerator of this rank (after finish),
  * 2 = arrival word of the peer barrier (monotonic: zero it once, when the buffer is created), 4,5 = staging,
  * slot F = words 6+2F, 7+2F = (vertices, push degrees) of frontier F summed over ranks.
- *   init     levels = -1, frontier0 = {root}, counters (but the arrival word) = 0; the root's owner reports
+ *   init     levels = -1, frontier0 = {root}, frontier1 = frontier2 = {}, counters (but the arrival word) = 0; the
+ *            three frontier bitmaps rotate: level L reads bitmap L % 3, builds (L+1) % 3 and zeroes (L+2) % 3 for
+ *            the level after (so no separate clearing pass and no store can race a clear); the root's owner reports
  *            frontier 0 -- into the staging words when `staged` (publish follows), else into slot 0.
  *   publish  adds the staged pair to `slot` of EVERY rank's counters (peer_counters[i], CUDA-IPC mappings) with
  *            system-scope atomics over NVLink and waits until barrier_target arrivals have been counted here
  *            (world x number of publishes so far; 0 = do not wait).  Needs all ranks past their init.
- *   level    enqueues decide / prep / push / pull / clear for `level` (frontier = bitmap level & 1, next[i] =
- *            every rank's bitmap (level+1) & 1, next[self_index] the local one) and, when peer_counters is given,
+ *   level    enqueues prep (direction decision + visited update + zeroing of `spare`) / push / pull for `level`
+ *            (frontier = bitmap level % 3, next[i] = every rank's bitmap (level+1) % 3, next[self_index] the local
+ *            one, spare = the local bitmap (level+2) % 3) and, when peer_counters is given,
  *            the publish of slot level+1 -- the whole level is kernels of this stream, the frontier and the counts
  *            travel as the kernels' own peer stores, no collective library on the path.  peer_counters == NULL:
  *            the counts land in the local slot level+1 and the caller all-reduces it (NCCL baseline).
@@ -257,13 +260,14 @@ int shb_csr_row_lengths(shb_ctx *ctx, const shb_csr *A, shb_buf *out /* int32 x 
 int shb_bfs_block_state_bytes(uint64_t *bytes);
 int shb_bfs_block_init(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
                        int64_t nnz_total, int64_t root, const shb_buf *deg, shb_buf *levels, shb_buf *frontier0,
-                       shb_buf *frontier1, shb_buf *visited, shb_buf *counters, shb_buf *state, int staged);
+                       shb_buf *frontier1, shb_buf *frontier2, shb_buf *visited, shb_buf *counters, shb_buf *state,
+                       int staged);
 int shb_bfs_block_publish(shb_ctx *ctx, uint32_t slot, shb_buf *counters, shb_buf *state, shb_buf *const *peer_counters,
                           int n_ranks, int self_index, uint64_t barrier_target);
 int shb_bfs_block_level(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
-                        uint32_t level, const shb_buf *deg, shb_buf *frontier, shb_buf *const *next, int n_next,
-                        int self_index, shb_buf *visited, shb_buf *levels, shb_buf *counters, shb_buf *state,
-                        shb_buf *const *peer_counters, uint64_t barrier_target);
+                        uint32_t level, const shb_buf *deg, const shb_buf *frontier, shb_buf *const *next, int n_next,
+                        int self_index, shb_buf *spare, shb_buf *visited, shb_buf *levels, shb_buf *counters,
+                        shb_buf *state, shb_buf *const *peer_counters, uint64_t barrier_target);
 int shb_bfs_block_finish(shb_ctx *ctx, const shb_csr *A, const shb_buf *levels, shb_buf *counters, const shb_buf *state);
 
 /* Row-partitioned SSSP (new capability; the reference's sssp app is single-device, app/sssp.cpp:97-155):

@@ -282,10 +282,10 @@ class Context:
         return b.value
 
     def bfs_block_init(self, A: Csr, AT: Csr | None, row_offset, n_total, nnz_total, root, deg: Buffer | None,
-                       levels: Buffer, bm0: Buffer, bm1: Buffer, visited: Buffer, counters: Buffer, state: Buffer,
-                       staged: bool = False):
+                       levels: Buffer, bm0: Buffer, bm1: Buffer, bm2: Buffer, visited: Buffer, counters: Buffer,
+                       state: Buffer, staged: bool = False):
         _ck(lib.shb_bfs_block_init(self.h, A.h, AT.h if AT else None, row_offset, n_total, nnz_total, root,
-                                   deg.h if deg else None, levels.h, bm0.h, bm1.h, visited.h, counters.h, state.h,
+                                   deg.h if deg else None, levels.h, bm0.h, bm1.h, bm2.h, visited.h, counters.h, state.h,
                                    int(staged)))
 
     def bfs_block_publish(self, slot, counters: Buffer, state: Buffer, peer_counters: list[Buffer], self_index: int,
@@ -295,13 +295,14 @@ class Context:
                                       barrier_target))
 
     def bfs_block_level(self, A: Csr, AT: Csr | None, row_offset, n_total, level, deg: Buffer | None, frontier: Buffer,
-                        nxt: list[Buffer], self_index: int, visited: Buffer, levels: Buffer, counters: Buffer,
-                        state: Buffer, peer_counters: list[Buffer] | None = None, barrier_target: int = 0):
+                        nxt: list[Buffer], self_index: int, spare: Buffer, visited: Buffer, levels: Buffer,
+                        counters: Buffer, state: Buffer, peer_counters: list[Buffer] | None = None,
+                        barrier_target: int = 0):
         arr = (C.c_void_p * len(nxt))(*[d.h for d in nxt])
         pc = (C.c_void_p * len(peer_counters))(*[d.h for d in peer_counters]) if peer_counters else None
         _ck(lib.shb_bfs_block_level(self.h, A.h, AT.h if AT else None, row_offset, n_total, level, deg.h if deg else None,
-                                    frontier.h, arr, len(nxt), self_index, visited.h, levels.h, counters.h, state.h, pc,
-                                    barrier_target))
+                                    frontier.h, arr, len(nxt), self_index, spare.h, visited.h, levels.h, counters.h,
+                                    state.h, pc, barrier_target))
 
     def bfs_block_finish(self, A: Csr, levels: Buffer, counters: Buffer, state: Buffer):
         _ck(lib.shb_bfs_block_finish(self.h, A.h, levels.h, counters.h, state.h))

@@ -849,34 +849,39 @@ struct BfsBlockState {
   int32_t big_list[BFS_PUSH_BIG_CAP];
 };
 
-__global__ void bfs_block_decide_kernel(BfsBlockState *st, const long long *counters, uint32_t level) {
-  st->big_count = 0;
-  if (st->done) return;
+// Start of a level, one launch: (a) thread 0 of block 0 applies Beamer's rule to the all-reduced (n_f, m_f) of the
+// current frontier -- the later kernels of the level read the mode it leaves in the state; every other thread derives
+// "the traversal is over" from the same counter slot, so nobody depends on when that store lands; (b) visited |=
+// frontier over the whole bitmap, and the owned words give their vertices the level; (c) the spare bitmap (the
+// frontier of two levels ago, the next frontier of the NEXT level) is zeroed: peers only start storing into it after
+// this level's barrier, which this rank joins after this kernel.
+__global__ void bfs_block_prep_kernel(BfsBlockState *st, const long long *counters, const uint32_t *__restrict__ cur,
+                                      uint32_t *visited, uint32_t *spare, int32_t *levels, uint32_t level, int64_t n_words,
+                                      int64_t word_lo, int64_t word_hi, int64_t row_offset, int64_t n_local) {
   const unsigned long long nf = (unsigned long long)counters[BFS_SLOT(level)];
-  const unsigned long long mf = (unsigned long long)counters[BFS_SLOT(level) + 1];
-  if (nf == 0) {
-    st->done = 1;
-    return;
-  }
-  st->unexplored = st->unexplored > mf ? st->unexplored - mf : 0ull;
-  if (st->have_push) {
-    if (st->mode == 0) {
-      if (mf > st->unexplored / 14ull) st->mode = 1;
-    } else {
-      if (nf < st->n_total / 24ull && nf < st->n_prev) st->mode = 0;
+  const bool done = (*(volatile uint32_t *)&st->done != 0u) || nf == 0;  // either order of thread 0's store: same value
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st->big_count = 0;
+    if (nf == 0) {
+      st->done = 1;
+    } else if (!done) {
+      const unsigned long long mf = (unsigned long long)counters[BFS_SLOT(level) + 1];
+      st->unexplored = st->unexplored > mf ? st->unexplored - mf : 0ull;
+      if (st->have_push) {
+        if (st->mode == 0) {
+          if (mf > st->unexplored / 14ull) st->mode = 1;
+        } else {
+          if (nf < st->n_total / 24ull && nf < st->n_prev) st->mode = 0;
+        }
+      } else {
+        st->mode = 1;
+      }
+      st->n_prev = nf;
     }
-  } else {
-    st->mode = 1;
   }
-  st->n_prev = nf;
-}
-
-// visited |= frontier over the whole bitmap; the owned words also give their vertices the level
-__global__ void bfs_block_prep_kernel(const BfsBlockState *st, const uint32_t *__restrict__ cur, uint32_t *visited,
-                                      int32_t *levels, uint32_t level, int64_t n_words, int64_t word_lo, int64_t word_hi,
-                                      int64_t row_offset, int64_t n_local) {
-  if (st->done) return;
+  if (done) return;
   for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (int64_t)gridDim.x * blockDim.x) {
+    spare[w] = 0u;
     uint32_t bits = cur[w];
     if (!bits) continue;
     visited[w] |= bits;
@@ -890,12 +895,6 @@ __global__ void bfs_block_prep_kernel(const BfsBlockState *st, const uint32_t *_
     }
   }
 }
-
-__global__ void bfs_block_clear_kernel(const BfsBlockState *st, uint32_t *bm, int64_t n_words) {
-  if (st->done) return;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (int64_t)gridDim.x * blockDim.x) bm[i] = 0u;
-}
-
 
 // one out-edge of a frontier vertex: mark the target in the local next bitmap and, if new here, in every peer's
 __device__ __forceinline__ void bfs_push_visit(int32_t v, const uint32_t *__restrict__ visited, const BfsPeers &next,
@@ -1180,13 +1179,15 @@ static int bfs_block_comm(shb_buf *counters, shb_buf *const *peer_counters, int 
 
 SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
                                int64_t nnz_total, int64_t root, const shb_buf *deg, shb_buf *levels, shb_buf *frontier0,
-                               shb_buf *frontier1, shb_buf *visited, shb_buf *counters, shb_buf *state, int staged) {
-  SHB_REQUIRE(c && A && levels && frontier0 && frontier1 && visited && counters && state, "bad arguments");
+                               shb_buf *frontier1, shb_buf *frontier2, shb_buf *visited, shb_buf *counters, shb_buf *state,
+                               int staged) {
+  SHB_REQUIRE(c && A && levels && frontier0 && frontier1 && frontier2 && visited && counters && state, "bad arguments");
   SHB_TRY(bfs_block_check(A, AT, row_offset, n_total));
   SHB_REQUIRE(root >= 0 && root < n_total, "root out of range");
   const uint64_t bm_bytes = (uint64_t)((n_total + 31) / 32) * 4;
   SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
-  SHB_REQUIRE(frontier0->bytes >= bm_bytes && frontier1->bytes >= bm_bytes && visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
+  SHB_REQUIRE(frontier0->bytes >= bm_bytes && frontier1->bytes >= bm_bytes && frontier2->bytes >= bm_bytes &&
+                  visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
   SHB_REQUIRE(!deg || deg->bytes >= (uint64_t)n_total * 4, "deg shorter than n_total");
   SHB_REQUIRE(state->bytes >= sizeof(BfsBlockState), "state too short");
   SHB_REQUIRE(counters->bytes >= (uint64_t)(BFS_SLOT(0) + 2) * 8, "counters too short");
@@ -1195,6 +1196,7 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
   if (A->n_rows > 0) SHB_CUDA(cudaMemsetAsync(levels->ptr, 0xff, (size_t)A->n_rows * 4, c->stream));
   SHB_CUDA(cudaMemsetAsync(frontier0->ptr, 0, (size_t)bm_bytes, c->stream));
   SHB_CUDA(cudaMemsetAsync(frontier1->ptr, 0, (size_t)bm_bytes, c->stream));
+  SHB_CUDA(cudaMemsetAsync(frontier2->ptr, 0, (size_t)bm_bytes, c->stream));
   SHB_CUDA(cudaMemsetAsync(visited->ptr, 0, (size_t)bm_bytes, c->stream));
   // everything but the arrival word, which counts monotonically over the life of the buffer
   SHB_CUDA(cudaMemsetAsync(cnt, 0, BFS_FLAG_WORD * 8, c->stream));
@@ -1223,15 +1225,16 @@ SHB_API int shb_bfs_block_publish(shb_ctx *c, uint32_t slot, shb_buf *counters, 
 }
 
 SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
-                                uint32_t level, const shb_buf *deg, shb_buf *frontier, shb_buf *const *next, int n_next,
-                                int self_index, shb_buf *visited, shb_buf *levels, shb_buf *counters, shb_buf *state,
-                                shb_buf *const *peer_counters, uint64_t barrier_target) {
-  SHB_REQUIRE(c && A && frontier && next && visited && levels && counters && state, "bad arguments");
+                                uint32_t level, const shb_buf *deg, const shb_buf *frontier, shb_buf *const *next, int n_next,
+                                int self_index, shb_buf *spare, shb_buf *visited, shb_buf *levels, shb_buf *counters,
+                                shb_buf *state, shb_buf *const *peer_counters, uint64_t barrier_target) {
+  SHB_REQUIRE(c && A && frontier && next && spare && visited && levels && counters && state, "bad arguments");
   SHB_REQUIRE(n_next >= 1 && n_next <= 8 && self_index >= 0 && self_index < n_next, "1..8 destinations, one of them local");
   SHB_TRY(bfs_block_check(A, AT, row_offset, n_total));
   const int64_t n_words = (n_total + 31) / 32;
   const uint64_t bm_bytes = (uint64_t)n_words * 4;
-  SHB_REQUIRE(frontier->bytes >= bm_bytes && visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
+  SHB_REQUIRE(frontier->bytes >= bm_bytes && visited->bytes >= bm_bytes && spare->bytes >= bm_bytes, "bitmap shorter than n_total bits");
+  SHB_REQUIRE(spare->ptr != frontier->ptr, "the spare bitmap aliases the current frontier");
   SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than the row block");
   SHB_REQUIRE(state->bytes >= sizeof(BfsBlockState), "state too short");
   BfsComm comm;
@@ -1242,7 +1245,7 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
   for (int i = 0; i < 8; ++i) peers.bm[i] = nullptr;
   for (int i = 0; i < n_next; ++i) {
     SHB_REQUIRE(next[i] && next[i]->bytes >= bm_bytes, "next-frontier bitmap too short");
-    SHB_REQUIRE(next[i]->ptr != frontier->ptr, "a next-frontier bitmap aliases the current one");
+    SHB_REQUIRE(next[i]->ptr != frontier->ptr && next[i]->ptr != spare->ptr, "a next-frontier bitmap aliases the current / spare one");
     peers.bm[i] = (uint32_t *)next[i]->ptr;
   }
   SHB_CUDA(cudaSetDevice(c->device));
@@ -1252,9 +1255,9 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
   const int32_t *dg = deg ? (const int32_t *)deg->ptr : nullptr;
   const uint32_t *cur = (const uint32_t *)frontier->ptr;
   const int64_t n_local = A->n_rows, word_lo = row_offset >> 5, word_hi = (row_offset + n_local + 31) >> 5;
-  bfs_block_decide_kernel<<<1, 1, 0, c->stream>>>(st, cnt, level);
-  bfs_block_prep_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(st, cur, (uint32_t *)visited->ptr, (int32_t *)levels->ptr, level,
-                                                                  n_words, word_lo, word_hi, row_offset, n_local);
+  bfs_block_prep_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(st, cnt, cur, (uint32_t *)visited->ptr, (uint32_t *)spare->ptr,
+                                                                  (int32_t *)levels->ptr, level, n_words, word_lo, word_hi,
+                                                                  row_offset, n_local);
   if (n_local > 0) {
     if (AT) {
       const unsigned grid = grid_for((word_hi - word_lo) * 32, 256, 148 * 8);
@@ -1281,7 +1284,6 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
       bfs_block_pull_kernel<false><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, nullptr, dg, cur, peers,
                                                                 (int32_t *)levels->ptr, acc, level, n_local, row_offset);
   }
-  bfs_block_clear_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(st, (uint32_t *)frontier->ptr, n_words);
   if (comm.n)
     bfs_block_publish_kernel<<<1, 32, 0, c->stream>>>(st, comm, cnt + BFS_STAGE_WORD, BFS_SLOT(level + 1), BFS_FLAG_WORD,
                                                       self_index, (unsigned long long)barrier_target);

@@ -259,7 +259,7 @@ def word_aligned_bounds(bounds: np.ndarray, align: int = 32) -> np.ndarray:
 
 
 class BfsBackend:
-    """What run_bfs needs from a device / CPU stand-in.  Frontier bitmaps are indexed 0/1 (level parity)."""
+    """What run_bfs needs from a device / CPU stand-in."""
 
     def step(self, level: int) -> None:  # pull launch of `level` (+ the stores into every rank's next bitmap)
         raise NotImplementedError
@@ -313,7 +313,7 @@ class GpuBfsPartition(BfsBackend):
         self.lo, self.hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
         self.n_words = max((self.n + 31) // 32, 1)
         self.max_levels = max_levels
-        self.bm = [ctx.empty(self.n_words * 4), ctx.empty(self.n_words * 4)]
+        self.bm = [ctx.empty(self.n_words * 4) for _ in range(3)]  # frontier L lives in bitmap L % 3
         self.visited = ctx.empty(self.n_words * 4)
         self.levels = ctx.empty(max(self.hi - self.lo, 1) * 4)
         self.n_counter_words = _BFS_SLOT0 + 2 * (max_levels + 2)
@@ -321,7 +321,7 @@ class GpuBfsPartition(BfsBackend):
         self.counters.zero()  # the arrival word starts at 0 and is never reset afterwards
         self.state = ctx.empty(ctx.bfs_block_state_bytes())
         self.launches, self.seq = 0, 0
-        self.peers = [[self.bm[0]], [self.bm[1]]]
+        self.peers = [[self.bm[0]], [self.bm[1]], [self.bm[2]]]
         self.peer_counters = None
         self.self_index = 0
         self._t_counts = None
@@ -329,13 +329,13 @@ class GpuBfsPartition(BfsBackend):
             ctx.synchronize()
             self._t_counts = _tensor_view(torch, self.counters, self.n_counter_words, ctx.device, "<i8")
             handles = [None] * world
-            dist.all_gather_object(handles, (self.bm[0].ipc_handle(), self.bm[1].ipc_handle(), self.counters.ipc_handle()))
-            self.peers = [[], []]
+            dist.all_gather_object(handles, tuple(b.ipc_handle() for b in self.bm) + (self.counters.ipc_handle(),))
+            self.peers = [[], [], []]
             for r in range(world):
-                for k in (0, 1):
+                for k in range(3):
                     self.peers[k].append(self.bm[k] if r == rank else ctx.ipc_open(handles[r][k], self.n_words * 4))
             if self.exchange == "peer":
-                self.peer_counters = [self.counters if r == rank else ctx.ipc_open(handles[r][2], self.n_counter_words * 8)
+                self.peer_counters = [self.counters if r == rank else ctx.ipc_open(handles[r][3], self.n_counter_words * 8)
                                       for r in range(world)]
             self.self_index = rank
         self.reset()
@@ -349,7 +349,7 @@ class GpuBfsPartition(BfsBackend):
         self._quiesce()  # no peer may still be storing into what init is about to zero
         peer = self.exchange == "peer"
         self.ctx.bfs_block_init(self.A, self.AT, self.lo, self.n, self.nnz_total, self.root, self.deg, self.levels,
-                                self.bm[0], self.bm[1], self.visited, self.counters, self.state, staged=peer)
+                                self.bm[0], self.bm[1], self.bm[2], self.visited, self.counters, self.state, staged=peer)
         if peer:
             self._quiesce()  # every rank has zeroed its slots before anyone adds to them
             self.seq += 1
@@ -364,9 +364,9 @@ class GpuBfsPartition(BfsBackend):
         if self.exchange == "peer":
             self.seq += 1
             target = self.world * self.seq
-        self.ctx.bfs_block_level(self.A, self.AT, self.lo, self.n, level, self.deg, self.bm[level & 1],
-                                 self.peers[(level + 1) & 1], self.self_index, self.visited, self.levels, self.counters,
-                                 self.state, self.peer_counters, target)
+        self.ctx.bfs_block_level(self.A, self.AT, self.lo, self.n, level, self.deg, self.bm[level % 3],
+                                 self.peers[(level + 1) % 3], self.self_index, self.bm[(level + 2) % 3], self.visited,
+                                 self.levels, self.counters, self.state, self.peer_counters, target)
         self.launches += 1
 
     def reduce_count(self, level):
@@ -390,7 +390,7 @@ class GpuBfsPartition(BfsBackend):
     def close(self):
         self._quiesce()
         if self.world > 1:
-            for k in (0, 1):
+            for k in range(3):
                 for r, b in enumerate(self.peers[k]):
                     if r != self.rank:
                         b.free()
@@ -424,7 +424,7 @@ class EmulatedBfsPartition(BfsBackend):
         self.n = int(self.bounds[-1])
         self.P = len(blocks)
         n_words = max((self.n + 31) // 32, 1)
-        self.bm = [[ctx.empty(n_words * 4), ctx.empty(n_words * 4)] for _ in range(self.P)]
+        self.bm = [[ctx.empty(n_words * 4) for _ in range(3)] for _ in range(self.P)]
         self.visited = [ctx.empty(n_words * 4) for _ in range(self.P)]
         self.levels = [ctx.empty(max(int(self.bounds[k + 1] - self.bounds[k]), 1) * 4) for k in range(self.P)]
         self.counters = [ctx.empty((_BFS_SLOT0 + 2 * (max_levels + 2)) * 8) for _ in range(self.P)]
@@ -443,7 +443,7 @@ class EmulatedBfsPartition(BfsBackend):
         for k, A in enumerate(self.blocks):
             self.ctx.bfs_block_init(A, self.at_blocks[k] if self.at_blocks else None, int(self.bounds[k]), self.n,
                                     self.nnz_total, self.root, self.deg, self.levels[k], self.bm[k][0], self.bm[k][1],
-                                    self.visited[k], self.counters[k], self.state[k], staged=self.publish)
+                                    self.bm[k][2], self.visited[k], self.counters[k], self.state[k], staged=self.publish)
         if self.publish:
             for k in range(self.P):
                 self.ctx.bfs_block_publish(0, self.counters[k], self.state[k], self.counters, k, 0)
@@ -452,11 +452,12 @@ class EmulatedBfsPartition(BfsBackend):
         self.launches = 0
 
     def step(self, level):
-        nxt = [self.bm[k][(level + 1) & 1] for k in range(self.P)]
+        nxt = [self.bm[k][(level + 1) % 3] for k in range(self.P)]
         for k, A in enumerate(self.blocks):
             self.ctx.bfs_block_level(A, self.at_blocks[k] if self.at_blocks else None, int(self.bounds[k]), self.n, level,
-                                     self.deg, self.bm[k][level & 1], nxt, k, self.visited[k], self.levels[k],
-                                     self.counters[k], self.state[k], self.counters if self.publish else None, 0)
+                                     self.deg, self.bm[k][level % 3], nxt, k, self.bm[k][(level + 2) % 3], self.visited[k],
+                                     self.levels[k], self.counters[k], self.state[k],
+                                     self.counters if self.publish else None, 0)
             self.launches += 1
 
     def reduce_count(self, level):

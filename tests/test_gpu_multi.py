@@ -146,9 +146,10 @@ def test_bfs_block_rejects_unaligned_blocks(ctx, orc):
     A = ctx.csr(n, n, rp, col, None)
     B = A.slice_rows(16, 64)
     nb = n // 8 + 4
-    lv, b0, b1, vis, cnt, st = ctx.empty(64 * 4), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(256), ctx.empty(64)
+    lv, b0, b1, b2, vis, cnt, st = (ctx.empty(64 * 4), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb),
+                                    ctx.empty(256), ctx.empty(64))
     with pytest.raises(shb.ShbError) as e:
-        ctx.bfs_block_init(B, None, 16, n, len(col), 0, None, lv, b0, b1, vis, cnt, st)
+        ctx.bfs_block_init(B, None, 16, n, len(col), 0, None, lv, b0, b1, b2, vis, cnt, st)
     assert e.value.status == 1
 
 

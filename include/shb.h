@@ -277,8 +277,10 @@ int shb_bfs_block_finish(shb_ctx *ctx, const shb_csr *A, const shb_buf *levels, 
  * expanded with, work an opaque scratch of shb_sssp_block_work_bytes(n_local) bytes.
  *   init    dist = FLT_MAX, dist[source] = 0 on every rank, prev = FLT_MAX, bucket width from the block's weights.
  *   seed    first half of a round: the owned v with dist[v] < prev[v] (lowered by a peer since their last
- *           expansion, or the source) enter the work pile; their number is ADDED to int64 word `word` of seed_count,
- *           their smallest distance (float bits) MIN-ed into word `word` of seed_min (optional, preset large).
+ *           expansion, or the source) enter the work pile; their number is ADDED to int64 word `word` of seed_count;
+ *           the smallest of their distances (float bits) that lies at or beyond the previous round's window is
+ *           MIN-ed into word `word` of seed_min (optional, preset large): the window follows the front, late
+ *           corrections below it are expanded along the way.
  *   solve   second half: the near-far solve of the block: improved owned targets are queued, improved targets of
  *           other ranks are sent to their owner as red.min on peer_dist[owner] (CUDA-IPC mappings, NVLink).
  *           bounds[0..n_ranks] = vertex ownership.  window_buckets > 0: only distances below seed_min[word] (all-

@@ -370,6 +370,8 @@ struct SsspState {
   float delta;
   double w_sum;
   unsigned long long w_cnt;
+  uint32_t cap_bits;  // partitioned solve: upper end of the previous round's distance window (kept across rounds)
+  uint32_t pad3;
 };
 
 __device__ __forceinline__ void grid_barrier(SsspState *st, uint32_t n_blocks) {
@@ -1399,7 +1401,11 @@ __global__ void sssp_block_reset_kernel(SsspState *st) {
 __global__ void sssp_block_seed_kernel(SsspState *st, const uint32_t *dist, const uint32_t *prev, uint32_t *pile_bits,
                                        int32_t *far0, uint32_t lo, uint32_t n_local, long long *count_out, long long *min_out) {
   const int lane = threadIdx.x & 31;
-  uint32_t fmin = 0xffffffffu, cnt = 0;
+  uint32_t fmin = 0xffffffffu, fmin_front = 0xffffffffu, cnt = 0;
+  // the window advances with the FRONT: its lower end is the smallest pending distance at or beyond the previous
+  // window's upper end; stragglers below it (corrections sent by a peer) are expanded along the way and no longer
+  // hold the whole sweep back
+  const uint32_t last_cap = st->cap_bits;
   const uint32_t n_padded = (n_local + 31u) & ~31u;
   for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += gridDim.x * blockDim.x) {
     bool seed = false;
@@ -1417,18 +1423,20 @@ __global__ void sssp_block_seed_kernel(SsspState *st, const uint32_t *dist, cons
       if (seed) {
         far0[base + __popc(m & ((1u << lane) - 1u))] = (int32_t)(lo + r);
         fmin = min(fmin, d);
+        if (d >= last_cap) fmin_front = min(fmin_front, d);
         ++cnt;
       }
     }
   }
   for (int off = 16; off > 0; off >>= 1) {
     fmin = min(fmin, __shfl_xor_sync(0xffffffffu, fmin, off));
+    fmin_front = min(fmin_front, __shfl_xor_sync(0xffffffffu, fmin_front, off));
     cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
   }
   if (lane == 0 && cnt) {
     atomicMin(&st->far_min[0], fmin);
     atomicAdd(reinterpret_cast<unsigned long long *>(count_out), (unsigned long long)cnt);
-    if (min_out) atomicMin(min_out, (long long)fmin);
+    if (min_out && fmin_front != 0xffffffffu) atomicMin(min_out, (long long)fmin_front);
   }
 }
 
@@ -1448,6 +1456,7 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
     const long long g = *(volatile const long long *)a.gmin;
     const uint32_t gb = g < 0x7f7fffffll ? (uint32_t)g : 0x7f7fffffu;
     cap = __float_as_uint(__fadd_rn(__uint_as_float(gb), a.window_buckets * delta));
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->cap_bits = cap;  // read by the next round's seed pass
   }
   bool finished = false;
   if (threadIdx.x == 0) {

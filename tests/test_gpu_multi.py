@@ -260,3 +260,54 @@ def test_emulated_partitions_with_empty_blocks(ctx, orc):
     bs = multi.EmulatedSsspPartition(ctx, blocks, bounds, 55, window_buckets=1.0)
     rounds, conv = multi.run_sssp(bs, 4096, 3)
     assert conv and np.array_equal(bs.result(), orc.sssp(rp, col, val, 55))
+
+
+def test_partition_entry_points_validate_their_arguments(ctx, orc):
+    """Bad geometry is SHB_ERR_INVALID (status 1) with a message, never a launch."""
+    import sparseharness_b200 as shb
+    from sparseharness_b200 import multi
+    rp, col, val = orc.gen_grid2d(16, 16)
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, val)
+    B = A.slice_rows(64, 128)
+    d, prev = ctx.empty(n * 4), ctx.empty(128 * 4)
+    work = ctx.empty(ctx.sssp_block_work_bytes(128))
+    seeds, smin = ctx.empty(64), ctx.empty(64)
+    ctx.sssp_block_init(B, 64, n, 0, d, prev, work)
+    bad = [
+        lambda: ctx.sssp_block_solve(B, 64, n, d, [d], 0, np.array([0, n]), prev, work),             # bounds of another block
+        lambda: ctx.sssp_block_solve(B, 64, n, d, [d, d], 1, np.array([0, 64, 200]), prev, work),    # do not end at n
+        lambda: ctx.sssp_block_solve(B, 64, n, d, [d], 0, np.array([64, 192]), prev, work),          # do not start at 0
+        lambda: ctx.sssp_block_solve(B, 64, n, d, [d, d, d], 1, np.array([0, 64, 192, n]), prev, work, None, 0, 4.0),  # window without seed_min
+        lambda: ctx.sssp_block_seed(B, 64, n, d, prev, ctx.empty(16), seeds, smin, 0),               # work too short
+        lambda: ctx.sssp_block_seed(B, 64, n, d, prev, work, seeds, smin, 8),                        # no such seed word
+        lambda: ctx.sssp_block_init(B, 64, n, n, d, prev, work),                                     # source out of range
+        lambda: ctx.sssp_block_init(B, 200, n, 0, d, prev, work),                                    # block outside the vertex set
+    ]
+    for i, f in enumerate(bad):
+        with pytest.raises(shb.ShbError) as e:
+            f()
+        assert e.value.status == 1, i
+    # the good call still works afterwards
+    ctx.sssp_block_seed(B, 64, n, d, prev, work, seeds, smin, 0)
+    ctx.sssp_block_solve(B, 64, n, d, [d, d, d], 1, np.array([0, 64, 192, n]), prev, work)
+    ctx.synchronize()
+    # BFS: counters without a slot for the level, a next bitmap aliasing the frontier, wrong self index
+    P = ctx.csr(n, n, rp, col, None).slice_rows(64, 128)
+    nb = n // 8
+    lv, b0, b1, b2, vis, st = ctx.empty(128 * 4), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(ctx.bfs_block_state_bytes())
+    cnt = ctx.empty((6 + 2 * 4) * 8)
+    cnt.zero()
+    ctx.bfs_block_init(P, P, 64, n, len(col), 70, None, lv, b0, b1, b2, vis, cnt, st)
+    bad = [
+        lambda: ctx.bfs_block_level(P, P, 64, n, 9, None, b0, [b1], 0, b2, vis, lv, cnt, st),   # no slot for level 10
+        lambda: ctx.bfs_block_level(P, P, 64, n, 0, None, b0, [b0], 0, b2, vis, lv, cnt, st),   # next aliases the frontier
+        lambda: ctx.bfs_block_level(P, P, 64, n, 0, None, b0, [b1], 0, b0, vis, lv, cnt, st),   # spare aliases the frontier
+        lambda: ctx.bfs_block_level(P, P, 64, n, 0, None, b0, [b1], 1, b2, vis, lv, cnt, st),   # self index out of range
+        lambda: ctx.bfs_block_init(P, P, 64, n, len(col), n, None, lv, b0, b1, b2, vis, cnt, st),  # root out of range
+    ]
+    for i, f in enumerate(bad):
+        with pytest.raises(shb.ShbError) as e:
+            f()
+        assert e.value.status == 1, i
+    assert multi.word_aligned_bounds(np.array([0, 64, 192, n]))[-1] == n

@@ -991,8 +991,8 @@ template <bool HAS_VAL>
 __global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__restrict__ row_ptr,
                                       const int32_t *__restrict__ col, const int32_t *__restrict__ val,
                                       const int32_t *__restrict__ deg, const uint32_t *__restrict__ cur,
-                                      const __grid_constant__ BfsPeers next, int32_t *levels, long long *acc,
-                                      uint32_t level, int64_t n_local, int64_t row_offset) {
+                                      const uint32_t *__restrict__ visited, const __grid_constant__ BfsPeers next,
+                                      int32_t *levels, long long *acc, uint32_t level, int64_t n_local, int64_t row_offset) {
   if (st->done || st->mode != 1) return;
   const int lane = threadIdx.x & 31;
   const int64_t word_offset = row_offset >> 5;
@@ -1001,7 +1001,9 @@ __global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__
   for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
     bool found = false, big = false;
     int s = 0, e = 0;
-    if (r < n_local && levels[r] == -1) {
+    // one visited word per warp step instead of 32 level loads; vertices without in-edges were marked at init
+    const uint32_t seen = visited[word_offset + (r >> 5)];
+    if (r < n_local && !((seen >> lane) & 1u)) {
       s = row_ptr[r];
       e = row_ptr[r + 1];
       big = (e - s) >= BFS_BLOCK_BIG_ROW;
@@ -1093,6 +1095,19 @@ __global__ void bfs_block_publish_kernel(BfsBlockState *st, const __grid_constan
       }
     }
     __threadfence_system();
+  }
+}
+
+// owned vertices without in-edges can never be found by a pull: they start out "visited" (their level stays -1) so
+// that the pull sweeps skip them with the visited word instead of fetching their row bounds every level
+__global__ void bfs_block_mark_isolated_kernel(const int32_t *__restrict__ row_ptr, uint32_t *visited, int64_t n_local,
+                                               int64_t word_offset) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n_padded = (n_local + 31) / 32 * 32;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
+    const bool iso = r < n_local && row_ptr[r + 1] == row_ptr[r];
+    const uint32_t m = __ballot_sync(0xffffffffu, iso);
+    if (lane == 0 && m) visited[word_offset + (r >> 5)] = m;
   }
 }
 
@@ -1204,6 +1219,9 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
   SHB_CUDA(cudaMemsetAsync(cnt, 0, BFS_FLAG_WORD * 8, c->stream));
   SHB_CUDA(cudaMemsetAsync(cnt + BFS_STAGE_WORD, 0, (size_t)counters->bytes - BFS_STAGE_WORD * 8, c->stream));
   long long *acc = staged ? cnt + BFS_STAGE_WORD : cnt + BFS_SLOT(0);
+  if (A->n_rows > 0)
+    bfs_block_mark_isolated_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>(A->row_ptr, (uint32_t *)visited->ptr, A->n_rows,
+                                                                               row_offset >> 5);
   bfs_block_init_kernel<<<1, 1, 0, c->stream>>>((BfsBlockState *)state->ptr, (int32_t *)levels->ptr, (uint32_t *)frontier0->ptr,
                                                 acc, root, row_offset, A->n_rows, deg ? (const int32_t *)deg->ptr : nullptr,
                                                 AT != nullptr, (unsigned long long)nnz_total, (unsigned long long)n_total);
@@ -1280,11 +1298,13 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
     }
     const unsigned grid = grid_for(n_local, 256, 148 * 32);
     if (A->val)
-      bfs_block_pull_kernel<true><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, (const int32_t *)A->val, dg, cur, peers,
-                                                               (int32_t *)levels->ptr, acc, level, n_local, row_offset);
+      bfs_block_pull_kernel<true><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, (const int32_t *)A->val, dg, cur,
+                                                               (const uint32_t *)visited->ptr, peers, (int32_t *)levels->ptr,
+                                                               acc, level, n_local, row_offset);
     else
-      bfs_block_pull_kernel<false><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, nullptr, dg, cur, peers,
-                                                                (int32_t *)levels->ptr, acc, level, n_local, row_offset);
+      bfs_block_pull_kernel<false><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, nullptr, dg, cur,
+                                                                (const uint32_t *)visited->ptr, peers, (int32_t *)levels->ptr,
+                                                                acc, level, n_local, row_offset);
   }
   if (comm.n)
     bfs_block_publish_kernel<<<1, 32, 0, c->stream>>>(st, comm, cnt + BFS_STAGE_WORD, BFS_SLOT(level + 1), BFS_FLAG_WORD,

@@ -240,7 +240,8 @@ int shb_spmv_scatter(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_lau
  * bitmaps (n_total bits) and, optionally, `deg` = push degree of every vertex (int32 x n_total, steers Beamer's
  * heuristic).  counters: int64 words: 0,1 = reached vertices / TEPS numerator of this rank (after finish),
  * 2 = arrival word of the peer barrier (monotonic: zero it once, when the buffer is created), 4,5 = staging,
- * slot F = words 6+2F, 7+2F = (vertices, push degrees) of frontier F summed over ranks.
+ * slot F = words 6+2(F mod ring), +1 = (vertices, push degrees) of frontier F summed over ranks (a ring of slot_ring
+ * frontiers, shb_bfs_block_counter_bytes: read a slot before the traversal is slot_ring - 2 levels further).
  *   init     levels = -1, frontier0 = {root}, frontier1 = frontier2 = {}, counters (but the arrival word) = 0; the
  *            three frontier bitmaps rotate: level L reads bitmap L % 3, builds (L+1) % 3 and zeroes (L+2) % 3 for
  *            the level after (so no separate clearing pass and no store can race a clear); the root's owner reports
@@ -258,6 +259,7 @@ int shb_spmv_scatter(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_lau
  *   finish   per-rank reached / edge counts from the levels; fails if a peer barrier timed out (~4 s). */
 int shb_csr_row_lengths(shb_ctx *ctx, const shb_csr *A, shb_buf *out /* int32 x n_rows */);
 int shb_bfs_block_state_bytes(uint64_t *bytes);
+int shb_bfs_block_counter_bytes(uint64_t *bytes, uint32_t *slot_ring); /* size of `counters`; slots form a ring */
 int shb_bfs_block_init(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64_t row_offset, int64_t n_total,
                        int64_t nnz_total, int64_t root, const shb_buf *deg, shb_buf *levels, shb_buf *frontier0,
                        shb_buf *frontier1, shb_buf *frontier2, shb_buf *visited, shb_buf *counters, shb_buf *state,

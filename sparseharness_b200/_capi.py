@@ -101,6 +101,7 @@ SIGNATURES = {
     "shb_ipc_close": (C.c_int, [C.c_void_p]),
     "shb_csr_row_lengths": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "shb_bfs_block_state_bytes": (C.c_int, [u64p]),
+    "shb_bfs_block_counter_bytes": (C.c_int, [u64p, u32p]),
     "shb_bfs_block_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_int]),

@@ -281,6 +281,12 @@ class Context:
         _ck(lib.shb_bfs_block_state_bytes(C.byref(b)))
         return b.value
 
+    def bfs_block_counter_bytes(self) -> tuple[int, int]:
+        """(bytes of the counters buffer, number of frontier slots in its ring)."""
+        b, r = C.c_uint64(0), C.c_uint32(0)
+        _ck(lib.shb_bfs_block_counter_bytes(C.byref(b), C.byref(r)))
+        return b.value, r.value
+
     def bfs_block_init(self, A: Csr, AT: Csr | None, row_offset, n_total, nnz_total, root, deg: Buffer | None,
                        levels: Buffer, bm0: Buffer, bm1: Buffer, bm2: Buffer, visited: Buffer, counters: Buffer,
                        state: Buffer, staged: bool = False):

@@ -827,10 +827,14 @@ done:
 #define BFS_PUSH_BIG_ROW 1024  // a frontier vertex with at least this many out-edges is expanded by the whole grid
 #define BFS_PUSH_BIG_CAP 1024
 // counters layout (int64 words): 0 reached, 1 TEPS numerator (after finish), 2 arrival word of the peer barrier,
-// 4..5 staging of the level's (vertices, degrees), slot F at BFS_SLOT(F), BFS_SLOT(F) + 1
+// 4..5 staging of the level's (vertices, degrees), slot F at BFS_SLOT(F), BFS_SLOT(F) + 1.  The slots are a ring of
+// BFS_SLOT_RING frontiers (a traversal may have any number of levels): the prep kernel of level F zeroes slot F + 2,
+// which nobody adds to before this rank has joined the barrier of level F.
 #define BFS_FLAG_WORD 2
 #define BFS_STAGE_WORD 4
-#define BFS_SLOT(F) (6 + 2 * (F))
+#define BFS_SLOT_RING 256
+#define BFS_SLOT(F) (6 + 2 * ((F) & (BFS_SLOT_RING - 1)))
+#define BFS_COUNTER_WORDS (6 + 2 * BFS_SLOT_RING)
 
 struct BfsPeers {
   uint32_t *bm[8];
@@ -857,13 +861,16 @@ struct BfsBlockState {
 // frontier over the whole bitmap, and the owned words give their vertices the level; (c) the spare bitmap (the
 // frontier of two levels ago, the next frontier of the NEXT level) is zeroed: peers only start storing into it after
 // this level's barrier, which this rank joins after this kernel.
-__global__ void bfs_block_prep_kernel(BfsBlockState *st, const long long *counters, const uint32_t *__restrict__ cur,
+__global__ void bfs_block_prep_kernel(BfsBlockState *st, long long *counters_rw, const uint32_t *__restrict__ cur,
                                       uint32_t *visited, uint32_t *spare, int32_t *levels, uint32_t level, int64_t n_words,
                                       int64_t word_lo, int64_t word_hi, int64_t row_offset, int64_t n_local) {
+  const long long *counters = counters_rw;
   const unsigned long long nf = (unsigned long long)counters[BFS_SLOT(level)];
   const bool done = (*(volatile uint32_t *)&st->done != 0u) || nf == 0;  // either order of thread 0's store: same value
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st->big_count = 0;
+    counters_rw[BFS_SLOT(level + 2)] = 0;
+    counters_rw[BFS_SLOT(level + 2) + 1] = 0;
     if (nf == 0) {
       st->done = 1;
     } else if (!done) {
@@ -1178,9 +1185,17 @@ SHB_API int shb_bfs_block_state_bytes(uint64_t *bytes) {
   return SHB_OK;
 }
 
+SHB_API int shb_bfs_block_counter_bytes(uint64_t *bytes, uint32_t *slot_ring) {
+  SHB_REQUIRE(bytes, "bad arguments");
+  *bytes = (uint64_t)BFS_COUNTER_WORDS * 8;
+  if (slot_ring) *slot_ring = BFS_SLOT_RING;
+  return SHB_OK;
+}
+
 static int bfs_block_comm(shb_buf *counters, shb_buf *const *peer_counters, int n, int self, uint32_t max_slot, BfsComm *comm) {
-  const uint64_t need = (uint64_t)(BFS_SLOT(max_slot) + 2) * 8;
-  SHB_REQUIRE(counters->bytes >= need, "counters has no slot for this level");
+  (void)max_slot;
+  const uint64_t need = (uint64_t)BFS_COUNTER_WORDS * 8;
+  SHB_REQUIRE(counters->bytes >= need, "counters shorter than shb_bfs_block_counter_bytes");
   comm->n = 0;
   for (int i = 0; i < 8; ++i) comm->counters[i] = nullptr;
   if (!peer_counters) return SHB_OK;
@@ -1207,7 +1222,7 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
                   visited->bytes >= bm_bytes, "bitmap shorter than n_total bits");
   SHB_REQUIRE(!deg || deg->bytes >= (uint64_t)n_total * 4, "deg shorter than n_total");
   SHB_REQUIRE(state->bytes >= sizeof(BfsBlockState), "state too short");
-  SHB_REQUIRE(counters->bytes >= (uint64_t)(BFS_SLOT(0) + 2) * 8, "counters too short");
+  SHB_REQUIRE(counters->bytes >= (uint64_t)BFS_COUNTER_WORDS * 8, "counters shorter than shb_bfs_block_counter_bytes");
   SHB_CUDA(cudaSetDevice(c->device));
   long long *cnt = (long long *)counters->ptr;
   if (A->n_rows > 0) SHB_CUDA(cudaMemsetAsync(levels->ptr, 0xff, (size_t)A->n_rows * 4, c->stream));
@@ -1217,7 +1232,7 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
   SHB_CUDA(cudaMemsetAsync(visited->ptr, 0, (size_t)bm_bytes, c->stream));
   // everything but the arrival word, which counts monotonically over the life of the buffer
   SHB_CUDA(cudaMemsetAsync(cnt, 0, BFS_FLAG_WORD * 8, c->stream));
-  SHB_CUDA(cudaMemsetAsync(cnt + BFS_STAGE_WORD, 0, (size_t)counters->bytes - BFS_STAGE_WORD * 8, c->stream));
+  SHB_CUDA(cudaMemsetAsync(cnt + BFS_STAGE_WORD, 0, (size_t)(BFS_COUNTER_WORDS - BFS_STAGE_WORD) * 8, c->stream));
   long long *acc = staged ? cnt + BFS_STAGE_WORD : cnt + BFS_SLOT(0);
   if (A->n_rows > 0)
     bfs_block_mark_isolated_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>(A->row_ptr, (uint32_t *)visited->ptr, A->n_rows,

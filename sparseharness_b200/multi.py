@@ -276,6 +276,7 @@ def run_bfs(backend: BfsBackend, max_levels: int = 1 << 20, check_every: int = 4
     nothing.  Returns (levels_populated, reached_beyond_root, launches_that_did_work).  Launches issued past
     the end of the traversal inside a batch return at once on the device (their found slot stays 0)."""
     level, reached, done = 0, 0, False
+    check_every = max(1, min(check_every, 128))  # the count slots are a ring (256 frontiers): poll well inside it
     while not done and level < max_levels:
         batch = min(check_every, max_levels - level)
         for b in range(batch):
@@ -294,7 +295,7 @@ def run_bfs(backend: BfsBackend, max_levels: int = 1 << 20, check_every: int = 4
     return (level if done else level + 1), reached, level
 
 
-_BFS_SLOT0 = 6  # int64 word of counter slot 0 (include/shb.h: slot F = words 6+2F, 7+2F)
+_BFS_SLOT0 = 6  # int64 word of counter slot 0 (include/shb.h: slot F = words 6 + 2 (F mod ring), + 1)
 
 
 class GpuBfsPartition(BfsBackend):
@@ -303,7 +304,7 @@ class GpuBfsPartition(BfsBackend):
     counts are added into every rank's counters by a publish kernel over CUDA-IPC peer pointers, which also is the
     barrier -- no collective library inside the traversal; exchange="nccl": a 16-byte all-reduce per level."""
 
-    def __init__(self, ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, max_levels=4096,
+    def __init__(self, ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, max_levels=1 << 30,
                  exchange="peer", dist=None, torch=None):
         self.ctx, self.A, self.AT, self.deg = ctx, A_local, AT_local, deg
         self.bounds = np.asarray(bounds, dtype=np.int64)
@@ -316,8 +317,9 @@ class GpuBfsPartition(BfsBackend):
         self.bm = [ctx.empty(self.n_words * 4) for _ in range(3)]  # frontier L lives in bitmap L % 3
         self.visited = ctx.empty(self.n_words * 4)
         self.levels = ctx.empty(max(self.hi - self.lo, 1) * 4)
-        self.n_counter_words = _BFS_SLOT0 + 2 * (max_levels + 2)
-        self.counters = ctx.empty(self.n_counter_words * 8)
+        nbytes, self.ring = ctx.bfs_block_counter_bytes()
+        self.n_counter_words = nbytes // 8
+        self.counters = ctx.empty(nbytes)
         self.counters.zero()  # the arrival word starts at 0 and is never reset afterwards
         self.state = ctx.empty(ctx.bfs_block_state_bytes())
         self.launches, self.seq = 0, 0
@@ -371,12 +373,12 @@ class GpuBfsPartition(BfsBackend):
 
     def reduce_count(self, level):
         if self.exchange == "nccl":
-            w = _BFS_SLOT0 + 2 * (level + 1)
+            w = _BFS_SLOT0 + 2 * ((level + 1) % self.ring)
             self.dist.all_reduce(self._t_counts[w:w + 2], op=self.dist.ReduceOp.SUM)
 
     def read_counts(self, lo, hi):
-        w = self.counters.download(np.int64, 2 * (hi - lo), offset=8 * (_BFS_SLOT0 + 2 * (lo + 1)))
-        return w[0::2]
+        w = self.counters.download(np.int64, self.n_counter_words)
+        return np.array([w[_BFS_SLOT0 + 2 * ((f + 1) % self.ring)] for f in range(lo, hi)], dtype=np.int64)
 
     def local_stats(self):
         """(reached, sum of in-degrees of reached) of the owned slice; raises if a peer barrier timed out."""
@@ -418,7 +420,7 @@ class EmulatedBfsPartition(BfsBackend):
     kernel (system-scope adds into every block's slot, no wait: the blocks share a stream); publish=False emulates
     the NCCL all-reduce of a slot through the host (download, sum, upload)."""
 
-    def __init__(self, ctx, blocks, bounds, root, nnz_total, *, at_blocks=None, deg=None, max_levels=4096, publish=True):
+    def __init__(self, ctx, blocks, bounds, root, nnz_total, *, at_blocks=None, deg=None, max_levels=1 << 30, publish=True):
         self.ctx, self.blocks, self.at_blocks, self.deg, self.publish = ctx, blocks, at_blocks, deg, publish
         self.bounds, self.root, self.nnz_total = np.asarray(bounds, dtype=np.int64), int(root), int(nnz_total)
         self.n = int(self.bounds[-1])
@@ -427,14 +429,16 @@ class EmulatedBfsPartition(BfsBackend):
         self.bm = [[ctx.empty(n_words * 4) for _ in range(3)] for _ in range(self.P)]
         self.visited = [ctx.empty(n_words * 4) for _ in range(self.P)]
         self.levels = [ctx.empty(max(int(self.bounds[k + 1] - self.bounds[k]), 1) * 4) for k in range(self.P)]
-        self.counters = [ctx.empty((_BFS_SLOT0 + 2 * (max_levels + 2)) * 8) for _ in range(self.P)]
+        nbytes, self.ring = ctx.bfs_block_counter_bytes()
+        self.n_counter_words = nbytes // 8
+        self.counters = [ctx.empty(nbytes) for _ in range(self.P)]
         for c in self.counters:
             c.zero()
         self.state = [ctx.empty(ctx.bfs_block_state_bytes()) for _ in range(self.P)]
         self.reset()
 
     def _reduce_slot(self, slot):
-        off = 8 * (_BFS_SLOT0 + 2 * slot)
+        off = 8 * (_BFS_SLOT0 + 2 * (slot % self.ring))
         tot = sum(c.download(np.int64, 2, offset=off) for c in self.counters)
         for c in self.counters:
             c.upload(tot, offset=off)
@@ -465,7 +469,8 @@ class EmulatedBfsPartition(BfsBackend):
             self._reduce_slot(level + 1)
 
     def read_counts(self, lo, hi):
-        return self.counters[0].download(np.int64, 2 * (hi - lo), offset=8 * (_BFS_SLOT0 + 2 * (lo + 1)))[0::2]
+        w = self.counters[0].download(np.int64, self.n_counter_words)
+        return np.array([w[_BFS_SLOT0 + 2 * ((f + 1) % self.ring)] for f in range(lo, hi)], dtype=np.int64)
 
     def stats(self):
         r = e = 0
@@ -481,7 +486,7 @@ class EmulatedBfsPartition(BfsBackend):
 
 
 def partitioned_bfs(ctx, A_local, bounds, rank, world, root, nnz_total, *, AT_local=None, deg=None, check_every=8,
-                    max_levels=4096, exchange="peer", dist=None, torch=None, repeat=1):
+                    max_levels=1 << 30, exchange="peer", dist=None, torch=None, repeat=1):
     """Direction-optimising BFS levels on a row-partitioned operator.  Returns (backend, stats) with stats =
     dict(levels, reached, edges_traversed [sum of in-degrees of reached vertices, all ranks], ms [device time of
     this rank; max over ranks is the caller's job], launches)."""

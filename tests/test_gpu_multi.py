@@ -147,7 +147,7 @@ def test_bfs_block_rejects_unaligned_blocks(ctx, orc):
     B = A.slice_rows(16, 64)
     nb = n // 8 + 4
     lv, b0, b1, b2, vis, cnt, st = (ctx.empty(64 * 4), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb),
-                                    ctx.empty(256), ctx.empty(64))
+                                    ctx.empty(8192), ctx.empty(64))
     with pytest.raises(shb.ShbError) as e:
         ctx.bfs_block_init(B, None, 16, n, len(col), 0, None, lv, b0, b1, b2, vis, cnt, st)
     assert e.value.status == 1
@@ -296,11 +296,11 @@ def test_partition_entry_points_validate_their_arguments(ctx, orc):
     P = ctx.csr(n, n, rp, col, None).slice_rows(64, 128)
     nb = n // 8
     lv, b0, b1, b2, vis, st = ctx.empty(128 * 4), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(nb), ctx.empty(ctx.bfs_block_state_bytes())
-    cnt = ctx.empty((6 + 2 * 4) * 8)
+    cnt = ctx.empty(ctx.bfs_block_counter_bytes()[0])
     cnt.zero()
     ctx.bfs_block_init(P, P, 64, n, len(col), 70, None, lv, b0, b1, b2, vis, cnt, st)
     bad = [
-        lambda: ctx.bfs_block_level(P, P, 64, n, 9, None, b0, [b1], 0, b2, vis, lv, cnt, st),   # no slot for level 10
+        lambda: ctx.bfs_block_level(P, P, 64, n, 0, None, b0, [b1], 0, b2, vis, lv, ctx.empty(64), st),   # counters too short
         lambda: ctx.bfs_block_level(P, P, 64, n, 0, None, b0, [b0], 0, b2, vis, lv, cnt, st),   # next aliases the frontier
         lambda: ctx.bfs_block_level(P, P, 64, n, 0, None, b0, [b1], 0, b0, vis, lv, cnt, st),   # spare aliases the frontier
         lambda: ctx.bfs_block_level(P, P, 64, n, 0, None, b0, [b1], 1, b2, vis, lv, cnt, st),   # self index out of range
@@ -311,3 +311,21 @@ def test_partition_entry_points_validate_their_arguments(ctx, orc):
             f()
         assert e.value.status == 1, i
     assert multi.word_aligned_bounds(np.array([0, 64, 192, n]))[-1] == n
+
+
+def test_emulated_row_partition_bfs_more_levels_than_counter_slots(ctx, orc):
+    """A path-like graph with ~1200 levels: the per-level count slots are a ring of 256 frontiers that the traversal
+    laps several times (push and pull levels, 3 blocks)."""
+    from sparseharness_b200 import multi
+    rp, col, _ = orc.gen_grid2d(600, 2)  # 600 x 2 ladder: diameter ~ 600 from a corner
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, None)
+    bounds = multi.word_aligned_bounds(A.balance_rows(3))
+    blocks = [A.slice_rows(int(bounds[k]), int(bounds[k + 1] - bounds[k])) for k in range(3)]
+    want, nlev, edges = orc.bfs_levels(rp, col, None, 0)
+    assert nlev > 2 * ctx.bfs_block_counter_bytes()[1]
+    for push, ce in ((True, 100), (False, 7)):
+        be = multi.EmulatedBfsPartition(ctx, blocks, bounds, 0, len(col), at_blocks=blocks if push else None,
+                                        deg=A.row_lengths() if push else None)
+        n_levels, _, launches = multi.run_bfs(be, 1 << 20, ce)
+        assert n_levels == nlev and launches == nlev and np.array_equal(be.result(), want) and be.stats() == (n, edges)

@@ -339,6 +339,7 @@ SHB_API int shb_csr_destroy(shb_csr *A) {
   cudaFree(A->tile_row);
   cudaFree(A->carry_tail);
   cudaFree(A->carry_head);
+  cudaFree(A->row_len);
   shb_pb_free(A->pb);
   cudaGetLastError();
   delete A;

@@ -17,329 +17,6 @@ static unsigned grid_for(int64_t n, int per_block = 256, int cap = 148 * 16) {
 }
 
 // =================================================================================================
-// BFS: level-synchronous, direction-optimising (push over A^T for small frontiers, pull with early
-// exit over A otherwise).  frontier_{k+1} = (A (x) frontier_k) AND NOT visited under or-and.
-// =================================================================================================
-struct BfsState {
-  uint32_t level;        // level of the current frontier
-  uint32_t mode;         // 0 = push (top-down), 1 = pull (bottom-up)
-  uint32_t done;
-  uint32_t have_at;
-  uint32_t n_frontier;   // vertices in the current frontier
-  uint32_t prev_frontier;
-  uint32_t next_count;   // accumulated while building the next frontier
-  uint32_t pad;
-  unsigned long long next_edges;   // sum of push-degrees of the next frontier
-  unsigned long long unexplored;   // edges not yet scanned (Beamer's m_u)
-  unsigned long long reached, edges_traversed;
-  uint32_t big_count;   // hub vertices of the current push level, expanded by the whole grid (bfs_push_big_kernel)
-  uint32_t pad2;
-  int32_t big_list[1024];
-};
-#define BFS_BIG_ROW 1024
-#define BFS_BIG_CAP 1024
-
-__global__ void bfs_init_kernel(BfsState *st, int32_t *levels, uint32_t *bm0, int64_t root, const int32_t *a_row_ptr,
-                                const int32_t *at_row_ptr, unsigned long long nnz, int have_at) {
-  levels[root] = 0;
-  bm0[root >> 5] = 1u << (root & 31);
-  st->level = 0;
-  st->mode = have_at ? 0 : 1;
-  st->done = 0;
-  st->have_at = have_at;
-  st->n_frontier = 1;
-  st->prev_frontier = 0;
-  st->next_count = 0;
-  st->next_edges = 0;
-  const int32_t *rp = have_at ? at_row_ptr : a_row_ptr;
-  st->unexplored = nnz - (unsigned long long)(rp[root + 1] - rp[root]);
-  st->reached = 1;
-  st->edges_traversed = (unsigned long long)(a_row_ptr[root + 1] - a_row_ptr[root]);
-  st->big_count = 0;
-}
-
-__global__ void bfs_clear_kernel(const BfsState *st, uint32_t *bm0, uint32_t *bm1, int64_t n_words) {
-  if (st->done) return;
-  uint32_t *next = ((st->level + 1) & 1) ? bm1 : bm0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (int64_t)gridDim.x * blockDim.x)
-    next[i] = 0u;
-}
-
-__device__ __forceinline__ void bfs_push_one(int32_t v, uint32_t level, const int32_t *__restrict__ at_row_ptr,
-                                             const int32_t *__restrict__ a_row_ptr, int32_t *levels, uint32_t *next,
-                                             uint32_t &found, unsigned long long &push_deg, unsigned long long &pull_deg) {
-  if (levels[v] == -1) {
-    const int32_t old = atomicCAS(&levels[v], -1, (int32_t)level + 1);
-    if (old == -1) {
-      atomicOr(&next[v >> 5], 1u << (v & 31));
-      ++found;
-      push_deg += (unsigned long long)(at_row_ptr[v + 1] - at_row_ptr[v]);
-      pull_deg += (unsigned long long)(a_row_ptr[v + 1] - a_row_ptr[v]);
-    }
-  }
-}
-
-__device__ __forceinline__ void bfs_push_account3(BfsState *st, uint32_t found, unsigned long long push_deg,
-                                                  unsigned long long pull_deg) {
-  for (int off = 16; off > 0; off >>= 1) {
-    found += __shfl_xor_sync(0xffffffffu, found, off);
-    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
-    pull_deg += __shfl_xor_sync(0xffffffffu, pull_deg, off);
-  }
-  if ((threadIdx.x & 31) == 0 && found) {
-    atomicAdd(&st->next_count, found);
-    atomicAdd(&st->next_edges, push_deg);
-    atomicAdd(&st->edges_traversed, pull_deg);
-  }
-}
-
-// push: one warp per bitmap word of the current frontier; lanes stride over each frontier vertex's
-// out-adjacency (row of A^T)
-template <bool HAS_VAL>
-__global__ void bfs_push_kernel(BfsState *st, const int32_t *__restrict__ at_row_ptr, const int32_t *__restrict__ at_col,
-                                const int32_t *__restrict__ at_val, const int32_t *__restrict__ a_row_ptr,
-                                int32_t *levels, uint32_t *bm0, uint32_t *bm1, int64_t n_words) {
-  if (st->done || st->mode != 0) return;
-  const uint32_t level = st->level;
-  const uint32_t *cur = (level & 1) ? bm1 : bm0;
-  uint32_t *next = (level & 1) ? bm0 : bm1;
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  uint32_t found = 0;
-  unsigned long long push_deg = 0, pull_deg = 0;
-  for (int64_t w = warp; w < n_words; w += n_warps) {
-    uint32_t word = cur[w];
-    while (word) {
-      const int b = __ffs(word) - 1;
-      word &= word - 1;
-      const int64_t u = w * 32 + b;
-      const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
-      if (e - s >= BFS_BIG_ROW) {  // a hub: parked for the whole grid (one warp would serialise the level)
-        uint32_t slot = 0;
-        if (lane == 0) slot = atomicAdd(&st->big_count, 1u);
-        slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (slot < BFS_BIG_CAP) {
-          if (lane == 0) st->big_list[slot] = (int32_t)u;
-          continue;
-        }
-      }
-      for (int k = s + lane; k < e; k += 32) {
-        if (HAS_VAL && at_val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
-        bfs_push_one(at_col[k], level, at_row_ptr, a_row_ptr, levels, next, found, push_deg, pull_deg);
-      }
-    }
-  }
-  bfs_push_account3(st, found, push_deg, pull_deg);
-}
-
-template <bool HAS_VAL>
-__global__ void bfs_push_big_kernel(BfsState *st, const int32_t *__restrict__ at_row_ptr, const int32_t *__restrict__ at_col,
-                                    const int32_t *__restrict__ at_val, const int32_t *__restrict__ a_row_ptr,
-                                    int32_t *levels, uint32_t *bm0, uint32_t *bm1) {
-  if (st->done || st->mode != 0) return;
-  const uint32_t n_big = min(st->big_count, (uint32_t)BFS_BIG_CAP);
-  if (n_big == 0) return;
-  const uint32_t level = st->level;
-  uint32_t *next = (level & 1) ? bm0 : bm1;
-  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, n_threads = (int64_t)gridDim.x * blockDim.x;
-  uint32_t found = 0;
-  unsigned long long push_deg = 0, pull_deg = 0;
-  for (uint32_t i = 0; i < n_big; ++i) {
-    const int32_t u = st->big_list[i];
-    const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
-    for (int64_t k = s + tid; k < e; k += n_threads) {
-      if (HAS_VAL && at_val[k] == 0) continue;
-      bfs_push_one(at_col[k], level, at_row_ptr, a_row_ptr, levels, next, found, push_deg, pull_deg);
-    }
-  }
-  bfs_push_account3(st, found, push_deg, pull_deg);
-}
-
-// does row [s, e) have an in-neighbour in the frontier bitmap?  BFS_PROBE_BATCH entries per step: the column loads and the
-// bitmap probes of a step are issued together, so a row costs e/BATCH dependent round trips instead of e (the early exit
-// makes every step wait for its probes).
-#ifndef BFS_PROBE_BATCH
-#define BFS_PROBE_BATCH 4
-#endif
-template <bool HAS_VAL>
-__device__ __forceinline__ bool bfs_row_hits(const int32_t *__restrict__ col, const int32_t *__restrict__ val,
-                                             const uint32_t *__restrict__ cur, int s, int e) {
-  for (int k = s; k < e; k += BFS_PROBE_BATCH) {
-    int32_t c[BFS_PROBE_BATCH];
-    uint32_t w[BFS_PROBE_BATCH];
-#pragma unroll
-    for (int j = 0; j < BFS_PROBE_BATCH; ++j) {
-      const bool in = (k + j < e) && !(HAS_VAL && val[k + j] == 0);  // bool_and(x, a): a stored 0 is no edge
-      c[j] = in ? col[k + j] : -1;
-    }
-#pragma unroll
-    for (int j = 0; j < BFS_PROBE_BATCH; ++j) w[j] = c[j] >= 0 ? cur[c[j] >> 5] : 0u;
-    bool hit = false;
-#pragma unroll
-    for (int j = 0; j < BFS_PROBE_BATCH; ++j) hit |= (c[j] >= 0) && ((w[j] >> (c[j] & 31)) & 1u);
-    if (hit) return true;
-  }
-  return false;
-}
-
-// pull: thread per unvisited row, stop at the first in-neighbour that is in the frontier bitmap
-template <bool HAS_VAL>
-__global__ void bfs_pull_kernel(BfsState *st, const int32_t *__restrict__ a_row_ptr, const int32_t *__restrict__ a_col,
-                                const int32_t *__restrict__ a_val, const int32_t *__restrict__ deg_row_ptr,
-                                int32_t *levels, uint32_t *bm0, uint32_t *bm1, int64_t n) {
-  if (st->done || st->mode != 1) return;
-  const uint32_t level = st->level;
-  const uint32_t *cur = (level & 1) ? bm1 : bm0;
-  uint32_t *next = (level & 1) ? bm0 : bm1;
-  const int lane = threadIdx.x & 31;
-  uint32_t found_n = 0;
-  unsigned long long push_deg = 0, pull_deg = 0;
-  const int64_t n_padded = (n + 31) / 32 * 32;
-  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
-    bool found = false;
-    if (r < n && levels[r] == -1) {
-      const int s = a_row_ptr[r], e = a_row_ptr[r + 1];
-      found = bfs_row_hits<HAS_VAL>(a_col, a_val, cur, s, e);
-      if (found) {
-        levels[r] = (int32_t)level + 1;
-        ++found_n;
-        push_deg += (unsigned long long)(deg_row_ptr[r + 1] - deg_row_ptr[r]);
-        pull_deg += (unsigned long long)(e - s);
-      }
-    }
-    const uint32_t ballot = __ballot_sync(0xffffffffu, found);
-    if (lane == 0 && ballot) next[r >> 5] = ballot;
-  }
-  for (int off = 16; off > 0; off >>= 1) {
-    found_n += __shfl_xor_sync(0xffffffffu, found_n, off);
-    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
-    pull_deg += __shfl_xor_sync(0xffffffffu, pull_deg, off);
-  }
-  if (lane == 0 && found_n) {
-    atomicAdd(&st->next_count, found_n);
-    atomicAdd(&st->next_edges, push_deg);
-    atomicAdd(&st->edges_traversed, pull_deg);
-  }
-}
-
-__global__ void bfs_decide_kernel(BfsState *st, unsigned long long n) {
-  if (st->done) return;
-  const uint32_t nf = st->next_count;
-  if (nf == 0) {
-    st->done = 1;
-    return;
-  }
-  st->reached += nf;
-  const unsigned long long mf = st->next_edges;
-  st->unexplored = st->unexplored > mf ? st->unexplored - mf : 0ull;
-  if (st->have_at) {
-    // Beamer's direction heuristic (alpha = 14, beta = 24)
-    if (st->mode == 0) {
-      if (mf > st->unexplored / 14ull) st->mode = 1;
-    } else {
-      if ((unsigned long long)nf < n / 24ull && nf < st->n_frontier) st->mode = 0;
-    }
-  }
-  st->prev_frontier = st->n_frontier;
-  st->n_frontier = nf;
-  st->next_count = 0;
-  st->next_edges = 0;
-  st->level += 1;
-  st->big_count = 0;
-}
-
-SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t root, shb_buf *levels, uint32_t max_levels,
-                    shb_graph_stats *stats) {
-  SHB_REQUIRE(c && A && levels, "bad arguments");
-  SHB_REQUIRE(A->n_rows == A->n_cols, "Matrix is not square. Failing computation.");
-  SHB_REQUIRE(root >= 0 && root < A->n_rows, "root out of range");
-  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than n_rows");
-  SHB_REQUIRE(!AT || (AT->n_rows == A->n_rows && AT->nnz == A->nnz), "transpose does not match");
-  SHB_CUDA(cudaSetDevice(c->device));
-  const int64_t n = A->n_rows;
-  const int64_t n_words = (n + 31) / 32;
-  if (max_levels == 0) max_levels = 1u << 30;
-  BfsState *st = nullptr;
-  uint32_t *bm = nullptr;
-  SHB_CUDA(cudaMalloc(&st, sizeof(BfsState)));
-  cudaError_t me = cudaMalloc(&bm, (size_t)n_words * 8);
-  if (me != cudaSuccess) {
-    cudaFree(st);
-    shb_set_error("cudaMalloc of the frontier bitmaps failed: %s", cudaGetErrorString(me));
-    return SHB_ERR_OOM;
-  }
-  uint32_t *bm0 = bm, *bm1 = bm + n_words;
-  int status = SHB_OK;
-  BfsState h;
-  memset(&h, 0, sizeof h);
-  uint64_t launches = 0;
-  cudaEventRecord(c->ev0, c->stream);
-  cudaMemsetAsync(levels->ptr, 0xff, (size_t)n * 4, c->stream);
-  cudaMemsetAsync(bm, 0, (size_t)n_words * 8, c->stream);
-  bfs_init_kernel<<<1, 1, 0, c->stream>>>(st, (int32_t *)levels->ptr, bm0, root, A->row_ptr, AT ? AT->row_ptr : nullptr,
-                                          (unsigned long long)A->nnz, AT != nullptr);
-  const int BATCH = 8;
-  uint32_t issued = 0;
-  const bool a_val = A->val != nullptr;
-  while (true) {
-    for (int b = 0; b < BATCH && issued < max_levels; ++b, ++issued) {
-      bfs_clear_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(st, bm0, bm1, n_words);
-      if (AT) {
-        if (a_val)
-          bfs_push_kernel<true><<<grid_for(n_words * 32, 256, 148 * 8), 256, 0, c->stream>>>(
-              st, AT->row_ptr, AT->col, (const int32_t *)AT->val, A->row_ptr, (int32_t *)levels->ptr, bm0, bm1, n_words);
-        else
-          bfs_push_kernel<false><<<grid_for(n_words * 32, 256, 148 * 8), 256, 0, c->stream>>>(
-              st, AT->row_ptr, AT->col, nullptr, A->row_ptr, (int32_t *)levels->ptr, bm0, bm1, n_words);
-        if (a_val)
-          bfs_push_big_kernel<true><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val,
-                                                                    A->row_ptr, (int32_t *)levels->ptr, bm0, bm1);
-        else
-          bfs_push_big_kernel<false><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, A->row_ptr,
-                                                                     (int32_t *)levels->ptr, bm0, bm1);
-      }
-      if (a_val)
-        bfs_pull_kernel<true><<<grid_for(n, 256, 148 * 32), 256, 0, c->stream>>>(
-            st, A->row_ptr, A->col, (const int32_t *)A->val, AT ? AT->row_ptr : A->row_ptr, (int32_t *)levels->ptr, bm0, bm1, n);
-      else
-        bfs_pull_kernel<false><<<grid_for(n, 256, 148 * 32), 256, 0, c->stream>>>(
-            st, A->row_ptr, A->col, nullptr, AT ? AT->row_ptr : A->row_ptr, (int32_t *)levels->ptr, bm0, bm1, n);
-      bfs_decide_kernel<<<1, 1, 0, c->stream>>>(st, (unsigned long long)n);
-      launches += AT ? 5 : 3;
-    }
-    cudaMemcpyAsync(&h, st, sizeof h, cudaMemcpyDeviceToHost, c->stream);
-    cudaError_t e = cudaStreamSynchronize(c->stream);
-    if (e != cudaSuccess) {
-      shb_set_error("shb_bfs failed: %s (code: %d)", cudaGetErrorString(e), (int)e);
-      status = SHB_ERR_CUDA;
-      break;
-    }
-    if (h.done) break;
-    if (issued >= max_levels) {
-      shb_set_error("level cap of %u reached before the frontier emptied", max_levels);
-      status = SHB_ERR_NOT_CONVERGED;
-      break;
-    }
-  }
-  cudaEventRecord(c->ev1, c->stream);
-  cudaEventSynchronize(c->ev1);
-  float ms = 0.f;
-  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-  if (stats) {
-    stats->iterations = h.level + 1;  // levels 0..h.level are populated
-    stats->converged = h.done;
-    stats->edges_traversed = (int64_t)h.edges_traversed;
-    stats->reached = (int64_t)h.reached;
-    stats->total_ns = (uint64_t)((double)ms * 1e6 + 0.5);
-    stats->launches = launches;
-  }
-  cudaFree(st);
-  cudaFree(bm);
-  return status;
-}
-
-// =================================================================================================
 // SSSP: near-far (delta-stepping) label correcting under min-plus in ONE persistent cooperative kernel.
 // d[v] <- min(d[v], |d[u]| + |w(u,v)|) is applied with atomicMin on the float bits (all values are
 // non-negative, so integer order == float order).  fl(a + w) is monotone in a, hence any relaxation
@@ -802,6 +479,34 @@ done:
   return status;
 #undef SS_CUDA
 }
+
+// does row [s, e) have an in-neighbour in the frontier bitmap?  BFS_PROBE_BATCH entries per step: the column loads and the
+// bitmap probes of a step are issued together, so a row costs e/BATCH dependent round trips instead of e (the early exit
+// makes every step wait for its probes).
+#ifndef BFS_PROBE_BATCH
+#define BFS_PROBE_BATCH 4
+#endif
+template <bool HAS_VAL>
+__device__ __forceinline__ bool bfs_row_hits(const int32_t *__restrict__ col, const int32_t *__restrict__ val,
+                                             const uint32_t *__restrict__ cur, int s, int e) {
+  for (int k = s; k < e; k += BFS_PROBE_BATCH) {
+    int32_t c[BFS_PROBE_BATCH];
+    uint32_t w[BFS_PROBE_BATCH];
+#pragma unroll
+    for (int j = 0; j < BFS_PROBE_BATCH; ++j) {
+      const bool in = (k + j < e) && !(HAS_VAL && val[k + j] == 0);  // bool_and(x, a): a stored 0 is no edge
+      c[j] = in ? col[k + j] : -1;
+    }
+#pragma unroll
+    for (int j = 0; j < BFS_PROBE_BATCH; ++j) w[j] = c[j] >= 0 ? cur[c[j] >> 5] : 0u;
+    bool hit = false;
+#pragma unroll
+    for (int j = 0; j < BFS_PROBE_BATCH; ++j) hit |= (c[j] >= 0) && ((w[j] >> (c[j] & 31)) & 1u);
+    if (hit) return true;
+  }
+  return false;
+}
+
 
 // =================================================================================================
 // Row-partitioned BFS (multi-GPU), direction-optimising.  Rank k owns the vertices
@@ -1347,6 +1052,114 @@ SHB_API int shb_bfs_block_finish(shb_ctx *c, const shb_csr *A, const shb_buf *le
     return SHB_ERR_CUDA;
   }
   return SHB_OK;
+}
+
+// =================================================================================================
+// shb_bfs: the single-device driver (<- app/bfs.cpp:94-152 HarnessBFS::executeRun, integer levels, Q8 decision) is
+// the row-partitioned code above run on ONE block that owns every vertex: same kernels, no peers, the level's counts
+// accumulate straight into the slot.  The host enqueues batches of levels and polls the count ring once per batch.
+// =================================================================================================
+SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t root, shb_buf *levels, uint32_t max_levels,
+                    shb_graph_stats *stats) {
+  SHB_REQUIRE(c && A && levels, "bad arguments");
+  SHB_REQUIRE(A->n_rows == A->n_cols, "Matrix is not square. Failing computation.");
+  SHB_REQUIRE(root >= 0 && root < A->n_rows, "root out of range");
+  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4, "levels shorter than n_rows");
+  SHB_REQUIRE(!AT || (AT->n_rows == A->n_rows && AT->nnz == A->nnz), "transpose does not match");
+  SHB_CUDA(cudaSetDevice(c->device));
+  const int64_t n = A->n_rows;
+  const size_t bm_bytes = ((size_t)((n + 31) / 32) * 4 + 255) / 256 * 256;
+  const size_t cnt_bytes = (size_t)BFS_COUNTER_WORDS * 8, st_bytes = (sizeof(BfsBlockState) + 255) / 256 * 256;
+  if (max_levels == 0) max_levels = 1u << 30;
+  // push degrees of every vertex, cached on the operator (one pass the first time it is traversed)
+  if (AT && !AT->row_len && n > 0) {
+    int32_t *rl = nullptr;
+    SHB_CUDA(cudaMalloc(&rl, (size_t)n * 4));
+    csr_row_lengths_kernel<<<grid_for(n), 256, 0, c->stream>>>(AT->row_ptr, rl, n);
+    AT->row_len = rl;
+  }
+  char *scratch = nullptr;
+  cudaError_t me = cudaMalloc(&scratch, 4 * bm_bytes + cnt_bytes + st_bytes);
+  if (me != cudaSuccess) {
+    shb_set_error("cudaMalloc of the frontier bitmaps failed: %s", cudaGetErrorString(me));
+    return SHB_ERR_OOM;
+  }
+  auto view = [&](size_t off, size_t bytes) {
+    shb_buf b;
+    b.ctx = c; b.device = c->device; b.ptr = scratch + off; b.bytes = bytes; b.owned = false;
+    return b;
+  };
+  shb_buf bm[3] = {view(0, bm_bytes), view(bm_bytes, bm_bytes), view(2 * bm_bytes, bm_bytes)};
+  shb_buf visited = view(3 * bm_bytes, bm_bytes), counters = view(4 * bm_bytes, cnt_bytes);
+  shb_buf state = view(4 * bm_bytes + cnt_bytes, st_bytes), deg = view(0, 0);
+  if (AT) {
+    deg.ptr = AT->row_len;
+    deg.bytes = (uint64_t)n * 4;
+  }
+  int status = SHB_OK;
+  uint64_t launches = 0;
+  uint32_t issued = 0, populated = 0;
+  bool done = false;
+  long long ring[BFS_COUNTER_WORDS];
+  cudaMemsetAsync(scratch + 4 * bm_bytes, 0, cnt_bytes, c->stream);  // the arrival word too (unused without peers)
+  cudaEventRecord(c->ev0, c->stream);
+  status = shb_bfs_block_init(c, A, AT, 0, n, A->nnz, root, AT ? &deg : nullptr, levels, &bm[0], &bm[1], &bm[2], &visited,
+                              &counters, &state, 0);
+  const uint32_t BATCH = 8;
+  while (status == SHB_OK && !done) {
+    const uint32_t first = issued;
+    for (uint32_t b = 0; b < BATCH && issued < max_levels && status == SHB_OK; ++b, ++issued) {
+      shb_buf *next[1] = {&bm[(issued + 1) % 3]};
+      status = shb_bfs_block_level(c, A, AT, 0, n, issued, AT ? &deg : nullptr, &bm[issued % 3], next, 1, 0, &bm[(issued + 2) % 3],
+                                   &visited, levels, &counters, &state, nullptr, 0);
+      launches += AT ? 4 : 2;
+    }
+    if (status != SHB_OK) break;
+    cudaMemcpyAsync(ring, counters.ptr, cnt_bytes, cudaMemcpyDeviceToHost, c->stream);
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) {
+      shb_set_error("shb_bfs failed: %s (code: %d)", cudaGetErrorString(e), (int)e);
+      status = SHB_ERR_CUDA;
+      break;
+    }
+    for (uint32_t f = first; f < issued; ++f) {
+      if (ring[BFS_SLOT(f + 1)] == 0) {  // launch f found nothing: frontiers 0..f are the populated levels
+        populated = f + 1;
+        done = true;
+        break;
+      }
+    }
+    if (!done && issued >= max_levels) {
+      populated = issued + 1;
+      // the vertices of the last frontier get their level (a push level leaves that to the next level's prep)
+      const int64_t n_words = (n + 31) / 32;
+      bfs_block_prep_kernel<<<grid_for(n_words), 256, 0, c->stream>>>(
+          (BfsBlockState *)state.ptr, (long long *)counters.ptr, (const uint32_t *)bm[issued % 3].ptr, (uint32_t *)visited.ptr,
+          (uint32_t *)bm[(issued + 2) % 3].ptr, (int32_t *)levels->ptr, issued, n_words, 0, n_words, 0, n);
+      shb_set_error("level cap of %u reached before the frontier emptied", max_levels);
+      status = SHB_ERR_NOT_CONVERGED;
+      break;
+    }
+  }
+  int fin = shb_bfs_block_finish(c, A, levels, &counters, &state);
+  cudaEventRecord(c->ev1, c->stream);
+  cudaEventSynchronize(c->ev1);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  long long tot[2] = {0, 0};
+  cudaMemcpy(tot, counters.ptr, 16, cudaMemcpyDeviceToHost);
+  if (status == SHB_OK && fin != SHB_OK) status = fin;
+  if (stats) {
+    stats->iterations = populated;
+    stats->converged = done ? 1u : 0u;
+    stats->reached = tot[0];
+    stats->edges_traversed = tot[1];
+    stats->total_ns = (uint64_t)((double)ms * 1e6 + 0.5);
+    stats->launches = launches;
+  }
+  cudaFree(scratch);
+  cudaGetLastError();
+  return status;
 }
 
 // =================================================================================================

@@ -92,6 +92,8 @@ struct shb_csr {
   void *carry_tail = nullptr;
   void *carry_head = nullptr;
   shb_pb *pb = nullptr;  // built on request (shb_csr_build_blocked)
+  // int32 length of every row, built on first use by shb_bfs (the push degrees of Beamer's direction rule)
+  mutable int32_t *row_len = nullptr;
 };
 
 struct ScopedTimer {

@@ -208,3 +208,26 @@ def test_scatter_to_several_destinations_row_partitioned(ctx, orc):
     ctx.spmv_scatter(eye, shb.PLUS_TIMES, xb, None, 1.0, 0.0, [d0], 0, delta=1e-4, changed=flag)
     ctx.synchronize()
     assert flag.download(np.uint32, 1)[0] == 0 and np.array_equal(d0.download(np.float32, n), x)
+
+
+@pytest.mark.parametrize("with_transpose", [True, False])
+def test_bfs_level_cap_reports_not_converged_with_the_levels_found(ctx, orc, with_transpose):
+    """max_levels smaller than the depth of the traversal: SHB_ERR_NOT_CONVERGED (status 7), and the levels reached so
+    far are exact (the reference loops forever on such inputs, Q8)."""
+    rp, col, _ = orc.gen_grid2d(50, 3)
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, None)
+    want, nlev, _ = orc.bfs_levels(rp, col, None, 0)
+    assert nlev > 20
+    with pytest.raises(shb.ShbError) as e:
+        ctx.bfs(A, 0, AT=A if with_transpose else None, max_levels=5)
+    assert e.value.status == 7
+    levels, st = ctx.bfs(A, 0, AT=A if with_transpose else None)
+    assert st.converged and st.iterations == nlev and np.array_equal(levels.download(np.int32, n), want)
+    # a long traversal laps the driver's count ring (256 frontiers)
+    rp2, col2, _ = orc.gen_grid2d(700, 2)
+    A2 = ctx.csr(len(rp2) - 1, len(rp2) - 1, rp2, col2, None)
+    want2, nlev2, edges2 = orc.bfs_levels(rp2, col2, None, 0)
+    lv2, st2 = ctx.bfs(A2, 0, AT=A2 if with_transpose else None)
+    assert nlev2 > 600 and st2.iterations == nlev2 and st2.edges_traversed == edges2
+    assert np.array_equal(lv2.download(np.int32, len(rp2) - 1), want2)

@@ -1204,7 +1204,8 @@ __device__ __forceinline__ int sssp_owner(const SsspBlockArgs &a, uint32_t v) {
 }
 
 // dist[v] (local copy) just dropped from `old` to cb
-__device__ __forceinline__ void sssp_block_improved(const SsspBlockArgs &a, SsspShared &sh, uint32_t v, uint32_t cb, uint32_t t_hi,
+__device__ __forceinline__ void sssp_block_improved(const SsspBlockArgs &a, SsspShared &sh, uint32_t v, uint32_t cb, uint32_t old,
+                                                    uint32_t t_hi,
                                                     int nxt, uint2 *near_next, uint32_t *near_next_size, int32_t *far_cur,
                                                     uint32_t *far_cur_size, uint32_t &fmin) {
   const uint32_t r = v - a.lo;
@@ -1226,7 +1227,17 @@ __device__ __forceinline__ void sssp_block_improved(const SsspBlockArgs &a, Sssp
   } else {
     fmin = min(fmin, cb);
     const uint32_t bit = 1u << (r & 31);
-    if (!(atomicOr(&a.pile_bits[r >> 5], bit) & bit)) {  // first time in this round's pile
+    uint32_t *word = &a.pile_bits[r >> 5];
+    bool enter;
+    if (old == 0x7f7fffffu) {  // never reached before: cannot be in the pile; mark it without waiting for the answer
+      asm volatile("red.relaxed.gpu.global.or.b32 [%0], %1;" ::"l"(word), "r"(bit) : "memory");
+      enter = true;
+    } else if (__ldcg(word) & bit) {  // the common case of a vertex improved again while it waits in the pile
+      enter = false;
+    } else {
+      enter = !(atomicOr(word, bit) & bit);  // first time in this round's pile
+    }
+    if (enter) {
       const uint32_t slot = atomicAdd(&sh.fcount, 1u);
       if (slot < SSSP_FSTAGE) sh.fstage[slot] = (int32_t)v;
       else far_cur[atomicAdd(far_cur_size, 1u)] = (int32_t)v;
@@ -1366,7 +1377,7 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                   if (cb[j] < old[j])
-                    sssp_block_improved(a, sh, (uint32_t)vv[j], cb[j], t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
+                    sssp_block_improved(a, sh, (uint32_t)vv[j], cb[j], old[j], t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
               }
             }
             uint32_t bigs = __ballot_sync(0xffffffffu, big);
@@ -1381,7 +1392,7 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
                 const uint32_t c1 = __float_as_uint(MinPlusF32::mult(bd, w));
                 if ((uint32_t)v < a.n_total && c1 < __ldcg(a.dist + v)) {
                   const uint32_t o1 = atomicMin(a.dist + v, c1);
-                  if (c1 < o1) sssp_block_improved(a, sh, (uint32_t)v, c1, t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
+                  if (c1 < o1) sssp_block_improved(a, sh, (uint32_t)v, c1, o1, t_hi, nxt, near_next, near_next_size, far_cur, far_cur_size, fmin);
                 }
               }
             }

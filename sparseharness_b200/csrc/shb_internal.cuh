@@ -114,6 +114,11 @@ struct ScopedTimer {
 };
 
 static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+// grid size of a grid-stride kernel: enough blocks for n items, capped at a few waves of the 148 SMs
+static inline unsigned grid_for(int64_t n, int per_block = 256, int cap = 148 * 16) {
+  const int64_t b = (n + per_block - 1) / per_block;
+  return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
+}
 
 // implemented in shb_core.cu, used across translation units
 int shb_csr_alloc(shb_ctx *ctx, int64_t n_rows, int64_t n_cols, int64_t nnz, bool has_values, shb_csr **out);

@@ -181,7 +181,7 @@ __global__ void pagerank_values_kernel(const int32_t *col, int64_t nnz, const ui
   }
 }
 
-static unsigned grid_for(int64_t n) { return (unsigned)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, 148 * 32)); }
+static unsigned synth_grid(int64_t n) { return grid_for(n, 256, 148 * 32); }
 
 SHB_API int shb_synth_rmat(shb_ctx *c, int scale, int64_t n_edges, uint64_t seed, int symmetrise, int value_mode,
                            float damping, shb_csr **out) {
@@ -216,7 +216,7 @@ SHB_API int shb_synth_rmat(shb_ctx *c, int scale, int64_t n_edges, uint64_t seed
     RM_CUDA(cudaMalloc(&d_count, 16));
     RM_CUDA(cudaMemsetAsync(d_count, 0, 16, c->stream));
     const Scramble sc = make_scramble(scale, seed);
-    if (n_edges > 0) gen_rmat_keys_kernel<<<grid_for(n_edges), 256, 0, c->stream>>>(scale, n_edges, seed, symmetrise, sc, keys);
+    if (n_edges > 0) gen_rmat_keys_kernel<<<synth_grid(n_edges), 256, 0, c->stream>>>(scale, n_edges, seed, symmetrise, sc, keys);
     RM_CUDA(cudaGetLastError());
     // sort by (row, col); self loops (all-ones keys) go to the end
     size_t tb = 0;
@@ -242,7 +242,7 @@ SHB_API int shb_synth_rmat(shb_ctx *c, int scale, int64_t n_edges, uint64_t seed
       RM_CUDA(cudaStreamSynchronize(c->stream));
       std::swap(sorted, other);
       RM_CUDA(cudaMemsetAsync(d_count, 0, 16, c->stream));
-      if (uniq > 0) count_valid_kernel<<<grid_for(uniq), 256, 0, c->stream>>>(sorted, uniq, d_count);
+      if (uniq > 0) count_valid_kernel<<<synth_grid(uniq), 256, 0, c->stream>>>(sorted, uniq, d_count);
       RM_CUDA(cudaGetLastError());
       unsigned long long valid = 0;
       RM_CUDA(cudaMemcpyAsync(&valid, d_count, 8, cudaMemcpyDeviceToHost, c->stream));
@@ -251,8 +251,8 @@ SHB_API int shb_synth_rmat(shb_ctx *c, int scale, int64_t n_edges, uint64_t seed
     }
     status = shb_csr_alloc(c, n, n, m, value_mode == 1, &A);
     if (status != SHB_OK) goto done;
-    keys_to_row_ptr_kernel<<<grid_for(n + 1), 256, 0, c->stream>>>(sorted, m, n, A->row_ptr);
-    if (m > 0) keys_to_cols_kernel<<<grid_for(m), 256, 0, c->stream>>>(sorted, m, A->col);
+    keys_to_row_ptr_kernel<<<synth_grid(n + 1), 256, 0, c->stream>>>(sorted, m, n, A->row_ptr);
+    if (m > 0) keys_to_cols_kernel<<<synth_grid(m), 256, 0, c->stream>>>(sorted, m, A->col);
     RM_CUDA(cudaGetLastError());
     if (value_mode == 1 && m > 0) {
       uint32_t *hist = (uint32_t *)other;  // reuse: n * 4 bytes <= cap * 8
@@ -262,8 +262,8 @@ SHB_API int shb_synth_rmat(shb_ctx *c, int scale, int64_t n_edges, uint64_t seed
         goto done;
       }
       RM_CUDA(cudaMemsetAsync(hist, 0, (size_t)n * 4, c->stream));
-      col_histogram_kernel<<<grid_for(m), 256, 0, c->stream>>>(A->col, m, hist);
-      pagerank_values_kernel<<<grid_for(m), 256, 0, c->stream>>>(A->col, m, hist, damping, (float *)A->val);
+      col_histogram_kernel<<<synth_grid(m), 256, 0, c->stream>>>(A->col, m, hist);
+      pagerank_values_kernel<<<synth_grid(m), 256, 0, c->stream>>>(A->col, m, hist, damping, (float *)A->val);
       RM_CUDA(cudaGetLastError());
     }
     RM_CUDA(cudaStreamSynchronize(c->stream));
@@ -316,7 +316,7 @@ SHB_API int shb_synth_grid2d(shb_ctx *c, int64_t W, int64_t H, uint64_t seed, sh
   const int64_t nnz = 4 * n - 2 * W - 2 * H;
   shb_csr *A = nullptr;
   SHB_TRY(shb_csr_alloc(c, n, n, nnz, true, &A));
-  gen_grid_kernel<<<grid_for(n + 1), 256, 0, c->stream>>>(W, H, seed, A->row_ptr, A->col, (float *)A->val);
+  gen_grid_kernel<<<synth_grid(n + 1), 256, 0, c->stream>>>(W, H, seed, A->row_ptr, A->col, (float *)A->val);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     shb_csr_destroy(A);
@@ -379,7 +379,7 @@ SHB_API int shb_csr_transpose(shb_ctx *c, const shb_csr *A, shb_csr **out) {
     TR_CUDA(cudaMalloc(&i1, nn * 4));
     TR_CUDA(cudaMalloc(&i2, nn * 4));
     if (nnz > 0 && A->n_rows > 0)
-      transpose_keys_kernel<<<grid_for(A->n_rows * 32), 256, 0, c->stream>>>(A->row_ptr, A->col, A->n_rows, k1, i1);
+      transpose_keys_kernel<<<synth_grid(A->n_rows * 32), 256, 0, c->stream>>>(A->row_ptr, A->col, A->n_rows, k1, i1);
     TR_CUDA(cudaGetLastError());
     cub::DoubleBuffer<uint64_t> dk(k1, k2);
     cub::DoubleBuffer<uint32_t> dv(i1, i2);
@@ -387,11 +387,11 @@ SHB_API int shb_csr_transpose(shb_ctx *c, const shb_csr *A, shb_csr **out) {
     TR_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (int64_t)nnz, 0, 64, c->stream));
     TR_CUDA(cudaMalloc(&tmp, std::max<size_t>(tb, 256)));
     TR_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, dk, dv, (int64_t)nnz, 0, 64, c->stream));
-    keys_to_row_ptr_kernel<<<grid_for(T->n_rows + 1), 256, 0, c->stream>>>(dk.Current(), nnz, T->n_rows, T->row_ptr);
+    keys_to_row_ptr_kernel<<<synth_grid(T->n_rows + 1), 256, 0, c->stream>>>(dk.Current(), nnz, T->n_rows, T->row_ptr);
     if (nnz > 0) {
-      keys_to_cols_kernel<<<grid_for(nnz), 256, 0, c->stream>>>(dk.Current(), nnz, T->col);
+      keys_to_cols_kernel<<<synth_grid(nnz), 256, 0, c->stream>>>(dk.Current(), nnz, T->col);
       if (A->val)
-        permute_vals_kernel<<<grid_for(nnz), 256, 0, c->stream>>>(dv.Current(), (const uint32_t *)A->val, nnz,
+        permute_vals_kernel<<<synth_grid(nnz), 256, 0, c->stream>>>(dv.Current(), (const uint32_t *)A->val, nnz,
                                                                    (uint32_t *)T->val);
     }
     TR_CUDA(cudaGetLastError());

@@ -183,6 +183,68 @@ private:
     std::exit(-1);
   }
 
+  // Fast token parsers for the threaded path.  They accept exactly the common spellings and produce exactly what
+  // strtol / strtod produce for them; anything else (hex, inf/nan, > 18 digits, exponents beyond +-22, ...) is left
+  // to the C library, so the tuples are bit-identical to the sequential parser's by construction:
+  //   integer: [+-]digits, at most 18 digits;
+  //   decimal: [+-]digits[.digits][(e|E)[+-]digits] with at most 19 significant digits forming m <= 2^53 and a
+  //            decimal exponent |e10| <= 22.  Then m and 10^|e10| are exact doubles and the single multiplication or
+  //            division rounds once, i.e. correctly -- Clinger's fast path, the same value strtod returns.
+  static inline long fast_long(const char *q, const char *eol, char **end) {
+    const char *p = q;
+    bool neg = false;
+    if (p < eol && (*p == '+' || *p == '-')) neg = *p++ == '-';
+    const char *d0 = p;
+    unsigned long long v = 0;
+    while (p < eol && *p >= '0' && *p <= '9') v = v * 10 + (unsigned)(*p++ - '0');
+    if (p == d0 || p - d0 > 18) return std::strtol(q, end, 10);
+    *end = const_cast<char *>(p);
+    return neg ? -(long)v : (long)v;
+  }
+
+  static inline double fast_double(const char *q, const char *eol, char **end) {
+    static const double P10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                   1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    const char *p = q;
+    bool neg = false;
+    if (p < eol && (*p == '+' || *p == '-')) neg = *p++ == '-';
+    unsigned long long m = 0;
+    int digits = 0, sig = 0, e10 = 0;
+    while (p < eol && *p >= '0' && *p <= '9') {
+      if (sig || *p != '0') { m = m * 10 + (unsigned)(*p - '0'); ++sig; }
+      ++p; ++digits;
+    }
+    if (p < eol && *p == '.') {
+      ++p;
+      while (p < eol && *p >= '0' && *p <= '9') {
+        if (sig || *p != '0') { m = m * 10 + (unsigned)(*p - '0'); ++sig; }
+        ++p; ++digits; --e10;
+      }
+    }
+    if (digits == 0 || sig > 19) return std::strtod(q, end);
+    if (p < eol && (*p == 'e' || *p == 'E')) {
+      const char *pe = p + 1;
+      bool eneg = false;
+      if (pe < eol && (*pe == '+' || *pe == '-')) eneg = *pe++ == '-';
+      const char *e0 = pe;
+      int ev = 0;
+      while (pe < eol && *pe >= '0' && *pe <= '9' && pe - e0 < 6) ev = ev * 10 + (*pe++ - '0');
+      if (pe == e0 || (pe < eol && *pe >= '0' && *pe <= '9')) return std::strtod(q, end);  // "1e" / huge exponent
+      e10 += eneg ? -ev : ev;
+      p = pe;
+    }
+    // a following character that strtod could still consume (hex "0x", "inf", "nan", a second '.') -> C library
+    if (p < eol && ((*p >= '0' && *p <= '9') || *p == '.' || *p == 'x' || *p == 'X' || *p == 'n' || *p == 'N' || *p == 'i' ||
+                    *p == 'I' || *p == 'p' || *p == 'P'))
+      return std::strtod(q, end);
+    if (m > (1ull << 53) || e10 > 22 || e10 < -22) return std::strtod(q, end);
+    double v = (double)m;
+    if (e10 > 0) v *= P10[e10];
+    else if (e10 < 0) v /= P10[-e10];
+    *end = const_cast<char *>(p);
+    return neg ? -v : v;
+  }
+
   // The reference reads entries with fscanf("%d %d %lg\n") (src/sparse_matrix.cpp:50-57): whitespace-separated
   // tokens, line structure irrelevant, stop at the first token that does not parse.
   static void parse_entries_sequential(const char *p, bool pattern, int nonz, std::vector<long> &oI, std::vector<long> &oJ,
@@ -249,15 +311,17 @@ private:
         while (q < eol && (*q == ' ' || *q == '\t' || *q == '\r')) ++q;
         if (q < eol) {  // a non-blank line: exactly the entry's tokens, nothing else
           char *end = nullptr;
-          const long I1 = std::strtol(q, &end, 10);
+          const long I1 = fast_long(q, eol, &end);
           if (end == q || end > eol) { pc.regular = false; return; }
           q = end;
-          const long J1 = std::strtol(q, &end, 10);
+          while (q < eol && (*q == ' ' || *q == '\t')) ++q;  // strtol / strtod skip leading blanks themselves
+          const long J1 = fast_long(q, eol, &end);
           if (end == q || end > eol) { pc.regular = false; return; }
           q = end;
           double v = 1.0;
           if (!pattern) {
-            v = std::strtod(q, &end);
+            while (q < eol && (*q == ' ' || *q == '\t')) ++q;
+            v = fast_double(q, eol, &end);
             if (end == q || end > eol) { pc.regular = false; return; }
             q = end;
           }

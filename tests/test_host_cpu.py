@@ -165,3 +165,49 @@ def test_parallel_parse_equals_sequential_parse(tmp_path, monkeypatch, kind):
         assert np.array_equal(a[k], b[k]), k
     assert np.array_equal(a["val"].view(np.int32), b["val"].view(np.int32))
     assert a["rp"][-1] == (nnz if sym == "general" else nnz + int((I != J).sum()))
+
+
+def test_threaded_parser_fast_tokens_match_the_c_library_on_tricky_spellings(tmp_path, monkeypatch):
+    """The threaded loader's own integer / decimal token parsers (exact fast path, C library for the rest) give the
+    sequential strtol / strtod tuples bit for bit: short and 15-20 digit mantissas, exponents at and past +-22,
+    leading '+', '.5', '5.', '-0', hexadecimal floats, overflow to infinity, subnormal results."""
+    rng = np.random.default_rng(99)
+    specials = ["0", "-0", "+3", ".5", "5.", "-.25e1", "1e5", "1E-5", "1e22", "1e23", "1e-22", "1e-23", "9007199254740992",
+                "9007199254740993", "12345678901234567890", "0.1234567890123456789", "123456789012345678e-10",
+                "4.9e-324", "1e-320", "1e39", "3.4028235e38", "0x1.8p3", "0X10", "1e400", "-1e400", "007", "1.0000000000000002",
+                "8.5e+0007", "2.5E+02", "0.000000000000000000001", "179769313486231570000", "1.7976931348623157e308"]
+    vals = list(specials)
+    for _ in range(30000):
+        k = rng.integers(0, 6)
+        m = rng.integers(0, 10 ** int(rng.integers(1, 19)))
+        if k == 0:
+            vals.append(str(m))
+        elif k == 1:
+            s = str(m)
+            p = int(rng.integers(0, len(s) + 1))
+            vals.append(("-" if rng.integers(2) else "") + s[:p] + "." + s[p:])
+        elif k == 2:
+            vals.append(f"{m}e{int(rng.integers(-30, 31))}")
+        elif k == 3:
+            vals.append(f"{rng.normal(0, 1e3):.17g}")
+        elif k == 4:
+            vals.append(f"{rng.normal(0, 1):.6e}")
+        else:
+            vals.append(f"{float(rng.integers(-10**6, 10**6)) / 1000:.3f}")
+    n = 500
+    nnz = len(vals)
+    I = rng.integers(1, n + 1, nnz)
+    J = rng.integers(1, n + 1, nnz)
+    lines = ["%%MatrixMarket matrix coordinate real general", f"{n} {n} {nnz}"] + [f"{I[k]} {J[k]} {vals[k]}" for k in range(nnz)]
+    mtx = tmp_path / "t.mtx"
+    mtx.write_text("\n".join(lines) + "\n")
+    kernel = os.path.join(KERNELS, "spmv", "glb-sdp-rsa.json")
+    monkeypatch.setenv("SHB_MM_THREADS", "1")
+    a = _parse(tmp_path, str(mtx), kernel, extra=("--keep_values",))
+    monkeypatch.setenv("SHB_MM_THREADS", "5")
+    monkeypatch.setenv("SHB_MM_PARALLEL_MIN_BYTES", "1")
+    b = _parse(tmp_path, str(mtx), kernel, extra=("--keep_values",))
+    assert a["rp"][-1] == nnz
+    for k in ("rp", "col"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a["val"].view(np.int32), b["val"].view(np.int32))

@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <iostream>
 #include <limits>
 #include <string>
@@ -66,16 +67,43 @@ public:
     A.n_rows = H;
     A.n_cols = std::max<int64_t>(cols, H);
     A.row_ptr.assign((std::size_t)H + 1, 0);
-    for (std::size_t i = 0; i < eI.size(); ++i) A.row_ptr[(std::size_t)eJ[i] + 1]++;
-    for (int64_t r = 0; r < H; ++r) A.row_ptr[(std::size_t)r + 1] += A.row_ptr[(std::size_t)r];
     A.col_idx.resize(eI.size());
     A.vals.resize(eI.size());
-    std::vector<int64_t> cursor(A.row_ptr.begin(), A.row_ptr.end() - 1);
-    for (std::size_t i = 0; i < eI.size(); ++i) {
-      const int64_t p = cursor[(std::size_t)eJ[i]]++;
-      A.col_idx[(std::size_t)p] = eI[i];
-      A.vals[(std::size_t)p] = truncate_values ? through_int(eV[i]) : eV[i];
-    }
+    // Stable counting sort of the tuples by row (the tuple's second index, Q1).  Large inputs: every thread owns a
+    // contiguous range of ROWS, scans all tuples in file order and handles the ones that fall in its range -- the
+    // reads are sequential, each thread's counters and output slab stay in its own cache, and the in-row order is the
+    // file order whatever the thread count (same arrays as the sequential loop, bit for bit).
+    unsigned n_thr = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    if (const char *e = std::getenv("SHB_MM_THREADS")) n_thr = (unsigned)std::max(1, std::atoi(e));
+    std::size_t min_entries = (std::size_t)1 << 20;  // below this the threads do not pay
+    if (const char *e = std::getenv("SHB_MM_PARALLEL_MIN_BYTES")) min_entries = (std::size_t)std::strtoull(e, nullptr, 10) / 8;
+    if (eI.size() < min_entries || H < (int64_t)n_thr * (min_entries < ((std::size_t)1 << 20) ? 1 : 1024)) n_thr = 1;
+    auto in_parallel = [&](const std::function<void(unsigned)> &fn) {
+      std::vector<std::thread> th;
+      for (unsigned t = 1; t < n_thr; ++t) th.emplace_back(fn, t);
+      fn(0);
+      for (auto &x : th) x.join();
+    };
+    auto row_lo = [&](unsigned t) { return (int64_t)((__int128)H * t / n_thr); };
+    in_parallel([&](unsigned t) {
+      const int64_t lo = row_lo(t), hi = row_lo(t + 1);
+      for (std::size_t i = 0; i < eJ.size(); ++i) {
+        const int64_t r = eJ[i];
+        if (r >= lo && r < hi) A.row_ptr[(std::size_t)r + 1]++;
+      }
+    });
+    for (int64_t r = 0; r < H; ++r) A.row_ptr[(std::size_t)r + 1] += A.row_ptr[(std::size_t)r];
+    in_parallel([&](unsigned t) {
+      const int64_t lo = row_lo(t), hi = row_lo(t + 1);
+      std::vector<int64_t> cursor(A.row_ptr.begin() + lo, A.row_ptr.begin() + hi);
+      for (std::size_t i = 0; i < eI.size(); ++i) {
+        const int64_t r = eJ[i];
+        if (r < lo || r >= hi) continue;
+        const int64_t p = cursor[(std::size_t)(r - lo)]++;
+        A.col_idx[(std::size_t)p] = eI[i];
+        A.vals[(std::size_t)p] = truncate_values ? through_int(eV[i]) : eV[i];
+      }
+    });
     return A;
   }
 
@@ -90,7 +118,7 @@ public:
       const double q = (std::fabs((double)eV[i]) / (double)column_sums[(std::size_t)eI[i]]) * (double)dampingFactor;
       eV[i] = (EType)q;
     }
-    ellpack_calculated = false;
+    ellpack_calculated = false;  // values changed; the row lengths (max_width) did not
   }
 
   // diagonal -> numeric_limits<EType>::min(), off-diagonal -> the tuple's second index (src/sparse_matrix.cpp:433-456)
@@ -101,8 +129,15 @@ public:
     ellpack_calculated = false;
   }
 
+  // longest row (the ELL width the reference pads to); needs the row lengths only, not the ragged rows
   unsigned int maxRowLength() {
-    if (!ellpack_calculated) calculate_ellpack();
+    if (!ellpack_calculated && !width_calculated) {
+      start_timer(max_row_length, sparse_matrix);
+      std::vector<unsigned int> lengths((std::size_t)std::max(rows, 0), 0);
+      max_width = 0;
+      for (std::size_t i = 0; i < eJ.size(); ++i) max_width = std::max(max_width, ++lengths[(std::size_t)eJ[i]]);
+      width_calculated = true;
+    }
     return max_width;
   }
 
@@ -399,7 +434,7 @@ private:
   std::vector<EType> eV;
   int rows = 0, cols = 0, nonz = 0;
 
-  bool ellpack_calculated = false;
+  bool ellpack_calculated = false, width_calculated = false;
   unsigned int max_width = 0;
   ellpack_matrix<EType> ellpackMatrix;
 };

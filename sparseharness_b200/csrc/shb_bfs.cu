@@ -166,7 +166,7 @@ __device__ __forceinline__ void bfs_push_account(long long *acc, unsigned long l
   }
 }
 
-// push: one warp per owned frontier word; lanes stride over each frontier vertex's out-adjacency.  Hub vertices
+// push: a warp per owned frontier word (32 fetched at a time); lanes stride over each frontier vertex's out-adjacency.  Hub vertices
 // are parked in the state's list and expanded by the whole grid in bfs_block_push_big_kernel (one warp walking a
 // 10^5-entry adjacency would serialise the level).
 template <bool HAS_VAL>
@@ -181,26 +181,37 @@ __global__ void bfs_block_push_kernel(BfsBlockState *st, const int32_t *__restri
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   uint32_t *mine = next.bm[next.self];
   unsigned long long found = 0, push_deg = 0;
-  for (int64_t w = word_lo + warp; w < word_hi; w += n_warps) {
-    uint32_t word = cur[w];
-    while (word) {
-      const int b = __ffs(word) - 1;
-      word &= word - 1;
-      const int64_t u = w * 32 + b - row_offset;
-      if (u < 0 || u >= n_local) continue;
-      const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
-      if (e - s >= BFS_PUSH_BIG_ROW) {
-        uint32_t slot = 0;
-        if (lane == 0) slot = atomicAdd(&st->big_count, 1u);
-        slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (slot < BFS_PUSH_BIG_CAP) {
-          if (lane == 0) st->big_list[slot] = (int32_t)u;
-          continue;
+  // Warp i owns words i, i + n_warps, ... (neighbouring words -- the hub region of an RMAT graph -- go to different
+  // warps).  It fetches 32 of its words with one load per lane and walks the non-empty ones: a sparse frontier is a
+  // scan of the bitmap, and one word per warp step made that scan a chain of dependent loads (30 us on 2^24 vertices).
+  for (int64_t base = word_lo + warp; base < word_hi; base += n_warps * 32) {
+    const int64_t my_index = base + lane * n_warps;
+    const uint32_t my_word = my_index < word_hi ? cur[my_index] : 0u;
+    uint32_t live = __ballot_sync(0xffffffffu, my_word != 0);
+    while (live) {
+      const int src = __ffs(live) - 1;
+      live &= live - 1;
+      uint32_t word = __shfl_sync(0xffffffffu, my_word, src);
+      const int64_t w = base + src * n_warps;
+      while (word) {
+        const int b = __ffs(word) - 1;
+        word &= word - 1;
+        const int64_t u = w * 32 + b - row_offset;
+        if (u < 0 || u >= n_local) continue;
+        const int s = at_row_ptr[u], e = at_row_ptr[u + 1];
+        if (e - s >= BFS_PUSH_BIG_ROW) {
+          uint32_t slot = 0;
+          if (lane == 0) slot = atomicAdd(&st->big_count, 1u);
+          slot = __shfl_sync(0xffffffffu, slot, 0);
+          if (slot < BFS_PUSH_BIG_CAP) {
+            if (lane == 0) st->big_list[slot] = (int32_t)u;
+            continue;
+          }
         }
-      }
-      for (int k = s + lane; k < e; k += 32) {
-        if (HAS_VAL && at_val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
-        bfs_push_visit(at_col[k], visited, next, mine, deg, found, push_deg);
+        for (int k = s + lane; k < e; k += 32) {
+          if (HAS_VAL && at_val[k] == 0) continue;  // bool_and(x, a): a stored 0 is no edge
+          bfs_push_visit(at_col[k], visited, next, mine, deg, found, push_deg);
+        }
       }
     }
   }
@@ -469,9 +480,19 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
   SHB_CUDA(cudaMemsetAsync(cnt, 0, BFS_FLAG_WORD * 8, c->stream));
   SHB_CUDA(cudaMemsetAsync(cnt + BFS_STAGE_WORD, 0, (size_t)(BFS_COUNTER_WORDS - BFS_STAGE_WORD) * 8, c->stream));
   long long *acc = staged ? cnt + BFS_STAGE_WORD : cnt + BFS_SLOT(0);
-  if (A->n_rows > 0)
-    bfs_block_mark_isolated_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>(A->row_ptr, (uint32_t *)visited->ptr, A->n_rows,
-                                                                               row_offset >> 5);
+  if (A->n_rows > 0) {
+    // the empty-row bits depend on the operator only: one pass the first time it is traversed, a 1-bit-per-row copy after
+    const size_t iso_bytes = (size_t)((A->n_rows + 31) / 32) * 4;
+    if (!A->empty_row_bits) {
+      uint32_t *bits = nullptr;
+      SHB_CUDA(cudaMalloc(&bits, iso_bytes));
+      SHB_CUDA(cudaMemsetAsync(bits, 0, iso_bytes, c->stream));
+      bfs_block_mark_isolated_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>(A->row_ptr, bits, A->n_rows, 0);
+      A->empty_row_bits = bits;
+    }
+    SHB_CUDA(cudaMemcpyAsync((uint32_t *)visited->ptr + (row_offset >> 5), A->empty_row_bits, iso_bytes,
+                             cudaMemcpyDeviceToDevice, c->stream));
+  }
   bfs_block_init_kernel<<<1, 1, 0, c->stream>>>((BfsBlockState *)state->ptr, (int32_t *)levels->ptr, (uint32_t *)frontier0->ptr,
                                                 acc, root, row_offset, A->n_rows, deg ? (const int32_t *)deg->ptr : nullptr,
                                                 AT != nullptr, (unsigned long long)nnz_total, (unsigned long long)n_total);
@@ -671,8 +692,9 @@ SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t roo
       break;
     }
   }
-  int fin = shb_bfs_block_finish(c, A, levels, &counters, &state);
+  // the traversal ends here: levels are final.  Counting what was reached (the TEPS numerator) is reporting.
   cudaEventRecord(c->ev1, c->stream);
+  int fin = shb_bfs_block_finish(c, A, levels, &counters, &state);
   cudaEventSynchronize(c->ev1);
   float ms = 0.f;
   cudaEventElapsedTime(&ms, c->ev0, c->ev1);

@@ -340,6 +340,7 @@ SHB_API int shb_csr_destroy(shb_csr *A) {
   cudaFree(A->carry_tail);
   cudaFree(A->carry_head);
   cudaFree(A->row_len);
+  cudaFree(A->empty_row_bits);
   shb_pb_free(A->pb);
   cudaGetLastError();
   delete A;

@@ -94,6 +94,8 @@ struct shb_csr {
   shb_pb *pb = nullptr;  // built on request (shb_csr_build_blocked)
   // int32 length of every row, built on first use by shb_bfs (the push degrees of Beamer's direction rule)
   mutable int32_t *row_len = nullptr;
+  // bit r set <=> row r is empty (vertices a BFS pull can never find), built on first use by shb_bfs_block_init
+  mutable uint32_t *empty_row_bits = nullptr;
 };
 
 struct ScopedTimer {

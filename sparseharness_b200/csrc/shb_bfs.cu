@@ -7,6 +7,8 @@
 // than levels.  Here the frontier, the visited set, the levels and the termination state never leave
 // the device; the host enqueues batches of levels and polls a 4 KB count ring once per batch.
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 
 #include "shb_internal.cuh"
 
@@ -240,13 +242,13 @@ __global__ void bfs_block_push_big_kernel(const BfsBlockState *st, const int32_t
   bfs_push_account(acc, found, push_deg);
 }
 
+// pull, thread per row (SHB_BFS_PULL=rows: kept as the comparison for the compacted mapping below)
 template <bool HAS_VAL>
-__global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__restrict__ row_ptr,
-                                      const int32_t *__restrict__ col, const int32_t *__restrict__ val,
-                                      const int32_t *__restrict__ deg, const uint32_t *__restrict__ cur,
-                                      const uint32_t *__restrict__ visited, const __grid_constant__ BfsPeers next,
-                                      int32_t *levels, long long *acc, uint32_t level, int64_t n_local, int64_t row_offset) {
-  if (st->done || st->mode != 1) return;
+__device__ __forceinline__ void bfs_pull_rows(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                                              const int32_t *__restrict__ val, const int32_t *__restrict__ deg,
+                                              const uint32_t *__restrict__ cur, const uint32_t *__restrict__ visited,
+                                              const BfsPeers &next, int32_t *levels, long long *acc, uint32_t level,
+                                              int64_t n_local, int64_t row_offset) {
   const int lane = threadIdx.x & 31;
   const int64_t word_offset = row_offset >> 5;
   unsigned long long found_n = 0, push_deg = 0;
@@ -299,6 +301,111 @@ __global__ void bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__
     atomicAdd(reinterpret_cast<unsigned long long *>(&acc[0]), found_n);
     atomicAdd(reinterpret_cast<unsigned long long *>(&acc[1]), push_deg);
   }
+}
+
+// Pull, compacted: thread-per-row leaves most lanes idle once a good part of the rows is visited (visited and empty
+// rows are skipped; ncu on the first big pull level: 9.7 active threads per instruction).  A warp takes 256 rows,
+// compacts the unvisited ones into its own shared-memory list with the 8 visited words, and its lanes then walk that
+// list densely (hub rows by the whole warp, as above).  The group's 8 next-frontier words are assembled in shared
+// memory and stored once into every rank's bitmap.  No CTA barrier: warps stay independent.  RMAT 24 on one GPU:
+// 0.90 -> 0.77 ms for the traversal.
+#define BFS_PULL_GROUP_WORDS 8
+template <bool HAS_VAL>
+__device__ __forceinline__ void bfs_pull_compact(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                                                 const int32_t *__restrict__ val, const int32_t *__restrict__ deg,
+                                                 const uint32_t *__restrict__ cur, const uint32_t *__restrict__ visited,
+                                                 const BfsPeers &next, int32_t *levels, long long *acc, uint32_t level,
+                                                 int64_t n_local, int64_t row_offset) {
+  __shared__ uint8_t s_rows[8][BFS_PULL_GROUP_WORDS * 32];
+  __shared__ uint32_t s_bits[8][BFS_PULL_GROUP_WORDS];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t word_offset = row_offset >> 5;
+  const int64_t n_words = (n_local + 31) >> 5;
+  const int64_t n_groups = (n_words + BFS_PULL_GROUP_WORDS - 1) / BFS_PULL_GROUP_WORDS;
+  unsigned long long found_n = 0, push_deg = 0;
+  for (int64_t g = warp; g < n_groups; g += n_warps) {
+    const int64_t w0 = g * BFS_PULL_GROUP_WORDS;
+    const bool word_lane = lane < BFS_PULL_GROUP_WORDS && w0 + lane < n_words;
+    const uint32_t seen_mine = word_lane ? visited[word_offset + w0 + lane] : 0xffffffffu;
+    if (lane < BFS_PULL_GROUP_WORDS) s_bits[wib][lane] = 0u;
+    uint32_t n_act = 0;
+#pragma unroll
+    for (int j = 0; j < BFS_PULL_GROUP_WORDS; ++j) {
+      const uint32_t seen = __shfl_sync(0xffffffffu, seen_mine, j);
+      const bool active = (w0 + j) * 32 + lane < n_local && !((seen >> lane) & 1u);
+      const uint32_t m = __ballot_sync(0xffffffffu, active);
+      if (active) s_rows[wib][n_act + __popc(m & ((1u << lane) - 1u))] = (uint8_t)(j * 32 + lane);
+      n_act += __popc(m);
+    }
+    __syncwarp();
+    for (uint32_t i0 = 0; i0 < n_act; i0 += 32) {
+      const uint32_t i = i0 + lane;
+      bool found = false, big = false;
+      int s = 0, e = 0;
+      uint32_t rt = 0;
+      int64_t r = 0;
+      if (i < n_act) {
+        rt = s_rows[wib][i];
+        r = w0 * 32 + rt;
+        s = row_ptr[r];
+        e = row_ptr[r + 1];
+        big = (e - s) >= BFS_BLOCK_BIG_ROW;
+        if (!big) found = bfs_row_hits<HAS_VAL>(col, val, cur, s, e);
+      }
+      // hub rows: the whole warp scans, 32 entries per step, until one lane sees a frontier neighbour
+      uint32_t bigs = __ballot_sync(0xffffffffu, big);
+      while (bigs) {
+        const int src = __ffs(bigs) - 1;
+        bigs &= bigs - 1;
+        const int bs = __shfl_sync(0xffffffffu, s, src), be = __shfl_sync(0xffffffffu, e, src);
+        bool hit = false;
+        for (int k0 = bs; k0 < be && !hit; k0 += 32) {
+          const int k = k0 + lane;
+          bool h = false;
+          if (k < be && !(HAS_VAL && val[k] == 0)) {
+            const int32_t c = col[k];
+            h = ((cur[c >> 5] >> (c & 31)) & 1u) != 0u;
+          }
+          hit = __any_sync(0xffffffffu, h);
+        }
+        if (lane == src) found = hit;
+      }
+      if (found) {
+        levels[r] = (int32_t)level + 1;
+        atomicOr(&s_bits[wib][rt >> 5], 1u << (rt & 31));
+        ++found_n;
+        push_deg += (unsigned long long)(deg ? deg[row_offset + r] : 1);
+      }
+    }
+    __syncwarp();
+    if (word_lane) {
+      const uint32_t bits = s_bits[wib][lane];
+      for (int i = 0; i < next.n; ++i) next.bm[i][word_offset + w0 + lane] = bits;
+    }
+    __syncwarp();
+  }
+  for (int off = 16; off > 0; off >>= 1) {
+    found_n += __shfl_xor_sync(0xffffffffu, found_n, off);
+    push_deg += __shfl_xor_sync(0xffffffffu, push_deg, off);
+  }
+  if (lane == 0 && found_n) {
+    atomicAdd(reinterpret_cast<unsigned long long *>(&acc[0]), found_n);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&acc[1]), push_deg);
+  }
+}
+
+// One launch per level.  by_rows selects the thread-per-row mapping (SHB_BFS_PULL=rows, kept for comparison).
+template <bool HAS_VAL>
+__global__ void __launch_bounds__(256, 8)
+    bfs_block_pull_kernel(const BfsBlockState *st, const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                          const int32_t *__restrict__ val, const int32_t *__restrict__ deg, const uint32_t *__restrict__ cur,
+                          const uint32_t *__restrict__ visited, const __grid_constant__ BfsPeers next, int32_t *levels,
+                          long long *acc, uint32_t level, int64_t n_local, int64_t row_offset, int by_rows) {
+  if (st->done || st->mode != 1) return;
+  if (by_rows) bfs_pull_rows<HAS_VAL>(row_ptr, col, val, deg, cur, visited, next, levels, acc, level, n_local, row_offset);
+  else bfs_pull_compact<HAS_VAL>(row_ptr, col, val, deg, cur, visited, next, levels, acc, level, n_local, row_offset);
 }
 
 // The exchange of a counter slot without a collective library: lane i adds this rank's staged (vertices,
@@ -567,15 +674,17 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
         bfs_block_push_big_kernel<false><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, dg,
                                                                          (const uint32_t *)visited->ptr, peers, acc);
     }
-    const unsigned grid = grid_for(n_local, 256, 148 * 32);
+    static const int by_rows = [] { const char *e = getenv("SHB_BFS_PULL"); return e && !strcmp(e, "rows") ? 1 : 0; }();
+    static const int grid_mult = [] { const char *e = getenv("SHB_BFS_PULL_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 32; }();
+    const unsigned grid = grid_for(n_local, 256, 148 * grid_mult);
     if (A->val)
       bfs_block_pull_kernel<true><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, (const int32_t *)A->val, dg, cur,
                                                                (const uint32_t *)visited->ptr, peers, (int32_t *)levels->ptr,
-                                                               acc, level, n_local, row_offset);
+                                                               acc, level, n_local, row_offset, by_rows);
     else
       bfs_block_pull_kernel<false><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, nullptr, dg, cur,
                                                                 (const uint32_t *)visited->ptr, peers, (int32_t *)levels->ptr,
-                                                                acc, level, n_local, row_offset);
+                                                                acc, level, n_local, row_offset, by_rows);
   }
   if (comm.n)
     bfs_block_publish_kernel<<<1, 32, 0, c->stream>>>(st, comm, cnt + BFS_STAGE_WORD, BFS_SLOT(level + 1), BFS_FLAG_WORD,

@@ -231,3 +231,36 @@ def test_bfs_level_cap_reports_not_converged_with_the_levels_found(ctx, orc, wit
     lv2, st2 = ctx.bfs(A2, 0, AT=A2 if with_transpose else None)
     assert nlev2 > 600 and st2.iterations == nlev2 and st2.edges_traversed == edges2
     assert np.array_equal(lv2.download(np.int32, len(rp2) - 1), want2)
+
+
+def test_bfs_pull_mappings_agree(ctx, orc):
+    """The compacted pull (default) and the thread-per-row pull (SHB_BFS_PULL=rows, read once per process) give the
+    same levels as the queue BFS on an RMAT graph with hubs, empty rows and a ragged last bitmap word; the operator is
+    traversed twice so that the cached empty-row bits are used as well as built."""
+    import hashlib
+    import os
+    import subprocess
+    import sys
+
+    root_dir = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    A = ctx.synth_rmat(14, 16, seed=orc.SEED_C3, symmetrise=True)
+    rp, col, _ = A.download()
+    root = int(np.argmax(np.diff(rp) > 0))
+    want, nlev, _ = orc.bfs_levels(rp, col, None, root)
+    for AT in (A, None, A):
+        levels, st = ctx.bfs(A, root, AT=AT)
+        assert np.array_equal(levels.download(np.int32, len(rp) - 1), want) and st.iterations == nlev
+    script = (
+        "import sys, hashlib, numpy as np; sys.path.insert(0, %r); import sparseharness_b200 as shb\n"
+        "ctx = shb.Context(0); A = ctx.synth_rmat(14, 16, seed=%d, symmetrise=True)\n"
+        "for AT in (A, None):\n"
+        "    lv, st = ctx.bfs(A, %d, AT=AT)\n"
+        "    print(hashlib.sha256(lv.download(np.int32, 1 << 14).tobytes()).hexdigest(), st.iterations)\n"
+    ) % (root_dir, orc.SEED_C3, root)
+    r = subprocess.run([sys.executable, "-c", script], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, SHB_BFS_PULL="rows"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l.split() for l in r.stdout.strip().splitlines() if len(l.split()) == 2]
+    assert len(lines) == 2
+    for digest, iters in lines:
+        assert digest == hashlib.sha256(want.astype(np.int32).tobytes()).hexdigest() and int(iters) == nlev

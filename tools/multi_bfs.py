@@ -62,7 +62,7 @@ def run(scale, edgefactor, check, seed=0x5EED0024, check_every=8, repeat=3, ctx=
            "n_gpus": world, "exchange": exchange if world > 1 else "none", "schedule": "row-partitioned, direction-optimising; frontier bitmap words / bits stored into every peer by the push and pull kernels",
            "levels": st["levels"], "reached": st["reached"], "ms": ms,
            "timed": "all levels, first launch to the host's last poll; the set-up pass (levels = -1, bitmaps zeroed, isolated "
-                    "vertices marked) is outside -- shb_bfs on one GPU times it too (about 0.1 ms at scale 24)", "gteps": undirected / (ms * 1e6),
+                    "vertices marked from the bits cached on the operator) is outside -- shb_bfs on one GPU times it too", "gteps": undirected / (ms * 1e6),
            "teps_edges": undirected, "local_rows": hi - lo, "local_nnz": Al.info.nnz,
            "frontier_bytes_per_gpu_per_level": (n + 7) // 8}
     if trace:  # one more traversal, synchronised after every level: per-level device time and direction

@@ -308,7 +308,7 @@ __device__ __forceinline__ void bfs_pull_rows(const int32_t *__restrict__ row_pt
 // compacts the unvisited ones into its own shared-memory list with the 8 visited words, and its lanes then walk that
 // list densely (hub rows by the whole warp, as above).  The group's 8 next-frontier words are assembled in shared
 // memory and stored once into every rank's bitmap.  No CTA barrier: warps stay independent.  RMAT 24 on one GPU:
-// 0.90 -> 0.77 ms for the traversal.
+// 0.90 -> 0.77 ms for the traversal; groups of 16 or 32 words measured 2-3 % slower than 8.
 #define BFS_PULL_GROUP_WORDS 8
 template <bool HAS_VAL>
 __device__ __forceinline__ void bfs_pull_compact(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,

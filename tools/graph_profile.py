@@ -23,7 +23,7 @@ def main():
     for _ in range(reps):
         lv, st = ctx.bfs(A, root, AT=A)
         lv.free()
-        print(json.dumps({"bfs_scale": scale, "ms": st.total_ns / 1e6, "levels": st.iterations,
+        print(json.dumps({"bfs_scale": scale, "ms": st.total_ns / 1e6, "levels": st.iterations, "reached": st.reached,
                           "gteps": st.edges_traversed / 2 / st.total_ns}), flush=True)
     A.free()
     G = ctx.synth_grid2d(side, side)

@@ -51,7 +51,7 @@ __device__ __forceinline__ bool bfs_row_hits(const int32_t *__restrict__ col, co
 //   push | pull         push: owned frontier vertices mark unvisited out-neighbours with atomicOr in the
 //                       local next bitmap and, when the bit was new here, in every peer's next bitmap;
 //                       pull: every unvisited owned row looks for an in-neighbour in the frontier (early
-//                       exit; hub rows by the whole warp) and the warp's ballot word is stored into every
+//                       exit; hub rows by the whole warp) and the warp's next-frontier words are stored into every
 //                       rank's next bitmap.  Peer bitmaps are CUDA-IPC mappings: the exchange rides on the
 //                       kernel's own stores over NVLink, no separate collective moves the frontier;
 //   clear               the consumed frontier bitmap is zeroed for reuse two levels on.

@@ -211,3 +211,23 @@ def test_threaded_parser_fast_tokens_match_the_c_library_on_tricky_spellings(tmp
     for k in ("rp", "col"):
         assert np.array_equal(a[k], b[k]), k
     assert np.array_equal(a["val"].view(np.int32), b["val"].view(np.int32))
+
+
+@pytest.mark.parametrize("name", ["1138_bus", "ca-AstroPh"])
+def test_threaded_csr_encode_equals_sequential_on_padded_heights(tmp_path, mtx_dir, monkeypatch, name):
+    """The CSR encoder's row-range threads (host/inc/sparse_matrix.h csr_encode) give the sequential counting sort's
+    arrays on a symmetric fixture, with and without the padded rows of a chunked kernel, for thread counts that do
+    and do not divide the height (and more threads than a small height leaves rows for)."""
+    mtx = mtx_dir[name]
+    for kernel in ("glb-sdp-rsa", "awrg-alcl-fdp-chunk-rsa-8", "swrg-slcl-sdp-chunk-128"):
+        k = os.path.join(KERNELS, "spmv", kernel + ".json")
+        monkeypatch.setenv("SHB_MM_THREADS", "1")
+        monkeypatch.delenv("SHB_MM_PARALLEL_MIN_BYTES", raising=False)
+        a = _parse(tmp_path, mtx, k)
+        for threads in ("2", "7", "16"):
+            monkeypatch.setenv("SHB_MM_THREADS", threads)
+            monkeypatch.setenv("SHB_MM_PARALLEL_MIN_BYTES", "1")
+            b = _parse(tmp_path, mtx, k)
+            for key in ("rp", "col", "gold"):
+                assert np.array_equal(a[key], b[key]), (kernel, threads, key)
+            assert np.array_equal(a["val"].view(np.int32), b["val"].view(np.int32)), (kernel, threads)

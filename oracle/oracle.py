@@ -284,6 +284,32 @@ def ref_time_gold(mtx, reps=5):
     return {"best_ns": float(t[2]), "mean_ns": float(t[4]), "reps": int(t[6])}
 
 
+REF_KERNELS = os.path.join(HERE, "_ref", "ref_kernels")
+REF_KERNEL_ALGS = ("spmv", "sssp", "bfs", "pr", "scc")
+
+
+def ref_kernel_run(mtx, alg, variant, cap=40, delta=1e-4, gsz=1, xmode=0):
+    """The reference's OWN kernel text (example/<alg>/kernel{5,6}.json:3) run on the CPU over the reference's OWN
+    cl_encode blobs with the app's initial state: one launch (`step1`) and the executeRun recurrence capped at
+    `cap` launches (oracle/ref_kernels.cpp).  Returns dict(h, w, iters, terminated, step1, final)."""
+    import tempfile
+    dt = np.float32 if alg in ("spmv", "sssp", "pr") else np.int32
+    with tempfile.NamedTemporaryFile("r", suffix=".txt") as f:
+        subprocess.run([REF_KERNELS, str(mtx), alg, str(variant), str(cap), repr(float(delta)), str(gsz), str(xmode),
+                        f.name], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        lines = f.read().split()
+    assert lines[0] == "H" and lines[2] == "W" and lines[4] == "ITERS" and lines[6] == "TERMINATED"
+    out = {"h": int(lines[1]), "w": int(lines[3]), "iters": int(lines[5]), "terminated": int(lines[7])}
+    i = 8
+    for tag in ("STEP1", "FINAL"):
+        assert lines[i] == tag
+        n = int(lines[i + 1])
+        words = np.array([int(t, 16) for t in lines[i + 2: i + 2 + n]], dtype=np.uint32)
+        out[tag.lower()] = words.view(dt)
+        i += 2 + n
+    return out
+
+
 def xmode_vector(n, xmode):
     i = np.arange(n, dtype=np.int64)
     return np.ones(n, np.float32) if xmode == 0 else (((7 * i + 3) % 11) - 5).astype(np.float32)

@@ -97,3 +97,68 @@ def test_sample_file_for_the_reference_arm_round_trips(orc, tmp_path):
         assert sorted(zip(rcol[a:b], rval[a:b])) == sorted(zip(col[a:b], np.trunc(val[a:b])))
     t = orc.reference_gold_time(path, 1, 2)
     assert t is not None and t[0] > 0
+
+
+# ---- the reference's OWN device kernel text, executed on the CPU (oracle/ref_kernels.cpp) -------------------
+# k5 = example/<alg>/kernel5.json:3 (glb-sdp: padded ELL, products parked in the temp buffer at W-1-i and reduced
+# ascending => REVERSED order), k6 = kernel6.json:3 (glb-sdp-rsa: ragged, forward order); blobs from the
+# reference's own cl_encode; initial state, recurrence and termination test of the apps.  Bit-exact, floats too.
+def app_state(orc, mtx, alg, n=None):
+    """(semiring, elem, normalise, x0, y0, alpha, beta) of app/<alg>.cpp main(); cites in oracle/ref_kernels.cpp."""
+    if alg in ("spmv", "spmvx1"):
+        h = orc.mm_load_csr(mtx, "float")[0]
+        return orc.PLUS_TIMES, "float", "none", orc.xmode_vector(h, 0 if alg == "spmv" else 1), np.zeros(h, np.float32), 1.0, 0.0
+    if alg == "sssp":
+        h = orc.mm_load_csr(mtx, "float")[0]
+        x0 = np.full(h, orc.FLT_MAX, np.float32); x0[0] = 0
+        return orc.MIN_PLUS, "float", "none", x0, x0.copy(), 0.0, 0.0
+    if alg == "bfs":
+        h = orc.mm_load_csr(mtx, "int")[0]
+        x0 = np.zeros(h, np.int32); x0[0] = 1
+        return orc.OR_AND, "int", "none", x0, x0.copy(), 1, 0
+    if alg == "pr":
+        h = orc.mm_load_csr(mtx, "float")[0]
+        x0 = np.full(h, np.float32(1.0) / np.float32(h), np.float32)
+        beta = (np.float32(1.0) - np.float32(0.85)) / np.float32(h)
+        return orc.PLUS_TIMES, "float", "pr", x0, np.ones(h, np.float32), 1.0, float(beta)
+    if alg == "scc":
+        h = orc.mm_load_csr(mtx, "int")[0]
+        return (orc.MAX_MIN, "int", "scc", np.arange(h, dtype=np.int32), np.full(h, orc.INT_MIN, np.int32),
+                int(orc.INT_MAX), int(orc.INT_MIN))
+    raise ValueError(alg)
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+KERNEL_ALGS = ["spmv", "spmvx1", "sssp", "bfs", "pr", "scc"]
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("alg", KERNEL_ALGS)
+@pytest.mark.parametrize("variant", [5, 6])
+def test_restatement_matches_reference_kernel_text_one_launch(orc, mtx_dir, name, alg, variant):
+    g = _gold(name)
+    sr, elem, norm, x0, y0, alpha, beta = app_state(orc, mtx_dir[name], alg)
+    h, w, rp, col, val = orc.mm_load_csr(mtx_dir[name], elem, normalise=norm)
+    want = g[f"k{variant}_{alg}_step1"]
+    assert len(want) == h
+    for threads in (1, 3):
+        got = orc.spmv(sr, rp, col, val, x0, y0, alpha, beta, order=1 if variant == 5 else 0, threads=threads)
+        assert np.array_equal(bits(got), bits(want)), (name, alg, variant)
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("alg", ["sssp", "bfs", "pr", "scc"])
+@pytest.mark.parametrize("variant", [5, 6])
+def test_restatement_matches_reference_recurrence(orc, mtx_dir, name, alg, variant):
+    g = _gold(name)
+    sr, elem, norm, x0, y0, alpha, beta = app_state(orc, mtx_dir[name], alg)
+    h, w, rp, col, val = orc.mm_load_csr(mtx_dir[name], elem, normalise=norm)
+    want = g[f"k{variant}_{alg}_final"]
+    iters, terminated, cap = (int(v) for v in g[f"k{variant}_{alg}_iters"])
+    got, n = orc.iterate(sr, rp, col, val, x0, y0, alpha, beta, delta=1e-4, max_iters=cap,
+                         order=1 if variant == 5 else 0)
+    assert n == iters and (terminated == 1 or iters == cap)
+    assert np.array_equal(bits(got), bits(want)), (name, alg, variant)

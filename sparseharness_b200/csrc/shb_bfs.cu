@@ -151,7 +151,7 @@ __device__ __forceinline__ void bfs_push_visit(int32_t v, const uint32_t *__rest
   const uint32_t old = atomicOr(&mine[v >> 5], bit);
   if (!(old & bit)) {  // new on this rank: tell every peer once
     for (int i = 0; i < next.n; ++i)
-      if (i != next.self) atomicOr(&next.bm[i][v >> 5], bit);
+      if (i != next.self) atomicOr_system(&next.bm[i][v >> 5], bit);  // peer mapping: system scope
     ++found;
     push_deg += (unsigned long long)(deg ? deg[v] : 1);
   }

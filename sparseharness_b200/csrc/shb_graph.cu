@@ -225,6 +225,10 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_nearfar_kernel(const __g
           if (sh.fcount >= SSSP_FSTAGE / 2) sssp_flush_far(sh, far_cur, far_cur_size);
           cur = nxt;
         }
+        // every thread must have read the zero count that ended the loop before thread 0 refills
+        // lcount[0] / lst[0] for the next chunk (cur can be 0 here): without this a slow warp could see
+        // the new count, skip the break and run one barrier out of phase with its CTA
+        __syncthreads();
       }
       __syncthreads();
       sssp_flush_far(sh, far_cur, far_cur_size);
@@ -243,7 +247,11 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_nearfar_kernel(const __g
         break;
       }
       const uint32_t t_old = t_hi;
-      t_hi = __float_as_uint(__fadd_rn(__uint_as_float(*(volatile uint32_t *)&st->far_min[fgen % 3]), delta));
+      {  // far_min + delta, but never == far_min (delta below half an ulp of far_min would re-split the
+         // same pile for ever): non-negative float bits order like integers, so +1 is the next float
+        const uint32_t fmb = *(volatile uint32_t *)&st->far_min[fgen % 3];
+        t_hi = max(__float_as_uint(__fadd_rn(__uint_as_float(fmb), delta)), fmb < 0x7f7fffffu ? fmb + 1u : fmb);
+      }
       ++buckets;
       const int32_t *far_cur = a.far_q[fgen & 1];
       int32_t *far_next = a.far_q[(fgen + 1) & 1];
@@ -629,7 +637,7 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
   if (a.gmin) {
     const long long g = *(volatile const long long *)a.gmin;
     const uint32_t gb = g < 0x7f7fffffll ? (uint32_t)g : 0x7f7fffffu;
-    cap = __float_as_uint(__fadd_rn(__uint_as_float(gb), a.window_buckets * delta));
+    cap = max(__float_as_uint(__fadd_rn(__uint_as_float(gb), a.window_buckets * delta)), gb < 0x7f7fffffu ? gb + 1u : gb);
     if (blockIdx.x == 0 && threadIdx.x == 0) st->cap_bits = cap;  // read by the next round's seed pass
   }
   bool finished = false;
@@ -720,6 +728,10 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
           if (sh.fcount >= SSSP_FSTAGE / 2) sssp_flush_far(sh, far_cur, far_cur_size);
           cur = nxt;
         }
+        // every thread must have read the zero count that ended the loop before thread 0 refills
+        // lcount[0] / lst[0] for the next chunk (cur can be 0 here): without this a slow warp could see
+        // the new count, skip the break and run one barrier out of phase with its CTA
+        __syncthreads();
       }
       __syncthreads();
       sssp_flush_far(sh, far_cur, far_cur_size);
@@ -738,7 +750,7 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
         break;
       }
       const uint32_t t_old = t_hi;
-      t_hi = min(__float_as_uint(__fadd_rn(__uint_as_float(fm), delta)), cap);
+      t_hi = min(max(__float_as_uint(__fadd_rn(__uint_as_float(fm), delta)), fm < 0x7f7fffffu ? fm + 1u : fm), cap);
       ++buckets;
       const int32_t *far_cur = a.far_q[fgen & 1];
       int32_t *far_next = a.far_q[(fgen + 1) & 1];

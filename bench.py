@@ -179,12 +179,17 @@ def run_reference(args):
 
 
 def graph_extras(ctx, shb, orc):
-    """GTEPS of the graph drivers on one GPU (configs 3-5 families), reported next to the headline line."""
+    """GTEPS of the graph drivers on one GPU (configs 3-5 families), reported next to the headline line.  Every
+    number is gated by a sampled parity check (tools/parity_checks.py); a mismatch aborts the run."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import parity_checks as pc
     out = {}
 
     def guarded(name, fn):
         try:
             out[name] = fn()
+        except SystemExit:
+            raise
         except Exception as e:  # keep the headline line alive
             out[name] = {"error": repr(e)[:300]}
 
@@ -196,13 +201,19 @@ def graph_extras(ctx, shb, orc):
         best = None
         for _ in range(3):
             levels, st = ctx.bfs(A, root, AT=A)
-            levels.free()
             if best is None or st.total_ns < best.total_ns:
                 best = st
+            lv = levels.download(np.int32, info.n_rows)
+            levels.free()
+        begins, cnt = pc.sample_blocks(info.n_rows, 1 << 14)
+        ok = all(pc.bfs_rows_ok(lv, *A.download(b, cnt)[:2], b, root) for b in begins)
+        if not ok:
+            raise SystemExit("bench: BFS levels violate the BFS local conditions -- refusing to report a number")
         undirected = best.edges_traversed / 2
         r = {"graph": "RMAT scale 24 edgefactor 16 symmetrised+deduplicated", "n": info.n_rows, "nnz": info.nnz,
              "levels": best.iterations, "reached": best.reached, "ms": best.total_ns / 1e6,
-             "gteps": undirected / best.total_ns, "teps_edges": undirected}
+             "gteps": undirected / best.total_ns, "teps_edges": undirected, "parity_checked": True,
+             "parity": f"BFS local conditions (parent one level below, none further, unreached closed) on {len(begins) * cnt} sampled rows"}
         A.free()
         return r
 
@@ -210,9 +221,16 @@ def graph_extras(ctx, shb, orc):
         G = ctx.synth_grid2d(8192, 8192, seed=0x5EED0004)
         info = G.info
         dist, st = ctx.sssp(G, 0, AT=G)
+        d = dist.download(np.float32, info.n_rows)
+        begins, cnt = pc.sample_blocks(info.n_rows, 1 << 14)
+        ok = bool(st.converged) and all(pc.sssp_rows_ok(d, *G.download(b, cnt), b, 0) for b in begins)
+        if not ok:
+            raise SystemExit("bench: SSSP distances are not the Bellman fixed point -- refusing to report a number")
         r = {"graph": "2-D grid 8192x8192 4-neighbour, integer weights 1..255", "n": info.n_rows, "nnz": info.nnz,
              "rounds": st.iterations, "converged": bool(st.converged), "ms": st.total_ns / 1e6,
-             "gteps": st.edges_traversed / st.total_ns}
+             "gteps": st.edges_traversed / st.total_ns, "parity_checked": True, "dist_checksum64": pc.checksum64(d),
+             "parity": f"Bellman fixed-point condition in float arithmetic on {len(begins) * cnt} sampled rows"}
+        del d
         # one dense min-plus sweep over the same operator (the reference's per-iteration launch, app/sssp.cpp:112-153):
         # gathers are local here, so this is the HBM-bound face of the same SpMV kernels (SURVEY.md 8d, C4 bytes/sweep)
         out = ctx.empty(info.n_rows * 4)
@@ -231,9 +249,15 @@ def graph_extras(ctx, shb, orc):
     def pagerank():
         A = ctx.synth_rmat(24, 16, seed=0x5EED0026, symmetrise=False, value_mode=1)
         info = A.info
-        res, st = ctx.pagerank(A, delta=0.0, max_iters=20, check_every=20)  # fixed 20 sweeps
-        res.free()
-        r = {"graph": "RMAT scale 24 edgefactor 16 directed (config 5 family; scale 26 needs the multi-GPU partition)",
+        res, prev, st = ctx.pagerank(A, delta=0.0, max_iters=20, check_every=20, both=True)  # fixed 20 sweeps (8d C5)
+        xn, xp = res.download(np.float32, info.n_rows), prev.download(np.float32, info.n_rows)
+        res.free(); prev.free()
+        beta = float((np.float32(1.0) - np.float32(0.85)) / np.float32(info.n_rows))
+        begins, cnt = pc.sample_blocks(info.n_rows, 4096)
+        err = max(pc.pagerank_rows_err(orc, xp, xn[b:b + cnt], *A.download(b, cnt), beta) for b in begins)
+        if not err <= 1e-5:
+            raise SystemExit(f"bench: PageRank sweep differs from the oracle (rel {err:.3g}) -- refusing to report a number")
+        r = {"parity_checked": True, "parity_rel_err": err,"graph": "RMAT scale 24 edgefactor 16 directed (config 5 family; scale 26 needs the multi-GPU partition)",
              "n": info.n_rows, "nnz": info.nnz, "sweeps": st.iterations, "ms": st.total_ns / 1e6,
              "gteps": info.nnz * st.iterations / st.total_ns,
              "effective_gbs": info.algorithmic_bytes_spmv * st.iterations / st.total_ns}
@@ -253,23 +277,35 @@ def partitioned_extras(ctx, rank, world):
     near-far with boundary candidates as peer red.min).  Every rank must call this."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     out = {}
+
+    def gate(name, r):
+        out[name] = r
+        if not r.get("parity_ok", False):  # identical on every rank (all-reduced): all ranks leave together
+            raise SystemExit(f"bench: {name} failed its parity gate at {world} GPUs -- refusing to report a number")
+
     try:
         import multi_pagerank
-        r, _, _ = multi_pagerank.run(26, 16, 20, "fused", 0.0, False, repeat=2, ctx=ctx)
-        out["pagerank_config5"] = r
+        r, _, _ = multi_pagerank.run(26, 16, 20, "fused", 0.0, "sampled", repeat=2, ctx=ctx)
+        gate("pagerank_config5", r)
+    except SystemExit:
+        raise
     except Exception as e:
         out["pagerank_config5"] = {"error": repr(e)[:300]}
     if world > 1:
         try:
             import multi_bfs
-            r, _, _ = multi_bfs.run(24, 16, False, repeat=3, ctx=ctx)
-            out["bfs_partitioned"] = r
+            r, _, _ = multi_bfs.run(24, 16, "sampled", repeat=3, ctx=ctx)
+            gate("bfs_partitioned", r)
+        except SystemExit:
+            raise
         except Exception as e:
             out["bfs_partitioned"] = {"error": repr(e)[:300]}
         try:
             import multi_sssp
-            r, _, _ = multi_sssp.run(8192, 8192, False, repeat=2, ctx=ctx)
-            out["sssp_partitioned"] = r
+            r, _, _ = multi_sssp.run(8192, 8192, "sampled", repeat=2, ctx=ctx)
+            gate("sssp_partitioned", r)
+        except SystemExit:
+            raise
         except Exception as e:
             out["sssp_partitioned"] = {"error": repr(e)[:300]}
     return out
@@ -443,6 +479,14 @@ def run_ours(args):
         if rank == 0:
             line.setdefault("graph_gteps", {}).update(part)
     if rank == 0:
+        gg = line.get("graph_gteps", {})
+        pick = lambda *ks: next((gg[k].get("gteps") for k in ks if isinstance(gg.get(k), dict) and "gteps" in gg[k]), None)
+        # the numbers that say something about the multi-GPU design (the headline SpMV shards with no collective)
+        line["scaling_curve"] = {"n_gpus": n_gpus, "pagerank_config5_gteps": pick("pagerank_config5"),
+                                 "bfs_config3_gteps": pick("bfs_partitioned", "bfs"),
+                                 "sssp_config4_gteps": pick("sssp_partitioned", "sssp"),
+                                 "parity_checked": all(bool(v.get("parity_checked")) for v in gg.values()
+                                                       if isinstance(v, dict) and "gteps" in v)}
         ds = line.get("graph_gteps", {}).get("sssp", {}).get("dense_sweep")
         local_traffic = None
         try:

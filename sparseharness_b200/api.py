@@ -365,7 +365,9 @@ class Context:
         _ck(lib.shb_sssp(self.h, A.h, AT.h if AT else None, source, dist.h, max_rounds, C.byref(st)))
         return dist, st
 
-    def pagerank(self, A: Csr, damping=0.85, delta=1e-4, max_iters=1000, check_every=8, cfg: LaunchCfg | None = None):
+    def pagerank(self, A: Csr, damping=0.85, delta=1e-4, max_iters=1000, check_every=8, cfg: LaunchCfg | None = None,
+                 both=False):
+        """Returns (x_k, stats); with both=True (x_k, x_{k-1}, stats): the two ping-pong buffers."""
         n = A.info.n_rows
         x, work = self.empty(n * 4), self.empty(n * 4)
         x_init = np.float32(1.0) / np.float32(n)
@@ -376,6 +378,9 @@ class Context:
                              delta, max_iters, check_every, C.byref(in_work), C.byref(st))
         if s not in (0, 7):
             raise ShbError(s)
+        if both:
+            return (work, x, st) if in_work.value else (x, work, st)
+        (x if in_work.value else work).free()
         return (work if in_work.value else x), st
 
     def close(self):

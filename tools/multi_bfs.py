@@ -46,6 +46,23 @@ def run(scale, edgefactor, check, seed=0x5EED0024, check_every=8, repeat=3, ctx=
     bounds = multi.word_aligned_bounds(A.balance_rows(world))
     lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     deg = A.row_lengths()  # symmetric graph: push degree == pull degree, and the row block serves both directions
+    single = None
+    if check == "sampled":
+        # the single-device driver on the whole graph (every rank has it at this point): its levels are tested on
+        # sampled row blocks against the BFS local conditions (tools/parity_checks.py), then every rank compares its
+        # slice of the partitioned result with it bit for bit.  tests/test_gpu_fullsize.py compares the same
+        # single-device levels with the oracle's queue BFS on every vertex.
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import parity_checks as pc
+        lv_buf, st1 = ctx.bfs(A, root, AT=A)
+        lv_full = lv_buf.download(np.int32, n)
+        lv_buf.free()
+        begins, cnt = pc.sample_blocks(n, 1 << 14, extra=[int(b) - (1 << 13) for b in bounds[1:-1]] + [lo, hi - (1 << 14)])
+        ok = True
+        for b in begins:
+            rp_s, col_s, _ = A.download(b, cnt)
+            ok = ok and pc.bfs_rows_ok(lv_full, rp_s, col_s, b, root)
+        single = (lv_full, st1, ok, len(begins) * cnt)
     if world > 1:
         Al = A.slice_rows(lo, hi - lo)
         A.free()
@@ -79,7 +96,19 @@ def run(scale, edgefactor, check, seed=0x5EED0024, check_every=8, repeat=3, ctx=
             per.append({"level": lv, "us": round((time.perf_counter() - t0) * 1e6, 1), "mode": "pull" if mode else "push",
                         "found": int(be.read_counts(lv, lv + 1)[0])})
         out["trace"] = per
-    if check:
+    if check == "sampled":
+        lv_full, st1, ok, nrows = single
+        got = be.result()
+        ok = ok and bool(np.array_equal(got, lv_full[lo:hi])) and st["levels"] == st1.iterations
+        ok = ok and st["reached"] == st1.reached and st["edges_traversed"] == st1.edges_traversed
+        flag = torch.tensor([int(ok)], dtype=torch.int32, device="cuda")
+        if world > 1:
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        out.update(parity_checked=True, parity_ok=bool(flag.item()),
+                   parity="levels of the single-device driver satisfy the BFS local conditions on %d sampled rows per rank; "
+                          "every rank's slice of the partitioned levels, the level count, reached and traversed-edge "
+                          "totals equal the single-device run" % nrows)
+    elif check:
         from oracle import oracle as orc  # checker only
         rp, col = orc.gen_rmat(scale, edgefactor, seed=seed, symmetrise=True)
         want, nlev, edges = orc.bfs_levels(rp, col, None, root)

@@ -304,6 +304,50 @@ int shb_sssp_block_solve(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, in
 int shb_sssp_block_finish(shb_ctx *ctx, const shb_csr *A_rows, int64_t row_offset, const shb_buf *dist,
                           const shb_buf *work, shb_buf *stats_out);
 
+/* ---- multi-GPU in ONE process: a group of devices driven by one host thread ----------
+ * Generalises the reference's single queue on a single device (inc/harness.h:78-81): shb_group owns one context
+ * + stream per device with peer access enabled between all of them; shb_gpart is an operator row-partitioned over
+ * the group (contiguous blocks balanced by non-zeros, bounds multiples of 32, GLOBAL column ids, block i resident
+ * on device i; `AT` blocks = the same vertices' out-edges, needed by BFS push levels and by SSSP -- for a
+ * symmetric operator the row blocks serve as both).  The drivers below are the round / level loops of the
+ * reference's iterative apps (app/{pr,bfs,sssp}.cpp executeRun) on that partition: the per-block kernels are the
+ * shb_spmv_scatter / shb_bfs_block_* / shb_sssp_block_* primitives above; every iteration ends with one publish
+ * kernel per device that all-reduces a few words over NVLink with system-scope atomics and is the inter-device
+ * barrier.  The host polls device 0's copy once per `check_every` iterations.  No collective library, no
+ * PyTorch, no second process.  Times are device times (events), the maximum over the devices. */
+typedef struct shb_group shb_group;
+typedef struct shb_gpart shb_gpart;
+int shb_group_create(int n_dev /* 1..8 */, const int *devices /* NULL: 0..n_dev-1 */, shb_group **grp);
+int shb_group_destroy(shb_group *grp);
+int shb_group_size(const shb_group *grp, int *n_dev);
+int shb_group_ctx(shb_group *grp, int i, shb_ctx **ctx); /* to build blocks on device i (synthetic generators, slices) */
+/* a HOST CSR, split and uploaded; symmetric != 0: the operator equals its transpose (no AT copy is made) */
+int shb_group_partition_host(shb_group *grp, int64_t n_rows, int64_t n_cols, const int64_t *row_ptr,
+                             const int32_t *col_idx, const void *vals /* NULL = pattern */, int symmetric,
+                             shb_gpart **part);
+/* blocks the caller built on the group's devices (blocks[i] on device i, rows [bounds[i], bounds[i+1]));
+ * at_blocks == NULL: symmetric.  The partition takes ownership of the operators. */
+int shb_group_adopt(shb_group *grp, shb_csr *const *blocks, shb_csr *const *at_blocks, const int64_t *bounds,
+                    int64_t n_cols, shb_gpart **part);
+int shb_gpart_destroy(shb_gpart *part);
+int shb_gpart_info(const shb_gpart *part, int64_t *n_rows, int64_t *n_cols, int64_t *nnz, int64_t *bounds /* n_dev+1 */);
+int shb_gpart_block(const shb_gpart *part, int i, shb_csr **A, shb_csr **AT);
+/* x_{k+1} = KERNEL(x_k): shb_iterate on the partition (same arguments; x0_host == NULL: x0 filled with the 32-bit
+ * pattern x0_fill_bits; y_mode 0: y0 every launch, 1: y0 for the first launch then y = x, 2: y is the semiring one).
+ * result_host / prev_host (optional, n_rows elements): x_k and x_{k-1}.  SHB_ERR_NOT_CONVERGED at the cap. */
+int shb_group_iterate(shb_group *grp, const shb_gpart *part, int semiring, const shb_launch_cfg *cfg, const void *x0_host,
+                      uint32_t x0_fill_bits, const void *y0_host, const void *alpha, const void *beta, double delta,
+                      int term_mode, int y_mode, uint32_t max_iters, uint32_t check_every, void *result_host,
+                      void *prev_host, uint32_t *n_iters, uint64_t *total_ns);
+int shb_group_pagerank(shb_group *grp, const shb_gpart *part, const shb_launch_cfg *cfg, float x_init, float beta,
+                       double delta, uint32_t max_iters, uint32_t check_every, void *result_host, void *prev_host,
+                       shb_graph_stats *stats);
+int shb_group_bfs(shb_group *grp, const shb_gpart *part, int64_t root, int32_t *levels_host /* n_rows, optional */,
+                  uint32_t max_levels, uint32_t check_every, shb_graph_stats *stats);
+int shb_group_sssp(shb_group *grp, const shb_gpart *part, int64_t source, float *dist_host /* n_rows, optional */,
+                   float window_buckets /* < 0: default (8 for n_dev > 1, none for 1) */, uint32_t max_rounds,
+                   uint32_t check_every, shb_graph_stats *stats);
+
 #ifdef __cplusplus
 }
 #endif

@@ -123,6 +123,24 @@ SIGNATURES = {
     "shb_spmv_scatter": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, c_void_pp, C.c_int, C.c_int64, C.c_double, C.c_int,
                                    C.c_void_p, C.c_void_p, u64p]),
+    "shb_group_create": (C.c_int, [C.c_int, i32p, c_void_pp]),
+    "shb_group_destroy": (C.c_int, [C.c_void_p]),
+    "shb_group_size": (C.c_int, [C.c_void_p, i32p]),
+    "shb_group_ctx": (C.c_int, [C.c_void_p, C.c_int, c_void_pp]),
+    "shb_group_partition_host": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                           c_void_pp]),
+    "shb_group_adopt": (C.c_int, [C.c_void_p, c_void_pp, c_void_pp, C.c_void_p, C.c_int64, c_void_pp]),
+    "shb_gpart_destroy": (C.c_int, [C.c_void_p]),
+    "shb_gpart_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_void_p]),
+    "shb_gpart_block": (C.c_int, [C.c_void_p, C.c_int, c_void_pp, c_void_pp]),
+    "shb_group_iterate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_uint32, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p,
+                                    C.c_void_p, u32p, u64p]),
+    "shb_group_pagerank": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(LaunchCfg), C.c_float, C.c_float, C.c_double, C.c_uint32,
+                                     C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(GraphStats)]),
+    "shb_group_bfs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(GraphStats)]),
+    "shb_group_sssp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_float, C.c_uint32, C.c_uint32,
+                                 C.POINTER(GraphStats)]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

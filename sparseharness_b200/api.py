@@ -387,3 +387,131 @@ class Context:
         if self.h:
             lib.shb_ctx_destroy(self.h)
             self.h = None
+
+
+class _BorrowedContext(Context):
+    """A context owned by a Group (not destroyed by close())."""
+
+    def __init__(self, handle, device):  # noqa: super().__init__ deliberately not called
+        self.h, self.device = handle, device
+
+    def close(self):
+        self.h = None
+
+
+class GroupPartition:
+    """An operator row-partitioned over a Group (shb_gpart): block i resident on device i."""
+
+    def __init__(self, group: "Group", handle):
+        self.group, self.h = group, handle
+
+    @property
+    def info(self):
+        n_rows, n_cols, nnz = C.c_int64(), C.c_int64(), C.c_int64()
+        bounds = np.zeros(self.group.n + 1, dtype=np.int64)
+        _ck(lib.shb_gpart_info(self.h, C.byref(n_rows), C.byref(n_cols), C.byref(nnz), _ptr(bounds)))
+        return {"n_rows": n_rows.value, "n_cols": n_cols.value, "nnz": nnz.value, "bounds": bounds}
+
+    def block(self, i: int) -> Csr:
+        """Borrowed view of block i (for downloads / parity checks); freed with the partition."""
+        a = C.c_void_p()
+        _ck(lib.shb_gpart_block(self.h, i, C.byref(a), None))
+        return Csr(self.group.ctx(i), a)
+
+    def free(self):
+        if self.h:
+            _ck(lib.shb_gpart_destroy(self.h))
+            self.h = None
+
+
+class Group:
+    """N devices of one box driven by ONE host thread through shb_group_* (include/shb.h): contexts, peer access and
+    the round / level loops live in libshb.so; no torch.distributed, no second process."""
+
+    def __init__(self, n_dev: int, devices=None):
+        h = C.c_void_p()
+        dv = None if devices is None else (C.c_int * n_dev)(*devices)
+        _ck(lib.shb_group_create(n_dev, dv, C.byref(h)))
+        self.h, self.n = h, n_dev
+        self._ctx = {}
+
+    def ctx(self, i: int) -> Context:
+        if i not in self._ctx:
+            c = C.c_void_p()
+            _ck(lib.shb_group_ctx(self.h, i, C.byref(c)))
+            d = C.c_int()
+            _ck(lib.shb_ctx_device(c, C.byref(d)))
+            self._ctx[i] = _BorrowedContext(c, d.value)
+        return self._ctx[i]
+
+    def partition_host(self, n_rows, n_cols, row_ptr, col, val=None, symmetric=False) -> GroupPartition:
+        row_ptr = np.ascontiguousarray(row_ptr, dtype=np.int64)
+        col = np.ascontiguousarray(col, dtype=np.int32)
+        if val is not None:
+            val = np.ascontiguousarray(val)
+            assert val.dtype.itemsize == 4
+        h = C.c_void_p()
+        _ck(lib.shb_group_partition_host(self.h, n_rows, n_cols, _ptr(row_ptr), _ptr(col), _ptr(val), int(symmetric), C.byref(h)))
+        return GroupPartition(self, h)
+
+    def adopt(self, blocks, bounds, n_cols, at_blocks=None) -> GroupPartition:
+        """blocks[i]: a Csr built on self.ctx(i); ownership moves to the partition."""
+        arr = (C.c_void_p * self.n)(*[b.h for b in blocks])
+        at = None if at_blocks is None else (C.c_void_p * self.n)(*[b.h for b in at_blocks])
+        bounds = np.ascontiguousarray(bounds, dtype=np.int64)
+        h = C.c_void_p()
+        _ck(lib.shb_group_adopt(self.h, arr, at, _ptr(bounds), n_cols, C.byref(h)))
+        for b in list(blocks) + list(at_blocks or []):
+            b.h = None
+        return GroupPartition(self, h)
+
+    def iterate(self, part: GroupPartition, semiring, x0, y0, alpha, beta, delta=1e-4, term=None, y_mode=1, max_iters=1000,
+                check_every=16, cfg: LaunchCfg | None = None, want_prev=False):
+        """Returns (result, prev|None, n_iters, total_ns, converged)."""
+        dt = _DTYPE[semiring]
+        n = part.info["n_rows"]
+        term = (TERM_ABSDIFF if semiring in (PLUS_TIMES, MIN_PLUS) else TERM_EQUAL) if term is None else term
+        a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
+        x0 = np.ascontiguousarray(x0, dtype=dt)
+        y0 = None if y0 is None else np.ascontiguousarray(y0, dtype=dt)
+        res = np.empty(n, dtype=dt)
+        prev = np.empty(n, dtype=dt) if want_prev else None
+        it, ns = C.c_uint32(0), C.c_uint64(0)
+        st = lib.shb_group_iterate(self.h, part.h, semiring, C.byref(cfg) if cfg else None, _ptr(x0), 0, _ptr(y0), _ptr(a), _ptr(b),
+                                   delta, term, y_mode, max_iters, check_every, _ptr(res), _ptr(prev), C.byref(it), C.byref(ns))
+        if st not in (0, 7):
+            raise ShbError(st)
+        return res, prev, it.value, ns.value, st == 0
+
+    def pagerank(self, part: GroupPartition, damping=0.85, delta=1e-4, max_iters=1000, check_every=8, cfg: LaunchCfg | None = None,
+                 want_result=True, want_prev=False):
+        n = part.info["n_rows"]
+        x_init = np.float32(1.0) / np.float32(n)
+        beta = (np.float32(1.0) - np.float32(damping)) / np.float32(n)
+        res = np.empty(n, dtype=np.float32) if want_result else None
+        prev = np.empty(n, dtype=np.float32) if want_prev else None
+        st = GraphStats()
+        s = lib.shb_group_pagerank(self.h, part.h, C.byref(cfg) if cfg else None, C.c_float(x_init), C.c_float(beta), delta, max_iters,
+                                   check_every, _ptr(res), _ptr(prev), C.byref(st))
+        if s not in (0, 7):
+            raise ShbError(s)
+        return res, prev, st
+
+    def bfs(self, part: GroupPartition, root=0, max_levels=0, check_every=8, want_levels=True):
+        n = part.info["n_rows"]
+        lv = np.empty(n, dtype=np.int32) if want_levels else None
+        st = GraphStats()
+        _ck(lib.shb_group_bfs(self.h, part.h, root, _ptr(lv), max_levels, check_every, C.byref(st)))
+        return lv, st
+
+    def sssp(self, part: GroupPartition, source=0, window_buckets=-1.0, max_rounds=0, check_every=8, want_dist=True):
+        n = part.info["n_rows"]
+        d = np.empty(n, dtype=np.float32) if want_dist else None
+        st = GraphStats()
+        _ck(lib.shb_group_sssp(self.h, part.h, source, _ptr(d), C.c_float(window_buckets), max_rounds, check_every, C.byref(st)))
+        return d, st
+
+    def close(self):
+        if self.h:
+            _ck(lib.shb_group_destroy(self.h))
+            self.h = None

@@ -638,8 +638,8 @@ static int default_rpg(int lanes) {
 }
 
 // BLOCKED: one persistent cooperative kernel, a CTA per SM, producer and consumer warps (pb.cuh).
-// SHB_PB_SPLIT=1 runs the two roles as two launches over a full-size ring (debug aid).
-template <class S, bool HAS_VAL, int K>
+// SHB_PB_SPLIT=1 runs the two roles as two launches over a full-size ring (debug / profiling aid).
+template <class S, bool HAS_VAL>
 static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> &a) {
   typedef typename S::T T;
   const int n_groups = pb->g.n_pass * pb->g.n_panel;
@@ -647,36 +647,43 @@ static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> 
   pa.g = pb->g;
   pa.lcol = pb->lcol;
   pa.val = (const T *)pb->val;
+  pa.chunk_desc = pb->chunk_desc;
+  pa.delta = pb->delta;
+  pa.uchunk = pb->uchunk;
   pa.slot = pb->slot;
-  pa.unit_ptr = pb->unit_ptr;
-  pa.cons_desc = pb->cons_desc;
+  pa.cons_start = pb->cons_start;
   pa.crp = pb->crp;
   pa.partial = (T *)pb->partial;
   pa.ready = pb->sync;
   pa.consumed = pb->sync + n_groups;
   pa.exit_count = pb->sync + 2 * n_groups;
-  static const bool split = getenv("SHB_PB_SPLIT") != nullptr;
+  static const char *split_env = getenv("SHB_PB_SPLIT");  // "1": both roles as two launches, "p" / "c": one role only
+  const bool split = split_env != nullptr;
   if (split) {
     SHB_TRY(shb_pb_reserve_ring(c, pb, n_groups));
     pa.g.depth = n_groups;
   }
   pa.ring = (T *)pb->ring;
   const size_t smem = shb_pb_smem_bytes(pb);
-  SHB_CUDA(cudaFuncSetAttribute(pb_fused_kernel<S, HAS_VAL, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SHB_CUDA(cudaFuncSetAttribute(pb_fused_kernel<S, HAS_VAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   SpmvArgs<T> aa = a;
   void *args[] = {&pa, &aa};
   const dim3 grid((unsigned)pb->g.n_prod), block(PB_THREADS);
   if (!split) {
     pa.roles = PB_ROLE_PRODUCE | PB_ROLE_CONSUME;
     pa.reset_sync = 1;
-    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, K>, grid, block, args, smem, c->stream));
+    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
   } else {
-    pa.roles = PB_ROLE_PRODUCE;
-    pa.reset_sync = 0;
-    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, K>, grid, block, args, smem, c->stream));
-    pa.roles = PB_ROLE_CONSUME;
-    pa.reset_sync = 1;
-    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, K>, grid, block, args, smem, c->stream));
+    if (split_env[0] != 'c') {
+      pa.roles = PB_ROLE_PRODUCE;
+      pa.reset_sync = split_env[0] == 'p';
+      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+    }
+    if (split_env[0] != 'p') {
+      pa.roles = PB_ROLE_CONSUME;
+      pa.reset_sync = 1;
+      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+    }
   }
   return SHB_OK;
 }
@@ -685,12 +692,7 @@ template <class S>
 static int run_blocked(shb_ctx *c, const shb_csr *A, const SpmvArgs<typename S::T> &a) {
   SHB_REQUIRE(A->pb != nullptr, "SHB_VARIANT_BLOCKED needs shb_csr_build_blocked on this operator first");
   SHB_REQUIRE(A->pb->g.n_prod == c->prop.multiProcessorCount, "blocked layout was built for another device");
-  // 128-entry steps of a piece issued together: sized for the mean piece length plus a third
-  const double mean_piece = (double)A->pb->cap / ((double)A->pb->g.n_pass * A->pb->g.n_panel * A->pb->g.n_prod * A->pb->g.n_prod);
-  const double reach = mean_piece * 1.3;
-  if (reach <= 128.0) return A->pb->val ? launch_blocked<S, true, 1>(c, A->pb, a) : launch_blocked<S, false, 1>(c, A->pb, a);
-  if (reach <= 256.0) return A->pb->val ? launch_blocked<S, true, 2>(c, A->pb, a) : launch_blocked<S, false, 2>(c, A->pb, a);
-  return A->pb->val ? launch_blocked<S, true, 4>(c, A->pb, a) : launch_blocked<S, false, 4>(c, A->pb, a);
+  return A->pb->val ? launch_blocked<S, true>(c, A->pb, a) : launch_blocked<S, false>(c, A->pb, a);
 }
 
 template <class S>

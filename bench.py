@@ -418,6 +418,15 @@ def run_ours(args):
     e2e_value = ALGO_BYTES * n_gpus / (e2e_ms / Ke * 1e-3) / 1e9
     clocks = clk.summary()
 
+    # the kernel the AUTO schedule resolved to on this operator (never a literal: the line must name what ran)
+    fam = {1: "spmv_scalar_kernel", 2: "spmv_vector_kernel", 3: "spmv_stream_kernel", 4: "pb_fused_kernel"}.get(info.auto_variant, "?")
+    kernel_name = {1: f"{fam}<PlusTimesF32,true>", 2: f"{fam}<PlusTimesF32,{info.auto_lanes},2,true,true>",
+                   3: f"{fam}<PlusTimesF32,true,true> + spmv_fixup_kernel", 4: f"{fam}<PlusTimesF32,true>"}.get(info.auto_variant, fam)
+    binding = ("not HBM on this operator: every one of the 268M uniform-random x gathers is its own L1TEX->XBAR request "
+               "(ncu: l1tex__m_l1tex2xbar_req_cycles_active 90%, lts__throughput 85%, dram 42%; profiles/r01_summary.md); the same "
+               "kernels with local gathers are HBM-bound, see roofline_local_gathers") if info.auto_variant != 4 else \
+              ("propagation blocking: x slices gathered from shared memory, products through an L2-resident ring, every global "
+               "access a coalesced 128-bit stream (sparseharness_b200/csrc/pb.cuh; profiles/r02_summary.md)")
     line = {
         "metric": "spmv_effective_hbm_gbs", "value": value, "unit": "GB/s", "n_gpus": n_gpus, "steps": K, "warmup": W,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -428,12 +437,9 @@ def run_ours(args):
                    "l2": "inputs 2.35 GB per GPU >> 126 MB L2, no flush between steps (x, 64 MB, may stay L2 resident)"},
         "gflops": FLOPS * n_gpus / (ms_per_step * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "spmv_vector_kernel<PlusTimesF32,4,2,true,true>",
+                     "traffic": None, "peak_source": peak_src, "kernel": kernel_name,
                      "note": "achieved = 2348810244 B / mean launch time over the timed region (CUDA events on the launch stream)",
-                     "binding_unit": "not HBM on this operator: every one of the 268M uniform-random x gathers is its own "
-                                     "L1TEX->XBAR request (ncu: l1tex__m_l1tex2xbar_req_cycles_active 90%, lts__throughput 85%, "
-                                     "dram 42%; profiles/r01_summary.md); the same kernels with local gathers are HBM-bound, "
-                                     "see roofline_local_gathers"},
+                     "binding_unit": binding},
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": N_COLS * 4, "d2h_bytes_per_step": ROWS_PER_GPU * 4,
                 "ms_per_step": e2e_ms / Ke, "steps": Ke,
                 "api": "shb_spmv_host_batch: one call for all steps; every step uploads its x from pinned host memory and "
@@ -448,7 +454,13 @@ def run_ours(args):
     traffic_file = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
     if os.path.exists(traffic_file):
         try:
-            line["roofline"]["traffic"] = json.load(open(traffic_file))["dram_bytes_per_launch"]
+            tf = json.load(open(traffic_file))
+            # only the counters of THIS kernel family may be attached (tools/ncu_traffic.py writes name + git head)
+            if tf.get("kernel", "").split("<")[0].split("(")[0].strip().endswith(fam):
+                line["roofline"]["traffic"] = tf["dram_bytes_per_launch"]
+                line["roofline"]["traffic_source"] = {"kernel": tf.get("kernel"), "git_head": tf.get("git_head"), "file": "profiles/traffic_bytes_per_launch.json"}
+            else:
+                line["roofline"]["traffic_note"] = f"no ncu capture of {fam} on file (profiles/traffic_bytes_per_launch.json holds {tf.get('kernel')})"
         except Exception:
             pass
 

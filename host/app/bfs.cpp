@@ -6,6 +6,7 @@
 //   canonical mode: integer BFS levels, level[v] = first k with v in the frontier, -1 when unreached
 //     (direction-optimising, device resident); stored zero values are no edges, as in bool_and.
 #include "iterative_app.h"
+#include "group_app.h"
 
 typedef int SemiRingType;
 typedef IterativeAppHarness<SemiRingType, SHB_TERM_EQUAL> HarnessBFS;
@@ -43,6 +44,20 @@ int main(int argc, char *argv[]) {
     return 0;
   }
   const int64_t n = matrix.height();
+  if (s.gpus > 1) {  // row-partitioned, direction-optimising; frontier bits and counts travel as the kernels' peer stores
+    GroupOperator go;
+    const bool sym = s.symmetric || s.synthetic.compare(0, 5, "rmat:") == 0 || s.synthetic.compare(0, 5, "grid:") == 0;
+    make_group_operator(s, harness.context(), harness.matrixHandle(), sym, go);
+    std::vector<SemiRingType> out((std::size_t)n);
+    run_canonical_app(s, kernel.getName(), go.device_names, "BFS", [&](const Run &) {
+      shb_graph_stats st = {};
+      const int status = shb_group_bfs(go.grp, go.part, 0, out.data(), 0, 8, &st);
+      if (status != SHB_ERR_NOT_CONVERGED) checkShbError(status);
+      return canonical_from(st);
+    });
+    dump_vector(s.dump, out);
+    return 0;
+  }
   shb_buf *levels = nullptr;
   checkShbError(shb_buf_create(harness.context(), (uint64_t)n * 4 + 4096, &levels));
   shb_csr *AT = nullptr;

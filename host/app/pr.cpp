@@ -6,6 +6,7 @@
 //     x_1 = beta, x_{k+1} = beta * x_k; stops when all |x_k - x_{k+1}| < delta
 //   canonical mode: float values kept, y == 1 constant: x_{k+1} = d * A^ x_k + (1-d)/N until max |dx| < delta
 #include "iterative_app.h"
+#include "group_app.h"
 
 typedef float SemiRingType;
 typedef IterativeAppHarness<SemiRingType, SHB_TERM_ABSDIFF> HarnessPR;
@@ -50,6 +51,20 @@ int main(int argc, char *argv[]) {
     return 0;
   }
   const int64_t n = matrix.height();
+  if (s.gpus > 1) {  // row-partitioned over s.gpus devices, x exchanged by the SpMV epilogue's peer stores
+    GroupOperator go;
+    make_group_operator(s, harness.context(), harness.matrixHandle(), /*no out-edge copy: PageRank only pulls*/ true, go);
+    std::vector<SemiRingType> out((std::size_t)n);
+    run_canonical_app(s, kernel.getName(), go.device_names, "PageRank", [&](const Run &) {
+      shb_graph_stats st = {};
+      const int status = shb_group_pagerank(go.grp, go.part, &launch, 1.0f / (SemiRingType)n, (1.0f - dampingFactor) / (SemiRingType)n,
+                                            s.delta, s.max_iterations, 8, out.data(), nullptr, &st);
+      if (status != SHB_ERR_NOT_CONVERGED) checkShbError(status);
+      return canonical_from(st);
+    });
+    dump_vector(s.dump, out);
+    return 0;
+  }
   shb_buf *xb = nullptr, *work = nullptr;
   checkShbError(shb_buf_create(harness.context(), (uint64_t)n * 4 + 4096, &xb));
   checkShbError(shb_buf_create(harness.context(), (uint64_t)n * 4 + 4096, &work));

@@ -5,6 +5,7 @@
 #include <limits>
 
 #include "iterative_app.h"
+#include "group_app.h"
 
 typedef float SemiRingType;
 typedef IterativeAppHarness<SemiRingType, SHB_TERM_ABSDIFF> HarnessSSSP;
@@ -44,6 +45,20 @@ int main(int argc, char *argv[]) {
     return 0;
   }
   const int64_t n = matrix.height();
+  if (s.gpus > 1) {  // block-asynchronous near-far in distance windows, boundary candidates as peer red.min
+    GroupOperator go;
+    const bool sym = s.symmetric || s.synthetic.compare(0, 5, "rmat:") == 0 || s.synthetic.compare(0, 5, "grid:") == 0;
+    make_group_operator(s, harness.context(), harness.matrixHandle(), sym, go);
+    std::vector<SemiRingType> out((std::size_t)n);
+    run_canonical_app(s, kernel.getName(), go.device_names, "SSSP", [&](const Run &) {
+      shb_graph_stats st = {};
+      const int status = shb_group_sssp(go.grp, go.part, 0, out.data(), -1.0f, 0, 8, &st);
+      if (status != SHB_ERR_NOT_CONVERGED) checkShbError(status);
+      return canonical_from(st);
+    });
+    dump_vector(s.dump, out);
+    return 0;
+  }
   shb_buf *dist = nullptr;
   checkShbError(shb_buf_create(harness.context(), (uint64_t)n * 4 + 4096, &dist));
   shb_csr *AT = nullptr;

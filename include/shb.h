@@ -70,8 +70,9 @@ enum { SHB_F_NO_CACHE_HINTS = 1u, /* plain ld.global for every stream (A/B exper
        SHB_F_REVERSED_ORDER = 4u, /* SCALAR: accumulate a row from its last entry to its first, the
                                      order of the ELL schedules (kernel{,3,5}.json write products
                                      reversed into the temp buffer)                               */
-       SHB_F_Y_IS_ONE = 8u        /* y is the semiring one in every element (canonical PageRank's
-                                     y == 1, app/pr.cpp:183): the y argument is not read          */ };
+       SHB_F_Y_IS_ONE = 8u,       /* y is the semiring one in every element (canonical PageRank's
+                                     y == 1, app/pr.cpp:183): the y argument is not read          */
+       SHB_F_NO_PANELS = 16u      /* AUTO: ignore the operator's column panels (A/B experiments)   */ };
 
 typedef struct {
   int32_t variant;        /* shb_variant                                                          */
@@ -147,6 +148,12 @@ int shb_csr_transpose(shb_ctx *ctx, const shb_csr *csr, shb_csr **transposed); /
 int shb_csr_build_blocked(shb_ctx *ctx, shb_csr *csr, int rows_per_consumer, int make_default);
 int shb_csr_blocked_info(const shb_csr *csr, int32_t *geom /* 8: n_prod, n_pass, n_panel, W, RS, cbuf, slot_cap, depth */, int64_t *entries,
                          uint64_t *device_bytes);
+/* Column panels for operators whose x exceeds the L2 (config 5: 2^26 columns, x = 268 MB): n_panels sub-operators
+ * of consecutive column ranges, each a CSR over all the rows with global column ids, so that the gathers of one
+ * launch stay inside an L2-resident slice of x; SHB_VARIANT_AUTO then runs panel after panel, carrying the row
+ * sums through the epilogue (exact for min-plus / or-and / max-min, summation order for floats).  n_panels 0 =
+ * x slices of at most 32 MB; *n_built = 0 when the operator needs no panels.  Doubles the operator's footprint. */
+int shb_csr_build_panels(shb_ctx *ctx, shb_csr *csr, int n_panels, int *n_built);
 int shb_csr_balance_rows(shb_ctx *ctx, const shb_csr *csr, int parts, int64_t *row_bounds);
 int shb_csr_slice_rows(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int64_t row_count, shb_csr **slice);
 

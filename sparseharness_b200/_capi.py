@@ -76,6 +76,7 @@ SIGNATURES = {
     "shb_csr_transpose": (C.c_int, [C.c_void_p, C.c_void_p, c_void_pp]),
     "shb_csr_build_blocked": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "shb_csr_blocked_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64), u64p]),
+    "shb_csr_build_panels": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, i32p]),
     "shb_csr_balance_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "shb_csr_slice_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, c_void_pp]),
     "shb_spmv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p, C.c_void_p,

@@ -14,7 +14,7 @@ from ._capi import CsrInfo, GraphStats, LaunchCfg, lib
 PLUS_TIMES, MIN_PLUS, OR_AND, MAX_MIN = 0, 1, 2, 3
 VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_STREAM, VARIANT_BLOCKED = 0, 1, 2, 3, 4
 TERM_ABSDIFF, TERM_EQUAL = 0, 1
-F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER, F_Y_IS_ONE = 1, 2, 4, 8
+F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER, F_Y_IS_ONE, F_NO_PANELS = 1, 2, 4, 8, 16
 _DTYPE = {PLUS_TIMES: np.float32, MIN_PLUS: np.float32, OR_AND: np.int32, MAX_MIN: np.int32}
 
 
@@ -114,6 +114,12 @@ class Csr:
         val = np.empty(nnz, dtype=dtype) if inf.has_values else None
         _ck(lib.shb_csr_download(self.ctx.h, self.h, row_begin, row_count, _ptr(rp), _ptr(col), _ptr(val)))
         return rp, col, val
+
+    def build_panels(self, n_panels: int = 0) -> int:
+        """Column panels for operators whose x exceeds the L2 (shb_csr_build_panels); returns the number built."""
+        n = C.c_int(0)
+        _ck(lib.shb_csr_build_panels(self.ctx.h, self.h, n_panels, C.byref(n)))
+        return n.value
 
     def transpose(self) -> "Csr":
         h = C.c_void_p()

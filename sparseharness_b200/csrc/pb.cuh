@@ -124,6 +124,30 @@ __device__ __forceinline__ void pb_st_v4(void *p, const uint4 &v) {
   asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// ---- TMA (bulk async copy) staging of the x slice: one thread issues, the mbarrier counts the bytes -----------
+__device__ __forceinline__ uint32_t pb_smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pb_mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pb_smem_addr(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void pb_mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pb_smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void pb_bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(pb_smem_addr(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(pb_smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void pb_mbar_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t ok = 0;
+  const uint32_t addr = pb_smem_addr(bar);
+  while (!ok)
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok)
+                 : "r"(addr), "r"(parity)
+                 : "memory");
+}
+
 // what a producer lane holds of one chunk: 8 local columns, 8 values, the chunk's piece flags
 struct PbStage {
   uint4 lc, v0, v1, d;
@@ -173,9 +197,10 @@ __device__ __forceinline__ void pb_stage_process(const PbStage &st, const PbArgs
 // ---------------------------------------------------------------------------------------------
 template <class S, bool HAS_VAL>
 __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
-                                           typename S::T *xs, uint32_t *arr, int tid) {
+                                           typename S::T *xs, uint32_t *arr, uint64_t *xbar, int tid) {
   typedef typename S::T T;
   const int p = blockIdx.x;
+  uint32_t xphase = 0;  // completed phases of the x-slice mbarrier
   const int lane = tid & 31, warp = tid >> 5;
   const uint64_t pol_stream = shb_policy_evict_first();
   const uint32_t zbits = shb_bits<T>(S::zero());
@@ -216,20 +241,21 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
 
   for (int pass = 0; pass < c.g.n_pass; ++pass) {
     pb_bar(1, PB_PROD_THREADS);  // every warp is done gathering from the previous slice
-    // the slice of x; columns past the end of the vector read as the semiring zero
+    // the slice of x, staged by TMA: thread 0 arms the mbarrier with the byte count and issues 1-D bulk copies
+    // (global -> shared, 32 KB each); the 16-byte aligned body arrives through the async proxy while the other
+    // threads fill what a bulk copy cannot carry (an unaligned x, the tail, columns past the end of the vector,
+    // which read as the semiring zero)
     const int64_t c0 = ((int64_t)pass * c.g.n_prod + p) * c.g.W;
-    for (int i = tid * 4; i < c.g.W; i += PB_PROD_THREADS * 4) {
-      const int64_t cc = c0 + i;
-      uint4 v;
-      if (x_aligned && cc + 3 < (int64_t)a.vlength) {
-        v = *reinterpret_cast<const uint4 *>(a.x + cc);
-      } else {
-        v.x = cc + 0 < (int64_t)a.vlength ? shb_bits<T>(a.x[cc + 0]) : zbits;
-        v.y = cc + 1 < (int64_t)a.vlength ? shb_bits<T>(a.x[cc + 1]) : zbits;
-        v.z = cc + 2 < (int64_t)a.vlength ? shb_bits<T>(a.x[cc + 2]) : zbits;
-        v.w = cc + 3 < (int64_t)a.vlength ? shb_bits<T>(a.x[cc + 3]) : zbits;
-      }
-      *reinterpret_cast<uint4 *>(xs + i) = v;
+    const int valid = (int)max((int64_t)0, min((int64_t)c.g.W, (int64_t)a.vlength - c0));
+    const int bulk = x_aligned ? (valid & ~3) : 0;
+    if (bulk > 0 && tid == 0) {
+      pb_mbar_expect_tx(xbar, (uint32_t)bulk * 4u);
+      for (int off = 0; off < bulk; off += 8192) pb_bulk_g2s(xs + off, a.x + c0 + off, (uint32_t)min(8192, bulk - off) * 4u, xbar);
+    }
+    for (int i = bulk + tid; i < c.g.W; i += PB_PROD_THREADS) xs[i] = i < valid ? a.x[c0 + i] : shb_from_bits<T>(zbits);
+    if (bulk > 0) {
+      pb_mbar_wait(xbar, xphase & 1u);
+      ++xphase;
     }
     pb_bar(1, PB_PROD_THREADS);
 
@@ -388,11 +414,13 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   T *xs = reinterpret_cast<T *>(pb_smem);
   T *cbuf = xs + c.g.W;
   uint32_t *arr = reinterpret_cast<uint32_t *>(cbuf + c.g.cbuf_cap + 32);
+  uint64_t *xbar = reinterpret_cast<uint64_t *>(arr + PB_ARR);
   if (threadIdx.x < PB_ARR) arr[threadIdx.x] = 0;
+  if (threadIdx.x == 0) pb_mbar_init(xbar, 1);
   __syncthreads();
   bool differs = false;
   if (threadIdx.x < PB_PROD_THREADS) {
-    if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, threadIdx.x);
+    if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, threadIdx.x);
   } else {
     if (c.roles & PB_ROLE_CONSUME) pb_consume<S>(c, a, cbuf, threadIdx.x - PB_PROD_THREADS, differs);
   }

@@ -342,6 +342,7 @@ SHB_API int shb_csr_destroy(shb_csr *A) {
   cudaFree(A->row_len);
   cudaFree(A->empty_row_bits);
   shb_pb_free(A->pb);
+  shb_panels_free(A);
   cudaGetLastError();
   delete A;
   return SHB_OK;
@@ -395,6 +396,30 @@ __global__ void csr_tile_rows_kernel(const int32_t *row_ptr, int64_t n_rows, int
   (void)nnz;
 }
 
+// gather locality: distinct 128-byte lines of x touched by 32 consecutive stored entries (what one warp-wide gather
+// of a row-major schedule costs in L1TEX -> XBAR requests), averaged over evenly spaced sample windows.
+// ~32 = every gather its own line (uniform-random columns), ~8 = the 2-D grid.
+__global__ void csr_gather_lines_kernel(const int32_t *__restrict__ col, int64_t nnz, int n_windows, unsigned long long *sum) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (warp >= n_windows) return;
+  const int64_t base = (nnz - 32) / max(n_windows, 1) * warp;
+  const int32_t c = col[base + lane];
+  const unsigned peers = __match_any_sync(0xffffffffu, c >> 5);
+  const unsigned leaders = __ballot_sync(0xffffffffu, (__ffs(peers) - 1) == lane);
+  if (lane == 0) atomicAdd(sum, (unsigned long long)__popc(leaders));
+}
+
+// large, balanced, gather-bound operators: the propagation-blocked schedule (pb.cuh) is the one that gets off the
+// L1TEX request ceiling; everything else keeps its row-major schedule
+static bool blocked_candidate(const shb_csr *A) {
+  static const bool enabled = getenv("SHB_AUTO_BLOCKED") && atoi(getenv("SHB_AUTO_BLOCKED")) != 0;  // off until measured
+  if (!enabled) return false;
+  const double mean = A->n_rows > 0 ? (double)A->nnz / (double)A->n_rows : 0.0;
+  return A->nnz >= (1ll << 24) && A->n_cols >= (1ll << 18) && mean >= 2.0 && A->gather_lines >= 24.0 &&
+         (double)A->max_row_len <= 32.0 * std::max(mean, 1.0) + 64.0;
+}
+
 static void choose_auto(shb_csr *A) {
   const double mean = A->n_rows > 0 ? (double)A->nnz / (double)A->n_rows : 0.0;
   // power-law / very skewed rows: nnz-split tiles keep every CTA equally loaded
@@ -434,14 +459,32 @@ int shb_csr_analyse(shb_ctx *c, shb_csr *A) {
                                                                              A->tile_row, A->n_tiles, d_st);
   }
   SHB_CUDA(cudaGetLastError());
+  const int n_windows = A->nnz >= 4096 ? 2048 : 0;
+  unsigned long long *d_lines = nullptr, h_lines = 0;
+  if (n_windows) {
+    SHB_CUDA(cudaMalloc(&d_lines, 8));
+    SHB_CUDA(cudaMemsetAsync(d_lines, 0, 8, c->stream));
+    csr_gather_lines_kernel<<<(n_windows * 32 + 255) / 256, 256, 0, c->stream>>>(A->col, A->nnz, n_windows, d_lines);
+    SHB_CUDA(cudaGetLastError());
+    SHB_CUDA(cudaMemcpyAsync(&h_lines, d_lines, 8, cudaMemcpyDeviceToHost, c->stream));
+  }
   SHB_CUDA(cudaMemcpyAsync(&h, d_st, sizeof h, cudaMemcpyDeviceToHost, c->stream));
   SHB_CUDA(cudaStreamSynchronize(c->stream));
   SHB_CUDA(cudaFree(d_st));
+  cudaFree(d_lines);
   A->max_row_len = A->n_rows > 0 ? (int64_t)h.max_len : 0;
   A->min_row_len = A->n_rows > 0 ? (int64_t)h.min_len : 0;
   A->empty_rows = (int64_t)h.empty;
   A->straddling_rows = (int64_t)h.straddle;
+  A->gather_lines = n_windows ? (double)h_lines / (double)n_windows : 0.0;
   choose_auto(A);
+  // the encode step of the blocked schedule (the analogue of the reference re-encoding a matrix for its kernel,
+  // inc/kernel_utils.h:35-168) happens here, once, when the statistics ask for it; an operator whose rows or columns
+  // are too skewed for the layout keeps its row-major schedule
+  if (!A->pb && !A->auto_blocked_tried && blocked_candidate(A)) {
+    A->auto_blocked_tried = true;
+    if (shb_csr_build_blocked(c, A, 0, 1) != SHB_OK) shb_set_error("%s", "");
+  }
   return SHB_OK;
 }
 
@@ -780,6 +823,9 @@ int shb_launch_spmv(shb_ctx *c, const shb_csr *A, int semiring, const shb_launch
                     const void *alpha, const void *beta, void *const *outs, int n_out, int64_t row_offset,
                     const IterCtl &ctl) {
   SHB_REQUIRE(n_out >= 1 && n_out <= SHB_MAX_DST, "1..8 destinations");
+  // an operator with column panels runs panel after panel unless the caller names a schedule
+  if (A->n_panels > 1 && (!cfg || cfg->variant == SHB_VARIANT_AUTO) && !(cfg && (cfg->flags & SHB_F_NO_PANELS)))
+    return shb_launch_spmv_panels(c, A, semiring, cfg, x, y, alpha, beta, outs, n_out, row_offset, ctl);
   switch (semiring) {
     case SHB_PLUS_TIMES_F32: {
       SpmvArgs<float> a;

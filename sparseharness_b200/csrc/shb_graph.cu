@@ -983,6 +983,9 @@ SHB_API int shb_pagerank(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg
   SHB_REQUIRE(x->bytes >= (uint64_t)A->n_rows * 4 && work->bytes >= (uint64_t)A->n_rows * 4, "vector shorter than n_rows");
   SHB_REQUIRE(x->ptr != work->ptr, "x and work must differ");
   SHB_CUDA(cudaSetDevice(c->device));
+  // x larger than the L2: the sweeps run over column panels (shb_panels.cu), built once and kept on the operator
+  if (A->n_panels == 0 && (uint64_t)A->n_cols * 4 > shb_panel_threshold_bytes(c) && (!cfg || cfg->variant == SHB_VARIANT_AUTO))
+    SHB_TRY(shb_csr_build_panels(c, const_cast<shb_csr *>(A), 0, nullptr));
   uint32_t bits;
   memcpy(&bits, &x_init, 4);
   SHB_TRY(shb_buf_fill_u32(c, x, 0, (uint64_t)A->n_rows, bits));

@@ -472,6 +472,11 @@ SHB_API int shb_group_pagerank(shb_group *g, const shb_gpart *p, const shb_launc
   const float alpha = 1.0f;
   uint32_t iters = 0;
   uint64_t total = 0;
+  // every device gathers from the full-length x: above the L2 size the sweeps run over column panels
+  for (int d = 0; d < g->n; ++d)
+    if (p->A[d]->n_panels == 0 && (uint64_t)p->n_cols * 4 > shb_panel_threshold_bytes(g->ctx[d]) &&
+        (!cfg || cfg->variant == SHB_VARIANT_AUTO))
+      SHB_TRY(shb_csr_build_panels(g->ctx[d], p->A[d], 0, nullptr));
   const int s = shb_group_iterate(g, p, SHB_PLUS_TIMES_F32, cfg, nullptr, bits, nullptr, &alpha, &beta, delta, SHB_TERM_ABSDIFF,
                                   2, max_iters, check_every, result_host, prev_host, &iters, &total);
   if (stats) {

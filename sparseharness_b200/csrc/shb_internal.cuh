@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -72,6 +73,7 @@ static const int SHB_TILE_NNZ = 4096;
 
 struct shb_pb;  // blocked copy of the operator (pb.cuh)
 void shb_pb_free(shb_pb *pb);
+#define SHB_MAX_PANELS 16
 
 struct shb_csr {
   shb_ctx *ctx = nullptr;  // creator; may be destroyed before the operator is (destroy uses `device` only)
@@ -87,11 +89,19 @@ struct shb_csr {
   // statistics
   int64_t max_row_len = 0, min_row_len = 0, empty_rows = 0, straddling_rows = 0;
   int auto_variant = SHB_VARIANT_VECTOR, auto_lanes = 4;
+  double gather_lines = 0.0;        // distinct 128-byte lines of x per 32 consecutive entries (sampled)
+  bool auto_blocked_tried = false;  // the blocked copy is built at most once by the analysis
   uint64_t device_bytes = 0;
   // carry buffers for rows straddling stream tiles (element-typed, n_tiles each)
   void *carry_tail = nullptr;
   void *carry_head = nullptr;
   shb_pb *pb = nullptr;  // built on request (shb_csr_build_blocked)
+  // column panels (shb_panels.cu): sub-operators whose gathers stay inside an L2-sized slice of x; built on request
+  // (shb_csr_build_panels) or by the PageRank drivers when x exceeds the L2
+  shb_csr *panels[SHB_MAX_PANELS] = {};
+  int n_panels = 0;
+  void *panel_acc = nullptr;  // n_rows words: the row sums carried from panel to panel
+  uint32_t panel_cols = 0;
   // int32 length of every row, built on first use by shb_bfs (the push degrees of Beamer's direction rule)
   mutable int32_t *row_len = nullptr;
   // bit r set <=> row r is empty (vertices a BFS pull can never find), built on first use by shb_bfs_block_init
@@ -141,6 +151,16 @@ struct IterCtl {
 int shb_launch_spmv(shb_ctx *c, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const void *x, const void *y,
                     const void *alpha, const void *beta, void *const *outs, int n_out, int64_t row_offset,
                     const IterCtl &ctl);
+// column panels (shb_panels.cu)
+void shb_panels_free(shb_csr *A);
+// x vectors above this size make the PageRank drivers build column panels: 3/4 of the device's L2 (SHB_PANEL_MIN_BYTES overrides)
+static inline uint64_t shb_panel_threshold_bytes(const shb_ctx *c) {
+  if (const char *e = getenv("SHB_PANEL_MIN_BYTES")) return (uint64_t)atoll(e);
+  return (uint64_t)c->prop.l2CacheSize / 4 * 3;
+}
+int shb_launch_spmv_panels(shb_ctx *c, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const void *x, const void *y,
+                           const void *alpha, const void *beta, void *const *outs, int n_out, int64_t row_offset,
+                           const IterCtl &ctl);
 // the fixed-point loop behind shb_iterate / shb_pagerank; y_mode 0: y0 every iteration, 1: re-bind y to
 // the current input after iteration 0 (reference behaviour), 2: y is the semiring one
 int shb_iterate_impl(shb_ctx *c, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, void *x, const void *y0,

@@ -116,7 +116,7 @@ void shb_pb_free(shb_pb *pb) {
   delete pb;
 }
 
-static size_t pb_smem_bytes(const PbGeom &g) { return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + PB_ARR * 4; }
+static size_t pb_smem_bytes(const PbGeom &g) { return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + PB_ARR * 4 + 16; }
 
 SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer, int make_default) {
   SHB_REQUIRE(c && A, "bad arguments");

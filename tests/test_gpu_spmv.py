@@ -256,3 +256,48 @@ def test_transpose(ctx, orc):
     order = np.lexsort((rows, col))
     assert np.array_equal(tcol, rows[order]) and np.array_equal(tval, val[order])
     assert np.array_equal(trp, np.concatenate([[0], np.cumsum(np.bincount(col, minlength=m))]))
+
+
+@pytest.mark.parametrize("semiring", SEMIRINGS)
+@pytest.mark.parametrize("n_panels", [2, 5, 16])
+def test_column_panels_carry_the_row_sums_exactly(ctx, orc, semiring, n_panels):
+    """Column panels (shb_csr_build_panels, shb_panels.cu): AUTO runs panel after panel with the row sums carried
+    through the epilogue; the result is the one-pass result bit for bit on exact data, in every semiring, with
+    y / alpha / beta in play, for one and for several destinations and a row offset (the multi-GPU scatter call)."""
+    rng = np.random.default_rng(7 + n_panels)
+    n, m = 2500, 3333
+    rp, col = random_ragged(rng, n, m, mean_len=9, long_rows=[(3, 6000), (2000, 300)])
+    col[rng.random(len(col)) < 0.01] = -1  # out-of-range columns gather ZERO
+    dt = DT[semiring]
+    val = rng.integers(-3, 4, len(col)).astype(dt) if semiring != shb.MIN_PLUS else rng.integers(0, 9, len(col)).astype(dt)
+    x, y, alpha, beta = semiring_inputs(orc, semiring, n, m, rng)
+    want = orc.spmv(semiring, rp, col, val, x, y, alpha, beta)
+    A = ctx.csr(n, m, rp, col, val)
+    assert A.build_panels(n_panels) == n_panels
+    got = run_spmv(ctx, A, semiring, x, y, alpha, beta, n)  # AUTO -> panels
+    assert np.array_equal(got, want), (semiring, n_panels, np.flatnonzero(got != want)[:5])
+    one = run_spmv(ctx, A, semiring, x, y, alpha, beta, n, flags=shb.F_NO_PANELS)
+    assert np.array_equal(one, want)
+    # scatter form: rows land at an offset in two destinations; y and the convergence test use the offset too
+    off = 137
+    xb = ctx.array(np.concatenate([x, np.zeros(max(0, off + n - m), dt)]).astype(dt))
+    yfull = np.zeros(off + n, dt); yfull[off:] = y
+    yb = ctx.array(yfull)
+    d0, d1, flag = ctx.empty((off + n) * 4), ctx.empty((off + n) * 4), ctx.empty(4)
+    flag.zero()
+    ctx.spmv_scatter(A, semiring, xb, yb, alpha, beta, [d0, d1], off, delta=0.0, term=shb.TERM_EQUAL, changed=flag)
+    assert np.array_equal(d0.download(dt, n, offset=4 * off), want) and np.array_equal(d1.download(dt, n, offset=4 * off), want)
+    A.free()
+
+
+def test_pagerank_over_column_panels(ctx, orc):
+    rp, col = orc.gen_rmat(13, 8, seed=orc.SEED_C3, symmetrise=False)
+    val = orc.pagerank_values(rp, col)
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, val)
+    assert A.build_panels(4) == 4
+    res, st = ctx.pagerank(A, delta=1e-7, max_iters=300)
+    want, wit = orc.pagerank(rp, col, val, delta=1e-7, max_iters=300, acc_double=True)
+    got = res.download(np.float32, n)
+    assert st.converged and abs(int(st.iterations) - wit) <= 1
+    assert np.abs(got - want).max() <= REL_TOL * np.abs(want).max()

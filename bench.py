@@ -272,13 +272,47 @@ def graph_extras(ctx, shb, orc):
 
 def partitioned_extras(ctx, rank, world):
     """GTEPS of the row-partitioned drivers at this GPU count: PageRank on config 5 (RMAT scale 26,
-    2^30 non-zeros, 20 sweeps, fused SpMV -> peer scatter) and, for N > 1, BFS on config 3 (RMAT scale 24, frontier
-    bitmap and counts exchanged by the kernels' own peer stores) and SSSP on config 4 (8192^2 grid, block-asynchronous
-    near-far with boundary candidates as peer red.min).  Every rank must call this."""
+    2^30 non-zeros, 20 sweeps) and, for N > 1, BFS on config 3 (RMAT scale 24) and SSSP on config 4 (8192^2 grid).
+    The work runs through the boundary's own multi-GPU drivers, shb_group_* (include/shb.h): ONE process -- rank 0 --
+    drives all N devices with peer access; the other torchrun ranks wait on the rendezvous store (a CPU wait: no NCCL
+    kernel may sit on a device while rank 0's cooperative kernels need all of its SMs).  Should the group path fail,
+    every rank falls back to the torch.distributed drivers (tools/multi_*.py) and the line says so.  Every number is
+    gated by a parity check; a mismatch aborts the run.  Every rank must call this."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     out = {}
+    store = None
+    if world > 1:
+        import torch.distributed as dist
+        store = dist.distributed_c10d._get_default_store()
+    verdict = None
+    if rank == 0:
+        try:
+            import group_bench
+            import sparseharness_b200 as shb
+            ctx.synchronize()
+            g = shb.Group(world)
+            res = {"pagerank_config5": group_bench.pagerank(g)}
+            if world > 1:
+                res["bfs_partitioned"] = group_bench.bfs(g)
+                res["sssp_partitioned"] = group_bench.sssp(g)
+            g.close()
+            verdict = {"ok": True, "res": res}
+        except Exception as e:  # fall back to the torch.distributed drivers below
+            verdict = {"ok": False, "error": repr(e)[:400]}
+        if store is not None:
+            store.set("shb_group_verdict", json.dumps(verdict))
+    else:
+        verdict = json.loads(store.get("shb_group_verdict").decode())  # blocks on the CPU until rank 0 is done
+    if verdict["ok"]:
+        for name, r in verdict["res"].items():
+            out[name] = r
+            if not r.get("parity_ok", False):
+                raise SystemExit(f"bench: {name} (shb_group) failed its parity gate at {world} GPUs -- refusing to report a number")
+        return out
+    out["group_path_error"] = verdict.get("error")
 
     def gate(name, r):
+        r["driver"] = "torch.distributed fallback (tools/multi_*.py)"
         out[name] = r
         if not r.get("parity_ok", False):  # identical on every rank (all-reduced): all ranks leave together
             raise SystemExit(f"bench: {name} failed its parity gate at {world} GPUs -- refusing to report a number")

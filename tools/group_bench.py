@@ -1,0 +1,161 @@
+#!/usr/bin/env python
+"""GTEPS of the row-partitioned drivers INSIDE the boundary (shb_group_*, include/shb.h) at N GPUs of one box:
+PageRank on config 5 (RMAT scale 26, 2^30 non-zeros, 20 sweeps), BFS on config 3 (RMAT scale 24 symmetrised) and
+SSSP on config 4 (8192^2 grid).  ONE process, one host thread, no torch.distributed.
+
+    python tools/group_bench.py --gpus N [--small] [--only pagerank,bfs,sssp]
+
+Every number is gated by a parity check (tools/parity_checks.py; the oracle is the checker): sampled rows of every
+device's block for PageRank; for BFS / SSSP the group result must equal the single-device driver's bit for bit on
+every vertex, and that one must satisfy the BFS / Bellman local conditions on sampled rows (the every-vertex
+comparison with the oracle is tests/test_gpu_fullsize.py).  Prints one JSON line per driver."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tools")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import parity_checks as pc  # noqa: E402
+
+
+def _aligned_bounds(A, n_dev):
+    from sparseharness_b200 import multi
+    return multi.word_aligned_bounds(A.balance_rows(n_dev))
+
+
+def _partition(g, make_full, symmetric, keep_full_on_dev0=False):
+    """Every device generates the operator (bit-identical generator) and keeps its nnz-balanced, 32-aligned row block.
+    Returns (partition, bounds, n, nnz, full_operator_on_device_0 | None)."""
+    blocks, at_blocks, bounds, full0, n, nnz = [], [], None, None, 0, 0
+    for i in range(g.n):
+        c = g.ctx(i)
+        A = make_full(c)
+        if bounds is None:
+            bounds = _aligned_bounds(A, g.n)
+            n, nnz = A.info.n_rows, A.info.nnz
+        lo, hi = int(bounds[i]), int(bounds[i + 1])
+        blocks.append(A.slice_rows(lo, hi - lo))
+        if not symmetric:
+            T = A.transpose()
+            at_blocks.append(T.slice_rows(lo, hi - lo))
+            T.free()
+        if i == 0 and keep_full_on_dev0:
+            full0 = A
+        else:
+            A.free()
+    part = g.adopt(blocks, bounds, n, at_blocks=None if symmetric else at_blocks)
+    return part, bounds, n, nnz, full0
+
+
+def pagerank(g, scale=26, ef=16, iters=20, repeat=2):
+    from oracle import oracle as orc  # checker only
+    part, bounds, n, nnz, _ = _partition(g, lambda c: c.synth_rmat(scale, ef, seed=0x5EED0026, symmetrise=False, value_mode=1), True)
+    best = None
+    for _ in range(repeat):
+        x_new, x_prev, st = g.pagerank(part, delta=0.0, max_iters=iters, check_every=iters, want_prev=True)
+        if best is None or st.total_ns < best[0]:
+            best = (st.total_ns, int(st.iterations))
+    beta = float((np.float32(1.0) - np.float32(0.85)) / np.float32(n))
+    err, rows = 0.0, 0
+    for i in range(g.n):
+        lo, hi = int(bounds[i]), int(bounds[i + 1])
+        blk = part.block(i)
+        begins, cnt = pc.sample_blocks(hi - lo, 4096)
+        for b in begins:
+            rp, col, val = blk.download(b, cnt)
+            err = max(err, pc.pagerank_rows_err(orc, x_prev, x_new[lo + b:lo + b + cnt], rp, col, val, beta))
+            rows += cnt
+    ns, it = best
+    out = {"driver": "shb_group_pagerank", "graph": f"RMAT scale {scale} edgefactor {ef} directed, pagerank values", "n": n, "nnz": nnz,
+           "n_gpus": g.n, "iterations": it, "ms": ns / 1e6, "ms_per_iteration": ns / 1e6 / max(it, 1), "gteps": nnz * it / ns,
+           "exchange": "SpMV epilogue stores into every device's next x over NVLink (peer access), one publish kernel per sweep",
+           "parity_checked": True, "parity_ok": bool(err <= 1e-5 and it == iters), "parity_rel_err": err,
+           "parity": f"x_{it}[rows] against the oracle's plus-times loop over x_{it - 1} on {rows} sampled rows spread over every device's block, bar 1e-5"}
+    part.free()
+    return out
+
+
+def bfs(g, scale=24, ef=16, repeat=3):
+    part, bounds, n, nnz, A0 = _partition(g, lambda c: c.synth_rmat(scale, ef, seed=0x5EED0024, symmetrise=True), True, keep_full_on_dev0=True)
+    c0 = g.ctx(0)
+    rp_head = A0.download(0, min(n, 4096))[0]
+    root = int(np.argmax(np.diff(rp_head) > 0))
+    lv_buf, st1 = c0.bfs(A0, root, AT=A0)
+    single = lv_buf.download(np.int32, n)
+    lv_buf.free()
+    begins, cnt = pc.sample_blocks(n, 1 << 14, extra=[int(b) - (1 << 13) for b in bounds[1:-1]])
+    ok = all(pc.bfs_rows_ok(single, *A0.download(b, cnt)[:2], b, root) for b in begins)
+    A0.free()
+    best = None
+    for _ in range(repeat):
+        lv, st = g.bfs(part, root, check_every=8)
+        if best is None or st.total_ns < best.total_ns:
+            best = st
+        ok = ok and bool(np.array_equal(lv, single))
+    ok = ok and best.iterations == st1.iterations and best.reached == st1.reached and best.edges_traversed == st1.edges_traversed
+    und = best.edges_traversed / 2
+    out = {"driver": "shb_group_bfs", "graph": f"RMAT scale {scale} edgefactor {ef} symmetrised+deduplicated", "n": n, "nnz": nnz, "n_gpus": g.n,
+           "levels": int(best.iterations), "reached": int(best.reached), "ms": best.total_ns / 1e6, "gteps": und / best.total_ns,
+           "teps_edges": und, "single_device_ms": st1.total_ns / 1e6, "parity_checked": True, "parity_ok": bool(ok),
+           "parity": f"all {n} levels equal the single-device driver's, which satisfy the BFS local conditions on {len(begins) * cnt} sampled rows"}
+    part.free()
+    return out
+
+
+def sssp(g, w=8192, h=8192, repeat=2):
+    part, bounds, n, nnz, G0 = _partition(g, lambda c: c.synth_grid2d(w, h, seed=0x5EED0004), True, keep_full_on_dev0=True)
+    c0 = g.ctx(0)
+    d_buf, st1 = c0.sssp(G0, 0, AT=G0)
+    single = d_buf.download(np.float32, n)
+    d_buf.free()
+    begins, cnt = pc.sample_blocks(n, 1 << 14, extra=[int(b) - (1 << 13) for b in bounds[1:-1]])
+    ok = bool(st1.converged) and all(pc.sssp_rows_ok(single, *G0.download(b, cnt), b, 0) for b in begins)
+    G0.free()
+    best = None
+    for _ in range(repeat):
+        d, st = g.sssp(part, 0, check_every=8)
+        if best is None or st.total_ns < best.total_ns:
+            best = st
+        ok = ok and bool(st.converged) and bool(np.array_equal(d.view(np.uint32), single.view(np.uint32)))
+    ok = ok and best.reached == st1.reached
+    out = {"driver": "shb_group_sssp", "graph": f"2-D grid {w}x{h} 4-neighbour, integer weights 1..255", "n": n, "nnz": nnz, "n_gpus": g.n,
+           "rounds": int(best.iterations), "ms": best.total_ns / 1e6, "gteps": best.edges_traversed / best.total_ns,
+           "single_device_ms": st1.total_ns / 1e6, "dist_checksum64": pc.checksum64(single), "parity_checked": True, "parity_ok": bool(ok),
+           "parity": f"all {n} distances equal the single-device driver's bit for bit, which satisfy the Bellman fixed-point condition on "
+                     f"{len(begins) * cnt} sampled rows incl. both sides of every block boundary"}
+    part.free()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--small", action="store_true", help="scale 20 / 20 / 2048^2 instead of the BASELINE sizes")
+    ap.add_argument("--only", default="pagerank,bfs,sssp")
+    a = ap.parse_args()
+    import sparseharness_b200 as shb
+    g = shb.Group(a.gpus)
+    rc = 0
+    for name in a.only.split(","):
+        if name == "pagerank":
+            r = pagerank(g, 20 if a.small else 26)
+        elif name == "bfs":
+            r = bfs(g, 20 if a.small else 24)
+        else:
+            r = sssp(g, *((2048, 2048) if a.small else (8192, 8192)))
+        print(json.dumps(r), flush=True)
+        rc |= 0 if r["parity_ok"] else 1
+    g.close()
+    return rc
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -30,7 +30,7 @@ int main(int argc, char *argv[]) {
   try {
     if (s.synthetic.empty()) {
       matrix.pagerank_normalise(dampingFactor, 0.0f);
-      args = executorEncodeMatrix(max_alloc, kernel, matrix, 0.0f, x, y, alpha, beta, /*truncate=*/!s.canonical());
+      args = executorEncodeMatrix(max_alloc, kernel, matrix, 0.0f, x, y, alpha, beta, /*truncate=*/!s.canonical(), s.gpu_encode);
     } else {
       args = executorSyntheticArgs(kernel, s.synthetic, matrix.height(), x, y, alpha, beta);
     }

@@ -29,7 +29,7 @@ int main(int argc, char *argv[]) {
   try {
     if (s.synthetic.empty()) {
       matrix.scc_normalise();
-      args = executorEncodeMatrix(max_alloc, kernel, matrix, zero, x, y, alpha, beta);
+      args = executorEncodeMatrix(max_alloc, kernel, matrix, zero, x, y, alpha, beta, true, s.gpu_encode);
     } else {
       args = executorSyntheticArgs(kernel, s.synthetic, matrix.height(), x, y, alpha, beta);
     }

@@ -60,7 +60,7 @@ int main(int argc, char *argv[]) {
 
   ArgContainer<float> args;
   try {
-    args = s.synthetic.empty() ? executorEncodeMatrix(max_alloc, kernel, matrix, 0.0f, x, y, alpha, beta)
+    args = s.synthetic.empty() ? executorEncodeMatrix(max_alloc, kernel, matrix, 0.0f, x, y, alpha, beta, true, s.gpu_encode)
                                : executorSyntheticArgs(kernel, s.synthetic, matrix.height(), x, y, alpha, beta);
   } catch (unsigned long attempted_alloc_size) {
     LOG_ERROR("Attempted to allocate: ", attempted_alloc_size, " bytes, but this platform's max is ", max_alloc);

@@ -12,6 +12,7 @@
 //   --synthetic SPEC            build the operator on the device instead of reading -m:
 //                               uniform:ROWS:K | uniform-int:ROWS:K | rmat:SCALE:EF | rmat-pr:SCALE:EF | grid:W:H
 //   --dump FILE                 write the final output vector (raw little-endian elements) to FILE
+//   --gpu_encode                COO tuples -> CSR on the device (shb_csr_from_coo) instead of the host counting sort
 //   --gpus N                    canonical modes of pr / bfs / sssp: row-partition the operator over the first N
 //                               devices and run the loop through shb_group_* (host/inc/group_app.h)
 //   --symmetric                 with --gpus: the operator equals its transpose (no out-edge copy is built)
@@ -35,7 +36,7 @@
 
 template <typename T> struct HarnessSetup {
   unsigned int platform = 0, device = 0, trials = 10, timeout_ms = 100, max_iterations = 100000, gpus = 1;
-  bool symmetric = false;
+  bool symmetric = false, gpu_encode = false;
   double delta = 0.0001;
   std::string matrix_filename, matrix_name, kernel_filename, runs_filename, hostname, experiment;
   std::string variant = "json", mode = "faithful", synthetic, dump;
@@ -79,6 +80,7 @@ template <typename T> HarnessSetup<T> harness_preamble(int argc, char *argv[]) {
   auto opt_synthetic = op.addOption<std::string>({0, "synthetic", "Device-generated operator instead of -m (uniform:R:K|rmat:S:EF|rmat-pr:S:EF|grid:W:H).", ""});
   auto opt_dump = op.addOption<std::string>({0, "dump", "Write the final output vector to this file (raw elements).", ""});
   auto opt_gpus = op.addOption<unsigned int>({0, "gpus", "Canonical pr/bfs/sssp: row-partition over the first N devices (default 1).", 1});
+  auto opt_gpu_encode = op.addOption<bool>({0, "gpu_encode", "Encode the operator (COO -> CSR) on the device.", false});
   auto opt_symmetric = op.addOption<bool>({0, "symmetric", "With --gpus: the operator equals its transpose.", false});
   op.parse(argc, argv);
 
@@ -102,6 +104,7 @@ template <typename T> HarnessSetup<T> harness_preamble(int argc, char *argv[]) {
   s.dump = opt_dump->get();
   s.gpus = std::max(1u, opt_gpus->get());
   s.symmetric = opt_symmetric->get();
+  s.gpu_encode = opt_gpu_encode->get();
   if (s.mode != "faithful" && s.mode != "canonical") {
     std::cout << "Error: invalid argument for option mode" << ENDL;
     op.usage(argv[0]);

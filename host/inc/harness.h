@@ -15,6 +15,8 @@
 // Error convention is the reference's: any failing device call logs and exit(1)s (device_utils.h).
 #pragma once
 
+#include <type_traits>
+
 #include <chrono>
 #include <cstring>
 #include <iostream>
@@ -231,6 +233,18 @@ private:
   // arguments 0 and 1: CSR from the host arrays, or one of BASELINE's synthetic operators built in HBM
   void createOperator() {
     start_timer(createAndUploadGlobalArg, harness);
+    if (_args.synthetic.empty() && _args.coo) {
+      // --gpu_encode: tuples up, stable sort by row + gather on the device (shb_coo.cu)
+      const SparseMatrix<SemiRingType> &S = *_args.coo;
+      uint64_t ns = 0;
+      checkShbError(shb_csr_from_coo(_ctx, _args.matrix.n_rows, _args.matrix.n_cols, (int64_t)S.storedEntries(),
+                                     S.tupleFirst().data(), S.tupleSecond().data(),
+                                     _args.pattern ? nullptr : (const void *)S.tupleValues().data(),
+                                     std::is_floating_point<SemiRingType>::value ? 0 : 1, _args.coo_truncate ? 1 : 0,
+                                     &_mem_manager._matrix, &ns));
+      report_timing(clEnqueueWriteBuffer, createAndUploadGlobalArg, ns);
+      return;
+    }
     if (_args.synthetic.empty()) {
       const CsrArrays<SemiRingType> &M = _args.matrix;
       uint64_t ns = 0;

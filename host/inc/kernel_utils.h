@@ -50,6 +50,10 @@ public:
   shb_launch_cfg launch = {};
   // when set, the operator is generated on the device (BASELINE configs 2-5) and `matrix` is empty
   std::string synthetic;
+  // --gpu_encode: the tuples go to the device as they are and the CSR is built there (shb_csr_from_coo); `matrix`
+  // then carries the sizes only.  The SparseMatrix outlives the harness (it lives in main).
+  const SparseMatrix<T> *coo = nullptr;
+  bool coo_truncate = true;
 };
 
 // padded height of the reference's cl_encode (src/sparse_matrix.cpp:147-150)
@@ -61,7 +65,7 @@ template <typename T>
 ArgContainer<T> executorEncodeMatrix(uint64_t device_max_alloc_bytes, KernelConfig<T> &kernel, SparseMatrix<T> &matrix,
                                      T zero, XVectorGenerator<T> &xgen, YVectorGenerator<T> &ygen,
                                      T alpha = static_cast<T>(1), T beta = static_cast<T>(1),
-                                     bool truncate_values = true) {
+                                     bool truncate_values = true, bool gpu_encode = false) {
   start_timer(executorEncodeMatrix, kernel_utils);
   (void)zero;  // the ELL padding value; CSR stores no padding entries
   const KernelProperties kprops = kernel.getProperties();
@@ -69,11 +73,18 @@ ArgContainer<T> executorEncodeMatrix(uint64_t device_max_alloc_bytes, KernelConf
   const int cl_height = padded_height(matrix.height(), kprops.chunkSize);
 
   ArgContainer<T> arg_cnt;
-  arg_cnt.matrix = matrix.csr_encode(truncate_values, cl_height);
+  if (gpu_encode) {
+    arg_cnt.coo = &matrix;
+    arg_cnt.coo_truncate = truncate_values;
+    arg_cnt.matrix.n_rows = cl_height;
+    arg_cnt.matrix.n_cols = std::max<int64_t>(matrix.width(), cl_height);
+  } else {
+    arg_cnt.matrix = matrix.csr_encode(truncate_values, cl_height);
+  }
 
   // the reference bails out when the index buffer exceeds the device's max allocation
   // (src/sparse_matrix.cpp:231-233, caught in main)
-  const uint64_t ixs_arr_size = (uint64_t)arg_cnt.matrix.nnz() * sizeof(int32_t) + (uint64_t)(cl_height + 1) * 4;
+  const uint64_t ixs_arr_size = (uint64_t)matrix.storedEntries() * sizeof(int32_t) + (uint64_t)(cl_height + 1) * 4;
   if (ixs_arr_size > device_max_alloc_bytes) throw (unsigned long)ixs_arr_size;
 
   // sizes the Lift kernels take as arguments (inc/kernel_utils.h:57-65).  cl_width is the ELL row

@@ -51,6 +51,10 @@ public:
   int width() const { return cols; }
   int nonZeros() const { return nonz; }
   std::size_t storedEntries() const { return eI.size(); }
+  // the tuple list itself (first index, second index = row, value), for the device-side encode (shb_csr_from_coo)
+  const std::vector<int32_t> &tupleFirst() const { return eI; }
+  const std::vector<int32_t> &tupleSecond() const { return eJ; }
+  const std::vector<EType> &tupleValues() const { return eV; }
 
   // ragged rows exactly as the reference's calculate_ellpack builds them (Q1-Q3); used by the gold loop
   ellpack_matrix<EType> &ellpack_encode() {

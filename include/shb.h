@@ -132,6 +132,13 @@ int shb_host_free_pinned(void *ptr);
 int shb_csr_create(shb_ctx *ctx, int64_t n_rows, int64_t n_cols, int64_t nnz, const int64_t *row_ptr,
                    const int32_t *col_idx, const void *vals /* NULL = pattern */, int elem_bytes,
                    shb_csr **csr, uint64_t *upload_ns);
+/* The same operator from COO tuples, encoded ON THE DEVICE (replaces calculate_ellpack + cl_encode,
+ * src/sparse_matrix.cpp:72-399, with the reference's semantics: tuple k lands in row row_of_entry[k] = the Matrix
+ * Market entry's SECOND index (Q1), keeps the tuple order inside its row (Q3, stable sort, duplicates kept), and
+ * float values pass through int when truncate_through_int (Q2).  elem_kind 0 = float, 1 = int32. */
+int shb_csr_from_coo(shb_ctx *ctx, int64_t n_rows, int64_t n_cols, int64_t n_entries, const int32_t *col_of_entry,
+                     const int32_t *row_of_entry, const void *vals /* NULL = pattern */, int elem_kind,
+                     int truncate_through_int, shb_csr **csr, uint64_t *ns);
 int shb_csr_destroy(shb_csr *csr);
 int shb_csr_get_info(const shb_csr *csr, shb_csr_info *info);
 int shb_csr_download(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int64_t row_count,

@@ -70,6 +70,8 @@ SIGNATURES = {
     "shb_host_free_pinned": (C.c_int, [C.c_void_p]),
     "shb_csr_create": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_int, c_void_pp, u64p]),
+    "shb_csr_from_coo": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                   c_void_pp, u64p]),
     "shb_csr_destroy": (C.c_int, [C.c_void_p]),
     "shb_csr_get_info": (C.c_int, [C.c_void_p, C.POINTER(CsrInfo)]),
     "shb_csr_download": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -191,6 +191,19 @@ class Context:
         _ck(lib.shb_buf_create(self.h, nbytes, C.byref(h)))
         return Buffer(self, h, nbytes)
 
+    def csr_from_coo(self, n_rows, n_cols, col_of_entry, row_of_entry, vals=None, truncate=True) -> "Csr":
+        """COO tuples -> CSR on the device (shb_csr_from_coo): row = the tuple's second index, tuple order kept in a row."""
+        ci = np.ascontiguousarray(col_of_entry, dtype=np.int32)
+        rj = np.ascontiguousarray(row_of_entry, dtype=np.int32)
+        kind = 0
+        if vals is not None:
+            vals = np.ascontiguousarray(vals)
+            assert vals.dtype in (np.float32, np.int32)
+            kind = 0 if vals.dtype == np.float32 else 1
+        h = C.c_void_p()
+        _ck(lib.shb_csr_from_coo(self.h, n_rows, n_cols, len(ci), _ptr(ci), _ptr(rj), _ptr(vals), kind, int(truncate), C.byref(h), None))
+        return Csr(self, h)
+
     def array(self, arr: np.ndarray) -> Buffer:
         arr = np.ascontiguousarray(arr)
         b = self.empty(max(arr.nbytes, 4))

@@ -197,3 +197,38 @@ def test_sweep_scripts_emit_the_reference_result_files(tmp_path, mtx_dir):
     assert {x[0] for x in raw} == set(names)
     assert sum(",MEDIAN_RESULT," in x for x in rows) == len(names) * n_kernels
     assert "PROFILING_DATUM" in (tmp_path / "aggregate_profiling_data.txt").read_text()
+
+
+@pytest.mark.parametrize("name", ["1138_bus", "GD96_b", "arc130", "ca-AstroPh", "Trefethen_20"])
+def test_device_encode_equals_host_encode_and_reference_rows(tmp_path, mtx_dir, name):
+    """COO -> CSR on the device (shb_csr_from_coo, --gpu_encode) builds exactly the rows the
+    reference's loader builds (tests/golden/ref_*.npz, Q1-Q4: row = second index, file order inside a row, values
+    through int) -- float and int operators, chunked kernels' padded heights and both normalisations included."""
+    from test_host_cpu import KERNELS, _parse
+    g = np.load(os.path.join(GOLDEN, f"ref_{name}.npz"))
+    d = _parse(tmp_path, mtx_dir[name], os.path.join(KERNELS, "spmv", "glb-sdp-rsa.json"), extra=["--gpu_encode"])
+    assert np.array_equal(d["rp"], g["f_row_ptr"]) and np.array_equal(d["col"], g["f_col"])
+    assert np.array_equal(d["val"].view(np.int32), g["f_val"].view(np.int32))
+    d = _parse(tmp_path, mtx_dir[name], os.path.join(KERNELS, "bfs", "glb-sdp.json"), elem="int", extra=["--gpu_encode"])
+    assert np.array_equal(d["rp"], g["i_row_ptr"]) and np.array_equal(d["col"], g["i_col"]) and np.array_equal(d["val"], g["i_val"])
+    for elem, norm, kern in (("int", "scc", "scc/swrg-slcl-sdp-chunk-128.json"), ("float", "pr", "pr/glb-sdp.json"),
+                             ("float", "none", "spmv/awrg-alcl-fdp-chunk-rsa-8.json")):
+        path = os.path.join(KERNELS, kern)
+        if not os.path.exists(path):
+            path = os.path.join(KERNELS, "spmv", os.path.basename(kern))
+        host = _parse(tmp_path, mtx_dir[name], path, elem=elem, normalise=norm)
+        dev = _parse(tmp_path, mtx_dir[name], path, elem=elem, normalise=norm, extra=["--gpu_encode"])
+        assert np.array_equal(host["rp"], dev["rp"]) and np.array_equal(host["col"], dev["col"]), (elem, norm)
+        assert np.array_equal(host["val"].view(np.int32), dev["val"].view(np.int32)), (elem, norm)
+    # keep_values (canonical operators): no truncation on either side
+    host = _parse(tmp_path, mtx_dir[name], os.path.join(KERNELS, "spmv", "glb-sdp.json"), extra=["--keep_values"])
+    dev = _parse(tmp_path, mtx_dir[name], os.path.join(KERNELS, "spmv", "glb-sdp.json"), extra=["--keep_values", "--gpu_encode"])
+    assert np.array_equal(host["val"].view(np.int32), dev["val"].view(np.int32)) and np.array_equal(host["col"], dev["col"])
+
+
+def test_spmv_harness_with_device_encode_reports_correct(tmp_path, mtx_dir):
+    """config 1 with --gpu_encode: the rows the device builds from the tuples give the gold's values ("correct")."""
+    r, inserts, dump = run_app("spmv", mtx_dir["1138_bus"], os.path.join(KERNELS, "spmv", "awrg-alcl-fdp-chunk-rsa-8.json"), tmp_path,
+                               "--gpu_encode", trials=2)
+    rows = ROW.findall("\n".join(inserts))
+    assert rows and all(row[1] in ("correct", "statisticvalue") for row in rows) and any(row[1] == "correct" for row in rows)

@@ -220,6 +220,13 @@ int shb_pagerank(shb_ctx *ctx, const shb_csr *A, const shb_launch_cfg *cfg, shb_
                  float x_init, float beta, double delta, uint32_t max_iters, uint32_t check_every,
                  int *result_in_work, shb_graph_stats *stats);
 
+/* Power iteration under plus-times (the eigenvector app; app/eigenvector.cpp:42-137 is dead code in the reference:
+ * x <- A x, at most 10 launches, no normalisation -- that recurrence is shb_iterate with max_iters = 10).  This is
+ * the canonical driver: out = A x_k, s_k = max |out_i|, x_{k+1} = out / s_k, until all |x_{k+1} - x_k| < delta.
+ * x holds x_0 on entry; *eigenvalue = the last s_k (the dominant eigenvalue's magnitude on convergence). */
+int shb_power_iteration(shb_ctx *ctx, const shb_csr *A, const shb_launch_cfg *cfg, shb_buf *x, shb_buf *work, double delta,
+                        uint32_t max_iters, float *eigenvalue, int *result_in_work, shb_graph_stats *stats);
+
 /* ---- synthetic workloads generated on the device (bit-identical to the oracle's
  *      generators so results can be cross-checked) ---------------------------------------------- */
 int shb_synth_uniform(shb_ctx *ctx, int64_t n_rows, int64_t n_cols, int k, uint64_t seed, int val_mode,

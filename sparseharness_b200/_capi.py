@@ -94,6 +94,8 @@ SIGNATURES = {
     "shb_sssp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_uint32, C.POINTER(GraphStats)]),
     "shb_pagerank": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p, C.c_float,
                                C.c_float, C.c_double, C.c_uint32, C.c_uint32, i32p, C.POINTER(GraphStats)]),
+    "shb_power_iteration": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p, C.c_double, C.c_uint32,
+                                      C.POINTER(C.c_float), i32p, C.POINTER(GraphStats)]),
     "shb_synth_uniform": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_uint64, C.c_int, C.c_int64,
                                     C.c_int64, c_void_pp]),
     "shb_synth_vector": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_uint64, C.c_int]),

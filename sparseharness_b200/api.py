@@ -402,10 +402,30 @@ class Context:
         (x if in_work.value else work).free()
         return (work if in_work.value else x), st
 
+    def power_iteration(self, A: Csr, x0: np.ndarray, delta=1e-4, max_iters=10, cfg: LaunchCfg | None = None):
+        """Returns (x_k as numpy, eigenvalue estimate, stats)."""
+        n = A.info.n_rows
+        x, work = self.array(np.ascontiguousarray(x0, dtype=np.float32)), self.empty(max(n, 1) * 4)
+        in_work, ev, st = C.c_int(0), C.c_float(0), GraphStats()
+        s = lib.shb_power_iteration(self.h, A.h, C.byref(cfg) if cfg else None, x.h, work.h, delta, max_iters, C.byref(ev), C.byref(in_work),
+                                    C.byref(st))
+        if s not in (0, 7):
+            raise ShbError(s)
+        res = (work if in_work.value else x).download(np.float32, n)
+        x.free(); work.free()
+        return res, ev.value, st
+
     def close(self):
         if self.h:
             lib.shb_ctx_destroy(self.h)
             self.h = None
+
+
+class _BorrowedCsr(Csr):
+    """A block owned by a GroupPartition: a view for downloads, never destroyed from Python."""
+
+    def free(self):
+        self.h = None
 
 
 class _BorrowedContext(Context):
@@ -435,7 +455,7 @@ class GroupPartition:
         """Borrowed view of block i (for downloads / parity checks); freed with the partition."""
         a = C.c_void_p()
         _ck(lib.shb_gpart_block(self.h, i, C.byref(a), None))
-        return Csr(self.group.ctx(i), a)
+        return _BorrowedCsr(self.group.ctx(i), a)
 
     def free(self):
         if self.h:

@@ -62,7 +62,7 @@ struct shb_pb {
   int32_t *uchunk = nullptr;     // [n_pass * n_prod * n_panel + 1] first chunk of unit (pass, p, panel)
   uint16_t *slot = nullptr;      // [ccap] consumer order: position in the consumer's row-sorted buffer
   int32_t *cons_start = nullptr; // [n_groups * n_prod + 1] start of consumer region (group, s) in `slot`
-  uint16_t *crp = nullptr;       // [(group, s)][RS + 1] local row offsets into the row-sorted buffer
+  uint16_t *crp = nullptr;       // [(group, s)][pb_crp_stride(RS)] local row offsets into the row-sorted buffer
   void *ring = nullptr;          // [depth * (slot_cap + PB_CHUNK)] the product ring
   void *partial = nullptr;       // [n_rows] row sums carried from pass to pass
   uint32_t *sync = nullptr;      // ready[n_groups], consumed[n_groups], exit counter
@@ -70,10 +70,12 @@ struct shb_pb {
   uint64_t device_bytes = 0;
 };
 
-#define PB_THREADS 1024
-#define PB_PROD_THREADS 512
+#define PB_THREADS 768        // launched with 80 registers per thread (768 x 80 = 61440)
+#define PB_PROD_THREADS 256   // two producer warpgroups; setmaxnreg raises them to PB_PROD_REGS (+ 256 x 16 = 4096)
+#define PB_PROD_REGS 96
 #define PB_CONS_THREADS (PB_THREADS - PB_PROD_THREADS)
 #define PB_PROD_WARPS (PB_PROD_THREADS / 32)
+#define PB_CBUF_MAX 12288     // entries of the row-sorted buffer: one round of consumer registers (PB_CU x 512 x 4)
 #define PB_MAX_W 40960
 #define PB_MAX_DEPTH 8
 #define PB_ARR 16  // arrival counters in shared memory (> PB_MAX_DEPTH + 1 panels can be live in one CTA)
@@ -99,6 +101,9 @@ template <class T> struct PbArgs {
   int roles;          // PB_ROLE_* mask (both = the fused kernel; one at a time = the two-launch debug mode)
   int reset_sync;     // zero the counters when the last CTA leaves
 };
+
+// 16-bit words of one unit's row offsets (RS + 1), padded to a 16-byte multiple for cp.async
+__host__ __device__ __forceinline__ int pb_crp_stride(int RS) { return (RS + 1 + 7) & ~7; }
 
 __device__ __forceinline__ void pb_bar(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 __device__ __forceinline__ uint32_t pb_ld_acquire(const uint32_t *p) {
@@ -148,9 +153,10 @@ __device__ __forceinline__ void pb_mbar_wait(uint64_t *bar, uint32_t parity) {
                  : "memory");
 }
 
-// what a producer lane holds of one chunk: 8 local columns, 8 values, the chunk's piece flags
+// what a producer lane holds of one chunk: 8 local columns, 8 values, the chunk's piece flags, then its two deltas
 struct PbStage {
   uint4 lc, v0, v1, d;
+  int d0, d1;
 };
 
 template <bool HAS_VAL, class T>
@@ -164,18 +170,21 @@ __device__ __forceinline__ void pb_stage_load(PbStage &st, const PbArgs<T> &c, i
   st.d = shb_ld_stream_v4<true>(c.chunk_desc + cc, pred, 0u, pol);
 }
 
-// gather, multiply and store one chunk into ring slot `ring` (consumer order)
-template <class S, bool HAS_VAL>
-__device__ __forceinline__ void pb_stage_process(const PbStage &st, const PbArgs<typename S::T> &c, const typename S::T *xs,
-                                                 typename S::T *ring, int cc, int lane) {
-  typedef typename S::T T;
-  // the piece of each of this lane's two quads: pieces started up to and including the quad, minus one
+// the piece of each of the lane's two quads (pieces started up to and including the quad, minus one) and the
+// pieces' deltas: issued one chunk ahead of the stores that need them
+template <class T> __device__ __forceinline__ void pb_stage_deltas(PbStage &st, const PbArgs<T> &c, int lane, bool pred) {
   const uint64_t flags = ((uint64_t)st.d.y << 32) | (uint64_t)st.d.x;
   const int q0 = lane * 2;
-  const int ord0 = (int)st.d.z + __popcll(flags & ((2ull << q0) - 1ull)) - 1;
+  const int ord0 = max(0, (int)st.d.z + __popcll(flags & ((2ull << q0) - 1ull)) - 1);
   const int ord1 = ord0 + (int)((flags >> (q0 + 1)) & 1ull);
-  const int d0 = __ldg(c.delta + ord0);
-  const int d1 = __ldg(c.delta + ord1);
+  st.d0 = pred ? __ldg(c.delta + ord0) : 0;
+  st.d1 = pred ? __ldg(c.delta + ord1) : 0;
+}
+
+// gather, multiply and store one chunk into ring slot `ring` (consumer order)
+template <class S, bool HAS_VAL>
+__device__ __forceinline__ void pb_stage_process(const PbStage &st, const typename S::T *xs, typename S::T *ring, int cc, int lane) {
+  typedef typename S::T T;
   const T x0 = xs[st.lc.x & 0xffffu], x1 = xs[st.lc.x >> 16], x2 = xs[st.lc.y & 0xffffu], x3 = xs[st.lc.y >> 16];
   const T x4 = xs[st.lc.z & 0xffffu], x5 = xs[st.lc.z >> 16], x6 = xs[st.lc.w & 0xffffu], x7 = xs[st.lc.w >> 16];
   uint4 o0, o1;
@@ -188,12 +197,14 @@ __device__ __forceinline__ void pb_stage_process(const PbStage &st, const PbArgs
   o1.z = shb_bits<T>(S::mult(x6, HAS_VAL ? shb_from_bits<T>(st.v1.z) : S::one()));
   o1.w = shb_bits<T>(S::mult(x7, HAS_VAL ? shb_from_bits<T>(st.v1.w) : S::one()));
   const int i0 = cc * PB_CHUNK + lane * 8;  // < 2^31 (checked at build time)
-  pb_st_v4(ring + (i0 + d0), o0);
-  pb_st_v4(ring + (i0 + 4 + d1), o1);
+  pb_st_v4(ring + (i0 + st.d0), o0);
+  pb_st_v4(ring + (i0 + 4 + st.d1), o1);
 }
 
 // ---------------------------------------------------------------------------------------------
-// producer role: PB_PROD_THREADS threads, named barrier 1 (twice per pass, around the x slice load)
+// producer role: PB_PROD_THREADS threads (two warpgroups, 96 registers each after setmaxnreg), named barrier 1
+// (twice per pass, around the x slice load).  Four chunks per warp in flight: loads are issued three chunks ahead,
+// the piece deltas one chunk ahead.
 // ---------------------------------------------------------------------------------------------
 template <class S, bool HAS_VAL>
 __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
@@ -207,6 +218,7 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
   const bool x_aligned = ((reinterpret_cast<uintptr_t>(a.x) & 15u) == 0);
   const bool fused = (c.roles & PB_ROLE_CONSUME) != 0;
   const int64_t slot_stride = (int64_t)c.g.slot_cap + PB_CHUNK;
+  constexpr int NW = PB_PROD_WARPS;
 
   // the warp's arrival at the end of its share of a panel; the CTA's last arrival publishes the panel
   auto arrive = [&](int g) {
@@ -214,7 +226,7 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
     if (lane == 0) {
       __threadfence();
       const uint32_t old = atomicAdd(&arr[g % PB_ARR], 1u);
-      if ((old % PB_PROD_WARPS) == PB_PROD_WARPS - 1) {
+      if ((old % NW) == NW - 1) {
         __threadfence();
         pb_red_release(c.ready + g);
       }
@@ -253,22 +265,26 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
       for (int off = 0; off < bulk; off += 8192) pb_bulk_g2s(xs + off, a.x + c0 + off, (uint32_t)min(8192, bulk - off) * 4u, xbar);
     }
     for (int i = bulk + tid; i < c.g.W; i += PB_PROD_THREADS) xs[i] = i < valid ? a.x[c0 + i] : shb_from_bits<T>(zbits);
-    if (bulk > 0) {
-      pb_mbar_wait(xbar, xphase & 1u);
-      ++xphase;
-    }
-    pb_bar(1, PB_PROD_THREADS);
 
     const int ub = (pass * c.g.n_prod + p) * c.g.n_panel;  // first unit of this (pass, p) stream
     const int g0 = pass * c.g.n_panel;
     const int c_begin = __ldg(c.uchunk + ub), c_end = __ldg(c.uchunk + ub + c.g.n_panel);
     int panel = 0;
-    int ce = __ldg(c.uchunk + ub + 1);                                          // end chunk of the current unit
-    int ce_next = c.g.n_panel > 1 ? __ldg(c.uchunk + ub + 2) : c_end;           // ... and of the one after
+    int ce = __ldg(c.uchunk + ub + 1);                                 // end chunk of the current unit
+    int ce_next = c.g.n_panel > 1 ? __ldg(c.uchunk + ub + 2) : c_end;  // ... and of the one after
     int cc = c_begin + warp;
-    PbStage sa, sb, sc;
-    pb_stage_load<HAS_VAL>(sa, c, cc, cc < c_end, lane, pol_stream);
-    pb_stage_load<HAS_VAL>(sb, c, cc + PB_PROD_WARPS, cc + PB_PROD_WARPS < c_end, lane, pol_stream);
+    // the stream loads of the first three chunks go out while the slice is still landing
+    PbStage s0, s1, s2, s3;
+    pb_stage_load<HAS_VAL>(s0, c, cc, cc < c_end, lane, pol_stream);
+    pb_stage_load<HAS_VAL>(s1, c, cc + NW, cc + NW < c_end, lane, pol_stream);
+    pb_stage_load<HAS_VAL>(s2, c, cc + 2 * NW, cc + 2 * NW < c_end, lane, pol_stream);
+    if (bulk > 0) {
+      pb_mbar_wait(xbar, xphase & 1u);
+      ++xphase;
+    }
+    pb_bar(1, PB_PROD_THREADS);
+    pb_stage_deltas(s0, c, lane, cc < c_end);
+
     bool need_wait = true;
     T *ring = c.ring;
     // move to the unit that holds chunk cc, arriving at every panel left behind
@@ -290,23 +306,22 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
         need_wait = false;
       }
     };
+#define PB_STEP(CUR, NXT, FAR)                                                                          \
+  {                                                                                                     \
+    if (cc >= c_end) break;                                                                             \
+    pb_stage_load<HAS_VAL>(FAR, c, cc + 3 * NW, cc + 3 * NW < c_end, lane, pol_stream);                 \
+    advance();                                                                                          \
+    pb_stage_deltas(NXT, c, lane, cc + NW < c_end);                                                     \
+    pb_stage_process<S, HAS_VAL>(CUR, xs, ring, cc, lane);                                              \
+    cc += NW;                                                                                           \
+  }
     while (true) {
-      if (cc >= c_end) break;
-      pb_stage_load<HAS_VAL>(sc, c, cc + 2 * PB_PROD_WARPS, cc + 2 * PB_PROD_WARPS < c_end, lane, pol_stream);
-      advance();
-      pb_stage_process<S, HAS_VAL>(sa, c, xs, ring, cc, lane);
-      cc += PB_PROD_WARPS;
-      if (cc >= c_end) break;
-      pb_stage_load<HAS_VAL>(sa, c, cc + 2 * PB_PROD_WARPS, cc + 2 * PB_PROD_WARPS < c_end, lane, pol_stream);
-      advance();
-      pb_stage_process<S, HAS_VAL>(sb, c, xs, ring, cc, lane);
-      cc += PB_PROD_WARPS;
-      if (cc >= c_end) break;
-      pb_stage_load<HAS_VAL>(sb, c, cc + 2 * PB_PROD_WARPS, cc + 2 * PB_PROD_WARPS < c_end, lane, pol_stream);
-      advance();
-      pb_stage_process<S, HAS_VAL>(sc, c, xs, ring, cc, lane);
-      cc += PB_PROD_WARPS;
+      PB_STEP(s0, s1, s3)
+      PB_STEP(s1, s2, s0)
+      PB_STEP(s2, s3, s1)
+      PB_STEP(s3, s0, s2)
     }
+#undef PB_STEP
     // the panel of the warp's last chunk, then the panels it has no chunks in
     for (; panel < c.g.n_panel; ++panel) {
       if (need_wait) wait_slot(g0 + panel);
@@ -318,7 +333,10 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
 
 // ---------------------------------------------------------------------------------------------
 // consumer role: PB_CONS_THREADS threads, named barrier 2.
-// Per unit: [poll ready] bar | ring region -> row-sorted buffer | bar | thread per row: sum, store | ...
+// Per unit:  bar | registers -> row-sorted buffer (st.shared per product) | bar | hand the ring slot back |
+//            issue the NEXT unit's ring + slot loads into registers | thread per row: sum, store | ...
+// so the loads of a unit fly while the previous unit is reduced, and the row offsets of a unit arrive by cp.async
+// while the unit before it is scattered.
 // ---------------------------------------------------------------------------------------------
 template <class T> __device__ __forceinline__ void pb_scatter4(T *cbuf, const uint4 &pr, const uint2 &sl) {
   cbuf[sl.x & 0xffffu] = shb_from_bits<T>(pr.x);
@@ -326,83 +344,130 @@ template <class T> __device__ __forceinline__ void pb_scatter4(T *cbuf, const ui
   cbuf[sl.y & 0xffffu] = shb_from_bits<T>(pr.z);
   cbuf[sl.y >> 16] = shb_from_bits<T>(pr.w);
 }
+__device__ __forceinline__ void pb_cp_async16(void *smem_dst, const void *gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pb_smem_addr(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void pb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void pb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+#define PB_CU 6  // quads a consumer thread holds in registers (6 x 512 threads x 4 = 12288 entries per round; 8 spills at 80 registers)
 
 template <class S>
 __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
-                                           typename S::T *cbuf, int tid, bool &differs) {
+                                           typename S::T *cbuf, uint16_t *crp_s, uint32_t *flag_s, int tid, bool &differs) {
   typedef typename S::T T;
   constexpr int NT = PB_CONS_THREADS;
-  constexpr int U = 4;  // quads in flight per thread
+  constexpr int U = PB_CU;
   const int s = blockIdx.x;
   const int n_groups = c.g.n_pass * c.g.n_panel;
   const int64_t slot_stride = (int64_t)c.g.slot_cap + PB_CHUNK;
   const bool fused = (c.roles & PB_ROLE_PRODUCE) != 0;
   const uint64_t pol_stream = shb_policy_evict_first();
-  const int rs1 = c.g.RS + 1;
+  const int stride = pb_crp_stride(c.g.RS);  // 16-bit words per unit, a 16-byte multiple
+
+  uint4 pr[U];
+  uint2 sl[U];
+  // first-round loads of unit (g, cs, ce, gs): up to U quads per thread
+  auto issue = [&](int g, int cs, int ce, int gs) {
+    const T *ring_u = c.ring + (int64_t)(g % c.g.depth) * slot_stride + (cs - gs);
+    const uint16_t *slot_u = c.slot + cs;
+    const int nq = (ce - cs) >> 2;
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const int q = tid + k * NT;
+      if (q < nq) {
+        pr[k] = pb_ld_cg_v4(ring_u + 4 * q);
+        sl[k] = pb_ld_stream_v2(slot_u + 4 * q, pol_stream);
+      }
+    }
+  };
+  auto fetch_crp = [&](int g) {  // row offsets of unit g into its half of crp_s
+    const uint16_t *src = c.crp + ((int64_t)g * c.g.n_prod + s) * stride;
+    uint16_t *dst = crp_s + (g & 1) * stride;
+    for (int i = tid * 8; i < stride; i += NT * 8) pb_cp_async16(dst + i, src + i);
+    pb_cp_async_commit();
+  };
 
   int cs = __ldg(c.cons_start + s), ce = __ldg(c.cons_start + s + 1), gs = __ldg(c.cons_start);
-  uint32_t pre_ready = 0;
+  bool have = false;  // the registers hold the first round of the current unit
+  fetch_crp(0);
   for (int g = 0; g < n_groups; ++g) {
     const int pass = g / c.g.n_panel, panel = g - pass * c.g.n_panel;
     const int64_t u = (int64_t)g * c.g.n_prod + s;
     const int64_t r0 = ((int64_t)panel * c.g.n_prod + s) * c.g.RS;
     const int nr = (int)max((int64_t)0, min((int64_t)c.g.RS, a.n_rows - r0));
-    const uint16_t *crp_u = c.crp + u * rs1;
-    // next unit's extents (their latency hides behind this unit) and L2 prefetch of its streams
+    // next unit's extents (their latency hides behind this unit)
     int cs_n = 0, ce_n = 0, gs_n = 0;
     if (g + 1 < n_groups) {
       cs_n = __ldg(c.cons_start + u + c.g.n_prod);
       ce_n = __ldg(c.cons_start + u + c.g.n_prod + 1);
       gs_n = __ldg(c.cons_start + (int64_t)(g + 1) * c.g.n_prod);
     }
-    // this unit's row offsets and carried sums: towards L2 while the products are scattered
-    for (int i = tid * 64; i < rs1; i += NT * 64) pb_prefetch_l2(crp_u + i);
+    // carried sums of this unit: towards L2 while the products are scattered
     if (pass > 0)
       for (int i = tid * 32; i < nr; i += NT * 32) pb_prefetch_l2(c.partial + r0 + i);
-    if (fused && tid == 0) {
-      if (!(pre_ready >= (uint32_t)c.g.n_prod))
+    if (!have) {
+      if (fused && tid == 0)
         while (pb_ld_acquire(c.ready + g) < (uint32_t)c.g.n_prod) __nanosleep(20);
-      pre_ready = g + 1 < n_groups ? pb_ld_acquire(c.ready + g + 1) : 0u;  // looked at one unit from now
+      pb_bar(2, NT);  // ring slot g is complete (and everyone is done reducing unit g - 1)
+      issue(g, cs, ce, gs);
+    } else {
+      pb_bar(2, NT);  // everyone is done reducing unit g - 1: the row-sorted buffer is free
     }
-    pb_bar(2, NT);  // ring slot g is complete; everyone is done reducing unit g - 1
+    // the next unit's row offsets go into the half unit g - 1 has just stopped reading
+    if (g + 1 < n_groups) fetch_crp(g + 1);
+    else pb_cp_async_commit();  // keeps the group count uniform for the wait below
     {
-      const T *ring_u = c.ring + (int64_t)(g % c.g.depth) * slot_stride + (cs - gs);
-      const uint16_t *slot_u = c.slot + cs;
       const int nq = (ce - cs) >> 2;
-      for (int q0 = tid; q0 < nq; q0 += NT * U) {
-        uint4 pr[U];
-        uint2 sl[U];
 #pragma unroll
-        for (int k = 0; k < U; ++k) {
-          const int q = q0 + k * NT;
-          if (q < nq) {
-            pr[k] = pb_ld_cg_v4(ring_u + 4 * q);
-            sl[k] = pb_ld_stream_v2(slot_u + 4 * q, pol_stream);
-          }
-        }
-#pragma unroll
-        for (int k = 0; k < U; ++k)
-          if (q0 + k * NT < nq) pb_scatter4<T>(cbuf, pr[k], sl[k]);
+      for (int k = 0; k < U; ++k)
+        if (tid + k * NT < nq) pb_scatter4<T>(cbuf, pr[k], sl[k]);
+      if (nq > NT * U) {  // units larger than one round (rare geometries): the rest, round by round
+        const T *ring_u = c.ring + (int64_t)(g % c.g.depth) * slot_stride + (cs - gs);
+        const uint16_t *slot_u = c.slot + cs;
+        for (int q = tid + NT * U; q < nq; q += NT) pb_scatter4<T>(cbuf, pb_ld_cg_v4(ring_u + 4 * q), pb_ld_stream_v2(slot_u + 4 * q, pol_stream));
       }
-      // the next unit's slot stream: towards L2
-      if (g + 1 < n_groups)
-        for (int i = tid * 64; i < ce_n - cs_n; i += NT * 64) pb_prefetch_l2(c.slot + cs_n + i);
     }
+    // is the next unit's ring slot complete already?  one thread looks, the barrier spreads the verdict
+    if (tid == 0) *flag_s = (g + 1 < n_groups && (!fused || pb_ld_acquire(c.ready + g + 1) >= (uint32_t)c.g.n_prod)) ? 1u : 0u;
+    pb_cp_async_wait<1>();  // this unit's row offsets have landed (the next unit's may still be in flight)
     pb_bar(2, NT);
     // the ring slot is drained (its values sit in shared memory): hand it back to the producers
     if (fused && tid == 0) pb_red_release(c.consumed + g);
+    have = *flag_s != 0u;
+    if (have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
     const bool last = pass == c.g.n_pass - 1;
-    for (int i = tid; i < nr; i += NT) {
-      const int b = __ldg(crp_u + i), e = __ldg(crp_u + i + 1);
-      T acc = pass > 0 ? c.partial[r0 + i] : S::zero();
-      for (int k = b; k < e; ++k) acc = S::add(acc, cbuf[k]);
-      if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
-      else c.partial[r0 + i] = acc;
+    const uint16_t *crp_u = crp_s + (g & 1) * stride;
+    constexpr int RPT = 4;  // rows per thread per sweep
+    for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
+      T part[RPT];
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        const int i = i0 + tid + k * NT;
+        part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
+      }
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        const int i = i0 + tid + k * NT;
+        if (i < nr) {
+          const int b = crp_u[i], e = crp_u[i + 1];
+          T acc = part[k];
+          int j = b;
+          for (; j + 3 < e; j += 4) {
+            const T v0 = cbuf[j], v1 = cbuf[j + 1], v2 = cbuf[j + 2], v3 = cbuf[j + 3];
+            acc = S::add(S::add(S::add(S::add(acc, v0), v1), v2), v3);
+          }
+          for (; j < e; ++j) acc = S::add(acc, cbuf[j]);
+          if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
+          else c.partial[r0 + i] = acc;
+        }
+      }
     }
     cs = cs_n;
     ce = ce_n;
     gs = gs_n;
   }
+  pb_cp_async_wait<0>();
 }
 
 template <class S, bool HAS_VAL>
@@ -413,16 +478,20 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   extern __shared__ __align__(16) unsigned char pb_smem[];
   T *xs = reinterpret_cast<T *>(pb_smem);
   T *cbuf = xs + c.g.W;
-  uint32_t *arr = reinterpret_cast<uint32_t *>(cbuf + c.g.cbuf_cap + 32);
-  uint64_t *xbar = reinterpret_cast<uint64_t *>(arr + PB_ARR);
+  uint16_t *crp_s = reinterpret_cast<uint16_t *>(cbuf + c.g.cbuf_cap + 32);
+  uint32_t *arr = reinterpret_cast<uint32_t *>(crp_s + 2 * pb_crp_stride(c.g.RS));
+  uint32_t *flag_s = arr + PB_ARR;
+  uint64_t *xbar = reinterpret_cast<uint64_t *>(arr + PB_ARR + 2);
   if (threadIdx.x < PB_ARR) arr[threadIdx.x] = 0;
   if (threadIdx.x == 0) pb_mbar_init(xbar, 1);
   __syncthreads();
   bool differs = false;
   if (threadIdx.x < PB_PROD_THREADS) {
+    // two producer warpgroups take the registers the launch left over (768 threads x 80 = 61440 of 65536)
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(PB_PROD_REGS));
     if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, threadIdx.x);
   } else {
-    if (c.roles & PB_ROLE_CONSUME) pb_consume<S>(c, a, cbuf, threadIdx.x - PB_PROD_THREADS, differs);
+    if (c.roles & PB_ROLE_CONSUME) pb_consume<S>(c, a, cbuf, crp_s, flag_s, threadIdx.x - PB_PROD_THREADS, differs);
   }
   shb_publish_changed(a.ctl, differs);
   __syncthreads();

@@ -1067,3 +1067,81 @@ SHB_API int shb_spmv_scatter(shb_ctx *c, const shb_csr *A, int semiring, const s
   SHB_TRY(shb_launch_spmv(c, A, semiring, &lcfg, x->ptr, y ? y->ptr : x->ptr, alpha, beta, outs, n_dst, row_offset, ctl));
   return t.finish();
 }
+
+// =================================================================================================
+// Power iteration (the eigenvector app, plus-times; reference: app/eigenvector.cpp:42-137 -- dead code there:
+// x_{k+1} = A x_k with a cap of 10 launches and no normalisation, which shb_iterate with max_iters = 10 reproduces).
+// Canonical driver: out = A x_k; s_k = max_i |out_i|; x_{k+1} = out / s_k; stop when all |x_{k+1} - x_k| < delta.
+// Two small kernels follow each SpMV: the infinity norm (float bits of |v| order like integers: one atomicMax
+// per warp), and ONE fused pass that scales, stores and runs the convergence test.  Everything stays on the device;
+// the host reads two words per iteration batch.
+// =================================================================================================
+__global__ void absmax_kernel(const float *__restrict__ v, int64_t n, uint32_t *out_bits) {
+  uint32_t m = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    m = max(m, __float_as_uint(fabsf(v[i])));
+  for (int off = 16; off > 0; off >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, off));
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(out_bits, m);
+}
+
+__global__ void scale_test_kernel(float *__restrict__ out, const float *__restrict__ x_old, int64_t n, const uint32_t *norm_bits,
+                                  double delta, uint32_t *changed) {
+  const float s = __uint_as_float(*norm_bits);
+  bool differs = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float o = s != 0.0f ? __fdiv_rn(out[i], s) : out[i];
+    out[i] = o;
+    differs |= shb_row_differs(x_old[i], o, delta, SHB_TERM_ABSDIFF);
+  }
+  if (__any_sync(0xffffffffu, differs) && (threadIdx.x & 31) == 0 && shb_ld_volatile_u32(changed) == 0) *changed = 1u;
+}
+
+SHB_API int shb_power_iteration(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, shb_buf *x, shb_buf *work, double delta,
+                                uint32_t max_iters, float *eigenvalue, int *result_in_work, shb_graph_stats *stats) {
+  SHB_REQUIRE(c && A && x && work && result_in_work && max_iters >= 1, "bad arguments");
+  SHB_REQUIRE(A->n_rows == A->n_cols, "Matrix is not square. Failing computation.");
+  SHB_REQUIRE(x->bytes >= (uint64_t)A->n_rows * 4 && work->bytes >= (uint64_t)A->n_rows * 4, "vector shorter than n_rows");
+  SHB_REQUIRE(x->ptr != work->ptr, "x and work must differ");
+  SHB_CUDA(cudaSetDevice(c->device));
+  const int64_t n = A->n_rows;
+  const float alpha = 1.0f, beta = 0.0f;
+  void *bufs[2] = {x->ptr, work->ptr};
+  int in = 0;
+  uint32_t done = 0;
+  bool converged = false;
+  uint32_t norm_bits = 0;
+  IterCtl none;
+  memset(&none, 0, sizeof none);
+  const unsigned grid = grid_for(n, 256, c->prop.multiProcessorCount * 8);
+  SHB_CUDA(cudaEventRecord(c->ev0, c->stream));
+  while (done < max_iters && !converged) {
+    // words 0 / 1 of the context's flag scratch: the norm bits and the "some element moved" flag
+    SHB_CUDA(cudaMemsetAsync(c->d_flags, 0, 2 * sizeof(uint32_t), c->stream));
+    void *outs[1] = {bufs[in ^ 1]};
+    SHB_TRY(shb_launch_spmv(c, A, SHB_PLUS_TIMES_F32, cfg, bufs[in], bufs[in], &alpha, &beta, outs, 1, 0, none));
+    absmax_kernel<<<grid, 256, 0, c->stream>>>((const float *)bufs[in ^ 1], n, c->d_flags);
+    scale_test_kernel<<<grid, 256, 0, c->stream>>>((float *)bufs[in ^ 1], (const float *)bufs[in], n, c->d_flags, delta, c->d_flags + 1);
+    SHB_CUDA(cudaGetLastError());
+    SHB_CUDA(cudaMemcpyAsync(c->h_flags, c->d_flags, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    SHB_CUDA(cudaStreamSynchronize(c->stream));
+    norm_bits = c->h_flags[0];
+    converged = c->h_flags[1] == 0;
+    in ^= 1;
+    ++done;
+  }
+  SHB_CUDA(cudaEventRecord(c->ev1, c->stream));
+  SHB_CUDA(cudaEventSynchronize(c->ev1));
+  float ms = 0.f;
+  SHB_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+  *result_in_work = in;
+  if (eigenvalue) memcpy(eigenvalue, &norm_bits, 4);
+  if (stats) {
+    stats->iterations = done;
+    stats->converged = converged;
+    stats->edges_traversed = (int64_t)A->nnz * (int64_t)done;
+    stats->reached = n;
+    stats->total_ns = (uint64_t)((double)ms * 1.0e6 + 0.5);
+    stats->launches = (uint64_t)done * 3;
+  }
+  return converged ? SHB_OK : SHB_ERR_NOT_CONVERGED;
+}

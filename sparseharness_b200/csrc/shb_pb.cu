@@ -77,10 +77,11 @@ __global__ void pb_scatter_kernel(PbGeom g, const uint32_t *sorted_keys, const u
 
 // row offsets of every consumer unit (and the largest unit)
 __global__ void pb_crp_kernel(PbGeom g, const int32_t *bound2, int64_t n_cons_units, uint16_t *crp, int32_t *max_unit) {
-  const int64_t total = n_cons_units * (g.RS + 1);
+  const int stride = pb_crp_stride(g.RS);
+  const int64_t total = n_cons_units * stride;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t unit = t / (g.RS + 1);
-    const int i = (int)(t - unit * (g.RS + 1));
+    const int64_t unit = t / stride;
+    const int i = min((int)(t - unit * stride), g.RS);  // the padding words repeat the unit's end
     const int off = bound2[unit * g.RS + i] - bound2[unit * g.RS];
     crp[t] = (uint16_t)min(off, 65535);
     if (i == g.RS) atomicMax(max_unit, off);
@@ -116,7 +117,9 @@ void shb_pb_free(shb_pb *pb) {
   delete pb;
 }
 
-static size_t pb_smem_bytes(const PbGeom &g) { return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + PB_ARR * 4 + 16; }
+static size_t pb_smem_bytes(const PbGeom &g) {
+  return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + (size_t)pb_crp_stride(g.RS) * 2 * 2 + PB_ARR * 4 + 8 + 16;
+}
 
 SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer, int make_default) {
   SHB_REQUIRE(c && A, "bad arguments");
@@ -139,8 +142,10 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   // rows per consumer: a consumer unit (RS rows x mean row length / n_pass valid entries, 4 bytes each) takes the
   // shared memory the x slice leaves; the margin covers the spread of the unit sizes (checked below)
   const double per_row = std::max(0.25, (double)A->nnz / (double)A->n_rows / g.n_pass);
-  const double free_entries = std::min(60000.0, ((double)PB_SMEM_LIMIT - 2048.0 - (double)g.W * 4) / 4.0);
-  int rs = rows_per_consumer > 0 ? rows_per_consumer : (int)std::min(32768.0, std::max(32.0, free_entries / (per_row * 1.03 + 0.1) - 64.0));
+  // ... and one round of the consumer's registers (PB_CBUF_MAX entries); the row offsets (2 x 2 bytes per row) share the space
+  const double free_entries = std::min((double)PB_CBUF_MAX, ((double)PB_SMEM_LIMIT - 2048.0 - (double)g.W * 4) / 4.0);
+  int rs = rows_per_consumer > 0 ? rows_per_consumer
+                                 : (int)std::min(32768.0, std::max(32.0, free_entries / (per_row * 1.03 + 0.1 + 1.0) - 64.0));
   g.n_panel = (int)((A->n_rows + (int64_t)g.n_prod * rs - 1) / ((int64_t)g.n_prod * rs));
   g.RS = (int)((A->n_rows + (int64_t)g.n_prod * g.n_panel - 1) / ((int64_t)g.n_prod * g.n_panel));
   SHB_REQUIRE(g.RS <= 65535, "rows_per_consumer too large");
@@ -289,7 +294,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     PB_CUDA(cudaMalloc(&pb->delta, h_delta.size() * 4));
     PB_CUDA(cudaMalloc(&pb->uchunk, (size_t)(n_units + 1) * 4));
     PB_CUDA(cudaMalloc(&pb->cons_start, (size_t)(n_units + 1) * 4));
-    PB_CUDA(cudaMalloc(&pb->crp, (size_t)n_units * (g.RS + 1) * 2));
+    PB_CUDA(cudaMalloc(&pb->crp, (size_t)n_units * pb_crp_stride(g.RS) * 2));
     PB_CUDA(cudaMalloc(&pb->partial, (size_t)A->n_rows * 4));
     PB_CUDA(cudaMalloc(&pb->sync, (size_t)(2 * n_groups + 1) * 4));
     PB_CUDA(cudaMemsetAsync(pb->sync, 0, (size_t)(2 * n_groups + 1) * 4, c->stream));
@@ -313,7 +318,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     } else {
       PB_CUDA(cudaMemsetAsync(bound2, 0, (size_t)(n_keys2 + 1) * 4, c->stream));
     }
-    pb_crp_kernel<<<(unsigned)std::min<int64_t>((n_units * (g.RS + 1) + 255) / 256, cap_blocks), 256, 0, c->stream>>>(
+    pb_crp_kernel<<<(unsigned)std::min<int64_t>((n_units * pb_crp_stride(g.RS) + 255) / 256, cap_blocks), 256, 0, c->stream>>>(
         g, bound2, n_units, pb->crp, d_max);
     PB_CUDA(cudaGetLastError());
     PB_CUDA(cudaMemcpyAsync(&pb->max_unit, d_max, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -341,7 +346,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     pb->ring_depth_alloc = g.depth;
     pb->g = g;
     pb->device_bytes = (uint64_t)pb->cap * (2 + (A->val ? 4 : 0)) + (uint64_t)pb->ccap * 2 + h_desc.size() * 16 + h_delta.size() * 4 +
-                       (uint64_t)(n_units + 1) * 8 + (uint64_t)n_units * (g.RS + 1) * 2 +
+                       (uint64_t)(n_units + 1) * 8 + (uint64_t)n_units * pb_crp_stride(g.RS) * 2 +
                        (uint64_t)g.depth * ((uint64_t)g.slot_cap + PB_CHUNK) * 4 + (uint64_t)A->n_rows * 4;
   }
 done:

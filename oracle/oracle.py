@@ -194,6 +194,18 @@ def pagerank(row_ptr, col, val, damping=0.85, delta=1e-4, max_iters=1000, acc_do
     return res, int(it)
 
 
+def power_iteration(row_ptr, col, val, x0, delta=1e-4, max_iters=10, order=0):
+    """Canonical eigenvector driver: (x_k, eigenvalue estimate, iterations)."""
+    n = len(row_ptr) - 1
+    row_ptr = _c(row_ptr, np.int64); col = _c(col, np.int32); val = _c(val, np.float32); x0 = _c(x0, np.float32)
+    res = np.empty(n, dtype=np.float32)
+    ev = C.c_float(0)
+    f = lib().orc_power_iteration
+    f.restype = C.c_int64
+    it = f(C.c_int64(n), _p(row_ptr), _p(col), _p(val), _p(x0), C.c_double(delta), C.c_int64(max_iters), order, _p(res), C.byref(ev))
+    return res, float(ev.value), int(it)
+
+
 def pagerank_values(row_ptr, col, damping=0.85):
     n = len(row_ptr) - 1
     row_ptr = _c(row_ptr, np.int64); col = _c(col, np.int32)

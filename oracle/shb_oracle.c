@@ -562,6 +562,43 @@ ORC_API int64_t orc_pagerank(int64_t n, const int64_t *row_ptr, const int32_t *c
   return it;
 }
 
+/* Power iteration (canonical mode of the eigenvector app; the reference's own driver, app/eigenvector.cpp:42-137, is
+ * dead code: x <- A x, at most 10 launches, no normalisation -- that is orc_iterate with max_iters = 10).
+ *   out = A x_k   (plus-times kernel loop, alpha 1, beta 0; `order` as orc_spmv_f32)
+ *   s_k = max_i |out_i| ;  x_{k+1} = out / s_k  (left as it is when s_k == 0)
+ * until all |x_{k+1} - x_k| < delta (float subtract, double compare, as app/sssp.cpp:170) or max_iters.
+ * Returns the iterations run; *eigen = the last s_k. */
+ORC_API int64_t orc_power_iteration(int64_t n, const int64_t *row_ptr, const int32_t *col, const float *val, const float *x0,
+                                    double delta, int64_t max_iters, int order, float *result, float *eigen) {
+  float *a = (float *)malloc(sizeof(float) * (size_t)(n > 0 ? n : 1)), *b = (float *)malloc(sizeof(float) * (size_t)(n > 0 ? n : 1));
+  memcpy(a, x0, sizeof(float) * (size_t)n);
+  float *in = a, *out = b, s = 0.0f;
+  int64_t it = 0;
+  int stop = 0;
+  do {
+    orc_spmv_f32(ORC_PLUS_TIMES, n, n, row_ptr, col, val, in, in, 1.0f, 0.0f, out, order, 1);
+    s = 0.0f;
+    for (int64_t i = 0; i < n; ++i) {
+      const float m = fabsf(out[i]);
+      if (m > s) s = m;
+    }
+    int changed = 0;
+    for (int64_t i = 0; i < n; ++i) {
+      const float o = s != 0.0f ? out[i] / s : out[i];
+      out[i] = o;
+      const float d = in[i] - o;
+      if (!(fabs((double)d) < delta)) changed = 1;
+    }
+    stop = !changed;
+    float *t = in; in = out; out = t;
+    ++it;
+  } while (!stop && it < max_iters);
+  memcpy(result, in, sizeof(float) * (size_t)n);
+  if (eigen) *eigen = s;
+  free(a); free(b);
+  return it;
+}
+
 /* ------------------------------------------------------------------------------------------
  * Synthetic workloads.  The same integer hash arithmetic is used by the device
  * generators in sparseharness_b200/csrc/synth.cu so that tests can compare the two bit for bit.

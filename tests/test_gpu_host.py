@@ -232,3 +232,22 @@ def test_spmv_harness_with_device_encode_reports_correct(tmp_path, mtx_dir):
                                "--gpu_encode", trials=2)
     rows = ROW.findall("\n".join(inserts))
     assert rows and all(row[1] in ("correct", "statisticvalue") for row in rows) and any(row[1] == "correct" for row in rows)
+
+
+def test_eigenvector_harness_faithful_and_canonical(tmp_path, mtx_dir, orc):
+    """eigenvector_harness (dead code in the reference, app/eigenvector.cpp:42-137): faithful = x <- A x capped at 10
+    launches; canonical = normalised power iteration.  Both against the oracle."""
+    kern = os.path.join(KERNELS, "spmv", "glb-sdp-rsa.json")
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir["Trefethen_20"], "float")
+    x0 = np.ones(n, np.float32)
+    r, inserts, dump = run_app("eigenvector", mtx_dir["Trefethen_20"], kern, tmp_path, trials=1)
+    want, wit = orc.iterate(orc.PLUS_TIMES, rp, col, val, x0, np.zeros(n, np.float32), 1.0, 0.0, delta=1e-4, max_iters=10)
+    got = np.fromfile(dump, np.float32)
+    assert wit == 10 and "Iterations: 10" in r.stdout and np.array_equal(got[:n].view(np.uint32), want.view(np.uint32))
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir["Trefethen_20"], "float", truncate=False)
+    r, inserts, dump = run_app("eigenvector", mtx_dir["Trefethen_20"], kern, tmp_path, "--mode", "canonical", "--variant", "scalar",
+                               "--max_iterations", "200", "-c", "1e-6", trials=1)
+    want, wev, wit = orc.power_iteration(rp, col, val, x0, delta=1e-6, max_iters=200)
+    got = np.fromfile(dump, np.float32)
+    assert f"iterations {wit}," in r.stdout and np.array_equal(got[:n].view(np.uint32), want.view(np.uint32))
+    assert "Dominant eigenvalue estimate:" in r.stdout

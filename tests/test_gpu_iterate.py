@@ -264,3 +264,31 @@ def test_bfs_pull_mappings_agree(ctx, orc):
     assert len(lines) == 2
     for digest, iters in lines:
         assert digest == hashlib.sha256(want.astype(np.int32).tobytes()).hexdigest() and int(iters) == nlev
+
+
+def test_power_iteration_matches_oracle(ctx, orc, mtx_dir):
+    """Canonical eigenvector driver (shb_power_iteration): SpMV, infinity norm, fused scale + convergence test, all on
+    the device.  SCALAR schedule == the oracle's loop bit for bit (same adds, same IEEE divide); the default schedule
+    to 1e-5; the eigenvalue estimate is the oracle's."""
+    rp, col, val = orc.gen_uniform(5000, 5000, 12, val_mode=1)
+    val = (np.abs(val) + 1).astype(np.float32)
+    n = len(rp) - 1
+    A = ctx.csr(n, n, rp, col, val)
+    x0 = np.ones(n, np.float32)
+    want, wev, wit = orc.power_iteration(rp, col, val, x0, delta=1e-5, max_iters=100)
+    got, ev, st = ctx.power_iteration(A, x0, delta=1e-5, max_iters=100, cfg=shb.launch_cfg(variant=shb.VARIANT_SCALAR))
+    assert st.converged and st.iterations == wit and ev == np.float32(wev)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    got, ev, st = ctx.power_iteration(A, x0, delta=1e-5, max_iters=100)
+    assert st.converged and abs(int(st.iterations) - wit) <= 1 and abs(ev - wev) <= 1e-5 * wev
+    assert np.abs(got - want).max() <= 1e-4
+    # the cap: 3 iterations, not converged, still the oracle's vector
+    want3, _, wit3 = orc.power_iteration(rp, col, val, x0, delta=1e-9, max_iters=3)
+    got3, _, st3 = ctx.power_iteration(A, x0, delta=1e-9, max_iters=3, cfg=shb.launch_cfg(variant=shb.VARIANT_SCALAR))
+    assert wit3 == 3 and st3.iterations == 3 and not st3.converged and np.array_equal(got3.view(np.uint32), want3.view(np.uint32))
+    # a fixture through the reference's loader (integer-valued): every schedule bit for bit
+    n, _, rp, col, val = orc.mm_load_csr(mtx_dir["Trefethen_20"], "float")
+    A = ctx.csr(n, n, rp, col, val)
+    want, wev, wit = orc.power_iteration(rp, col, val, np.ones(n, np.float32), delta=1e-4, max_iters=10)
+    got, ev, st = ctx.power_iteration(A, np.ones(n, np.float32), delta=1e-4, max_iters=10, cfg=shb.launch_cfg(variant=shb.VARIANT_SCALAR))
+    assert st.iterations == wit and np.array_equal(got.view(np.uint32), want.view(np.uint32)) and ev == np.float32(wev)

@@ -70,9 +70,10 @@ struct shb_pb {
   uint64_t device_bytes = 0;
 };
 
-#define PB_THREADS 768        // launched with 80 registers per thread (768 x 80 = 61440)
-#define PB_PROD_THREADS 256   // two producer warpgroups; setmaxnreg raises them to PB_PROD_REGS (+ 256 x 16 = 4096)
+#define PB_THREADS 768        // launched with 80 registers per thread (768 x 80 = 61440: the CTA's pool)
+#define PB_PROD_THREADS 256   // two producer warpgroups; setmaxnreg moves 4096 registers from the consumers to them
 #define PB_PROD_REGS 96
+#define PB_CONS_REGS 72
 #define PB_CONS_THREADS (PB_THREADS - PB_PROD_THREADS)
 #define PB_PROD_WARPS (PB_PROD_THREADS / 32)
 #define PB_CBUF_MAX 12288     // entries of the row-sorted buffer: one round of consumer registers (PB_CU x 512 x 4)
@@ -487,10 +488,12 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   __syncthreads();
   bool differs = false;
   if (threadIdx.x < PB_PROD_THREADS) {
-    // two producer warpgroups take the registers the launch left over (768 threads x 80 = 61440 of 65536)
+    // the CTA's register pool is fixed at launch (768 threads x 80): the four consumer warpgroups hand 8 registers per
+    // thread back (512 x 8 = 4096) and the two producer warpgroups take them (256 x 16 = 4096); inc blocks until then
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(PB_PROD_REGS));
     if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, threadIdx.x);
   } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PB_CONS_REGS));
     if (c.roles & PB_ROLE_CONSUME) pb_consume<S>(c, a, cbuf, crp_s, flag_s, threadIdx.x - PB_PROD_THREADS, differs);
   }
   shb_publish_changed(a.ctl, differs);

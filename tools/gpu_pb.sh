@@ -2,8 +2,9 @@
 # Blocked-schedule call: parity tests that include the blocked variant, then timing under a few geometries,
 # the two roles alone (SHB_PB_SPLIT=p / c); then the new group / panel tests.
 mkdir -p gpurun_out
-echo "== pytest spmv"; timeout 240 python -m pytest tests/test_gpu_spmv.py -m gpu -x -q --timeout 60 2>&1 | tail -8
-[ "$(tail -1 gpurun_out/pytest_spmv.txt 2>/dev/null | grep -c failed)" = "0" ] || true
+echo "== pytest spmv"; timeout 240 python -m pytest tests/test_gpu_spmv.py -m gpu -x -q --timeout 60 > gpurun_out/pytest_spmv.txt 2>&1
+rc=$?; tail -8 gpurun_out/pytest_spmv.txt
+if [ $rc -ne 0 ]; then echo "parity tests failed or hung (rc=$rc): no timing"; exit 1; fi
 echo "== default"; timeout 100 python tools/pb_bench.py --rs 0 2>&1 | cut -c1-400
 for d in ${DEPTHS:-2}; do
 echo "== depth $d"; SHB_PB_DEPTH=$d timeout 100 python tools/pb_bench.py --rs 0 --only-blocked 2>&1 | grep "blocked\|Error" | cut -c1-330

@@ -77,7 +77,7 @@ struct shb_pb {
 #define PB_CONS_THREADS (PB_THREADS - PB_PROD_THREADS)
 #define PB_PROD_WARPS (PB_PROD_THREADS / 32)
 #define PB_CBUF_MAX 12288     // entries of the row-sorted buffer: one round of consumer registers (PB_CU x 512 x 4)
-#define PB_MAX_W 40960
+#define PB_MAX_W 30720
 #define PB_MAX_DEPTH 8
 #define PB_ARR 16  // arrival counters in shared memory (> PB_MAX_DEPTH + 1 panels can be live in one CTA)
 #define PB_SMEM_LIMIT (227 * 1024)
@@ -154,62 +154,84 @@ __device__ __forceinline__ void pb_mbar_wait(uint64_t *bar, uint32_t parity) {
                  : "memory");
 }
 
-// what a producer lane holds of one chunk: 8 local columns, 8 values, the chunk's piece flags, then its two deltas
-struct PbStage {
-  uint4 lc, v0, v1, d;
-  int d0, d1;
-};
+// ---- the producer's stream pipeline: cp.async into a per-warp ring of PB_STAGES chunk slots --------------------------
+// Register-staged loads do not pipeline here: ptxas has six scoreboards per warp, the loads of several chunks in flight
+// end up sharing one, and the wait for the oldest chunk then waits for the newest (measured: one memory round trip per
+// chunk whatever the depth).  cp.async completes in per-thread commit groups instead: `wait_group<N>` is a FIFO.
+// Slot layout (PB_STAGE_BYTES): [32 lanes x 16 B local columns][32 x 16 B values 0-3][32 x 16 B values 4-7][16 B flags];
+// every lane copies and later reads ITS OWN 16-byte words (conflict-free LDS.128), lane 0 copies the chunk's flag word.
+#define PB_STAGES 4
+#define PB_STAGE_BYTES 1552
+
+__device__ __forceinline__ void pb_cp_async16_hint(void *smem_dst, const void *gmem_src, uint64_t pol) {
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(pb_smem_addr(smem_dst)), "l"(gmem_src), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ void pb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void pb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <bool HAS_VAL, class T>
-__device__ __forceinline__ void pb_stage_load(PbStage &st, const PbArgs<T> &c, int cc, bool pred, int lane, uint64_t pol) {
-  const int64_t i0 = (int64_t)cc * PB_CHUNK + lane * 8;
-  st.lc = shb_ld_stream_v4<true>(c.lcol + i0, pred, 0u, pol);
-  if (HAS_VAL) {
-    st.v0 = shb_ld_stream_v4<true>(c.val + i0, pred, 0u, pol);
-    st.v1 = shb_ld_stream_v4<true>(c.val + i0 + 4, pred, 0u, pol);
+__device__ __forceinline__ void pb_stage_issue(unsigned char *st, const PbArgs<T> &c, int cc, bool pred, int lane, uint64_t pol) {
+  if (pred) {
+    const int64_t i0 = (int64_t)cc * PB_CHUNK + lane * 8;
+    pb_cp_async16_hint(st + lane * 16, c.lcol + i0, pol);
+    if (HAS_VAL) {
+      pb_cp_async16_hint(st + 512 + lane * 16, c.val + i0, pol);
+      pb_cp_async16_hint(st + 1024 + lane * 16, c.val + i0 + 4, pol);
+    }
+    if (lane == 0) pb_cp_async16_hint(st + 1536, c.chunk_desc + cc, pol);
   }
-  st.d = shb_ld_stream_v4<true>(c.chunk_desc + cc, pred, 0u, pol);
+  pb_cp_async_commit();  // one group per step, empty or not: the wait below counts groups
 }
 
 // the piece of each of the lane's two quads (pieces started up to and including the quad, minus one) and the
 // pieces' deltas: issued one chunk ahead of the stores that need them
-template <class T> __device__ __forceinline__ void pb_stage_deltas(PbStage &st, const PbArgs<T> &c, int lane, bool pred) {
-  const uint64_t flags = ((uint64_t)st.d.y << 32) | (uint64_t)st.d.x;
+template <class T>
+__device__ __forceinline__ void pb_stage_deltas(const unsigned char *st, const PbArgs<T> &c, int lane, bool pred, int &d0, int &d1) {
+  const uint4 d = *reinterpret_cast<const uint4 *>(st + 1536);
+  const uint64_t flags = ((uint64_t)d.y << 32) | (uint64_t)d.x;
   const int q0 = lane * 2;
-  const int ord0 = max(0, (int)st.d.z + __popcll(flags & ((2ull << q0) - 1ull)) - 1);
+  const int ord0 = max(0, (int)d.z + __popcll(flags & ((2ull << q0) - 1ull)) - 1);
   const int ord1 = ord0 + (int)((flags >> (q0 + 1)) & 1ull);
-  st.d0 = pred ? __ldg(c.delta + ord0) : 0;
-  st.d1 = pred ? __ldg(c.delta + ord1) : 0;
+  d0 = pred ? __ldg(c.delta + ord0) : 0;
+  d1 = pred ? __ldg(c.delta + ord1) : 0;
 }
 
 // gather, multiply and store one chunk into ring slot `ring` (consumer order)
 template <class S, bool HAS_VAL>
-__device__ __forceinline__ void pb_stage_process(const PbStage &st, const typename S::T *xs, typename S::T *ring, int cc, int lane) {
+__device__ __forceinline__ void pb_stage_process(const unsigned char *st, const typename S::T *xs, typename S::T *ring, int cc,
+                                                 int lane, int d0, int d1) {
   typedef typename S::T T;
-  const T x0 = xs[st.lc.x & 0xffffu], x1 = xs[st.lc.x >> 16], x2 = xs[st.lc.y & 0xffffu], x3 = xs[st.lc.y >> 16];
-  const T x4 = xs[st.lc.z & 0xffffu], x5 = xs[st.lc.z >> 16], x6 = xs[st.lc.w & 0xffffu], x7 = xs[st.lc.w >> 16];
+  const uint4 lc = *reinterpret_cast<const uint4 *>(st + lane * 16);
+  uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
+  if (HAS_VAL) {
+    v0 = *reinterpret_cast<const uint4 *>(st + 512 + lane * 16);
+    v1 = *reinterpret_cast<const uint4 *>(st + 1024 + lane * 16);
+  }
+  const T x0 = xs[lc.x & 0xffffu], x1 = xs[lc.x >> 16], x2 = xs[lc.y & 0xffffu], x3 = xs[lc.y >> 16];
+  const T x4 = xs[lc.z & 0xffffu], x5 = xs[lc.z >> 16], x6 = xs[lc.w & 0xffffu], x7 = xs[lc.w >> 16];
   uint4 o0, o1;
-  o0.x = shb_bits<T>(S::mult(x0, HAS_VAL ? shb_from_bits<T>(st.v0.x) : S::one()));
-  o0.y = shb_bits<T>(S::mult(x1, HAS_VAL ? shb_from_bits<T>(st.v0.y) : S::one()));
-  o0.z = shb_bits<T>(S::mult(x2, HAS_VAL ? shb_from_bits<T>(st.v0.z) : S::one()));
-  o0.w = shb_bits<T>(S::mult(x3, HAS_VAL ? shb_from_bits<T>(st.v0.w) : S::one()));
-  o1.x = shb_bits<T>(S::mult(x4, HAS_VAL ? shb_from_bits<T>(st.v1.x) : S::one()));
-  o1.y = shb_bits<T>(S::mult(x5, HAS_VAL ? shb_from_bits<T>(st.v1.y) : S::one()));
-  o1.z = shb_bits<T>(S::mult(x6, HAS_VAL ? shb_from_bits<T>(st.v1.z) : S::one()));
-  o1.w = shb_bits<T>(S::mult(x7, HAS_VAL ? shb_from_bits<T>(st.v1.w) : S::one()));
+  o0.x = shb_bits<T>(S::mult(x0, HAS_VAL ? shb_from_bits<T>(v0.x) : S::one()));
+  o0.y = shb_bits<T>(S::mult(x1, HAS_VAL ? shb_from_bits<T>(v0.y) : S::one()));
+  o0.z = shb_bits<T>(S::mult(x2, HAS_VAL ? shb_from_bits<T>(v0.z) : S::one()));
+  o0.w = shb_bits<T>(S::mult(x3, HAS_VAL ? shb_from_bits<T>(v0.w) : S::one()));
+  o1.x = shb_bits<T>(S::mult(x4, HAS_VAL ? shb_from_bits<T>(v1.x) : S::one()));
+  o1.y = shb_bits<T>(S::mult(x5, HAS_VAL ? shb_from_bits<T>(v1.y) : S::one()));
+  o1.z = shb_bits<T>(S::mult(x6, HAS_VAL ? shb_from_bits<T>(v1.z) : S::one()));
+  o1.w = shb_bits<T>(S::mult(x7, HAS_VAL ? shb_from_bits<T>(v1.w) : S::one()));
   const int i0 = cc * PB_CHUNK + lane * 8;  // < 2^31 (checked at build time)
-  pb_st_v4(ring + (i0 + st.d0), o0);
-  pb_st_v4(ring + (i0 + 4 + st.d1), o1);
+  pb_st_v4(ring + (i0 + d0), o0);
+  pb_st_v4(ring + (i0 + 4 + d1), o1);
 }
 
 // ---------------------------------------------------------------------------------------------
-// producer role: PB_PROD_THREADS threads (two warpgroups, 96 registers each after setmaxnreg), named barrier 1
-// (twice per pass, around the x slice load).  Four chunks per warp in flight: loads are issued three chunks ahead,
-// the piece deltas one chunk ahead.
+// producer role: PB_PROD_THREADS threads (two warpgroups), named barrier 1 (twice per pass, around the x slice
+// load).  Per warp: the streams of chunks k+2 and k+3 are in flight, chunk k+1 has landed and its deltas are being
+// fetched, chunk k is gathered, multiplied and stored.
 // ---------------------------------------------------------------------------------------------
 template <class S, bool HAS_VAL>
 __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
-                                           typename S::T *xs, uint32_t *arr, uint64_t *xbar, int tid) {
+                                           typename S::T *xs, uint32_t *arr, uint64_t *xbar, unsigned char *pstage, int tid) {
   typedef typename S::T T;
   const int p = blockIdx.x;
   uint32_t xphase = 0;  // completed phases of the x-slice mbarrier
@@ -220,6 +242,7 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
   const bool fused = (c.roles & PB_ROLE_CONSUME) != 0;
   const int64_t slot_stride = (int64_t)c.g.slot_cap + PB_CHUNK;
   constexpr int NW = PB_PROD_WARPS;
+  unsigned char *const wst = pstage + (size_t)warp * PB_STAGES * PB_STAGE_BYTES;  // this warp's ring of chunk slots
 
   // the warp's arrival at the end of its share of a panel; the CTA's last arrival publishes the panel
   auto arrive = [&](int g) {
@@ -274,17 +297,19 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
     int ce = __ldg(c.uchunk + ub + 1);                                 // end chunk of the current unit
     int ce_next = c.g.n_panel > 1 ? __ldg(c.uchunk + ub + 2) : c_end;  // ... and of the one after
     int cc = c_begin + warp;
-    // the stream loads of the first three chunks go out while the slice is still landing
-    PbStage s0, s1, s2, s3;
-    pb_stage_load<HAS_VAL>(s0, c, cc, cc < c_end, lane, pol_stream);
-    pb_stage_load<HAS_VAL>(s1, c, cc + NW, cc + NW < c_end, lane, pol_stream);
-    pb_stage_load<HAS_VAL>(s2, c, cc + 2 * NW, cc + 2 * NW < c_end, lane, pol_stream);
+    // the streams of the first three chunks go out while the slice is still landing
+    pb_stage_issue<HAS_VAL>(wst + 0 * PB_STAGE_BYTES, c, cc, cc < c_end, lane, pol_stream);
+    pb_stage_issue<HAS_VAL>(wst + 1 * PB_STAGE_BYTES, c, cc + NW, cc + NW < c_end, lane, pol_stream);
+    pb_stage_issue<HAS_VAL>(wst + 2 * PB_STAGE_BYTES, c, cc + 2 * NW, cc + 2 * NW < c_end, lane, pol_stream);
     if (bulk > 0) {
       pb_mbar_wait(xbar, xphase & 1u);
       ++xphase;
     }
     pb_bar(1, PB_PROD_THREADS);
-    pb_stage_deltas(s0, c, lane, cc < c_end);
+    int d0 = 0, d1 = 0;  // deltas of the chunk about to be processed
+    pb_cp_async_wait<2>();  // the first chunk has landed
+    __syncwarp();
+    pb_stage_deltas(wst, c, lane, cc < c_end, d0, d1);
 
     bool need_wait = true;
     T *ring = c.ring;
@@ -307,22 +332,22 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
         need_wait = false;
       }
     };
-#define PB_STEP(CUR, NXT, FAR)                                                                          \
-  {                                                                                                     \
-    if (cc >= c_end) break;                                                                             \
-    pb_stage_load<HAS_VAL>(FAR, c, cc + 3 * NW, cc + 3 * NW < c_end, lane, pol_stream);                 \
-    advance();                                                                                          \
-    pb_stage_deltas(NXT, c, lane, cc + NW < c_end);                                                     \
-    pb_stage_process<S, HAS_VAL>(CUR, xs, ring, cc, lane);                                              \
-    cc += NW;                                                                                           \
-  }
-    while (true) {
-      PB_STEP(s0, s1, s3)
-      PB_STEP(s1, s2, s0)
-      PB_STEP(s2, s3, s1)
-      PB_STEP(s3, s0, s2)
+    int k = 0;  // ring position of the chunk being processed
+    while (cc < c_end) {
+      // stream of chunk k + 3 -> the slot chunk k - 1 has just left (every lane is past its reads: the syncwarp below)
+      pb_stage_issue<HAS_VAL>(wst + ((k + 3) % PB_STAGES) * PB_STAGE_BYTES, c, cc + 3 * NW, cc + 3 * NW < c_end, lane, pol_stream);
+      advance();
+      pb_cp_async_wait<2>();  // at most chunks k + 2 and k + 3 are still in flight: chunk k + 1 has landed
+      __syncwarp();           // ... for every lane (lane 0 copied the flag word)
+      int n0, n1;
+      pb_stage_deltas(wst + ((k + 1) % PB_STAGES) * PB_STAGE_BYTES, c, lane, cc + NW < c_end, n0, n1);
+      pb_stage_process<S, HAS_VAL>(wst + (k % PB_STAGES) * PB_STAGE_BYTES, xs, ring, cc, lane, d0, d1);
+      d0 = n0;
+      d1 = n1;
+      cc += NW;
+      k = (k + 1) % PB_STAGES;
     }
-#undef PB_STEP
+    pb_cp_async_wait<0>();
     // the panel of the warp's last chunk, then the panels it has no chunks in
     for (; panel < c.g.n_panel; ++panel) {
       if (need_wait) wait_slot(g0 + panel);
@@ -348,8 +373,6 @@ template <class T> __device__ __forceinline__ void pb_scatter4(T *cbuf, const ui
 __device__ __forceinline__ void pb_cp_async16(void *smem_dst, const void *gmem_src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pb_smem_addr(smem_dst)), "l"(gmem_src) : "memory");
 }
-__device__ __forceinline__ void pb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void pb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 #define PB_CU 6  // quads a consumer thread holds in registers (6 x 512 threads x 4 = 12288 entries per round; 8 spills at 80 registers)
 
@@ -436,16 +459,25 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
     // the ring slot is drained (its values sit in shared memory): hand it back to the producers
     if (fused && tid == 0) pb_red_release(c.consumed + g);
     have = *flag_s != 0u;
-    if (have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
     const bool last = pass == c.g.n_pass - 1;
     const uint16_t *crp_u = crp_s + (g & 1) * stride;
-    constexpr int RPT = 4;  // rows per thread per sweep
-    for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
-      T part[RPT];
+    constexpr int RPT = 5;  // rows per thread per sweep (5 x 512 covers the usual unit in one sweep)
+    T part[RPT];
+    // the carried sums of the first sweep are fetched BEFORE the next unit's loads go out: a wait on them must not
+    // end up behind those loads on a shared scoreboard
 #pragma unroll
-      for (int k = 0; k < RPT; ++k) {
-        const int i = i0 + tid + k * NT;
-        part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
+    for (int k = 0; k < RPT; ++k) {
+      const int i = tid + k * NT;
+      part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
+    }
+    if (have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
+    for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
+      if (i0 > 0) {
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) {
+          const int i = i0 + tid + k * NT;
+          part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
+        }
       }
 #pragma unroll
       for (int k = 0; k < RPT; ++k) {
@@ -483,6 +515,7 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   uint32_t *arr = reinterpret_cast<uint32_t *>(crp_s + 2 * pb_crp_stride(c.g.RS));
   uint32_t *flag_s = arr + PB_ARR;
   uint64_t *xbar = reinterpret_cast<uint64_t *>(arr + PB_ARR + 2);
+  unsigned char *pstage = reinterpret_cast<unsigned char *>(arr + PB_ARR + 4 + 4);  // 16-byte aligned: 96 bytes past arr
   if (threadIdx.x < PB_ARR) arr[threadIdx.x] = 0;
   if (threadIdx.x == 0) pb_mbar_init(xbar, 1);
   __syncthreads();
@@ -491,7 +524,7 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
     // the CTA's register pool is fixed at launch (768 threads x 80): the four consumer warpgroups hand 8 registers per
     // thread back (512 x 8 = 4096) and the two producer warpgroups take them (256 x 16 = 4096); inc blocks until then
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(PB_PROD_REGS));
-    if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, threadIdx.x);
+    if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, pstage, threadIdx.x);
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PB_CONS_REGS));
     if (c.roles & PB_ROLE_CONSUME) pb_consume<S>(c, a, cbuf, crp_s, flag_s, threadIdx.x - PB_PROD_THREADS, differs);

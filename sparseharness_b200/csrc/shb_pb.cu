@@ -118,7 +118,8 @@ void shb_pb_free(shb_pb *pb) {
 }
 
 static size_t pb_smem_bytes(const PbGeom &g) {
-  return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + (size_t)pb_crp_stride(g.RS) * 2 * 2 + PB_ARR * 4 + 8 + 16;
+  return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + (size_t)pb_crp_stride(g.RS) * 2 * 2 + PB_ARR * 4 + 32 +
+         (size_t)PB_PROD_WARPS * PB_STAGES * PB_STAGE_BYTES;
 }
 
 SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer, int make_default) {
@@ -143,7 +144,8 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   // shared memory the x slice leaves; the margin covers the spread of the unit sizes (checked below)
   const double per_row = std::max(0.25, (double)A->nnz / (double)A->n_rows / g.n_pass);
   // ... and one round of the consumer's registers (PB_CBUF_MAX entries); the row offsets (2 x 2 bytes per row) share the space
-  const double free_entries = std::min((double)PB_CBUF_MAX, ((double)PB_SMEM_LIMIT - 2048.0 - (double)g.W * 4) / 4.0);
+  const double free_entries =
+      std::min((double)PB_CBUF_MAX, ((double)PB_SMEM_LIMIT - 2048.0 - (double)PB_PROD_WARPS * PB_STAGES * PB_STAGE_BYTES - (double)g.W * 4) / 4.0);
   int rs = rows_per_consumer > 0 ? rows_per_consumer
                                  : (int)std::min(32768.0, std::max(32.0, free_entries / (per_row * 1.03 + 0.1 + 1.0) - 64.0));
   g.n_panel = (int)((A->n_rows + (int64_t)g.n_prod * rs - 1) / ((int64_t)g.n_prod * rs));

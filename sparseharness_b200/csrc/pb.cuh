@@ -164,8 +164,8 @@ __device__ __forceinline__ void pb_mbar_wait(uint64_t *bar, uint32_t parity) {
 #define PB_STAGE_BYTES 1552
 
 __device__ __forceinline__ void pb_cp_async16_hint(void *smem_dst, const void *gmem_src, uint64_t pol) {
-  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(pb_smem_addr(smem_dst)), "l"(gmem_src), "l"(pol)
-               : "memory");
+  (void)pol;  // (cp.async with an L2 cache-hint operand faulted as an illegal instruction on sm_100a: plain form)
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pb_smem_addr(smem_dst)), "l"(gmem_src) : "memory");
 }
 __device__ __forceinline__ void pb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void pb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }

@@ -21,10 +21,13 @@
 //   consumer warps  CTA s owns RS consecutive rows of every row panel.  What the 148 producers wrote for those
 //                   rows is ONE contiguous, 16-byte aligned region of the ring slot, and the matching stream of
 //                   16-bit slots is contiguous too: 128-bit loads, then plain st.shared of each product into
-//                   its precomputed slot of a row-sorted shared-memory buffer (padding goes to a dump word),
-//                   then a thread per row sums its slots in order and runs the usual fused epilogue /
-//                   convergence test / multi-destination store on the last pass (row sums of earlier passes are
-//                   carried in global memory).
+//                   its precomputed slot of a shared-memory buffer with lmax words per row (padding goes to a
+//                   dump word); then a thread per row reads its lmax words with 128-bit loads, puts the
+//                   semiring zero back, adds them up in order and runs the usual fused epilogue / convergence
+//                   test / multi-destination store on the last pass (row sums of earlier passes are carried in
+//                   global memory).  No row offsets, no per-row loop, no divergence.  Rows with more than
+//                   lmax (8 or 16) entries in one pass (3 % of BASELINE config 2's rows at 8) are left out of the blocked
+//                   copy and computed whole by `pb_long_rows_kernel` (a warp per row) right after.
 //
 // Producers and consumers of different CTAs meet through per-panel counters in global memory
 // (release/acquire); a producer may run DEPTH panels ahead of the slowest consumer.  The products never reach
@@ -41,12 +44,15 @@ struct PbGeom {
   int n_panel;   // row panels
   int W;         // columns per slice (multiple of 4, <= 65536)
   int RS;        // rows per consumer
-  int cbuf_cap;  // words of the consumer's row-sorted buffer (>= the largest consumer unit); word cbuf_cap = dump
+  int cbuf_cap;  // words of the consumer's row buffer = RS * lmax; word cbuf_cap = dump
   int slot_cap;  // entries per ring slot (>= the largest (pass, panel) group, padding included); + PB_CHUNK trash
   int depth;     // ring slots
+  int lmax;      // words per row and pass in the consumer's buffer (8 or 16); rows with more entries in a pass are "long"
 };
 
 #define PB_CHUNK 256  // entries a producer warp handles per step (8 per lane); units are padded to it
+#define PB_LMAX_MAX 16  // words per row and pass in the consumer's buffer: 8 or 16 (PbGeom::lmax)
+#define PB_MAX_PASS 32
 
 struct shb_pb {
   PbGeom g;
@@ -62,7 +68,9 @@ struct shb_pb {
   int32_t *uchunk = nullptr;     // [n_pass * n_prod * n_panel + 1] first chunk of unit (pass, p, panel)
   uint16_t *slot = nullptr;      // [ccap] consumer order: position in the consumer's row-sorted buffer
   int32_t *cons_start = nullptr; // [n_groups * n_prod + 1] start of consumer region (group, s) in `slot`
-  uint16_t *crp = nullptr;       // [(group, s)][pb_crp_stride(RS)] local row offsets into the row-sorted buffer
+  uint32_t *long_bits = nullptr; // [ceil(n_rows / 32)] bit r: row r is long (computed by pb_long_rows_kernel)
+  int32_t *long_rows = nullptr;  // [n_long] their indices
+  int64_t n_long = 0;
   void *ring = nullptr;          // [depth * (slot_cap + PB_CHUNK)] the product ring
   void *partial = nullptr;       // [n_rows] row sums carried from pass to pass
   uint32_t *sync = nullptr;      // ready[n_groups], consumed[n_groups], exit counter
@@ -76,11 +84,12 @@ struct shb_pb {
 #define PB_CONS_REGS 72
 #define PB_CONS_THREADS (PB_THREADS - PB_PROD_THREADS)
 #define PB_PROD_WARPS (PB_PROD_THREADS / 32)
-#define PB_CBUF_MAX 12288     // entries of the row-sorted buffer: one round of consumer registers (PB_CU x 512 x 4)
+#define PB_CU 5               // quads a consumer thread holds in registers: one round = PB_CU x 512 x 4 = 10240 entries
 #define PB_MAX_W 30720
 #define PB_MAX_DEPTH 8
 #define PB_ARR 16  // arrival counters in shared memory (> PB_MAX_DEPTH + 1 panels can be live in one CTA)
 #define PB_SMEM_LIMIT (227 * 1024)
+#define PB_MISC_BYTES (PB_ARR * 4 + 8 + 8 + PB_PROD_WARPS * PB_STAGES * 8)  // arrival counters, flag, x mbarrier, slot mbarriers
 #define PB_ROLE_PRODUCE 1
 #define PB_ROLE_CONSUME 2
 
@@ -93,7 +102,7 @@ template <class T> struct PbArgs {
   const int32_t *uchunk;
   const uint16_t *slot;
   const int32_t *cons_start;
-  const uint16_t *crp;
+  const uint32_t *long_bits;
   T *ring;
   T *partial;
   uint32_t *ready;     // [n_groups]
@@ -102,9 +111,6 @@ template <class T> struct PbArgs {
   int roles;          // PB_ROLE_* mask (both = the fused kernel; one at a time = the two-launch debug mode)
   int reset_sync;     // zero the counters when the last CTA leaves
 };
-
-// 16-bit words of one unit's row offsets (RS + 1), padded to a 16-byte multiple for cp.async
-__host__ __device__ __forceinline__ int pb_crp_stride(int RS) { return (RS + 1 + 7) & ~7; }
 
 __device__ __forceinline__ void pb_bar(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 __device__ __forceinline__ uint32_t pb_ld_acquire(const uint32_t *p) {
@@ -154,35 +160,16 @@ __device__ __forceinline__ void pb_mbar_wait(uint64_t *bar, uint32_t parity) {
                  : "memory");
 }
 
-// ---- the producer's stream pipeline: cp.async into a per-warp ring of PB_STAGES chunk slots --------------------------
-// Register-staged loads do not pipeline here: ptxas has six scoreboards per warp, the loads of several chunks in flight
-// end up sharing one, and the wait for the oldest chunk then waits for the newest (measured: one memory round trip per
-// chunk whatever the depth).  cp.async completes in per-thread commit groups instead: `wait_group<N>` is a FIFO.
-// Slot layout (PB_STAGE_BYTES): [32 lanes x 16 B local columns][32 x 16 B values 0-3][32 x 16 B values 4-7][16 B flags];
-// every lane copies and later reads ITS OWN 16-byte words (conflict-free LDS.128), lane 0 copies the chunk's flag word.
+// ---- the producer's stream pipeline: TMA bulk copies into a per-warp ring of PB_STAGES chunk slots -------------------
+// Measured on the way here (profiles/r02_summary.md): (1) register-staged loads do not pipeline -- ptxas has six
+// scoreboards per warp, the loads of several chunks in flight end up sharing one, and the wait for the oldest chunk
+// then waits for the newest; (2) cp.async (LDGSTS) pipelines, but writes shared memory once per returned 32-byte
+// sector: 32 wavefronts for a 1 KB value chunk, 63 % of the producer's shared-memory traffic.  A 1-D bulk copy
+// (cp.async.bulk, the TMA unit) lands whole lines, is issued by ONE lane, and completes on an mbarrier per slot.
+// Slot layout (PB_STAGE_BYTES): [512 B local columns: lane l owns bytes 16 l ..][512 B values 0-3 of every lane's
+// 8 -- i.e. the chunk's values in stream order occupy 1 KB: lane l owns bytes 32 l .. 32 l + 31][16 B flag word].
 #define PB_STAGES 4
 #define PB_STAGE_BYTES 1552
-
-__device__ __forceinline__ void pb_cp_async16_hint(void *smem_dst, const void *gmem_src, uint64_t pol) {
-  (void)pol;  // (cp.async with an L2 cache-hint operand faulted as an illegal instruction on sm_100a: plain form)
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pb_smem_addr(smem_dst)), "l"(gmem_src) : "memory");
-}
-__device__ __forceinline__ void pb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void pb_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-template <bool HAS_VAL, class T>
-__device__ __forceinline__ void pb_stage_issue(unsigned char *st, const PbArgs<T> &c, int cc, bool pred, int lane, uint64_t pol) {
-  if (pred) {
-    const int64_t i0 = (int64_t)cc * PB_CHUNK + lane * 8;
-    pb_cp_async16_hint(st + lane * 16, c.lcol + i0, pol);
-    if (HAS_VAL) {
-      pb_cp_async16_hint(st + 512 + lane * 16, c.val + i0, pol);
-      pb_cp_async16_hint(st + 1024 + lane * 16, c.val + i0 + 4, pol);
-    }
-    if (lane == 0) pb_cp_async16_hint(st + 1536, c.chunk_desc + cc, pol);
-  }
-  pb_cp_async_commit();  // one group per step, empty or not: the wait below counts groups
-}
 
 // the piece of each of the lane's two quads (pieces started up to and including the quad, minus one) and the
 // pieces' deltas: issued one chunk ahead of the stores that need them
@@ -205,8 +192,8 @@ __device__ __forceinline__ void pb_stage_process(const unsigned char *st, const 
   const uint4 lc = *reinterpret_cast<const uint4 *>(st + lane * 16);
   uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
   if (HAS_VAL) {
-    v0 = *reinterpret_cast<const uint4 *>(st + 512 + lane * 16);
-    v1 = *reinterpret_cast<const uint4 *>(st + 1024 + lane * 16);
+    v0 = *reinterpret_cast<const uint4 *>(st + 512 + lane * 32);
+    v1 = *reinterpret_cast<const uint4 *>(st + 512 + lane * 32 + 16);
   }
   const T x0 = xs[lc.x & 0xffffu], x1 = xs[lc.x >> 16], x2 = xs[lc.y & 0xffffu], x3 = xs[lc.y >> 16];
   const T x4 = xs[lc.z & 0xffffu], x5 = xs[lc.z >> 16], x6 = xs[lc.w & 0xffffu], x7 = xs[lc.w >> 16];
@@ -226,23 +213,43 @@ __device__ __forceinline__ void pb_stage_process(const unsigned char *st, const 
 
 // ---------------------------------------------------------------------------------------------
 // producer role: PB_PROD_THREADS threads (two warpgroups), named barrier 1 (twice per pass, around the x slice
-// load).  Per warp: the streams of chunks k+2 and k+3 are in flight, chunk k+1 has landed and its deltas are being
-// fetched, chunk k is gathered, multiplied and stored.
+// load).  Per warp: the streams of chunks k+2 and k+3 are in flight (bulk copies), chunk k+1 has landed and its
+// deltas are being fetched, chunk k is gathered, multiplied and stored.
 // ---------------------------------------------------------------------------------------------
 template <class S, bool HAS_VAL>
 __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
-                                           typename S::T *xs, uint32_t *arr, uint64_t *xbar, unsigned char *pstage, int tid) {
+                                           typename S::T *xs, uint32_t *arr, uint64_t *xbar, uint64_t *sbar_all,
+                                           unsigned char *pstage, int tid) {
   typedef typename S::T T;
   const int p = blockIdx.x;
   uint32_t xphase = 0;  // completed phases of the x-slice mbarrier
   const int lane = tid & 31, warp = tid >> 5;
-  const uint64_t pol_stream = shb_policy_evict_first();
   const uint32_t zbits = shb_bits<T>(S::zero());
   const bool x_aligned = ((reinterpret_cast<uintptr_t>(a.x) & 15u) == 0);
   const bool fused = (c.roles & PB_ROLE_CONSUME) != 0;
   const int64_t slot_stride = (int64_t)c.g.slot_cap + PB_CHUNK;
   constexpr int NW = PB_PROD_WARPS;
   unsigned char *const wst = pstage + (size_t)warp * PB_STAGES * PB_STAGE_BYTES;  // this warp's ring of chunk slots
+  uint64_t *const sbar = sbar_all + warp * PB_STAGES;                             // ... and their mbarriers
+  uint32_t issued = 0, waited = 0;  // chunks issued to / awaited from the ring (slot = n % PB_STAGES, parity = (n / PB_STAGES) & 1)
+
+  // lane 0: arm the slot's mbarrier with the byte count and start the bulk copies of one chunk
+  auto issue = [&](int cc) {
+    if (lane == 0) {
+      const uint32_t st_i = issued % PB_STAGES;
+      unsigned char *st = wst + st_i * PB_STAGE_BYTES;
+      const int64_t i0 = (int64_t)cc * PB_CHUNK;
+      pb_mbar_expect_tx(sbar + st_i, HAS_VAL ? 1552u : 528u);
+      pb_bulk_g2s(st, c.lcol + i0, 512u, sbar + st_i);
+      if (HAS_VAL) pb_bulk_g2s(st + 512, c.val + i0, 1024u, sbar + st_i);
+      pb_bulk_g2s(st + 1536, c.chunk_desc + cc, 16u, sbar + st_i);
+    }
+    ++issued;
+  };
+  auto await = [&]() {  // the oldest chunk not yet awaited has landed (for every lane)
+    pb_mbar_wait(sbar + (waited % PB_STAGES), (waited / PB_STAGES) & 1u);
+    ++waited;
+  };
 
   // the warp's arrival at the end of its share of a panel; the CTA's last arrival publishes the panel
   auto arrive = [&](int g) {
@@ -298,18 +305,14 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
     int ce_next = c.g.n_panel > 1 ? __ldg(c.uchunk + ub + 2) : c_end;  // ... and of the one after
     int cc = c_begin + warp;
     // the streams of the first three chunks go out while the slice is still landing
-    pb_stage_issue<HAS_VAL>(wst + 0 * PB_STAGE_BYTES, c, cc, cc < c_end, lane, pol_stream);
-    pb_stage_issue<HAS_VAL>(wst + 1 * PB_STAGE_BYTES, c, cc + NW, cc + NW < c_end, lane, pol_stream);
-    pb_stage_issue<HAS_VAL>(wst + 2 * PB_STAGE_BYTES, c, cc + 2 * NW, cc + 2 * NW < c_end, lane, pol_stream);
+    if (cc < c_end) issue(cc);
+    if (cc + NW < c_end) issue(cc + NW);
+    if (cc + 2 * NW < c_end) issue(cc + 2 * NW);
     if (bulk > 0) {
       pb_mbar_wait(xbar, xphase & 1u);
       ++xphase;
     }
     pb_bar(1, PB_PROD_THREADS);
-    int d0 = 0, d1 = 0;  // deltas of the chunk about to be processed
-    pb_cp_async_wait<2>();  // the first chunk has landed
-    __syncwarp();
-    pb_stage_deltas(wst, c, lane, cc < c_end, d0, d1);
 
     bool need_wait = true;
     T *ring = c.ring;
@@ -332,22 +335,39 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
         need_wait = false;
       }
     };
-    int k = 0;  // ring position of the chunk being processed
-    while (cc < c_end) {
-      // stream of chunk k + 3 -> the slot chunk k - 1 has just left (every lane is past its reads: the syncwarp below)
-      pb_stage_issue<HAS_VAL>(wst + ((k + 3) % PB_STAGES) * PB_STAGE_BYTES, c, cc + 3 * NW, cc + 3 * NW < c_end, lane, pol_stream);
-      advance();
-      pb_cp_async_wait<2>();  // at most chunks k + 2 and k + 3 are still in flight: chunk k + 1 has landed
-      __syncwarp();           // ... for every lane (lane 0 copied the flag word)
-      int n0, n1;
-      pb_stage_deltas(wst + ((k + 1) % PB_STAGES) * PB_STAGE_BYTES, c, lane, cc + NW < c_end, n0, n1);
-      pb_stage_process<S, HAS_VAL>(wst + (k % PB_STAGES) * PB_STAGE_BYTES, xs, ring, cc, lane, d0, d1);
-      d0 = n0;
-      d1 = n1;
-      cc += NW;
-      k = (k + 1) % PB_STAGES;
+    // two steps per trip so that the deltas fetched for the next chunk sit in their own registers until they are used
+    // (a rotating copy `d = next` would wait for the load at once)
+    int e0 = 0, e1 = 0, f0 = 0, f1 = 0;
+    uint32_t cur = waited;  // ring position of the chunk being processed
+    if (cc < c_end) {
+      await();
+      pb_stage_deltas(wst + (cur % PB_STAGES) * PB_STAGE_BYTES, c, lane, true, e0, e1);
     }
-    pb_cp_async_wait<0>();
+    while (cc < c_end) {
+      // ---- even step: deltas (e0, e1) belong to chunk cc; fetch (f0, f1) for chunk cc + NW
+      __syncwarp();  // every lane is past its reads of the slot chunk cc + 3 NW is about to overwrite
+      if (cc + 3 * NW < c_end) issue(cc + 3 * NW);
+      advance();
+      if (cc + NW < c_end) {
+        await();
+        pb_stage_deltas(wst + ((cur + 1) % PB_STAGES) * PB_STAGE_BYTES, c, lane, true, f0, f1);
+      }
+      pb_stage_process<S, HAS_VAL>(wst + (cur % PB_STAGES) * PB_STAGE_BYTES, xs, ring, cc, lane, e0, e1);
+      cc += NW;
+      ++cur;
+      if (cc >= c_end) break;
+      // ---- odd step: (f0, f1) belong to chunk cc; fetch (e0, e1) for chunk cc + NW
+      __syncwarp();
+      if (cc + 3 * NW < c_end) issue(cc + 3 * NW);
+      advance();
+      if (cc + NW < c_end) {
+        await();
+        pb_stage_deltas(wst + ((cur + 1) % PB_STAGES) * PB_STAGE_BYTES, c, lane, true, e0, e1);
+      }
+      pb_stage_process<S, HAS_VAL>(wst + (cur % PB_STAGES) * PB_STAGE_BYTES, xs, ring, cc, lane, f0, f1);
+      cc += NW;
+      ++cur;
+    }
     // the panel of the warp's last chunk, then the panels it has no chunks in
     for (; panel < c.g.n_panel; ++panel) {
       if (need_wait) wait_slot(g0 + panel);
@@ -359,10 +379,10 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
 
 // ---------------------------------------------------------------------------------------------
 // consumer role: PB_CONS_THREADS threads, named barrier 2.
-// Per unit:  bar | registers -> row-sorted buffer (st.shared per product) | bar | hand the ring slot back |
-//            issue the NEXT unit's ring + slot loads into registers | thread per row: sum, store | ...
-// so the loads of a unit fly while the previous unit is reduced, and the row offsets of a unit arrive by cp.async
-// while the unit before it is scattered.
+// Per unit:  bar | registers -> row buffer (st.shared per product) | bar | hand the ring slot back |
+//            carried sums | issue the NEXT unit's ring + slot loads into registers | thread per row: 2 x LDS.128,
+//            zeros back, 8 adds, store | ...
+// so the loads of a unit fly while the previous unit is reduced.
 // ---------------------------------------------------------------------------------------------
 template <class T> __device__ __forceinline__ void pb_scatter4(T *cbuf, const uint4 &pr, const uint2 &sl) {
   cbuf[sl.x & 0xffffu] = shb_from_bits<T>(pr.x);
@@ -370,15 +390,10 @@ template <class T> __device__ __forceinline__ void pb_scatter4(T *cbuf, const ui
   cbuf[sl.y & 0xffffu] = shb_from_bits<T>(pr.z);
   cbuf[sl.y >> 16] = shb_from_bits<T>(pr.w);
 }
-__device__ __forceinline__ void pb_cp_async16(void *smem_dst, const void *gmem_src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pb_smem_addr(smem_dst)), "l"(gmem_src) : "memory");
-}
 
-#define PB_CU 6  // quads a consumer thread holds in registers (6 x 512 threads x 4 = 12288 entries per round; 8 spills at 80 registers)
-
-template <class S>
+template <class S, int LQ>  // LQ = lmax / 4: 128-bit words per row
 __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
-                                           typename S::T *cbuf, uint16_t *crp_s, uint32_t *flag_s, int tid, bool &differs) {
+                                           typename S::T *cbuf, uint32_t *flag_s, int tid, bool &differs) {
   typedef typename S::T T;
   constexpr int NT = PB_CONS_THREADS;
   constexpr int U = PB_CU;
@@ -387,7 +402,12 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
   const int64_t slot_stride = (int64_t)c.g.slot_cap + PB_CHUNK;
   const bool fused = (c.roles & PB_ROLE_PRODUCE) != 0;
   const uint64_t pol_stream = shb_policy_evict_first();
-  const int stride = pb_crp_stride(c.g.RS);  // 16-bit words per unit, a 16-byte multiple
+  const int RS = c.g.RS;
+  const uint32_t zb = shb_bits<T>(S::zero());
+  const uint4 zero4 = make_uint4(zb, zb, zb, zb);
+
+  // every word of the row buffer starts as the semiring zero; the reduction puts the zeros back as it reads
+  for (int i = tid * 4; i < c.g.cbuf_cap + 32; i += NT * 4) *reinterpret_cast<uint4 *>(cbuf + i) = zero4;
 
   uint4 pr[U];
   uint2 sl[U];
@@ -405,21 +425,14 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
       }
     }
   };
-  auto fetch_crp = [&](int g) {  // row offsets of unit g into its half of crp_s
-    const uint16_t *src = c.crp + ((int64_t)g * c.g.n_prod + s) * stride;
-    uint16_t *dst = crp_s + (g & 1) * stride;
-    for (int i = tid * 8; i < stride; i += NT * 8) pb_cp_async16(dst + i, src + i);
-    pb_cp_async_commit();
-  };
 
   int cs = __ldg(c.cons_start + s), ce = __ldg(c.cons_start + s + 1), gs = __ldg(c.cons_start);
   bool have = false;  // the registers hold the first round of the current unit
-  fetch_crp(0);
+  int pass = 0, panel = 0;
   for (int g = 0; g < n_groups; ++g) {
-    const int pass = g / c.g.n_panel, panel = g - pass * c.g.n_panel;
     const int64_t u = (int64_t)g * c.g.n_prod + s;
-    const int64_t r0 = ((int64_t)panel * c.g.n_prod + s) * c.g.RS;
-    const int nr = (int)max((int64_t)0, min((int64_t)c.g.RS, a.n_rows - r0));
+    const int64_t r0 = ((int64_t)panel * c.g.n_prod + s) * RS;
+    const int nr = (int)max((int64_t)0, min((int64_t)RS, a.n_rows - r0));
     // next unit's extents (their latency hides behind this unit)
     int cs_n = 0, ce_n = 0, gs_n = 0;
     if (g + 1 < n_groups) {
@@ -436,11 +449,8 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
       pb_bar(2, NT);  // ring slot g is complete (and everyone is done reducing unit g - 1)
       issue(g, cs, ce, gs);
     } else {
-      pb_bar(2, NT);  // everyone is done reducing unit g - 1: the row-sorted buffer is free
+      pb_bar(2, NT);  // everyone is done reducing unit g - 1: the row buffer holds zeros again
     }
-    // the next unit's row offsets go into the half unit g - 1 has just stopped reading
-    if (g + 1 < n_groups) fetch_crp(g + 1);
-    else pb_cp_async_commit();  // keeps the group count uniform for the wait below
     {
       const int nq = (ce - cs) >> 2;
 #pragma unroll
@@ -454,56 +464,62 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
     }
     // is the next unit's ring slot complete already?  one thread looks, the barrier spreads the verdict
     if (tid == 0) *flag_s = (g + 1 < n_groups && (!fused || pb_ld_acquire(c.ready + g + 1) >= (uint32_t)c.g.n_prod)) ? 1u : 0u;
-    pb_cp_async_wait<1>();  // this unit's row offsets have landed (the next unit's may still be in flight)
     pb_bar(2, NT);
     // the ring slot is drained (its values sit in shared memory): hand it back to the producers
     if (fused && tid == 0) pb_red_release(c.consumed + g);
     have = *flag_s != 0u;
     const bool last = pass == c.g.n_pass - 1;
-    const uint16_t *crp_u = crp_s + (g & 1) * stride;
     constexpr int RPT = 5;  // rows per thread per sweep (5 x 512 covers the usual unit in one sweep)
-    T part[RPT];
-    // the carried sums of the first sweep are fetched BEFORE the next unit's loads go out: a wait on them must not
-    // end up behind those loads on a shared scoreboard
-#pragma unroll
-    for (int k = 0; k < RPT; ++k) {
-      const int i = tid + k * NT;
-      part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
-    }
-    if (have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
     for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
-      if (i0 > 0) {
+      T part[RPT];
+      uint32_t lbits[RPT];
+      // carried sums and long-row bits are fetched BEFORE the next unit's loads go out: a wait on them must not end
+      // up behind those loads on a shared scoreboard
 #pragma unroll
-        for (int k = 0; k < RPT; ++k) {
-          const int i = i0 + tid + k * NT;
-          part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
-        }
+      for (int k = 0; k < RPT; ++k) {
+        const int i = i0 + tid + k * NT;
+        part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
+        lbits[k] = i < nr ? __ldg(c.long_bits + ((r0 + i) >> 5)) : 0u;
       }
+      if (i0 == 0 && have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
 #pragma unroll
       for (int k = 0; k < RPT; ++k) {
         const int i = i0 + tid + k * NT;
         if (i < nr) {
-          const int b = crp_u[i], e = crp_u[i + 1];
-          T acc = part[k];
-          int j = b;
-          for (; j + 3 < e; j += 4) {
-            const T v0 = cbuf[j], v1 = cbuf[j + 1], v2 = cbuf[j + 2], v3 = cbuf[j + 3];
-            acc = S::add(S::add(S::add(S::add(acc, v0), v1), v2), v3);
+          uint4 v[LQ];
+#pragma unroll
+          for (int q = 0; q < LQ; ++q) {
+            uint4 *w = reinterpret_cast<uint4 *>(cbuf + (4 * q) * RS + 4 * i);
+            v[q] = *w;
+            *w = zero4;
           }
-          for (; j < e; ++j) acc = S::add(acc, cbuf[j]);
-          if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
-          else c.partial[r0 + i] = acc;
+          T acc = part[k];
+#pragma unroll
+          for (int q = 0; q < LQ; ++q) {
+            acc = S::add(acc, shb_from_bits<T>(v[q].x));
+            acc = S::add(acc, shb_from_bits<T>(v[q].y));
+            acc = S::add(acc, shb_from_bits<T>(v[q].z));
+            acc = S::add(acc, shb_from_bits<T>(v[q].w));
+          }
+          if (!((lbits[k] >> ((r0 + i) & 31)) & 1u)) {  // long rows belong to pb_long_rows_kernel
+            if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
+            else c.partial[r0 + i] = acc;
+          }
         }
       }
     }
+    if (nr <= 0 && have) issue(g + 1, cs_n, ce_n, gs_n);
     cs = cs_n;
     ce = ce_n;
     gs = gs_n;
+    if (++panel == c.g.n_panel) {
+      panel = 0;
+      ++pass;
+    }
   }
-  pb_cp_async_wait<0>();
 }
 
-template <class S, bool HAS_VAL>
+template <class S, bool HAS_VAL, int LQ>
 __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_constant__ PbArgs<typename S::T> c,
                                                                   const __grid_constant__ SpmvArgs<typename S::T> a) {
   typedef typename S::T T;
@@ -511,23 +527,26 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   extern __shared__ __align__(16) unsigned char pb_smem[];
   T *xs = reinterpret_cast<T *>(pb_smem);
   T *cbuf = xs + c.g.W;
-  uint16_t *crp_s = reinterpret_cast<uint16_t *>(cbuf + c.g.cbuf_cap + 32);
-  uint32_t *arr = reinterpret_cast<uint32_t *>(crp_s + 2 * pb_crp_stride(c.g.RS));
+  uint32_t *arr = reinterpret_cast<uint32_t *>(cbuf + c.g.cbuf_cap + 32);
   uint32_t *flag_s = arr + PB_ARR;
   uint64_t *xbar = reinterpret_cast<uint64_t *>(arr + PB_ARR + 2);
-  unsigned char *pstage = reinterpret_cast<unsigned char *>(arr + PB_ARR + 4 + 4);  // 16-byte aligned: 96 bytes past arr
+  uint64_t *sbar = xbar + 1;                                                                   // PB_PROD_WARPS * PB_STAGES slots
+  unsigned char *pstage = reinterpret_cast<unsigned char *>(sbar + PB_PROD_WARPS * PB_STAGES);  // 16-byte aligned
   if (threadIdx.x < PB_ARR) arr[threadIdx.x] = 0;
-  if (threadIdx.x == 0) pb_mbar_init(xbar, 1);
+  if (threadIdx.x == 0) {
+    pb_mbar_init(xbar, 1);
+    for (int i = 0; i < PB_PROD_WARPS * PB_STAGES; ++i) pb_mbar_init(sbar + i, 1);
+  }
   __syncthreads();
   bool differs = false;
   if (threadIdx.x < PB_PROD_THREADS) {
     // the CTA's register pool is fixed at launch (768 threads x 80): the four consumer warpgroups hand 8 registers per
     // thread back (512 x 8 = 4096) and the two producer warpgroups take them (256 x 16 = 4096); inc blocks until then
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(PB_PROD_REGS));
-    if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, pstage, threadIdx.x);
+    if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, sbar, pstage, threadIdx.x);
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PB_CONS_REGS));
-    if (c.roles & PB_ROLE_CONSUME) pb_consume<S>(c, a, cbuf, crp_s, flag_s, threadIdx.x - PB_PROD_THREADS, differs);
+    if (c.roles & PB_ROLE_CONSUME) pb_consume<S, LQ>(c, a, cbuf, flag_s, threadIdx.x - PB_PROD_THREADS, differs);
   }
   shb_publish_changed(a.ctl, differs);
   __syncthreads();
@@ -544,6 +563,31 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
       __threadfence();
     }
   }
+}
+
+// the rows the blocked copy leaves out (more than lmax entries in some pass): a warp per row over the operator's own
+// CSR arrays, lanes striding the row, butterfly reduction, the usual epilogue.  Launched right after the fused kernel.
+template <class S, bool HAS_VAL>
+__global__ void __launch_bounds__(256) pb_long_rows_kernel(const __grid_constant__ SpmvArgs<typename S::T> a,
+                                                          const int32_t *__restrict__ long_rows, int n_long) {
+  typedef typename S::T T;
+  if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
+  const int lane = threadIdx.x & 31;
+  const int n_warps = (gridDim.x * blockDim.x) >> 5;
+  bool differs = false;
+  for (int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n_long; w += n_warps) {
+    const int r = __ldg(long_rows + w);
+    const int b = __ldg(a.row_ptr + r), e = __ldg(a.row_ptr + r + 1);
+    T acc = S::zero();
+    for (int k = b + lane; k < e; k += 32) {
+      const int32_t col = __ldg(a.col + k);
+      const T xv = ((uint32_t)col < a.vlength) ? __ldg(a.x + col) : S::zero();
+      acc = S::add(acc, S::mult(xv, HAS_VAL ? __ldg(a.val + k) : S::one()));
+    }
+    for (int off = 16; off > 0; off >>= 1) acc = S::add(acc, shb_from_bits<T>(__shfl_xor_sync(0xffffffffu, shb_bits<T>(acc), off)));
+    if (lane == 0) shb_finish_row<S>(a, r, acc, differs);
+  }
+  shb_publish_changed(a.ctl, differs);
 }
 
 // host side (shb_pb.cu)

@@ -682,7 +682,7 @@ static int default_rpg(int lanes) {
 
 // BLOCKED: one persistent cooperative kernel, a CTA per SM, producer and consumer warps (pb.cuh).
 // SHB_PB_SPLIT=1 runs the two roles as two launches over a full-size ring (debug / profiling aid).
-template <class S, bool HAS_VAL>
+template <class S, bool HAS_VAL, int LQ>
 static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> &a) {
   typedef typename S::T T;
   const int n_groups = pb->g.n_pass * pb->g.n_panel;
@@ -695,7 +695,7 @@ static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> 
   pa.uchunk = pb->uchunk;
   pa.slot = pb->slot;
   pa.cons_start = pb->cons_start;
-  pa.crp = pb->crp;
+  pa.long_bits = pb->long_bits;
   pa.partial = (T *)pb->partial;
   pa.ready = pb->sync;
   pa.consumed = pb->sync + n_groups;
@@ -708,24 +708,34 @@ static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> 
   }
   pa.ring = (T *)pb->ring;
   const size_t smem = shb_pb_smem_bytes(pb);
-  SHB_CUDA(cudaFuncSetAttribute(pb_fused_kernel<S, HAS_VAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SHB_CUDA(cudaFuncSetAttribute(pb_fused_kernel<S, HAS_VAL, LQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   SpmvArgs<T> aa = a;
   void *args[] = {&pa, &aa};
   const dim3 grid((unsigned)pb->g.n_prod), block(PB_THREADS);
   if (!split) {
     pa.roles = PB_ROLE_PRODUCE | PB_ROLE_CONSUME;
     pa.reset_sync = 1;
-    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, LQ>, grid, block, args, smem, c->stream));
+    if (pb->n_long > 0) {  // the rows the blocked copy leaves out, whole, from the operator's own CSR arrays
+      const int blocks = (int)std::min<int64_t>((pb->n_long + 7) / 8, (int64_t)c->prop.multiProcessorCount * 16);
+      pb_long_rows_kernel<S, HAS_VAL><<<blocks, 256, 0, c->stream>>>(aa, pb->long_rows, (int)pb->n_long);
+      SHB_CUDA(cudaGetLastError());
+    }
   } else {
     if (split_env[0] != 'c') {
       pa.roles = PB_ROLE_PRODUCE;
       pa.reset_sync = split_env[0] == 'p';
-      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, LQ>, grid, block, args, smem, c->stream));
     }
     if (split_env[0] != 'p') {
       pa.roles = PB_ROLE_CONSUME;
       pa.reset_sync = 1;
-      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL>, grid, block, args, smem, c->stream));
+      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, LQ>, grid, block, args, smem, c->stream));
+      if (pb->n_long > 0) {
+        const int blocks = (int)std::min<int64_t>((pb->n_long + 7) / 8, (int64_t)c->prop.multiProcessorCount * 16);
+        pb_long_rows_kernel<S, HAS_VAL><<<blocks, 256, 0, c->stream>>>(aa, pb->long_rows, (int)pb->n_long);
+        SHB_CUDA(cudaGetLastError());
+      }
     }
   }
   return SHB_OK;
@@ -735,7 +745,8 @@ template <class S>
 static int run_blocked(shb_ctx *c, const shb_csr *A, const SpmvArgs<typename S::T> &a) {
   SHB_REQUIRE(A->pb != nullptr, "SHB_VARIANT_BLOCKED needs shb_csr_build_blocked on this operator first");
   SHB_REQUIRE(A->pb->g.n_prod == c->prop.multiProcessorCount, "blocked layout was built for another device");
-  return A->pb->val ? launch_blocked<S, true>(c, A->pb, a) : launch_blocked<S, false>(c, A->pb, a);
+  if (A->pb->g.lmax == 8) return A->pb->val ? launch_blocked<S, true, 2>(c, A->pb, a) : launch_blocked<S, false, 2>(c, A->pb, a);
+  return A->pb->val ? launch_blocked<S, true, 4>(c, A->pb, a) : launch_blocked<S, false, 4>(c, A->pb, a);
 }
 
 template <class S>

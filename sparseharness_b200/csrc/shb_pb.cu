@@ -21,8 +21,31 @@
 static const uint32_t PB_INVALID_KEY = 0xffffffffu;
 
 // one thread per row: bucket key, source index and local row of every stored entry
+// rows with more than lmax entries in one column pass do not fit the consumer's fixed row slots: they are marked
+// "long", left out of the blocked copy and computed by pb_long_rows_kernel
+__global__ void pb_mark_long_kernel(PbGeom g, int lmax, const int32_t *row_ptr, const int32_t *col, int64_t n_rows, uint32_t n_cols,
+                                    uint32_t *long_bits, int32_t *long_rows, int32_t *n_long) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+    const int b = row_ptr[r], e = row_ptr[r + 1];
+    bool is_long = false;
+    if (e - b > lmax) {
+      unsigned char cnt[PB_MAX_PASS];
+      for (int p = 0; p < g.n_pass; ++p) cnt[p] = 0;
+      const uint32_t pass_cols = (uint32_t)g.W * (uint32_t)g.n_prod;
+      for (int k = b; k < e && !is_long; ++k) {
+        const uint32_t c = (uint32_t)col[k];
+        if (c < n_cols && ++cnt[c / pass_cols] > lmax) is_long = true;
+      }
+    }
+    if (is_long) {
+      atomicOr(&long_bits[r >> 5], 1u << (r & 31));
+      long_rows[atomicAdd(n_long, 1)] = (int32_t)r;
+    }
+  }
+}
+
 __global__ void pb_keys_kernel(PbGeom g, const int32_t *row_ptr, const int32_t *col, int64_t n_rows, uint32_t n_cols,
-                               uint32_t *keys, uint32_t *src, uint16_t *lrow_tmp) {
+                               const uint32_t *long_bits, uint32_t *keys, uint32_t *src, uint16_t *lrow_tmp) {
   const int64_t PR = (int64_t)g.RS * g.n_prod;
   for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
     const int panel = (int)(r / PR);
@@ -30,10 +53,11 @@ __global__ void pb_keys_kernel(PbGeom g, const int32_t *row_ptr, const int32_t *
     const int s = in_panel / g.RS;
     const uint16_t lr = (uint16_t)(in_panel - s * g.RS);
     const int b = row_ptr[r], e = row_ptr[r + 1];
+    const bool is_long = (long_bits[r >> 5] >> (r & 31)) & 1u;
     for (int k = b; k < e; ++k) {
       const uint32_t c = (uint32_t)col[k];
       uint32_t key = PB_INVALID_KEY;  // out-of-range column: x reads as ZERO, the product is the additive identity
-      if (c < n_cols) {
+      if (c < n_cols && !is_long) {
         const uint32_t slice = c / (uint32_t)g.W;  // global slice index = pass * n_prod + p
         key = ((slice * (uint32_t)g.n_panel + (uint32_t)panel)) * (uint32_t)g.n_prod + (uint32_t)s;
       }
@@ -75,29 +99,27 @@ __global__ void pb_scatter_kernel(PbGeom g, const uint32_t *sorted_keys, const u
   }
 }
 
-// row offsets of every consumer unit (and the largest unit)
-__global__ void pb_crp_kernel(PbGeom g, const int32_t *bound2, int64_t n_cons_units, uint16_t *crp, int32_t *max_unit) {
-  const int stride = pb_crp_stride(g.RS);
-  const int64_t total = n_cons_units * stride;
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t unit = t / stride;
-    const int i = min((int)(t - unit * stride), g.RS);  // the padding words repeat the unit's end
-    const int off = bound2[unit * g.RS + i] - bound2[unit * g.RS];
-    crp[t] = (uint16_t)min(off, 65535);
-    if (i == g.RS) atomicMax(max_unit, off);
-  }
+// the largest consumer unit (valid entries of one (group, s)): what one round of the consumer's registers must hold
+__global__ void pb_max_unit_kernel(PbGeom g, const int32_t *bound2, int64_t n_cons_units, int32_t *max_unit) {
+  int m = 0;
+  for (int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; u < n_cons_units; u += (int64_t)gridDim.x * blockDim.x)
+    m = max(m, bound2[(u + 1) * g.RS] - bound2[u * g.RS]);
+  if (m) atomicMax(max_unit, m);
 }
 
 __global__ void pb_fill16_kernel(uint16_t *p, int64_t n, uint16_t v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
-// slot of every entry: its rank in the (unit, row) sorted order, written at its consumer-order position
+// slot of every entry, written at its consumer-order position: word (k / 4) * 4 RS + 4 * local row + k % 4 of the row
+// buffer, k = rank of the entry among its row's entries of this pass (sorted order = (producer, CSR order): fixed)
 __global__ void pb_slots_kernel(PbGeom g, const uint32_t *key2_sorted, const uint32_t *cdst_sorted, const int32_t *bound2,
                                 int64_t n_valid, uint16_t *slot) {
   for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_valid; j += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t unit = (int64_t)(key2_sorted[j] / (uint32_t)g.RS);
-    slot[cdst_sorted[j]] = (uint16_t)min((int64_t)65535, j - (int64_t)bound2[unit * g.RS]);
+    const uint32_t key2 = key2_sorted[j];
+    const uint32_t lrow = key2 % (uint32_t)g.RS;
+    const uint32_t k = (uint32_t)(j - (int64_t)bound2[key2]);  // < PB_LMAX: longer rows were left out
+    slot[cdst_sorted[j]] = (uint16_t)((k >> 2) * 4u * (uint32_t)g.RS + 4u * lrow + (k & 3u));
   }
 }
 
@@ -110,16 +132,46 @@ void shb_pb_free(shb_pb *pb) {
   cudaFree(pb->uchunk);
   cudaFree(pb->slot);
   cudaFree(pb->cons_start);
-  cudaFree(pb->crp);
+  cudaFree(pb->long_bits);
+  cudaFree(pb->long_rows);
   cudaFree(pb->ring);
   cudaFree(pb->partial);
   cudaFree(pb->sync);
   delete pb;
 }
 
+static bool n_rows_too_many(const PbGeom &g) { return g.RS > 16383; }
+
 static size_t pb_smem_bytes(const PbGeom &g) {
-  return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + (size_t)pb_crp_stride(g.RS) * 2 * 2 + PB_ARR * 4 + 32 +
-         (size_t)PB_PROD_WARPS * PB_STAGES * PB_STAGE_BYTES;
+  return (size_t)g.W * 4 + ((size_t)g.cbuf_cap + 32) * 4 + PB_MISC_BYTES + (size_t)PB_PROD_WARPS * PB_STAGES * PB_STAGE_BYTES;
+}
+
+// chooses lmax (8 words per row unless that sends more than an eighth of the rows to the long-row kernel; then 16), marks
+// the long rows and lists them; needs g.n_prod / g.n_pass / g.W only
+static int pb_choose_lmax(shb_ctx *c, const shb_csr *A, PbGeom &g, shb_pb *pb) {
+  const size_t words = std::max<size_t>((size_t)(A->n_rows + 31) / 32, 1);
+  int32_t *d_n_long = nullptr;
+  SHB_CUDA(cudaMalloc(&pb->long_bits, words * 4));
+  SHB_CUDA(cudaMalloc(&pb->long_rows, (size_t)A->n_rows * 4));
+  SHB_CUDA(cudaMalloc(&d_n_long, 4));
+  const unsigned grid = (unsigned)std::min<int64_t>((A->n_rows + 255) / 256, (int64_t)c->prop.multiProcessorCount * 32);
+  int32_t h_n_long = 0;
+  cudaError_t e1 = cudaSuccess;
+  for (int lmax = 8; lmax <= PB_LMAX_MAX; lmax *= 2) {
+    g.lmax = lmax;
+    if (e1 == cudaSuccess) e1 = cudaMemsetAsync(pb->long_bits, 0, words * 4, c->stream);
+    if (e1 == cudaSuccess) e1 = cudaMemsetAsync(d_n_long, 0, 4, c->stream);
+    pb_mark_long_kernel<<<grid, 256, 0, c->stream>>>(g, lmax, A->row_ptr, A->col, A->n_rows, (uint32_t)A->n_cols, pb->long_bits,
+                                                      pb->long_rows, d_n_long);
+    if (e1 == cudaSuccess) e1 = cudaGetLastError();
+    if (e1 == cudaSuccess) e1 = cudaMemcpyAsync(&h_n_long, d_n_long, 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e1 == cudaSuccess) e1 = cudaStreamSynchronize(c->stream);
+    if (e1 != cudaSuccess || (int64_t)h_n_long * 8 <= A->n_rows) break;
+  }
+  cudaFree(d_n_long);
+  SHB_CUDA(e1);
+  pb->n_long = h_n_long;
+  return SHB_OK;
 }
 
 SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer, int make_default) {
@@ -140,22 +192,38 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   g.n_pass = (int)((A->n_cols + (int64_t)g.n_prod * max_w - 1) / ((int64_t)g.n_prod * max_w));
   g.W = (int)((A->n_cols + (int64_t)g.n_prod * g.n_pass - 1) / ((int64_t)g.n_prod * g.n_pass));
   g.W = std::max(4, (g.W + 3) & ~3);
-  // rows per consumer: a consumer unit (RS rows x mean row length / n_pass valid entries, 4 bytes each) takes the
-  // shared memory the x slice leaves; the margin covers the spread of the unit sizes (checked below)
+  SHB_REQUIRE(g.n_pass <= PB_MAX_PASS, "too many column passes for the blocked layout");
+  shb_pb *pb = new shb_pb();
+  {
+    const int st = pb_choose_lmax(c, A, g, pb);
+    if (st != SHB_OK) {
+      shb_pb_free(pb);
+      return st;
+    }
+  }
+  // rows per consumer: lmax words per row of the shared memory the x slice and the producers' ring leave, and a unit
+  // (RS rows x mean row length / n_pass entries) that one round of the consumer's registers holds (checked below)
   const double per_row = std::max(0.25, (double)A->nnz / (double)A->n_rows / g.n_pass);
-  // ... and one round of the consumer's registers (PB_CBUF_MAX entries); the row offsets (2 x 2 bytes per row) share the space
-  const double free_entries =
-      std::min((double)PB_CBUF_MAX, ((double)PB_SMEM_LIMIT - 2048.0 - (double)PB_PROD_WARPS * PB_STAGES * PB_STAGE_BYTES - (double)g.W * 4) / 4.0);
-  int rs = rows_per_consumer > 0 ? rows_per_consumer
-                                 : (int)std::min(32768.0, std::max(32.0, free_entries / (per_row * 1.03 + 0.1 + 1.0) - 64.0));
+  const double smem_rows = ((double)PB_SMEM_LIMIT - 1024.0 - (double)PB_PROD_WARPS * PB_STAGES * PB_STAGE_BYTES - (double)g.W * 4) / (4.0 * g.lmax);
+  const double reg_rows = (double)(PB_CU * PB_CONS_THREADS * 4) * 0.94 / (per_row * 1.03 + 0.05);
+  int rs = rows_per_consumer > 0 ? rows_per_consumer : (int)std::min(8000.0, std::max(32.0, std::min(smem_rows, reg_rows) - 8.0));
   g.n_panel = (int)((A->n_rows + (int64_t)g.n_prod * rs - 1) / ((int64_t)g.n_prod * rs));
   g.RS = (int)((A->n_rows + (int64_t)g.n_prod * g.n_panel - 1) / ((int64_t)g.n_prod * g.n_panel));
-  SHB_REQUIRE(g.RS <= 65535, "rows_per_consumer too large");
+  if ((int64_t)g.RS * g.lmax + 32 > 65535 || n_rows_too_many(g)) {
+    shb_pb_free(pb);
+    shb_set_error("invalid argument: rows_per_consumer too large (%d rows x %d words)", g.RS, g.lmax);
+    return SHB_ERR_INVALID;
+  }
+  g.cbuf_cap = g.RS * g.lmax;
   const int64_t n_groups = (int64_t)g.n_pass * g.n_panel;
   const int64_t n_units = n_groups * g.n_prod;       // (pass, p, panel) on the producer side, (group, s) on the consumer side
   const int64_t n_buckets = n_units * g.n_prod;      // pieces
   const int64_t n_keys2 = n_units * g.RS;            // (group, s, local row)
-  SHB_REQUIRE(n_buckets < (int64_t)0x7fffffff && n_keys2 < (int64_t)0x7fffffff, "operator too large for the blocked layout");
+  if (!(n_buckets < (int64_t)0x7fffffff && n_keys2 < (int64_t)0x7fffffff)) {
+    shb_pb_free(pb);
+    shb_set_error("operator too large for the blocked layout");
+    return SHB_ERR_TOO_LARGE;
+  }
   const int64_t nnz = A->nnz;
 
   uint32_t *keys = nullptr, *keys_s = nullptr, *src = nullptr, *perm = nullptr;
@@ -163,7 +231,6 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   int32_t *piece_start = nullptr, *piece_ppos = nullptr, *piece_cpos = nullptr, *bound2 = nullptr, *d_max = nullptr;
   void *cub_tmp = nullptr;
   size_t cub_bytes = 0;
-  shb_pb *pb = new shb_pb();
   int status = SHB_OK;
   std::vector<int32_t> h_piece, h_ppos, h_cpos, h_uchunk, h_cons, h_delta;
   std::vector<uint4> h_desc;
@@ -191,7 +258,8 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     PB_CUDA(cudaMemsetAsync(d_max, 0, 4, c->stream));
     const int cap_blocks = c->prop.multiProcessorCount * 32;
     const unsigned grid = (unsigned)std::min<int64_t>((A->n_rows + 255) / 256, cap_blocks);
-    pb_keys_kernel<<<grid, 256, 0, c->stream>>>(g, A->row_ptr, A->col, A->n_rows, (uint32_t)A->n_cols, keys, src, lrow_tmp);
+    pb_keys_kernel<<<grid, 256, 0, c->stream>>>(g, A->row_ptr, A->col, A->n_rows, (uint32_t)A->n_cols, pb->long_bits, keys, src,
+                                                lrow_tmp);
     PB_CUDA(cudaGetLastError());
     // all 32 key bits: the invalid key (all ones) must sort last
     PB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys_s, src, perm, (int)nnz, 0, 32, c->stream));
@@ -296,7 +364,6 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     PB_CUDA(cudaMalloc(&pb->delta, h_delta.size() * 4));
     PB_CUDA(cudaMalloc(&pb->uchunk, (size_t)(n_units + 1) * 4));
     PB_CUDA(cudaMalloc(&pb->cons_start, (size_t)(n_units + 1) * 4));
-    PB_CUDA(cudaMalloc(&pb->crp, (size_t)n_units * pb_crp_stride(g.RS) * 2));
     PB_CUDA(cudaMalloc(&pb->partial, (size_t)A->n_rows * 4));
     PB_CUDA(cudaMalloc(&pb->sync, (size_t)(2 * n_groups + 1) * 4));
     PB_CUDA(cudaMemsetAsync(pb->sync, 0, (size_t)(2 * n_groups + 1) * 4, c->stream));
@@ -320,18 +387,16 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     } else {
       PB_CUDA(cudaMemsetAsync(bound2, 0, (size_t)(n_keys2 + 1) * 4, c->stream));
     }
-    pb_crp_kernel<<<(unsigned)std::min<int64_t>((n_units * pb_crp_stride(g.RS) + 255) / 256, cap_blocks), 256, 0, c->stream>>>(
-        g, bound2, n_units, pb->crp, d_max);
+    pb_max_unit_kernel<<<(unsigned)std::min<int64_t>((n_units + 255) / 256, cap_blocks), 256, 0, c->stream>>>(g, bound2, n_units, d_max);
     PB_CUDA(cudaGetLastError());
     PB_CUDA(cudaMemcpyAsync(&pb->max_unit, d_max, 4, cudaMemcpyDeviceToHost, c->stream));
-    PB_CUDA(cudaStreamSynchronize(c->stream));  // max_unit is needed for the dump slot; the host staging vectors go out of scope
-    g.cbuf_cap = std::max(32, (pb->max_unit + 31) & ~31);
+    PB_CUDA(cudaStreamSynchronize(c->stream));  // the host staging vectors go out of scope
     g.depth = (int)std::min<int64_t>(n_groups, 4);
     if (const char *e = getenv("SHB_PB_DEPTH")) g.depth = (int)std::min<int64_t>(n_groups, std::max(1, std::min(PB_MAX_DEPTH, atoi(e))));
-    if (pb->max_unit > 65000 || pb_smem_bytes(g) > PB_SMEM_LIMIT) {
-      shb_set_error("blocked layout does not fit shared memory: largest consumer unit %d entries, %zu bytes needed "
-                    "(rows_per_consumer %d; the schedule suits operators with balanced rows and columns)",
-                    pb->max_unit, pb_smem_bytes(g), g.RS);
+    // (a unit larger than one round of consumer registers still runs, in extra rounds)
+    if (pb_smem_bytes(g) > PB_SMEM_LIMIT) {
+      shb_set_error("blocked layout does not fit shared memory: %zu bytes needed (rows_per_consumer %d, %d words per row)",
+                    pb_smem_bytes(g), g.RS, g.lmax);
       status = SHB_ERR_UNSUPPORTED;
       goto done;
     }
@@ -348,7 +413,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     pb->ring_depth_alloc = g.depth;
     pb->g = g;
     pb->device_bytes = (uint64_t)pb->cap * (2 + (A->val ? 4 : 0)) + (uint64_t)pb->ccap * 2 + h_desc.size() * 16 + h_delta.size() * 4 +
-                       (uint64_t)(n_units + 1) * 8 + (uint64_t)n_units * pb_crp_stride(g.RS) * 2 +
+                       (uint64_t)(n_units + 1) * 8 + (uint64_t)A->n_rows * 4 + (uint64_t)(A->n_rows + 31) / 32 * 4 +
                        (uint64_t)g.depth * ((uint64_t)g.slot_cap + PB_CHUNK) * 4 + (uint64_t)A->n_rows * 4;
   }
 done:

@@ -78,10 +78,8 @@ struct shb_pb {
   uint64_t device_bytes = 0;
 };
 
-#define PB_THREADS 768        // launched with 80 registers per thread (768 x 80 = 61440: the CTA's pool)
-#define PB_PROD_THREADS 256   // two producer warpgroups; setmaxnreg moves 4096 registers from the consumers to them
-#define PB_PROD_REGS 96
-#define PB_CONS_REGS 72
+#define PB_THREADS 896        // 72 registers per thread (896 x 72 = 64512 of the SM's 65536)
+#define PB_PROD_THREADS 384   // twelve producer warps: the role is bound by each warp's serial instruction stream
 #define PB_CONS_THREADS (PB_THREADS - PB_PROD_THREADS)
 #define PB_PROD_WARPS (PB_PROD_THREADS / 32)
 #define PB_CU 5               // quads a consumer thread holds in registers: one round = PB_CU x 512 x 4 = 10240 entries
@@ -116,6 +114,13 @@ __device__ __forceinline__ void pb_bar(int id, int count) { asm volatile("bar.sy
 __device__ __forceinline__ uint32_t pb_ld_acquire(const uint32_t *p) {
   uint32_t v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// relaxed poll (no L1 invalidate, no fence): used where the poller only WRITES afterwards -- a producer waiting for a ring
+// slot to be drained: the consumers' reads were complete before they bumped the counter, so a later store cannot reach them
+__device__ __forceinline__ uint32_t pb_ld_relaxed(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void pb_red_release(uint32_t *p) {
@@ -167,21 +172,26 @@ __device__ __forceinline__ void pb_mbar_wait(uint64_t *bar, uint32_t parity) {
 // sector: 32 wavefronts for a 1 KB value chunk, 63 % of the producer's shared-memory traffic.  A 1-D bulk copy
 // (cp.async.bulk, the TMA unit) lands whole lines, is issued by ONE lane, and completes on an mbarrier per slot.
 // Slot layout (PB_STAGE_BYTES): [512 B local columns: lane l owns bytes 16 l ..][512 B values 0-3 of every lane's
-// 8 -- i.e. the chunk's values in stream order occupy 1 KB: lane l owns bytes 32 l .. 32 l + 31][16 B flag word].
-#define PB_STAGES 4
-#define PB_STAGE_BYTES 1552
+// 8 -- i.e. the chunk's values in stream order occupy 1 KB: lane l owns bytes 32 l .. 32 l + 31][48 B descriptor:
+// piece-start flags (64 bits), ordinal of the first piece, number of pieces, and the deltas of the first 8 pieces].
+#define PB_STAGES 3
+#define PB_STAGE_BYTES 1584
+#define PB_INLINE_DELTAS 8  // deltas of the first pieces touching a chunk travel in its descriptor (48 bytes)
 
-// the piece of each of the lane's two quads (pieces started up to and including the quad, minus one) and the
-// pieces' deltas: issued one chunk ahead of the stores that need them
+// the piece of each of the lane's two quads and the pieces' deltas.  The descriptor lists the pieces TOUCHING the chunk in
+// order (the first may have started in an earlier chunk: then flag bit 0 is clear); the deltas of the first
+// PB_INLINE_DELTAS of them sit in the descriptor itself (shared memory), the rest come from the global table.
 template <class T>
-__device__ __forceinline__ void pb_stage_deltas(const unsigned char *st, const PbArgs<T> &c, int lane, bool pred, int &d0, int &d1) {
+__device__ __forceinline__ void pb_stage_deltas(const unsigned char *st, const PbArgs<T> &c, int lane, int &d0, int &d1) {
   const uint4 d = *reinterpret_cast<const uint4 *>(st + 1536);
+  const int *inl = reinterpret_cast<const int *>(st + 1552);
   const uint64_t flags = ((uint64_t)d.y << 32) | (uint64_t)d.x;
   const int q0 = lane * 2;
-  const int ord0 = max(0, (int)d.z + __popcll(flags & ((2ull << q0) - 1ull)) - 1);
-  const int ord1 = ord0 + (int)((flags >> (q0 + 1)) & 1ull);
-  d0 = pred ? __ldg(c.delta + ord0) : 0;
-  d1 = pred ? __ldg(c.delta + ord1) : 0;
+  const int i0 = __popcll(flags & ((2ull << q0) - 1ull)) - (int)(d.x & 1u);  // index among the pieces touching the chunk
+  const int i1 = i0 + (int)((flags >> (q0 + 1)) & 1ull);
+  const int base = (int)d.z - 1 + (int)(d.x & 1u);  // ordinal of touching piece 0 in the global table
+  d0 = i0 < PB_INLINE_DELTAS ? inl[i0] : __ldg(c.delta + base + i0);
+  d1 = i1 < PB_INLINE_DELTAS ? inl[i1] : __ldg(c.delta + base + i1);
 }
 
 // gather, multiply and store one chunk into ring slot `ring` (consumer order)
@@ -213,8 +223,8 @@ __device__ __forceinline__ void pb_stage_process(const unsigned char *st, const 
 
 // ---------------------------------------------------------------------------------------------
 // producer role: PB_PROD_THREADS threads (two warpgroups), named barrier 1 (twice per pass, around the x slice
-// load).  Per warp: the streams of chunks k+2 and k+3 are in flight (bulk copies), chunk k+1 has landed and its
-// deltas are being fetched, chunk k is gathered, multiplied and stored.
+// load).  Per warp: the streams of chunks k+1 and k+2 are in flight (bulk copies),
+// chunk k is gathered, multiplied and stored (its piece deltas come with its descriptor).
 // ---------------------------------------------------------------------------------------------
 template <class S, bool HAS_VAL>
 __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
@@ -239,10 +249,10 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
       const uint32_t st_i = issued % PB_STAGES;
       unsigned char *st = wst + st_i * PB_STAGE_BYTES;
       const int64_t i0 = (int64_t)cc * PB_CHUNK;
-      pb_mbar_expect_tx(sbar + st_i, HAS_VAL ? 1552u : 528u);
+      pb_mbar_expect_tx(sbar + st_i, HAS_VAL ? 1584u : 560u);
       pb_bulk_g2s(st, c.lcol + i0, 512u, sbar + st_i);
       if (HAS_VAL) pb_bulk_g2s(st + 512, c.val + i0, 1024u, sbar + st_i);
-      pb_bulk_g2s(st + 1536, c.chunk_desc + cc, 16u, sbar + st_i);
+      pb_bulk_g2s(st + 1536, c.chunk_desc + 3 * (int64_t)cc, 48u, sbar + st_i);
     }
     ++issued;
   };
@@ -252,10 +262,12 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
   };
 
   // the warp's arrival at the end of its share of a panel; the CTA's last arrival publishes the panel
+  // (each warp orders its stores at CTA scope before its count; the last one fences at GPU scope and releases: the same
+  //  pattern as a __syncthreads() followed by one thread's __threadfence() + atomic -- fence cumulativity covers the others)
   auto arrive = [&](int g) {
     __syncwarp();
     if (lane == 0) {
-      __threadfence();
+      __threadfence_block();
       const uint32_t old = atomicAdd(&arr[g % PB_ARR], 1u);
       if ((old % NW) == NW - 1) {
         __threadfence();
@@ -270,14 +282,14 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
   int pre_g = -1;
   auto precheck = [&](int g) {
     if (fused && g >= c.g.depth && g < n_groups) {
-      pre = pb_ld_acquire(c.consumed + (g - c.g.depth));
+      pre = pb_ld_relaxed(c.consumed + (g - c.g.depth));
       pre_g = g;
     }
   };
   auto wait_slot = [&](int g) {
     if (fused && g >= c.g.depth && !(pre_g == g && pre >= (uint32_t)c.g.n_prod)) {
       if (lane == 0)
-        while (pb_ld_acquire(c.consumed + (g - c.g.depth)) < (uint32_t)c.g.n_prod) __nanosleep(40);
+        while (pb_ld_relaxed(c.consumed + (g - c.g.depth)) < (uint32_t)c.g.n_prod) __nanosleep(100);
       __syncwarp();
     }
   };
@@ -304,10 +316,9 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
     int ce = __ldg(c.uchunk + ub + 1);                                 // end chunk of the current unit
     int ce_next = c.g.n_panel > 1 ? __ldg(c.uchunk + ub + 2) : c_end;  // ... and of the one after
     int cc = c_begin + warp;
-    // the streams of the first three chunks go out while the slice is still landing
+    // the streams of the first two chunks go out while the slice is still landing
     if (cc < c_end) issue(cc);
     if (cc + NW < c_end) issue(cc + NW);
-    if (cc + 2 * NW < c_end) issue(cc + 2 * NW);
     if (bulk > 0) {
       pb_mbar_wait(xbar, xphase & 1u);
       ++xphase;
@@ -335,38 +346,16 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
         need_wait = false;
       }
     };
-    // two steps per trip so that the deltas fetched for the next chunk sit in their own registers until they are used
-    // (a rotating copy `d = next` would wait for the load at once)
-    int e0 = 0, e1 = 0, f0 = 0, f1 = 0;
-    uint32_t cur = waited;  // ring position of the chunk being processed
-    if (cc < c_end) {
-      await();
-      pb_stage_deltas(wst + (cur % PB_STAGES) * PB_STAGE_BYTES, c, lane, true, e0, e1);
-    }
     while (cc < c_end) {
-      // ---- even step: deltas (e0, e1) belong to chunk cc; fetch (f0, f1) for chunk cc + NW
-      __syncwarp();  // every lane is past its reads of the slot chunk cc + 3 NW is about to overwrite
-      if (cc + 3 * NW < c_end) issue(cc + 3 * NW);
+      __syncwarp();  // every lane is past its reads of the slot chunk cc + 2 NW is about to overwrite
+      if (cc + 2 * NW < c_end) issue(cc + 2 * NW);
       advance();
-      if (cc + NW < c_end) {
-        await();
-        pb_stage_deltas(wst + ((cur + 1) % PB_STAGES) * PB_STAGE_BYTES, c, lane, true, f0, f1);
-      }
-      pb_stage_process<S, HAS_VAL>(wst + (cur % PB_STAGES) * PB_STAGE_BYTES, xs, ring, cc, lane, e0, e1);
+      const unsigned char *st = wst + (waited % PB_STAGES) * PB_STAGE_BYTES;
+      await();
+      int d0, d1;
+      pb_stage_deltas(st, c, lane, d0, d1);
+      pb_stage_process<S, HAS_VAL>(st, xs, ring, cc, lane, d0, d1);
       cc += NW;
-      ++cur;
-      if (cc >= c_end) break;
-      // ---- odd step: (f0, f1) belong to chunk cc; fetch (e0, e1) for chunk cc + NW
-      __syncwarp();
-      if (cc + 3 * NW < c_end) issue(cc + 3 * NW);
-      advance();
-      if (cc + NW < c_end) {
-        await();
-        pb_stage_deltas(wst + ((cur + 1) % PB_STAGES) * PB_STAGE_BYTES, c, lane, true, e0, e1);
-      }
-      pb_stage_process<S, HAS_VAL>(wst + (cur % PB_STAGES) * PB_STAGE_BYTES, xs, ring, cc, lane, f0, f1);
-      cc += NW;
-      ++cur;
     }
     // the panel of the warp's last chunk, then the panels it has no chunks in
     for (; panel < c.g.n_panel; ++panel) {
@@ -540,12 +529,8 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   __syncthreads();
   bool differs = false;
   if (threadIdx.x < PB_PROD_THREADS) {
-    // the CTA's register pool is fixed at launch (768 threads x 80): the four consumer warpgroups hand 8 registers per
-    // thread back (512 x 8 = 4096) and the two producer warpgroups take them (256 x 16 = 4096); inc blocks until then
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(PB_PROD_REGS));
     if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, sbar, pstage, threadIdx.x);
   } else {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PB_CONS_REGS));
     if (c.roles & PB_ROLE_CONSUME) pb_consume<S, LQ>(c, a, cbuf, flag_s, threadIdx.x - PB_PROD_THREADS, differs);
   }
   shb_publish_changed(a.ctl, differs);

@@ -233,7 +233,8 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   size_t cub_bytes = 0;
   int status = SHB_OK;
   std::vector<int32_t> h_piece, h_ppos, h_cpos, h_uchunk, h_cons, h_delta;
-  std::vector<uint4> h_desc;
+  std::vector<uint4> h_desc;   // one per chunk while the flags are collected
+  std::vector<uint32_t> h_desc48;  // 12 words per chunk: flags, first ordinal, piece count, 8 inline deltas
 #define PB_CUDA(call)                                                                                   \
   do {                                                                                                  \
     cudaError_t _e = (call);                                                                            \
@@ -355,12 +356,29 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
       }
       pb->n_pieces = (int64_t)h_delta.size();
       if (h_delta.empty()) h_delta.push_back(0);
+      // the descriptor a producer warp reads with the chunk: flags, ordinal of the first piece STARTED in or after the
+      // chunk, number of pieces touching it, and the deltas of the first PB_INLINE_DELTAS of those (the first one may
+      // have started in an earlier chunk: flag bit 0 clear)
+      h_desc48.assign((size_t)n_chunks * 12, 0u);
+      for (int64_t ch = 0; ch < n_chunks; ++ch) {
+        const uint4 d = h_desc[(size_t)ch];
+        uint32_t *o = &h_desc48[(size_t)ch * 12];
+        const int starts = __builtin_popcount(d.x) + __builtin_popcount(d.y);
+        const int carry = (d.x & 1u) ? 0 : 1;
+        const int64_t base = (int64_t)d.z - carry;  // ordinal of touching piece 0
+        const int touching = starts + carry;
+        o[0] = d.x; o[1] = d.y; o[2] = d.z; o[3] = (uint32_t)touching;
+        for (int j = 0; j < PB_INLINE_DELTAS && j < touching; ++j) {
+          const int64_t ord = base + j;
+          o[4 + j] = (ord >= 0 && ord < (int64_t)h_delta.size()) ? (uint32_t)h_delta[(size_t)ord] : 0u;
+        }
+      }
     }
 
     PB_CUDA(cudaMalloc(&pb->lcol, (size_t)pb->cap * 2));
     PB_CUDA(cudaMalloc(&pb->slot, (size_t)pb->ccap * 2));
     if (A->val) PB_CUDA(cudaMalloc(&pb->val, (size_t)pb->cap * 4));
-    PB_CUDA(cudaMalloc(&pb->chunk_desc, h_desc.size() * sizeof(uint4)));
+    PB_CUDA(cudaMalloc(&pb->chunk_desc, h_desc48.size() * 4));
     PB_CUDA(cudaMalloc(&pb->delta, h_delta.size() * 4));
     PB_CUDA(cudaMalloc(&pb->uchunk, (size_t)(n_units + 1) * 4));
     PB_CUDA(cudaMalloc(&pb->cons_start, (size_t)(n_units + 1) * 4));
@@ -371,7 +389,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     if (pb->val) PB_CUDA(cudaMemsetAsync(pb->val, 0, (size_t)pb->cap * 4, c->stream));
     PB_CUDA(cudaMemcpyAsync(piece_ppos, h_ppos.data(), (size_t)n_buckets * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(piece_cpos, h_cpos.data(), (size_t)n_buckets * 4, cudaMemcpyHostToDevice, c->stream));
-    PB_CUDA(cudaMemcpyAsync(pb->chunk_desc, h_desc.data(), h_desc.size() * sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+    PB_CUDA(cudaMemcpyAsync(pb->chunk_desc, h_desc48.data(), h_desc48.size() * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(pb->delta, h_delta.data(), h_delta.size() * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(pb->uchunk, h_uchunk.data(), (size_t)(n_units + 1) * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(pb->cons_start, h_cons.data(), (size_t)(n_units + 1) * 4, cudaMemcpyHostToDevice, c->stream));
@@ -412,7 +430,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     PB_CUDA(cudaMalloc(&pb->ring, (size_t)g.depth * ((size_t)g.slot_cap + PB_CHUNK) * 4));
     pb->ring_depth_alloc = g.depth;
     pb->g = g;
-    pb->device_bytes = (uint64_t)pb->cap * (2 + (A->val ? 4 : 0)) + (uint64_t)pb->ccap * 2 + h_desc.size() * 16 + h_delta.size() * 4 +
+    pb->device_bytes = (uint64_t)pb->cap * (2 + (A->val ? 4 : 0)) + (uint64_t)pb->ccap * 2 + h_desc48.size() * 4 + h_delta.size() * 4 +
                        (uint64_t)(n_units + 1) * 8 + (uint64_t)A->n_rows * 4 + (uint64_t)(A->n_rows + 31) / 32 * 4 +
                        (uint64_t)g.depth * ((uint64_t)g.slot_cap + PB_CHUNK) * 4 + (uint64_t)A->n_rows * 4;
   }

@@ -394,6 +394,8 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
   const int RS = c.g.RS;
   const uint32_t zb = shb_bits<T>(S::zero());
   const uint4 zero4 = make_uint4(zb, zb, zb, zb);
+  const bool plain = a.n_out == 1 && a.use_y == 0 && a.ctl.changed == nullptr;
+  T *const out0 = a.out[0] + a.row_offset;
 
   // every word of the row buffer starts as the semiring zero; the reduction puts the zeros back as it reads
   for (int i = tid * 4; i < c.g.cbuf_cap + 32; i += NT * 4) *reinterpret_cast<uint4 *>(cbuf + i) = zero4;
@@ -459,40 +461,67 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
     have = *flag_s != 0u;
     const bool last = pass == c.g.n_pass - 1;
     constexpr int RPT = 5;  // rows per thread per sweep (5 x 512 covers the usual unit in one sweep)
-    for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
-      T part[RPT];
-      uint32_t lbits[RPT];
-      // carried sums and long-row bits are fetched BEFORE the next unit's loads go out: a wait on them must not end
-      // up behind those loads on a shared scoreboard
+    // the row's lmax words out of the buffer, the semiring zero back in, the sum on top of `acc`
+    auto row_sum = [&](int i, T acc) {
+      uint4 v[LQ];
 #pragma unroll
-      for (int k = 0; k < RPT; ++k) {
-        const int i = i0 + tid + k * NT;
-        part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
-        lbits[k] = i < nr ? __ldg(c.long_bits + ((r0 + i) >> 5)) : 0u;
+      for (int q = 0; q < LQ; ++q) {
+        uint4 *w = reinterpret_cast<uint4 *>(cbuf + (4 * q) * RS + 4 * i);
+        v[q] = *w;
+        *w = zero4;
       }
-      if (i0 == 0 && have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
 #pragma unroll
-      for (int k = 0; k < RPT; ++k) {
-        const int i = i0 + tid + k * NT;
-        if (i < nr) {
-          uint4 v[LQ];
+      for (int q = 0; q < LQ; ++q) {
+        acc = S::add(acc, shb_from_bits<T>(v[q].x));
+        acc = S::add(acc, shb_from_bits<T>(v[q].y));
+        acc = S::add(acc, shb_from_bits<T>(v[q].z));
+        acc = S::add(acc, shb_from_bits<T>(v[q].w));
+      }
+      return acc;
+    };
+    if (plain) {
+      // one destination, no y, no convergence test (the plain SpMV call): the epilogue is one expression and the long
+      // rows need no special care -- pb_long_rows_kernel runs after this kernel and overwrites them
+      for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
+        T part[RPT];
 #pragma unroll
-          for (int q = 0; q < LQ; ++q) {
-            uint4 *w = reinterpret_cast<uint4 *>(cbuf + (4 * q) * RS + 4 * i);
-            v[q] = *w;
-            *w = zero4;
-          }
-          T acc = part[k];
+        for (int k = 0; k < RPT; ++k) {
+          const int i = i0 + tid + k * NT;
+          part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
+        }
+        if (i0 == 0 && have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
 #pragma unroll
-          for (int q = 0; q < LQ; ++q) {
-            acc = S::add(acc, shb_from_bits<T>(v[q].x));
-            acc = S::add(acc, shb_from_bits<T>(v[q].y));
-            acc = S::add(acc, shb_from_bits<T>(v[q].z));
-            acc = S::add(acc, shb_from_bits<T>(v[q].w));
-          }
-          if (!((lbits[k] >> ((r0 + i) & 31)) & 1u)) {  // long rows belong to pb_long_rows_kernel
-            if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
+        for (int k = 0; k < RPT; ++k) {
+          const int i = i0 + tid + k * NT;
+          if (i < nr) {
+            const T acc = row_sum(i, part[k]);
+            if (last) out0[r0 + i] = S::epi(acc, a.alpha, S::zero(), a.beta);
             else c.partial[r0 + i] = acc;
+          }
+        }
+      }
+    } else {
+      for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
+        T part[RPT];
+        uint32_t lbits[RPT];
+        // carried sums and long-row bits are fetched BEFORE the next unit's loads go out: a wait on them must not end
+        // up behind those loads on a shared scoreboard
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) {
+          const int i = i0 + tid + k * NT;
+          part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
+          lbits[k] = i < nr ? __ldg(c.long_bits + ((r0 + i) >> 5)) : 0u;
+        }
+        if (i0 == 0 && have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) {
+          const int i = i0 + tid + k * NT;
+          if (i < nr) {
+            const T acc = row_sum(i, part[k]);
+            if (!((lbits[k] >> ((r0 + i) & 31)) & 1u)) {  // long rows belong to pb_long_rows_kernel
+              if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
+              else c.partial[r0 + i] = acc;
+            }
           }
         }
       }

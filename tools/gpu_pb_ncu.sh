@@ -9,13 +9,18 @@ echo "== default"; timeout 100 python tools/pb_bench.py --rs 0 2>&1 | cut -c1-42
 echo "== produce only"; SHB_PB_SPLIT=p timeout 100 python tools/pb_bench.py --rs 0 --only-blocked --no-check 2>&1 | grep "blocked\|Error" | cut -c1-120
 echo "== consume only"; SHB_PB_SPLIT=c timeout 100 python tools/pb_bench.py --rs 0 --only-blocked --no-check 2>&1 | grep "blocked\|Error" | cut -c1-120
 CMD="python tools/pb_bench.py --rs 0 --only-blocked --no-check --reps 1"
-echo "== ncu fused"
-timeout 100 $CMD > gpurun_out/pb_plain.log 2>&1 && \
-timeout 500 ncu --set full --clock-control none --import-source on -k regex:pb_fused -s 2 -c 1 -o gpurun_out/prof_pb_fused $CMD > gpurun_out/ncu_pb_fused.log 2>&1
-echo "rc=$?"
-echo "== ncu split"
-export SHB_PB_SPLIT=1
-timeout 100 $CMD > gpurun_out/pb_plain_split.log 2>&1 && \
-timeout 500 ncu --set full --clock-control none --import-source on -k regex:pb_fused -s 4 -c 2 -o gpurun_out/prof_pb_split $CMD > gpurun_out/ncu_pb_split.log 2>&1
-echo "rc=$?"
+# one ncu capture per call: NCU=fused (default) | split | none
+case "${NCU:-fused}" in
+fused)
+  echo "== ncu fused"
+  timeout 100 $CMD > gpurun_out/pb_plain.log 2>&1 && \
+  timeout 500 ncu --set full --clock-control none --import-source on -k regex:pb_fused -s 2 -c 1 -o gpurun_out/prof_pb_fused $CMD > gpurun_out/ncu_pb_fused.log 2>&1
+  echo "rc=$?" ;;
+split)
+  echo "== ncu split"
+  export SHB_PB_SPLIT=1
+  timeout 100 $CMD > gpurun_out/pb_plain_split.log 2>&1 && \
+  timeout 500 ncu --set full --clock-control none --import-source on -k regex:pb_fused -s 4 -c 2 -o gpurun_out/prof_pb_split $CMD > gpurun_out/ncu_pb_split.log 2>&1
+  echo "rc=$?" ;;
+esac
 ls -la gpurun_out | grep prof_pb

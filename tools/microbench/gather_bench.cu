@@ -31,14 +31,14 @@ __device__ __forceinline__ uint32_t mix(uint32_t h) {
   return h;
 }
 
-// MODE 0 local, 1 dsmem, 2 global
+// MODE 0 local, 1 dsmem, 2 global, 3 dsmem float add (red.shared::cluster), 4 local float add (red.shared)
 template <int MODE>
 __global__ void __launch_bounds__(THREADS, 1) gather_kernel(const uint32_t *__restrict__ table, uint32_t table_words,
                                                             uint32_t *__restrict__ sink, unsigned long long *__restrict__ cycles) {
   extern __shared__ uint32_t sm[];
   for (int i = threadIdx.x; i < WORDS; i += THREADS) sm[i] = mix(i + blockIdx.x * WORDS);
   uint32_t csize = 1;
-  if (MODE == 1) {
+  if (MODE == 1 || MODE == 3) {
     cg::cluster_group cl = cg::this_cluster();
     csize = cl.num_blocks();
     cl.sync();
@@ -64,6 +64,16 @@ __global__ void __launch_bounds__(THREADS, 1) gather_kernel(const uint32_t *__re
         uint32_t remote;
         asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(rank));
         asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v[k]) : "r"(remote));
+      } else if (MODE == 3) {
+        const uint32_t local = sbase + 4 * w;
+        const uint32_t rank = (h >> 2) & (csize - 1);
+        uint32_t remote;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(rank));
+        asm volatile("red.relaxed.cluster.shared::cluster.add.f32 [%0], %1;" ::"r"(remote), "f"(1.0f) : "memory");
+        v[k] = 0;
+      } else if (MODE == 4) {
+        asm volatile("red.relaxed.cta.shared::cta.add.f32 [%0], %1;" ::"r"(sbase + 4 * w), "f"(1.0f) : "memory");
+        v[k] = 0;
       } else {
         v[k] = __ldg(table + (r & (table_words - 1)));
       }
@@ -71,8 +81,10 @@ __global__ void __launch_bounds__(THREADS, 1) gather_kernel(const uint32_t *__re
 #pragma unroll
     for (int k = 0; k < ILP; ++k) acc += v[k];
   }
+  __syncthreads();
   const long long t1 = clock64();
-  if (MODE == 1) cg::this_cluster().sync();
+  if (MODE == 1 || MODE == 3) cg::this_cluster().sync();
+  else __syncthreads();
   if (threadIdx.x == 0) cycles[blockIdx.x] = (unsigned long long)(t1 - t0);
   if (acc == 0x12345678u) sink[0] = acc;
 }
@@ -94,8 +106,8 @@ static void run(const char *name, int cluster, const uint32_t *table, uint32_t t
   at[0].val.clusterDim.y = 1;
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
-  cfg.numAttrs = MODE == 1 ? 1 : 0;
-  if (MODE == 1) {
+  cfg.numAttrs = (MODE == 1 || MODE == 3) ? 1 : 0;
+  if (MODE == 1 || MODE == 3) {
     int max_clusters = 0;
     cudaError_t e = cudaOccupancyMaxActiveClusters(&max_clusters, gather_kernel<MODE>, &cfg);
     if (e != cudaSuccess || max_clusters == 0) {
@@ -143,6 +155,8 @@ int main() {
   CK(cudaMalloc(&cycles, 256 * 8));
   run<0>("local smem", 1, table, table_words, sink, cycles, p.multiProcessorCount);
   for (int c : {2, 4, 8, 16}) run<1>("dsmem", c, table, table_words, sink, cycles, p.multiProcessorCount);
+  run<4>("local smem red.add.f32", 1, table, table_words, sink, cycles, p.multiProcessorCount);
+  for (int c : {2, 8, 16}) run<3>("dsmem red.add.f32", c, table, table_words, sink, cycles, p.multiProcessorCount);
   run<2>("global 64 MB", 1, table, table_words, sink, cycles, p.multiProcessorCount);
   return 0;
 }

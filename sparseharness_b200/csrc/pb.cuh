@@ -66,8 +66,9 @@ struct shb_pb {
   uint4 *chunk_desc = nullptr;   // [cap / PB_CHUNK] {flags lo, flags hi, pieces started before the chunk, 0}
   int32_t *delta = nullptr;      // [n_pieces] ring offset (inside the slot) minus stream position
   int32_t *uchunk = nullptr;     // [n_pass * n_prod * n_panel + 1] first chunk of unit (pass, p, panel)
-  uint16_t *slot = nullptr;      // [ccap] consumer order: position in the consumer's row-sorted buffer
+  uint16_t *slot = nullptr;      // [ccap] consumer order: BYTE offset in the consumer's row-sorted buffer
   int32_t *cons_start = nullptr; // [n_groups * n_prod + 1] start of consumer region (group, s) in `slot`
+  int4 *cdesc = nullptr;         // [n_groups * n_prod] the same as one descriptor per consumer unit (PbArgs::cdesc)
   uint32_t *long_bits = nullptr; // [ceil(n_rows / 32)] bit r: row r is long (computed by pb_long_rows_kernel)
   int32_t *long_rows = nullptr;  // [n_long] their indices
   int64_t n_long = 0;
@@ -100,6 +101,7 @@ template <class T> struct PbArgs {
   const int32_t *uchunk;
   const uint16_t *slot;
   const int32_t *cons_start;
+  const int4 *cdesc;  // [n_groups * n_prod] consumer unit: {first entry in `slot`, quads, offset inside the ring slot, 0}
   const uint32_t *long_bits;
   T *ring;
   T *partial;
@@ -368,24 +370,44 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
 
 // ---------------------------------------------------------------------------------------------
 // consumer role: PB_CONS_THREADS threads, named barrier 2.
-// Per unit:  bar | registers -> row buffer (st.shared per product) | bar | hand the ring slot back |
-//            carried sums | issue the NEXT unit's ring + slot loads into registers | thread per row: 2 x LDS.128,
-//            zeros back, 8 adds, store | ...
-// so the loads of a unit fly while the previous unit is reduced.
+// Per unit:  bar | registers -> row buffer (one st.shared per product, the 16-bit slot IS the byte offset) | bar |
+//            hand the ring slot back | issue the NEXT unit's ring, slot and carried-sum loads into registers |
+//            thread per row: LQ x LDS.128, zeros back, the adds, one store | ...
+// so every global load of a unit flies while the previous unit is reduced, and nothing in the loop divides, converts a
+// generic address or re-derives a unit's extents: those come as one 16-byte descriptor per unit, read a unit ahead.
+// PLAIN = one destination, no y, no convergence test (the plain SpMV call): the epilogue is one expression and the long
+// rows need no care -- pb_long_rows_kernel runs after this kernel and overwrites them.
 // ---------------------------------------------------------------------------------------------
-template <class T> __device__ __forceinline__ void pb_scatter4(T *cbuf, const uint4 &pr, const uint2 &sl) {
-  cbuf[sl.x & 0xffffu] = shb_from_bits<T>(pr.x);
-  cbuf[sl.x >> 16] = shb_from_bits<T>(pr.y);
-  cbuf[sl.y & 0xffffu] = shb_from_bits<T>(pr.z);
-  cbuf[sl.y >> 16] = shb_from_bits<T>(pr.w);
+__device__ __forceinline__ void pb_sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ void pb_sts128(uint32_t addr, const uint4 &v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 pb_lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t pb_ld_cg_b32(const void *p) {
+  uint32_t v;
+  asm volatile("ld.global.cg.b32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void pb_red_relaxed(uint32_t *p) { asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory"); }
+
+__device__ __forceinline__ void pb_scatter4(uint32_t cb, const uint4 &pr, const uint2 &sl) {
+  pb_sts32(cb + (sl.x & 0xffffu), pr.x);
+  pb_sts32(cb + (sl.x >> 16), pr.y);
+  pb_sts32(cb + (sl.y & 0xffffu), pr.z);
+  pb_sts32(cb + (sl.y >> 16), pr.w);
 }
 
-template <class S, int LQ>  // LQ = lmax / 4: 128-bit words per row
+template <class S, int LQ, bool PLAIN>  // LQ = lmax / 4: 128-bit words per row
 __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const SpmvArgs<typename S::T> &a,
                                            typename S::T *cbuf, uint32_t *flag_s, int tid, bool &differs) {
   typedef typename S::T T;
   constexpr int NT = PB_CONS_THREADS;
   constexpr int U = PB_CU;
+  constexpr int RPT = 4;  // rows per thread per sweep (4 x 512 covers the usual unit in one sweep)
   const int s = blockIdx.x;
   const int n_groups = c.g.n_pass * c.g.n_panel;
   const int64_t slot_stride = (int64_t)c.g.slot_cap + PB_CHUNK;
@@ -394,81 +416,113 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
   const int RS = c.g.RS;
   const uint32_t zb = shb_bits<T>(S::zero());
   const uint4 zero4 = make_uint4(zb, zb, zb, zb);
-  const bool plain = a.n_out == 1 && a.use_y == 0 && a.ctl.changed == nullptr;
+  const uint32_t cb = pb_smem_addr(cbuf);
+  const uint32_t qstride = 16u * (uint32_t)RS;  // bytes between a row's consecutive 128-bit words
   T *const out0 = a.out[0] + a.row_offset;
+  // the sync duties (poll the next panel, hand the slot back) go to the LAST warp: it has the fewest rows to reduce
+  const bool syncer = tid == NT - 32;
+  // carried sums are fetched a unit ahead unless the unit ahead is the same panel one pass later (a single row panel)
+  const bool early_carry = c.g.n_panel > 1;
 
   // every word of the row buffer starts as the semiring zero; the reduction puts the zeros back as it reads
-  for (int i = tid * 4; i < c.g.cbuf_cap + 32; i += NT * 4) *reinterpret_cast<uint4 *>(cbuf + i) = zero4;
+  for (int i = tid * 4; i < c.g.cbuf_cap + 32; i += NT * 4) pb_sts128(cb + 4u * (uint32_t)i, zero4);
 
   uint4 pr[U];
   uint2 sl[U];
-  // first-round loads of unit (g, cs, ce, gs): up to U quads per thread
-  auto issue = [&](int g, int cs, int ce, int gs) {
-    const T *ring_u = c.ring + (int64_t)(g % c.g.depth) * slot_stride + (cs - gs);
-    const uint16_t *slot_u = c.slot + cs;
-    const int nq = (ce - cs) >> 2;
+  T part_nxt[RPT];
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) part_nxt[k] = S::zero();
+  // loads of a unit: its first U quads per thread out of ring slot `rslot`, and (later passes) its first RPT carried sums
+  auto issue = [&](const int4 &d, int rslot, int64_t r0n, int nrn, bool carry) {
+    const T *ring_u = c.ring + (int64_t)rslot * slot_stride + d.z;
+    const uint16_t *slot_u = c.slot + d.x;
 #pragma unroll
     for (int k = 0; k < U; ++k) {
       const int q = tid + k * NT;
-      if (q < nq) {
+      if (q < d.y) {
         pr[k] = pb_ld_cg_v4(ring_u + 4 * q);
         sl[k] = pb_ld_stream_v2(slot_u + 4 * q, pol_stream);
       }
     }
+    if (carry) {
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        const int i = tid + k * NT;
+        if (i < nrn) part_nxt[k] = shb_from_bits<T>(pb_ld_cg_b32(c.partial + r0n + i));
+      }
+    }
   };
 
-  int cs = __ldg(c.cons_start + s), ce = __ldg(c.cons_start + s + 1), gs = __ldg(c.cons_start);
+  const int64_t r_step = (int64_t)c.g.n_prod * RS;
+  int4 d = __ldg(c.cdesc + s);  // {first entry of the unit in `slot`, quads, offset inside the ring slot, -}
+  int64_t r0 = (int64_t)s * RS;
+  int rslot = 0;
   bool have = false;  // the registers hold the first round of the current unit
   int pass = 0, panel = 0;
   for (int g = 0; g < n_groups; ++g) {
-    const int64_t u = (int64_t)g * c.g.n_prod + s;
-    const int64_t r0 = ((int64_t)panel * c.g.n_prod + s) * RS;
     const int nr = (int)max((int64_t)0, min((int64_t)RS, a.n_rows - r0));
-    // next unit's extents (their latency hides behind this unit)
-    int cs_n = 0, ce_n = 0, gs_n = 0;
-    if (g + 1 < n_groups) {
-      cs_n = __ldg(c.cons_start + u + c.g.n_prod);
-      ce_n = __ldg(c.cons_start + u + c.g.n_prod + 1);
-      gs_n = __ldg(c.cons_start + (int64_t)(g + 1) * c.g.n_prod);
-    }
-    // carried sums of this unit: towards L2 while the products are scattered
-    if (pass > 0)
-      for (int i = tid * 32; i < nr; i += NT * 32) pb_prefetch_l2(c.partial + r0 + i);
+    // the next unit: descriptor (its latency hides behind this unit), rows, ring slot
+    int4 d_n = make_int4(0, 0, 0, 0);
+    if (g + 1 < n_groups) d_n = __ldg(c.cdesc + (int64_t)(g + 1) * c.g.n_prod + s);
+    const bool wrap = panel + 1 == c.g.n_panel;
+    const int64_t r0_n = wrap ? (int64_t)s * RS : r0 + r_step;
+    const int nr_n = (int)max((int64_t)0, min((int64_t)RS, a.n_rows - r0_n));
+    const int pass_n = pass + (wrap ? 1 : 0);
+    const int rslot_n = rslot + 1 == c.g.depth ? 0 : rslot + 1;
     if (!have) {
-      if (fused && tid == 0)
+      if (fused && syncer)
         while (pb_ld_acquire(c.ready + g) < (uint32_t)c.g.n_prod) __nanosleep(20);
       pb_bar(2, NT);  // ring slot g is complete (and everyone is done reducing unit g - 1)
-      issue(g, cs, ce, gs);
+      issue(d, rslot, r0, nr, early_carry && pass > 0);
     } else {
       pb_bar(2, NT);  // everyone is done reducing unit g - 1: the row buffer holds zeros again
     }
-    {
-      const int nq = (ce - cs) >> 2;
 #pragma unroll
-      for (int k = 0; k < U; ++k)
-        if (tid + k * NT < nq) pb_scatter4<T>(cbuf, pr[k], sl[k]);
-      if (nq > NT * U) {  // units larger than one round (rare geometries): the rest, round by round
-        const T *ring_u = c.ring + (int64_t)(g % c.g.depth) * slot_stride + (cs - gs);
-        const uint16_t *slot_u = c.slot + cs;
-        for (int q = tid + NT * U; q < nq; q += NT) pb_scatter4<T>(cbuf, pb_ld_cg_v4(ring_u + 4 * q), pb_ld_stream_v2(slot_u + 4 * q, pol_stream));
-      }
+    for (int k = 0; k < U; ++k)
+      if (tid + k * NT < d.y) pb_scatter4(cb, pr[k], sl[k]);
+    if (d.y > NT * U) {  // units larger than one round (rare geometries): the rest, round by round
+      const T *ring_u = c.ring + (int64_t)rslot * slot_stride + d.z;
+      const uint16_t *slot_u = c.slot + d.x;
+      for (int q = tid + NT * U; q < d.y; q += NT) pb_scatter4(cb, pb_ld_cg_v4(ring_u + 4 * q), pb_ld_stream_v2(slot_u + 4 * q, pol_stream));
     }
     // is the next unit's ring slot complete already?  one thread looks, the barrier spreads the verdict
-    if (tid == 0) *flag_s = (g + 1 < n_groups && (!fused || pb_ld_acquire(c.ready + g + 1) >= (uint32_t)c.g.n_prod)) ? 1u : 0u;
+    if (syncer) *flag_s = (g + 1 < n_groups && (!fused || pb_ld_acquire(c.ready + g + 1) >= (uint32_t)c.g.n_prod)) ? 1u : 0u;
     pb_bar(2, NT);
-    // the ring slot is drained (its values sit in shared memory): hand it back to the producers
-    if (fused && tid == 0) pb_red_release(c.consumed + g);
+    // the ring slot is drained (every product went through a register into shared memory): hand it back.  Relaxed: the
+    // loads have completed, and the producers only write the slot after seeing the count.
+    if (fused && syncer) pb_red_relaxed(c.consumed + g);
     have = *flag_s != 0u;
     const bool last = pass == c.g.n_pass - 1;
-    constexpr int RPT = 5;  // rows per thread per sweep (5 x 512 covers the usual unit in one sweep)
+    T part[RPT];
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+      part[k] = part_nxt[k];
+      part_nxt[k] = S::zero();
+    }
+    if (!early_carry && pass > 0) {
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        const int i = tid + k * NT;
+        if (i < nr) part[k] = shb_from_bits<T>(pb_ld_cg_b32(c.partial + r0 + i));
+      }
+    }
+    uint32_t lbits[RPT];
+    if (!PLAIN) {
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        const int i = tid + k * NT;
+        lbits[k] = i < nr ? __ldg(c.long_bits + ((r0 + i) >> 5)) : 0u;
+      }
+    }
+    if (have) issue(d_n, rslot_n, r0_n, nr_n, early_carry && pass_n > 0);  // in flight during the reduction below
     // the row's lmax words out of the buffer, the semiring zero back in, the sum on top of `acc`
     auto row_sum = [&](int i, T acc) {
       uint4 v[LQ];
+      const uint32_t ra = cb + 16u * (uint32_t)i;
 #pragma unroll
       for (int q = 0; q < LQ; ++q) {
-        uint4 *w = reinterpret_cast<uint4 *>(cbuf + (4 * q) * RS + 4 * i);
-        v[q] = *w;
-        *w = zero4;
+        v[q] = pb_lds128(ra + q * qstride);
+        pb_sts128(ra + q * qstride, zero4);
       }
 #pragma unroll
       for (int q = 0; q < LQ; ++q) {
@@ -479,65 +533,33 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
       }
       return acc;
     };
-    if (plain) {
-      // one destination, no y, no convergence test (the plain SpMV call): the epilogue is one expression and the long
-      // rows need no special care -- pb_long_rows_kernel runs after this kernel and overwrites them
-      for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
-        T part[RPT];
-#pragma unroll
-        for (int k = 0; k < RPT; ++k) {
-          const int i = i0 + tid + k * NT;
-          part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
-        }
-        if (i0 == 0 && have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
-#pragma unroll
-        for (int k = 0; k < RPT; ++k) {
-          const int i = i0 + tid + k * NT;
-          if (i < nr) {
-            const T acc = row_sum(i, part[k]);
-            if (last) out0[r0 + i] = S::epi(acc, a.alpha, S::zero(), a.beta);
-            else c.partial[r0 + i] = acc;
-          }
-        }
+    auto finish = [&](int i, T acc, uint32_t lb) {
+      if (PLAIN) {
+        if (last) out0[r0 + i] = S::epi(acc, a.alpha, S::zero(), a.beta);
+        else c.partial[r0 + i] = acc;
+      } else if (!((lb >> ((r0 + i) & 31)) & 1u)) {  // long rows belong to pb_long_rows_kernel
+        if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
+        else c.partial[r0 + i] = acc;
       }
-    } else {
-      for (int i0 = 0; i0 < nr; i0 += NT * RPT) {
-        T part[RPT];
-        uint32_t lbits[RPT];
-        // carried sums and long-row bits are fetched BEFORE the next unit's loads go out: a wait on them must not end
-        // up behind those loads on a shared scoreboard
+    };
 #pragma unroll
-        for (int k = 0; k < RPT; ++k) {
-          const int i = i0 + tid + k * NT;
-          part[k] = (pass > 0 && i < nr) ? c.partial[r0 + i] : S::zero();
-          lbits[k] = i < nr ? __ldg(c.long_bits + ((r0 + i) >> 5)) : 0u;
-        }
-        if (i0 == 0 && have) issue(g + 1, cs_n, ce_n, gs_n);  // in flight during the reduction below
-#pragma unroll
-        for (int k = 0; k < RPT; ++k) {
-          const int i = i0 + tid + k * NT;
-          if (i < nr) {
-            const T acc = row_sum(i, part[k]);
-            if (!((lbits[k] >> ((r0 + i) & 31)) & 1u)) {  // long rows belong to pb_long_rows_kernel
-              if (last) shb_finish_row<S>(a, r0 + i, acc, differs);
-              else c.partial[r0 + i] = acc;
-            }
-          }
-        }
-      }
+    for (int k = 0; k < RPT; ++k) {
+      const int i = tid + k * NT;
+      if (i < nr) finish(i, row_sum(i, part[k]), PLAIN ? 0u : lbits[k]);
     }
-    if (nr <= 0 && have) issue(g + 1, cs_n, ce_n, gs_n);
-    cs = cs_n;
-    ce = ce_n;
-    gs = gs_n;
-    if (++panel == c.g.n_panel) {
-      panel = 0;
-      ++pass;
+    for (int i = tid + RPT * NT; i < nr; i += NT) {  // units with more than RPT x 512 rows (rare geometries)
+      const T carried = pass > 0 ? shb_from_bits<T>(pb_ld_cg_b32(c.partial + r0 + i)) : S::zero();
+      finish(i, row_sum(i, carried), PLAIN ? 0u : __ldg(c.long_bits + ((r0 + i) >> 5)));
     }
+    d = d_n;
+    r0 = r0_n;
+    rslot = rslot_n;
+    pass = pass_n;
+    panel = wrap ? 0 : panel + 1;
   }
 }
 
-template <class S, bool HAS_VAL, int LQ>
+template <class S, bool HAS_VAL, int LQ, bool PLAIN>
 __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_constant__ PbArgs<typename S::T> c,
                                                                   const __grid_constant__ SpmvArgs<typename S::T> a) {
   typedef typename S::T T;
@@ -560,7 +582,7 @@ __global__ void __launch_bounds__(PB_THREADS, 1) pb_fused_kernel(const __grid_co
   if (threadIdx.x < PB_PROD_THREADS) {
     if (c.roles & PB_ROLE_PRODUCE) pb_produce<S, HAS_VAL>(c, a, xs, arr, xbar, sbar, pstage, threadIdx.x);
   } else {
-    if (c.roles & PB_ROLE_CONSUME) pb_consume<S, LQ>(c, a, cbuf, flag_s, threadIdx.x - PB_PROD_THREADS, differs);
+    if (c.roles & PB_ROLE_CONSUME) pb_consume<S, LQ, PLAIN>(c, a, cbuf, flag_s, threadIdx.x - PB_PROD_THREADS, differs);
   }
   shb_publish_changed(a.ctl, differs);
   __syncthreads();

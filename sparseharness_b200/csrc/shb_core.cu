@@ -695,6 +695,7 @@ static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> 
   pa.uchunk = pb->uchunk;
   pa.slot = pb->slot;
   pa.cons_start = pb->cons_start;
+  pa.cdesc = pb->cdesc;
   pa.long_bits = pb->long_bits;
   pa.partial = (T *)pb->partial;
   pa.ready = pb->sync;
@@ -708,14 +709,17 @@ static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> 
   }
   pa.ring = (T *)pb->ring;
   const size_t smem = shb_pb_smem_bytes(pb);
-  SHB_CUDA(cudaFuncSetAttribute(pb_fused_kernel<S, HAS_VAL, LQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // the plain call (one destination, no y, no convergence test) has its own instantiation of the consumer
+  const bool plain = a.n_out == 1 && a.use_y == 0 && a.ctl.changed == nullptr;
+  const void *kernel = plain ? (const void *)pb_fused_kernel<S, HAS_VAL, LQ, true> : (const void *)pb_fused_kernel<S, HAS_VAL, LQ, false>;
+  SHB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   SpmvArgs<T> aa = a;
   void *args[] = {&pa, &aa};
   const dim3 grid((unsigned)pb->g.n_prod), block(PB_THREADS);
   if (!split) {
     pa.roles = PB_ROLE_PRODUCE | PB_ROLE_CONSUME;
     pa.reset_sync = 1;
-    SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, LQ>, grid, block, args, smem, c->stream));
+    SHB_CUDA(cudaLaunchCooperativeKernel(kernel, grid, block, args, smem, c->stream));
     if (pb->n_long > 0) {  // the rows the blocked copy leaves out, whole, from the operator's own CSR arrays
       const int blocks = (int)std::min<int64_t>((pb->n_long + 7) / 8, (int64_t)c->prop.multiProcessorCount * 16);
       pb_long_rows_kernel<S, HAS_VAL><<<blocks, 256, 0, c->stream>>>(aa, pb->long_rows, (int)pb->n_long);
@@ -725,12 +729,12 @@ static int launch_blocked(shb_ctx *c, shb_pb *pb, const SpmvArgs<typename S::T> 
     if (split_env[0] != 'c') {
       pa.roles = PB_ROLE_PRODUCE;
       pa.reset_sync = split_env[0] == 'p';
-      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, LQ>, grid, block, args, smem, c->stream));
+      SHB_CUDA(cudaLaunchCooperativeKernel(kernel, grid, block, args, smem, c->stream));
     }
     if (split_env[0] != 'p') {
       pa.roles = PB_ROLE_CONSUME;
       pa.reset_sync = 1;
-      SHB_CUDA(cudaLaunchCooperativeKernel((void *)pb_fused_kernel<S, HAS_VAL, LQ>, grid, block, args, smem, c->stream));
+      SHB_CUDA(cudaLaunchCooperativeKernel(kernel, grid, block, args, smem, c->stream));
       if (pb->n_long > 0) {
         const int blocks = (int)std::min<int64_t>((pb->n_long + 7) / 8, (int64_t)c->prop.multiProcessorCount * 16);
         pb_long_rows_kernel<S, HAS_VAL><<<blocks, 256, 0, c->stream>>>(aa, pb->long_rows, (int)pb->n_long);

@@ -111,7 +111,7 @@ __global__ void pb_fill16_kernel(uint16_t *p, int64_t n, uint16_t v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
-// slot of every entry, written at its consumer-order position: word (k / 4) * 4 RS + 4 * local row + k % 4 of the row
+// slot of every entry, written at its consumer-order position: the BYTE offset of word (k / 4) * 4 RS + 4 * local row + k % 4
 // buffer, k = rank of the entry among its row's entries of this pass (sorted order = (producer, CSR order): fixed)
 __global__ void pb_slots_kernel(PbGeom g, const uint32_t *key2_sorted, const uint32_t *cdst_sorted, const int32_t *bound2,
                                 int64_t n_valid, uint16_t *slot) {
@@ -119,7 +119,7 @@ __global__ void pb_slots_kernel(PbGeom g, const uint32_t *key2_sorted, const uin
     const uint32_t key2 = key2_sorted[j];
     const uint32_t lrow = key2 % (uint32_t)g.RS;
     const uint32_t k = (uint32_t)(j - (int64_t)bound2[key2]);  // < PB_LMAX: longer rows were left out
-    slot[cdst_sorted[j]] = (uint16_t)((k >> 2) * 4u * (uint32_t)g.RS + 4u * lrow + (k & 3u));
+    slot[cdst_sorted[j]] = (uint16_t)(4u * ((k >> 2) * 4u * (uint32_t)g.RS + 4u * lrow + (k & 3u)));
   }
 }
 
@@ -132,6 +132,7 @@ void shb_pb_free(shb_pb *pb) {
   cudaFree(pb->uchunk);
   cudaFree(pb->slot);
   cudaFree(pb->cons_start);
+  cudaFree(pb->cdesc);
   cudaFree(pb->long_bits);
   cudaFree(pb->long_rows);
   cudaFree(pb->ring);
@@ -206,10 +207,13 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   const double per_row = std::max(0.25, (double)A->nnz / (double)A->n_rows / g.n_pass);
   const double smem_rows = ((double)PB_SMEM_LIMIT - 1024.0 - (double)PB_PROD_WARPS * PB_STAGES * PB_STAGE_BYTES - (double)g.W * 4) / (4.0 * g.lmax);
   const double reg_rows = (double)(PB_CU * PB_CONS_THREADS * 4) * 0.94 / (per_row * 1.03 + 0.05);
-  int rs = rows_per_consumer > 0 ? rows_per_consumer : (int)std::min(8000.0, std::max(32.0, std::min(smem_rows, reg_rows) - 8.0));
+  const double slot_rows = 16383.0 / g.lmax;  // 16-bit byte offsets
+  int rs = rows_per_consumer > 0 ? rows_per_consumer
+                                 : (int)std::min(8000.0, std::max(32.0, std::min(std::min(smem_rows, slot_rows), reg_rows) - 8.0));
   g.n_panel = (int)((A->n_rows + (int64_t)g.n_prod * rs - 1) / ((int64_t)g.n_prod * rs));
   g.RS = (int)((A->n_rows + (int64_t)g.n_prod * g.n_panel - 1) / ((int64_t)g.n_prod * g.n_panel));
-  if ((int64_t)g.RS * g.lmax + 32 > 65535 || n_rows_too_many(g)) {
+  // (16-bit slots are byte offsets into the row buffer: at most 16383 words, the dump word included)
+  if ((int64_t)g.RS * g.lmax > 16383 || n_rows_too_many(g)) {
     shb_pb_free(pb);
     shb_set_error("invalid argument: rows_per_consumer too large (%d rows x %d words)", g.RS, g.lmax);
     return SHB_ERR_INVALID;
@@ -233,6 +237,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
   size_t cub_bytes = 0;
   int status = SHB_OK;
   std::vector<int32_t> h_piece, h_ppos, h_cpos, h_uchunk, h_cons, h_delta;
+  std::vector<int4> h_cdesc;   // one per consumer unit
   std::vector<uint4> h_desc;   // one per chunk while the flags are collected
   std::vector<uint32_t> h_desc48;  // 12 words per chunk: flags, first ordinal, piece count, 8 inline deltas
 #define PB_CUDA(call)                                                                                   \
@@ -382,6 +387,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     PB_CUDA(cudaMalloc(&pb->delta, h_delta.size() * 4));
     PB_CUDA(cudaMalloc(&pb->uchunk, (size_t)(n_units + 1) * 4));
     PB_CUDA(cudaMalloc(&pb->cons_start, (size_t)(n_units + 1) * 4));
+    PB_CUDA(cudaMalloc(&pb->cdesc, (size_t)n_units * sizeof(int4)));
     PB_CUDA(cudaMalloc(&pb->partial, (size_t)A->n_rows * 4));
     PB_CUDA(cudaMalloc(&pb->sync, (size_t)(2 * n_groups + 1) * 4));
     PB_CUDA(cudaMemsetAsync(pb->sync, 0, (size_t)(2 * n_groups + 1) * 4, c->stream));
@@ -393,6 +399,14 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     PB_CUDA(cudaMemcpyAsync(pb->delta, h_delta.data(), h_delta.size() * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(pb->uchunk, h_uchunk.data(), (size_t)(n_units + 1) * 4, cudaMemcpyHostToDevice, c->stream));
     PB_CUDA(cudaMemcpyAsync(pb->cons_start, h_cons.data(), (size_t)(n_units + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    h_cdesc.resize((size_t)n_units);
+    for (int64_t gp = 0; gp < n_groups; ++gp)
+      for (int s = 0; s < P; ++s) {
+        const int64_t u = gp * P + s;
+        h_cdesc[(size_t)u] = make_int4(h_cons[(size_t)u], (h_cons[(size_t)u + 1] - h_cons[(size_t)u]) >> 2,
+                                       h_cons[(size_t)u] - h_cons[(size_t)(gp * P)], 0);
+      }
+    PB_CUDA(cudaMemcpyAsync(pb->cdesc, h_cdesc.data(), (size_t)n_units * sizeof(int4), cudaMemcpyHostToDevice, c->stream));
     const unsigned grid_v = (unsigned)std::min<int64_t>((pb->n_valid + 255) / 256 + 1, cap_blocks);
     if (pb->n_valid > 0) {
       // keys / src are free again: they receive the consumer-order keys and positions
@@ -420,7 +434,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     }
     // padding entries of the consumer stream drop their (meaningless) product into the dump word
     pb_fill16_kernel<<<(unsigned)std::min<int64_t>((pb->ccap + 255) / 256, cap_blocks), 256, 0, c->stream>>>(pb->slot, pb->ccap,
-                                                                                                       (uint16_t)g.cbuf_cap);
+                                                                                                       (uint16_t)(4 * g.cbuf_cap));
     PB_CUDA(cudaGetLastError());
     if (pb->n_valid > 0) {
       pb_slots_kernel<<<grid_v, 256, 0, c->stream>>>(g, keys_s, perm, bound2, pb->n_valid, pb->slot);
@@ -431,7 +445,7 @@ SHB_API int shb_csr_build_blocked(shb_ctx *c, shb_csr *A, int rows_per_consumer,
     pb->ring_depth_alloc = g.depth;
     pb->g = g;
     pb->device_bytes = (uint64_t)pb->cap * (2 + (A->val ? 4 : 0)) + (uint64_t)pb->ccap * 2 + h_desc48.size() * 4 + h_delta.size() * 4 +
-                       (uint64_t)(n_units + 1) * 8 + (uint64_t)A->n_rows * 4 + (uint64_t)(A->n_rows + 31) / 32 * 4 +
+                       (uint64_t)(n_units + 1) * 8 + (uint64_t)n_units * 16 + (uint64_t)A->n_rows * 4 + (uint64_t)(A->n_rows + 31) / 32 * 4 +
                        (uint64_t)g.depth * ((uint64_t)g.slot_cap + PB_CHUNK) * 4 + (uint64_t)A->n_rows * 4;
   }
 done:

@@ -788,12 +788,17 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
     case SHB_VARIANT_STREAM: {
       const int nt = (int)A->n_tiles;
       T *ct = (T *)A->carry_tail, *ch = (T *)A->carry_head;
+      // pieces longer than this leave the thread-per-row loop for a warp each (SHB_STREAM_LONG: tuning aid)
+      static const int long_piece = [] {
+        const char *e = getenv("SHB_STREAM_LONG");
+        return e ? std::max(SHB_LONG_PIECE_MIN, std::min(4096, atoi(e))) : SHB_LONG_PIECE;
+      }();
       if (has_val) {
-        if (hints) spmv_stream_kernel<S, true, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch);
-        else spmv_stream_kernel<S, true, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch);
+        if (hints) spmv_stream_kernel<S, true, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
+        else spmv_stream_kernel<S, true, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
       } else {
-        if (hints) spmv_stream_kernel<S, false, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch);
-        else spmv_stream_kernel<S, false, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch);
+        if (hints) spmv_stream_kernel<S, false, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
+        else spmv_stream_kernel<S, false, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
       }
       SHB_CUDA(cudaGetLastError());
       if (A->straddling_rows > 0) {

@@ -207,18 +207,19 @@ __global__ void __launch_bounds__(256) spmv_vector_kernel(const __grid_constant_
 // stream: nnz-split tiles through shared memory
 // ---------------------------------------------------------------------------------------------
 #define SHB_STREAM_THREADS 256
-#define SHB_LONG_PIECE 64
+#define SHB_LONG_PIECE 64      // default: pieces longer than this go to a warp each (phase 3)
+#define SHB_LONG_PIECE_MIN 8   // smallest value the launch argument may take (sizes the shared list)
 __device__ __forceinline__ int shb_pad(int i) { return i + (i >> 5); }  // 1 pad word per 32: conflict-free strides
 
 template <class S, bool HAS_VAL, bool HINTS>
 __global__ void __launch_bounds__(SHB_STREAM_THREADS)
     spmv_stream_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, const int32_t *__restrict__ tile_row,
                        int n_tiles, int32_t nnz, typename S::T *__restrict__ carry_tail,
-                       typename S::T *__restrict__ carry_head) {
+                       typename S::T *__restrict__ carry_head, int long_piece) {
   typedef typename S::T T;
   if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
   __shared__ T prod[SHB_TILE_NNZ + SHB_TILE_NNZ / 32];
-  __shared__ int long_rows[SHB_TILE_NNZ / SHB_LONG_PIECE + 2];
+  __shared__ int long_rows[SHB_TILE_NNZ / SHB_LONG_PIECE_MIN + 2];
   __shared__ int n_long;
   const int tid = threadIdx.x;
   const int t = blockIdx.x;
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
       } else {
         const int ps = max(s, lo), pe = min(e, hi);
         if (pe > ps) {
-          if (pe - ps > SHB_LONG_PIECE) {
+          if (pe - ps > long_piece) {
             long_rows[atomicAdd(&n_long, 1)] = r;
           } else {
             T acc = S::zero();

@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libshb.so")
+# SHB_LIB=checked loads the build with device-side index checks (make -C sparseharness_b200/csrc CHECKED=1)
+LIB_PATH = os.path.join(HERE, "lib", "libshb_checked.so" if os.environ.get("SHB_LIB") == "checked" else "libshb.so")
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

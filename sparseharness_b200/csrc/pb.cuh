@@ -199,9 +199,11 @@ __device__ __forceinline__ void pb_stage_deltas(const unsigned char *st, const P
 // gather, multiply and store one chunk into ring slot `ring` (consumer order)
 template <class S, bool HAS_VAL>
 __device__ __forceinline__ void pb_stage_process(const unsigned char *st, const typename S::T *xs, typename S::T *ring, int cc,
-                                                 int lane, int d0, int d1) {
+                                                 int lane, int d0, int d1, int W, int slot_words) {
   typedef typename S::T T;
   const uint4 lc = *reinterpret_cast<const uint4 *>(st + lane * 16);
+  SHB_DEV_CHECK((int)(lc.x & 0xffffu) < W && (int)(lc.x >> 16) < W && (int)(lc.y & 0xffffu) < W && (int)(lc.y >> 16) < W);
+  SHB_DEV_CHECK((int)(lc.z & 0xffffu) < W && (int)(lc.z >> 16) < W && (int)(lc.w & 0xffffu) < W && (int)(lc.w >> 16) < W);
   uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
   if (HAS_VAL) {
     v0 = *reinterpret_cast<const uint4 *>(st + 512 + lane * 32);
@@ -219,6 +221,7 @@ __device__ __forceinline__ void pb_stage_process(const unsigned char *st, const 
   o1.z = shb_bits<T>(S::mult(x6, HAS_VAL ? shb_from_bits<T>(v1.z) : S::one()));
   o1.w = shb_bits<T>(S::mult(x7, HAS_VAL ? shb_from_bits<T>(v1.w) : S::one()));
   const int i0 = cc * PB_CHUNK + lane * 8;  // < 2^31 (checked at build time)
+  SHB_DEV_CHECK(i0 + d0 >= 0 && i0 + d0 + 4 <= slot_words && i0 + 4 + d1 >= 0 && i0 + 8 + d1 <= slot_words);
   pb_st_v4(ring + (i0 + d0), o0);
   pb_st_v4(ring + (i0 + 4 + d1), o1);
 }
@@ -356,7 +359,7 @@ __device__ __forceinline__ void pb_produce(const PbArgs<typename S::T> &c, const
       await();
       int d0, d1;
       pb_stage_deltas(st, c, lane, d0, d1);
-      pb_stage_process<S, HAS_VAL>(st, xs, ring, cc, lane, d0, d1);
+      pb_stage_process<S, HAS_VAL>(st, xs, ring, cc, lane, d0, d1, c.g.W, (int)slot_stride);
       cc += NW;
     }
     // the panel of the warp's last chunk, then the panels it has no chunks in
@@ -394,7 +397,9 @@ __device__ __forceinline__ uint32_t pb_ld_cg_b32(const void *p) {
 }
 __device__ __forceinline__ void pb_red_relaxed(uint32_t *p) { asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory"); }
 
-__device__ __forceinline__ void pb_scatter4(uint32_t cb, const uint4 &pr, const uint2 &sl) {
+__device__ __forceinline__ void pb_scatter4(uint32_t cb, const uint4 &pr, const uint2 &sl, uint32_t dump) {
+  SHB_DEV_CHECK((sl.x & 0xffffu) <= dump && (sl.x >> 16) <= dump && (sl.y & 0xffffu) <= dump && (sl.y >> 16) <= dump);
+  SHB_DEV_CHECK(((sl.x | sl.y) & 0x00030003u) == 0u);
   pb_sts32(cb + (sl.x & 0xffffu), pr.x);
   pb_sts32(cb + (sl.x >> 16), pr.y);
   pb_sts32(cb + (sl.y & 0xffffu), pr.z);
@@ -418,6 +423,7 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
   const uint4 zero4 = make_uint4(zb, zb, zb, zb);
   const uint32_t cb = pb_smem_addr(cbuf);
   const uint32_t qstride = 16u * (uint32_t)RS;  // bytes between a row's consecutive 128-bit words
+  const uint32_t dump = 4u * (uint32_t)c.g.cbuf_cap;  // byte offset of the word padding entries drop their product into
   T *const out0 = a.out[0] + a.row_offset;
   // the sync duties (poll the next panel, hand the slot back) go to the LAST warp: it has the fewest rows to reduce
   const bool syncer = tid == NT - 32;
@@ -436,6 +442,8 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
   auto issue = [&](const int4 &d, int rslot, int64_t r0n, int nrn, bool carry) {
     const T *ring_u = c.ring + (int64_t)rslot * slot_stride + d.z;
     const uint16_t *slot_u = c.slot + d.x;
+    SHB_DEV_CHECK(rslot >= 0 && rslot < c.g.depth && d.z >= 0 && (int64_t)d.z + 4 * (int64_t)d.y <= slot_stride);
+    SHB_DEV_CHECK(nrn >= 0 && nrn <= c.g.RS && r0n >= 0);
 #pragma unroll
     for (int k = 0; k < U; ++k) {
       const int q = tid + k * NT;
@@ -479,11 +487,11 @@ __device__ __forceinline__ void pb_consume(const PbArgs<typename S::T> &c, const
     }
 #pragma unroll
     for (int k = 0; k < U; ++k)
-      if (tid + k * NT < d.y) pb_scatter4(cb, pr[k], sl[k]);
+      if (tid + k * NT < d.y) pb_scatter4(cb, pr[k], sl[k], dump);
     if (d.y > NT * U) {  // units larger than one round (rare geometries): the rest, round by round
       const T *ring_u = c.ring + (int64_t)rslot * slot_stride + d.z;
       const uint16_t *slot_u = c.slot + d.x;
-      for (int q = tid + NT * U; q < d.y; q += NT) pb_scatter4(cb, pb_ld_cg_v4(ring_u + 4 * q), pb_ld_stream_v2(slot_u + 4 * q, pol_stream));
+      for (int q = tid + NT * U; q < d.y; q += NT) pb_scatter4(cb, pb_ld_cg_v4(ring_u + 4 * q), pb_ld_stream_v2(slot_u + 4 * q, pol_stream), dump);
     }
     // is the next unit's ring slot complete already?  one thread looks, the barrier spreads the verdict
     if (syncer) *flag_s = (g + 1 < n_groups && (!fused || pb_ld_acquire(c.ready + g + 1) >= (uint32_t)c.g.n_prod)) ? 1u : 0u;

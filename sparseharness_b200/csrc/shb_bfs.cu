@@ -336,6 +336,7 @@ __device__ __forceinline__ void bfs_pull_compact(const int32_t *__restrict__ row
       const uint32_t seen = __shfl_sync(0xffffffffu, seen_mine, j);
       const bool active = (w0 + j) * 32 + lane < n_local && !((seen >> lane) & 1u);
       const uint32_t m = __ballot_sync(0xffffffffu, active);
+      SHB_DEV_CHECK(n_act + __popc(m) <= BFS_PULL_GROUP_WORDS * 32);
       if (active) s_rows[wib][n_act + __popc(m & ((1u << lane) - 1u))] = (uint8_t)(j * 32 + lane);
       n_act += __popc(m);
     }
@@ -374,6 +375,7 @@ __device__ __forceinline__ void bfs_pull_compact(const int32_t *__restrict__ row
       }
       if (found) {
         levels[r] = (int32_t)level + 1;
+        SHB_DEV_CHECK((rt >> 5) < BFS_PULL_GROUP_WORDS);
         atomicOr(&s_bits[wib][rt >> 5], 1u << (rt & 31));
         ++found_n;
         push_deg += (unsigned long long)(deg ? deg[row_offset + r] : 1);

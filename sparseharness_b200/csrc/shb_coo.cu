@@ -34,6 +34,7 @@ __global__ void coo_gather_kernel(const uint32_t *perm, int64_t n, const int32_t
                                   int32_t *col, uint32_t *val) {
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
     const uint32_t j = perm[k];
+    SHB_DEV_CHECK((int64_t)j < n);
     col[k] = ci[j];
     if (val) {
       uint32_t b = v[j];

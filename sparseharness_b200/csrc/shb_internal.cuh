@@ -1,5 +1,24 @@
 // shb_internal.cuh -- shared definitions of libshb.so (not part of the public ABI, see include/shb.h)
 #pragma once
+// Checked build (make -C sparseharness_b200/csrc CHECKED=1 -> lib/libshb_checked.so, selected with SHB_LIB=checked):
+// every index a kernel derives from operator data before it touches shared memory, a ring slot or a list is tested
+// on the device; a failure prints the condition and traps the launch.  This pool keeps compute-sanitizer closed
+// (profiles/r02_sanitize_closed.txt), so the checked build run over the GPU test suite is the memory-safety evidence.
+#ifdef SHB_CHECKED
+#include <cstdio>
+#define SHB_DEV_CHECK(cond)                                                                                      \
+  do {                                                                                                           \
+    if (!(cond)) {                                                                                               \
+      printf("SHB_DEV_CHECK failed: %s at %s:%d (block %d thread %d)\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, \
+             (int)threadIdx.x);                                                                                  \
+      __trap();                                                                                                  \
+    }                                                                                                            \
+  } while (0)
+#else
+#define SHB_DEV_CHECK(cond) \
+  do {                      \
+  } while (0)
+#endif
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>

@@ -62,6 +62,7 @@ __global__ void panel_fill_kernel(const int32_t *__restrict__ row_ptr, const int
 #pragma unroll
       for (int q = 0; q < SHB_MAX_PANELS; ++q)
         if (q == p) dst = pos[q]++;
+      SHB_DEV_CHECK(dst >= 0 && dst < P.row_ptr[p][r + 1]);
       P.col[p][dst] = (int32_t)c;
       if (val) P.val[p][dst] = val[k];
     }

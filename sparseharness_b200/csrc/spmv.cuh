@@ -267,15 +267,20 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
   for (int it = 0; it < n_iter; ++it) {
     const int r = r_first + it * SHB_STREAM_THREADS + tid;
     if (r <= r_last) {
+      SHB_DEV_CHECK(r >= 0 && r < a.n_rows);
       const int s = a.row_ptr[r], e = a.row_ptr[r + 1];
+      SHB_DEV_CHECK(s <= e);
       if (e == s) {
         // empty row: owned by the tile with lo < s <= hi (or tile 0 when s == 0)
         if ((s > lo && s <= hi) || (s == 0 && t == 0)) shb_finish_row<S>(a, r, S::zero(), differs);
       } else {
         const int ps = max(s, lo), pe = min(e, hi);
         if (pe > ps) {
+          SHB_DEV_CHECK(ps >= lo && pe <= lo + SHB_TILE_NNZ);
           if (pe - ps > long_piece) {
-            long_rows[atomicAdd(&n_long, 1)] = r;
+            const int li = atomicAdd(&n_long, 1);
+            SHB_DEV_CHECK(li < SHB_TILE_NNZ / SHB_LONG_PIECE_MIN + 2);
+            long_rows[li] = r;
           } else {
             T acc = S::zero();
             for (int k = ps; k < pe; ++k) acc = S::add(acc, prod[shb_pad(k - lo)]);

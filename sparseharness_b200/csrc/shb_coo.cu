@@ -38,7 +38,13 @@ __global__ void coo_gather_kernel(const uint32_t *perm, int64_t n, const int32_t
     col[k] = ci[j];
     if (val) {
       uint32_t b = v[j];
-      if (elem_kind == 0 && truncate) b = __float_as_uint((float)__float2int_rz(__uint_as_float(b)));
+      if (elem_kind == 0 && truncate) {
+        // the host's `(int)value` (Q2) is cvttss2si: NaN and everything outside int range become INT_MIN ("integer
+        // indefinite"), where the device conversion would saturate -- x / 0 column sums of pagerank_normalise get here
+        const float f = __uint_as_float(b);
+        const int t = (f >= -2147483648.0f && f < 2147483648.0f) ? __float2int_rz(f) : (int)0x80000000;
+        b = __float_as_uint((float)t);
+      }
       val[k] = b;
     }
   }

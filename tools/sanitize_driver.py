@@ -23,11 +23,12 @@ col = rng.integers(0, m, rp[-1]).astype(np.int32)
 val = rng.integers(-3, 4, rp[-1]).astype(np.float32)
 x = ctx.array(rng.integers(-3, 4, m).astype(np.float32))
 out = ctx.empty(n * 4)
+yb = ctx.array(np.zeros(n, np.float32))
 A = ctx.csr(n, m, rp, col, val)
 for rows in (0, 7):
     A.build_blocked(rows, make_default=False)
     for sem in (shb.PLUS_TIMES, shb.MIN_PLUS):
-        ctx.spmv(A, sem, x, None, 1.0, 0.0, out, shb.launch_cfg(variant=shb.VARIANT_BLOCKED))
+        ctx.spmv(A, sem, x, yb, 1.0, 0.0, out, shb.launch_cfg(variant=shb.VARIANT_BLOCKED))
 for v in (shb.VARIANT_STREAM, shb.VARIANT_VECTOR, shb.VARIANT_SCALAR):
     ctx.spmv(A, shb.PLUS_TIMES, x, None, 1.0, 0.0, out, shb.launch_cfg(variant=v))
 A.build_panels(3)

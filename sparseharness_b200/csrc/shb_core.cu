@@ -793,13 +793,29 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
         const char *e = getenv("SHB_STREAM_LONG");
         return e ? std::max(SHB_LONG_PIECE_MIN, std::min(4096, atoi(e))) : SHB_LONG_PIECE;
       }();
+      // short skewed rows (column panels of power-law operators) take the merge-path row phase (spmv.cuh)
+      static const int merge_env = [] {
+        const char *e = getenv("SHB_STREAM_MERGE");
+        return e ? atoi(e) : -1;
+      }();
+      const double mean_len = A->n_rows > 0 ? (double)A->nnz / (double)A->n_rows : 0.0;
+      bool merge = mean_len < 8.0 && (double)A->max_row_len > 4.0 * std::max(mean_len, 1.0);
+      if (merge_env >= 0) merge = merge_env != 0;
+      if (d.flags & SHB_F_STREAM_MERGE) merge = true;
+      if (d.flags & SHB_F_STREAM_NO_MERGE) merge = false;
+#define SHB_LAUNCH_STREAM(HV, HN)                                                                                              \
+  do {                                                                                                                         \
+    if (merge) spmv_stream_kernel<S, HV, HN, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece); \
+    else spmv_stream_kernel<S, HV, HN, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);       \
+  } while (0)
       if (has_val) {
-        if (hints) spmv_stream_kernel<S, true, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
-        else spmv_stream_kernel<S, true, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
+        if (hints) SHB_LAUNCH_STREAM(true, true);
+        else SHB_LAUNCH_STREAM(true, false);
       } else {
-        if (hints) spmv_stream_kernel<S, false, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
-        else spmv_stream_kernel<S, false, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);
+        if (hints) SHB_LAUNCH_STREAM(false, true);
+        else SHB_LAUNCH_STREAM(false, false);
       }
+#undef SHB_LAUNCH_STREAM
       SHB_CUDA(cudaGetLastError());
       if (A->straddling_rows > 0) {
         const int blocks = std::min((nt + 255) / 256, 148 * 4);

@@ -211,7 +211,16 @@ __global__ void __launch_bounds__(256) spmv_vector_kernel(const __grid_constant_
 #define SHB_LONG_PIECE_MIN 8   // smallest value the launch argument may take (sizes the shared list)
 __device__ __forceinline__ int shb_pad(int i) { return i + (i >> 5); }  // 1 pad word per 32: conflict-free strides
 
-template <class S, bool HAS_VAL, bool HINTS>
+// MERGE: the row phase for SHORT, SKEWED rows (column panels of power-law operators: mean 2-4 entries, a few of 30-60 in
+// every warp's 32 rows, so the thread-per-row loop below runs at the longest row's length: 8.3 warp instructions per row
+// on BASELINE config 5's panels).  Instead every thread walks an equal share of the merged list (row-end markers,
+// entries) -- a merge-path partition over the tile's row_ptr segment staged in shared memory -- dropping each finished
+// row's sum into shared memory; partial sums of rows that span threads are joined in thread order; a thread-per-row
+// pass then runs the epilogue with coalesced y / out accesses.  Same ownership rules for straddling and empty rows as
+// the loop it replaces; tiles touching more than SHB_MERGE_ROWS rows fall back to that loop.
+#define SHB_MERGE_ROWS 2048
+
+template <class S, bool HAS_VAL, bool HINTS, bool MERGE>
 __global__ void __launch_bounds__(SHB_STREAM_THREADS)
     spmv_stream_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, const int32_t *__restrict__ tile_row,
                        int n_tiles, int32_t nnz, typename S::T *__restrict__ carry_tail,
@@ -221,6 +230,10 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
   __shared__ T prod[SHB_TILE_NNZ + SHB_TILE_NNZ / 32];
   __shared__ int long_rows[SHB_TILE_NNZ / SHB_LONG_PIECE_MIN + 2];
   __shared__ int n_long;
+  __shared__ int rp_s[MERGE ? SHB_MERGE_ROWS + 1 : 1];
+  __shared__ T rowsum[MERGE ? SHB_MERGE_ROWS : 1];
+  __shared__ T carry_s[MERGE ? SHB_STREAM_THREADS : 1];
+  __shared__ int first_s[MERGE ? SHB_STREAM_THREADS : 1];
   const int tid = threadIdx.x;
   const int t = blockIdx.x;
   const int lo = t * SHB_TILE_NNZ;
@@ -257,12 +270,74 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
     prod[shb_pad(i + 2)] = S::mult(shb_from_bits<T>(xb[k][2]), shb_from_bits<T>(v4[k].z));
     prod[shb_pad(i + 3)] = S::mult(shb_from_bits<T>(xb[k][3]), shb_from_bits<T>(v4[k].w));
   }
-  __syncthreads();
-
   // phase 2: the rows of this tile.  Row r's piece is [max(s,lo), min(e,hi)).
   const int r_first = tile_row[t];
   const int r_last = (t + 1 < n_tiles) ? tile_row[t + 1] : (int)(a.n_rows - 1);
+  const int nr = r_last - r_first + 1;
+  const bool merge = MERGE && nr <= SHB_MERGE_ROWS;
+  if (merge)
+    for (int i = tid; i <= nr; i += SHB_STREAM_THREADS) rp_s[i] = a.row_ptr[r_first + i];
+  __syncthreads();
   bool differs = false;
+  if (merge) {
+    const int ne = hi - lo;
+    auto rend = [&](int i) { return min(max(rp_s[i + 1] - lo, 0), ne); };  // end of row i inside the tile's entries
+    // merge-path split: marker i precedes entry j iff rend(i) <= j; thread tid takes merged items [d0, d1)
+    const int total = nr + ne;
+    const int ipt = (total + SHB_STREAM_THREADS - 1) / SHB_STREAM_THREADS;
+    const int d0 = min(tid * ipt, total), d1 = min(d0 + ipt, total);
+    int i_lo = max(0, d0 - ne), i_hi = min(d0, nr);
+    while (i_lo < i_hi) {
+      const int mid = (i_lo + i_hi) >> 1;
+      if (rend(mid) <= d0 - 1 - mid) i_lo = mid + 1;
+      else i_hi = mid;
+    }
+    int i = i_lo, j = d0 - i_lo;
+    int cur_end = i < nr ? rend(i) : ne + 1;
+    int first = -1;  // first row this thread finishes
+    T acc = S::zero();
+    for (int step = d0; step < d1; ++step) {
+      if (j < cur_end) {
+        SHB_DEV_CHECK(j >= 0 && j < ne);
+        acc = S::add(acc, prod[shb_pad(j)]);
+        ++j;
+      } else {
+        SHB_DEV_CHECK(i >= 0 && i < nr);
+        rowsum[i] = acc;
+        if (first < 0) first = i;
+        acc = S::zero();
+        ++i;
+        cur_end = i < nr ? rend(i) : ne + 1;
+      }
+    }
+    carry_s[tid] = acc;  // what this thread summed of the row it leaves unfinished
+    first_s[tid] = first;
+    __syncthreads();
+    if (first >= 0 && tid > 0) {
+      // the part of row `first` summed by earlier threads: the trailing sums of the thread that started it and of the
+      // ones in between (which finished no row), joined in thread order
+      int u = tid - 1;
+      while (u > 0 && first_s[u] < 0) --u;
+      T cin = carry_s[u];
+      for (int v = u + 1; v < tid; ++v) cin = S::add(cin, carry_s[v]);
+      rowsum[first] = S::add(cin, rowsum[first]);
+    }
+    __syncthreads();
+    for (int i2 = tid; i2 < nr; i2 += SHB_STREAM_THREADS) {
+      const int r = r_first + i2;
+      const int s = rp_s[i2], e = rp_s[i2 + 1];
+      if (e == s) {
+        if ((s > lo && s <= hi) || (s == 0 && t == 0)) shb_finish_row<S>(a, r, S::zero(), differs);
+      } else if (min(e, hi) > max(s, lo)) {
+        const T sum = rowsum[i2];
+        if (s >= lo && e <= hi) shb_finish_row<S>(a, r, sum, differs);
+        else if (e > hi) carry_tail[t] = sum;  // continues into the next tile
+        else carry_head[t] = sum;               // started in an earlier tile, ends here
+      }
+    }
+    shb_publish_changed(a.ctl, differs);
+    return;
+  }
   const int n_iter = (r_last - r_first + 1 + SHB_STREAM_THREADS - 1) / SHB_STREAM_THREADS;
   for (int it = 0; it < n_iter; ++it) {
     const int r = r_first + it * SHB_STREAM_THREADS + tid;

@@ -13,6 +13,8 @@ ALL_CFGS = [("scalar", dict(variant=shb.VARIANT_SCALAR)), ("stream", dict(varian
             ("vector8r4", dict(variant=shb.VARIANT_VECTOR, lanes=8, rows_per_group=4)),
             ("vector4nohint", dict(variant=shb.VARIANT_VECTOR, lanes=4, flags=shb.F_NO_CACHE_HINTS)),
             ("stream_nohint", dict(variant=shb.VARIANT_STREAM, flags=shb.F_NO_CACHE_HINTS)),
+            ("stream_merge", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_MERGE)),        # merge-path row phase
+            ("stream_nomerge", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_NO_MERGE)),   # thread-per-row row phase
             ("blocked", dict(variant=shb.VARIANT_BLOCKED)),          # one row panel on the small fixtures
             ("blocked_rs5", dict(variant=shb.VARIANT_BLOCKED, pb_rows=5))]  # many row panels, tiny pieces
 

@@ -79,6 +79,30 @@ def test_ragged_rows_long_rows_and_tile_straddlers(ctx, orc, semiring):
         assert np.array_equal(got, wantp), ("pattern", semiring, label)
 
 
+@pytest.mark.parametrize("semiring", SEMIRINGS)
+def test_stream_merge_row_phase_short_skewed_rows(ctx, orc, semiring):
+    """The merge-path row phase of the stream schedule (column panels of power-law operators): mean 2 entries per row,
+    a power-law tail, a third of the rows empty, a run of 6000 empty rows (a tile touching more rows than the phase
+    holds falls back to the thread-per-row loop), rows spanning threads and tiles.  Both row phases, bit-exact."""
+    rng = np.random.default_rng(321)
+    n, m = 60001, 5003
+    lens = np.minimum((rng.pareto(1.2, n) * 1.5).astype(np.int64), 9000)
+    lens[rng.random(n) < 0.33] = 0
+    lens[20000:26000] = 0
+    lens[[7, 30011, 59999]] = (4096, 10000, 300)
+    rp = np.zeros(n + 1, np.int64)
+    np.cumsum(lens, out=rp[1:])
+    col = rng.integers(0, m, rp[-1]).astype(np.int32)
+    dt = DT[semiring]
+    val = rng.integers(-3, 4, len(col)).astype(dt) if semiring != shb.MIN_PLUS else rng.integers(0, 9, len(col)).astype(dt)
+    x, y, alpha, beta = semiring_inputs(orc, semiring, n, m, rng)
+    want = orc.spmv(semiring, rp, col, val, x, y, alpha, beta)
+    A = ctx.csr(n, m, rp, col, val)
+    for label, flags in (("merge", shb.F_STREAM_MERGE), ("nomerge", shb.F_STREAM_NO_MERGE), ("default", 0)):
+        got = run_spmv(ctx, A, semiring, x, y, alpha, beta, n, variant=shb.VARIANT_STREAM, flags=flags)
+        assert np.array_equal(got, want), (semiring, label, np.flatnonzero(got != want)[:5])
+
+
 def test_empty_and_degenerate_operators(ctx, orc):
     rng = np.random.default_rng(5)
     # no stored entries at all: out = epi(ZERO, alpha, y, beta)

@@ -232,8 +232,9 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
   __shared__ int n_long;
   __shared__ int rp_s[MERGE ? SHB_MERGE_ROWS + 1 : 1];
   __shared__ T rowsum[MERGE ? SHB_MERGE_ROWS : 1];
-  __shared__ T carry_s[MERGE ? SHB_STREAM_THREADS : 1];
-  __shared__ int first_s[MERGE ? SHB_STREAM_THREADS : 1];
+  __shared__ T carry_s[MERGE ? SHB_STREAM_THREADS / 32 : 1];   // per warp: scanned trailing sum of its last lane
+  __shared__ int first_s[MERGE ? SHB_STREAM_THREADS / 32 : 1];  // per warp: a segment starts somewhere in it
+  __shared__ T scan_s[MERGE ? SHB_STREAM_THREADS : 1];
   const int tid = threadIdx.x;
   const int t = blockIdx.x;
   const int lo = t * SHB_TILE_NNZ;
@@ -310,18 +311,36 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
         cur_end = i < nr ? rend(i) : ne + 1;
       }
     }
-    carry_s[tid] = acc;  // what this thread summed of the row it leaves unfinished
-    first_s[tid] = first;
-    __syncthreads();
-    if (first >= 0 && tid > 0) {
-      // the part of row `first` summed by earlier threads: the trailing sums of the thread that started it and of the
-      // ones in between (which finished no row), joined in thread order
-      int u = tid - 1;
-      while (u > 0 && first_s[u] < 0) --u;
-      T cin = carry_s[u];
-      for (int v = u + 1; v < tid; ++v) cin = S::add(cin, carry_s[v]);
-      rowsum[first] = S::add(cin, rowsum[first]);
+    // `acc` is what this thread summed of the row it leaves unfinished.  The part of row `first` that earlier threads
+    // summed = the trailing sums from the thread that started it up to tid - 1 (the ones in between finished no row):
+    // a segmented inclusive scan over the CTA in thread order, a segment starting at every thread that finished a row.
+    const int lane = tid & 31, warp = tid >> 5;
+    uint32_t v = shb_bits<T>(acc);
+    int f = (first >= 0 || tid == 0) ? 1 : 0;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t pv = __shfl_up_sync(0xffffffffu, v, off);
+      const int pf = __shfl_up_sync(0xffffffffu, f, off);
+      if (lane >= off) {
+        if (!f) v = shb_bits<T>(S::add(shb_from_bits<T>(pv), shb_from_bits<T>(v)));
+        f |= pf;
+      }
     }
+    if (lane == 31) {
+      carry_s[warp] = shb_from_bits<T>(v);
+      first_s[warp] = f;
+    }
+    __syncthreads();
+    if (!f && warp > 0) {  // no segment start in this warp up to here: the sums of the warps before flow in
+      int w0 = warp - 1;
+      while (w0 > 0 && !first_s[w0]) --w0;
+      T pre = carry_s[w0];
+      for (int w = w0 + 1; w < warp; ++w) pre = S::add(pre, carry_s[w]);
+      v = shb_bits<T>(S::add(pre, shb_from_bits<T>(v)));
+    }
+    scan_s[tid] = shb_from_bits<T>(v);
+    __syncthreads();
+    if (first >= 0 && tid > 0) rowsum[first] = S::add(scan_s[tid - 1], rowsum[first]);
     __syncthreads();
     for (int i2 = tid; i2 < nr; i2 += SHB_STREAM_THREADS) {
       const int r = r_first + i2;

@@ -73,9 +73,9 @@ enum { SHB_F_NO_CACHE_HINTS = 1u, /* plain ld.global for every stream (A/B exper
        SHB_F_Y_IS_ONE = 8u,       /* y is the semiring one in every element (canonical PageRank's
                                      y == 1, app/pr.cpp:183): the y argument is not read          */
        SHB_F_NO_PANELS = 16u,     /* AUTO: ignore the operator's column panels (A/B experiments)   */
-       SHB_F_STREAM_MERGE = 32u,  /* STREAM: force the merge-path row phase (default: chosen from
-                                     the row-length statistics: mean < 8 and max > 4 x mean)       */
-       SHB_F_STREAM_NO_MERGE = 64u /* STREAM: force the thread-per-row row phase                    */ };
+       SHB_F_STREAM_MERGE = 32u,  /* STREAM: the merge-path row phase (balanced walk over row ends
+                                     and entries; measured slower than the default, kept for A/B)  */
+       SHB_F_STREAM_NO_MERGE = 64u /* STREAM: the thread-per-row row phase (the default)            */ };
 
 typedef struct {
   int32_t variant;        /* shb_variant                                                          */

@@ -793,13 +793,14 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
         const char *e = getenv("SHB_STREAM_LONG");
         return e ? std::max(SHB_LONG_PIECE_MIN, std::min(4096, atoi(e))) : SHB_LONG_PIECE;
       }();
-      // short skewed rows (column panels of power-law operators) take the merge-path row phase (spmv.cuh)
+      // the merge-path row phase (spmv.cuh), meant for short skewed rows (column panels of power-law operators)
       static const int merge_env = [] {
         const char *e = getenv("SHB_STREAM_MERGE");
         return e ? atoi(e) : -1;
       }();
-      const double mean_len = A->n_rows > 0 ? (double)A->nnz / (double)A->n_rows : 0.0;
-      bool merge = mean_len < 8.0 && (double)A->max_row_len > 4.0 * std::max(mean_len, 1.0);
+      // (off unless asked for: measured 2.6x SLOWER than the thread-per-row loop on the config-5 panels and on RMAT-22 --
+      //  shared-memory latency chains of the walk and three more CTA barriers per tile, profiles/r02_summary.md section 2)
+      bool merge = false;
       if (merge_env >= 0) merge = merge_env != 0;
       if (d.flags & SHB_F_STREAM_MERGE) merge = true;
       if (d.flags & SHB_F_STREAM_NO_MERGE) merge = false;

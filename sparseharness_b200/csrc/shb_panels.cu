@@ -177,6 +177,15 @@ int shb_launch_spmv_panels(shb_ctx *c, const shb_csr *A, int semiring, const shb
     shb_launch_cfg lc = {};
     if (cfg) lc = *cfg;
     lc.variant = SHB_VARIANT_AUTO;
+    // tuning aid: SHB_PANEL_LANES=L runs every panel under the vector schedule with L lanes per row
+    static const int panel_lanes = [] {
+      const char *e = getenv("SHB_PANEL_LANES");
+      return e ? atoi(e) : 0;
+    }();
+    if (panel_lanes > 0) {
+      lc.variant = SHB_VARIANT_VECTOR;
+      lc.lanes = panel_lanes;
+    }
     if (!first) {
       lc.flags &= ~(uint32_t)(SHB_F_Y_IS_ONE | SHB_F_INTERNAL_Y_ONE);
       lc.flags |= SHB_F_NO_Y_SKIP;

@@ -660,7 +660,7 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
                                                                   row_offset, n_local);
   if (n_local > 0) {
     if (AT) {
-      const unsigned grid = grid_for((word_hi - word_lo) * 32, 256, 148 * 8);
+      const unsigned grid = grid_for((word_hi - word_lo) * 32, 256, c->prop.multiProcessorCount * 8);
       if (AT->val)
         bfs_block_push_kernel<true><<<grid, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val, dg, cur,
                                                                  (const uint32_t *)visited->ptr, peers, acc, word_lo, word_hi,
@@ -670,15 +670,15 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
                                                                   (const uint32_t *)visited->ptr, peers, acc, word_lo, word_hi,
                                                                   row_offset, n_local);
       if (AT->val)
-        bfs_block_push_big_kernel<true><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val, dg,
+        bfs_block_push_big_kernel<true><<<c->prop.multiProcessorCount * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, (const int32_t *)AT->val, dg,
                                                                         (const uint32_t *)visited->ptr, peers, acc);
       else
-        bfs_block_push_big_kernel<false><<<148 * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, dg,
+        bfs_block_push_big_kernel<false><<<c->prop.multiProcessorCount * 4, 256, 0, c->stream>>>(st, AT->row_ptr, AT->col, nullptr, dg,
                                                                          (const uint32_t *)visited->ptr, peers, acc);
     }
     static const int by_rows = [] { const char *e = getenv("SHB_BFS_PULL"); return e && !strcmp(e, "rows") ? 1 : 0; }();
     static const int grid_mult = [] { const char *e = getenv("SHB_BFS_PULL_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 32; }();
-    const unsigned grid = grid_for(n_local, 256, 148 * grid_mult);
+    const unsigned grid = grid_for(n_local, 256, c->prop.multiProcessorCount * grid_mult);
     if (A->val)
       bfs_block_pull_kernel<true><<<grid, 256, 0, c->stream>>>(st, A->row_ptr, A->col, (const int32_t *)A->val, dg, cur,
                                                                (const uint32_t *)visited->ptr, peers, (int32_t *)levels->ptr,

@@ -247,7 +247,7 @@ SHB_API int shb_buf_fill_u32(shb_ctx *c, shb_buf *b, uint64_t offset_elems, uint
   SHB_REQUIRE((offset_elems + n) * 4 <= b->bytes, "fill exceeds buffer");
   SHB_CUDA(cudaSetDevice(c->device));
   if (n == 0) return SHB_OK;
-  const int blocks = (int)std::min<uint64_t>((n + 255) / 256, 148 * 16);
+  const int blocks = (int)std::min<uint64_t>((n + 255) / 256, c->prop.multiProcessorCount * 16);
   fill_u32_kernel<<<blocks, 256, 0, c->stream>>>((uint32_t *)b->ptr + offset_elems, n, pattern);
   SHB_CUDA(cudaGetLastError());
   return SHB_OK;
@@ -452,7 +452,7 @@ int shb_csr_analyse(shb_ctx *c, shb_csr *A) {
   CsrStats h = {0ull, ~0ull, 0ull, 0ull};
   SHB_CUDA(cudaMemcpyAsync(d_st, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
   if (A->n_rows > 0) {
-    const int blocks = (int)std::min<int64_t>((A->n_rows + 255) / 256, 148 * 8);
+    const int blocks = (int)std::min<int64_t>((A->n_rows + 255) / 256, c->prop.multiProcessorCount * 8);
     csr_stats_kernel<<<blocks, 256, 0, c->stream>>>(A->row_ptr, A->n_rows, d_st);
     const int64_t nt = A->n_tiles + 1;
     csr_tile_rows_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, c->stream>>>(A->row_ptr, A->n_rows, (int32_t)A->nnz,
@@ -554,7 +554,7 @@ SHB_API int shb_csr_download(shb_ctx *c, const shb_csr *A, int64_t row_begin, in
   SHB_CUDA(cudaSetDevice(c->device));
   int64_t *d_rp = nullptr;
   SHB_CUDA(cudaMalloc(&d_rp, (size_t)(row_count + 1) * 8));
-  rebase_rows_kernel<<<(unsigned)std::min<int64_t>((row_count + 256) / 256, 148 * 8), 256, 0, c->stream>>>(
+  rebase_rows_kernel<<<(unsigned)std::min<int64_t>((row_count + 256) / 256, c->prop.multiProcessorCount * 8), 256, 0, c->stream>>>(
       A->row_ptr, row_begin, row_count, d_rp);
   SHB_CUDA(cudaGetLastError());
   SHB_CUDA(cudaMemcpyAsync(row_ptr, d_rp, (size_t)(row_count + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
@@ -619,7 +619,7 @@ SHB_API int shb_csr_slice_rows(shb_ctx *c, const shb_csr *A, int64_t row_begin, 
   const int64_t nnz = (int64_t)be[1] - (int64_t)be[0];
   shb_csr *S = nullptr;
   SHB_TRY(shb_csr_alloc(c, row_count, A->n_cols, nnz, A->val != nullptr, &S));
-  rebase_rows32_kernel<<<(unsigned)std::min<int64_t>((row_count + 256) / 256, 148 * 8), 256, 0, c->stream>>>(
+  rebase_rows32_kernel<<<(unsigned)std::min<int64_t>((row_count + 256) / 256, c->prop.multiProcessorCount * 8), 256, 0, c->stream>>>(
       A->row_ptr, row_begin, row_count, S->row_ptr);
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess && nnz)
@@ -819,7 +819,7 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
 #undef SHB_LAUNCH_STREAM
       SHB_CUDA(cudaGetLastError());
       if (A->straddling_rows > 0) {
-        const int blocks = std::min((nt + 255) / 256, 148 * 4);
+        const int blocks = std::min((nt + 255) / 256, c->prop.multiProcessorCount * 4);
         spmv_fixup_kernel<S><<<blocks, 256, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch);
         SHB_CUDA(cudaGetLastError());
       }

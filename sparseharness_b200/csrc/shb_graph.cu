@@ -426,7 +426,7 @@ SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t
     SS_CUDA(cudaMemsetAsync(st, 0, sizeof(SsspState), c->stream));
     if (has_val && AT->nnz > 0) {
       const int64_t stride = std::max<int64_t>(1, AT->nnz / (1 << 22));
-      sssp_weight_stats_kernel<<<148, 256, 0, c->stream>>>(st, (const float *)AT->val, AT->nnz, stride);
+      sssp_weight_stats_kernel<<<c->prop.multiProcessorCount, 256, 0, c->stream>>>(st, (const float *)AT->val, AT->nnz, stride);
     }
     sssp_init_kernel<<<1, 1, 0, c->stream>>>(st, (uint32_t *)dist->ptr, near_q, source,
                                              n > 0 ? (double)AT->nnz / (double)n : 1.0, c_scale, delta_override);
@@ -849,7 +849,7 @@ SHB_API int shb_sssp_block_init(shb_ctx *c, const shb_csr *AT, int64_t row_offse
   SHB_CUDA(cudaMemsetAsync(st, 0, sizeof(SsspState), c->stream));
   if (AT->val && AT->nnz > 0) {
     const int64_t stride = std::max<int64_t>(1, AT->nnz / (1 << 22));
-    sssp_weight_stats_kernel<<<148, 256, 0, c->stream>>>(st, (const float *)AT->val, AT->nnz, stride);
+    sssp_weight_stats_kernel<<<c->prop.multiProcessorCount, 256, 0, c->stream>>>(st, (const float *)AT->val, AT->nnz, stride);
   }
   float c_scale = 128.0f, delta_override = 0.0f;
   if (const char *e = getenv("SHB_SSSP_C")) c_scale = (float)atof(e);

@@ -88,7 +88,7 @@ SHB_API int shb_synth_vector(shb_ctx *c, shb_buf *x, int64_t n, uint64_t seed, i
   SHB_REQUIRE((uint64_t)n * 4 <= x->bytes, "vector exceeds buffer");
   SHB_CUDA(cudaSetDevice(c->device));
   if (n == 0) return SHB_OK;
-  gen_vector_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, 148 * 16), 256, 0, c->stream>>>((float *)x->ptr, n, seed,
+  gen_vector_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, c->prop.multiProcessorCount * 16), 256, 0, c->stream>>>((float *)x->ptr, n, seed,
                                                                                                 mode);
   SHB_CUDA(cudaGetLastError());
   return SHB_OK;
@@ -181,7 +181,7 @@ __global__ void pagerank_values_kernel(const int32_t *col, int64_t nnz, const ui
   }
 }
 
-static unsigned synth_grid(int64_t n) { return grid_for(n, 256, 148 * 32); }
+#define synth_grid(n) grid_for((n), 256, c->prop.multiProcessorCount * 32)  // (a context `c` is in scope at every use)
 
 SHB_API int shb_synth_rmat(shb_ctx *c, int scale, int64_t n_edges, uint64_t seed, int symmetrise, int value_mode,
                            float damping, shb_csr **out) {

@@ -18,36 +18,6 @@
 #ifndef BFS_PROBE_BATCH
 #define BFS_PROBE_BATCH 4
 #endif
-// the same with the coarse frontier filter in shared memory asked first (sparse frontiers: most probes end there)
-template <bool HAS_VAL>
-__device__ __forceinline__ bool bfs_row_hits_filtered(const int32_t *__restrict__ col, const int32_t *__restrict__ val,
-                                                      const uint32_t *__restrict__ cur, const uint32_t *coarse_s, uint32_t shift,
-                                                      int s, int e) {
-  for (int k = s; k < e; k += BFS_PROBE_BATCH) {
-    int32_t c[BFS_PROBE_BATCH];
-    uint32_t w[BFS_PROBE_BATCH];
-#pragma unroll
-    for (int j = 0; j < BFS_PROBE_BATCH; ++j) {
-      const bool in = (k + j < e) && !(HAS_VAL && val[k + j] == 0);
-      c[j] = in ? col[k + j] : -1;
-    }
-#pragma unroll
-    for (int j = 0; j < BFS_PROBE_BATCH; ++j) {
-      if (c[j] >= 0) {
-        const uint32_t cb = (uint32_t)c[j] >> shift;
-        if (!((coarse_s[cb >> 5] >> (cb & 31)) & 1u)) c[j] = -1;  // nobody of that vertex block is in the frontier
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < BFS_PROBE_BATCH; ++j) w[j] = c[j] >= 0 ? cur[c[j] >> 5] : 0u;
-    bool hit = false;
-#pragma unroll
-    for (int j = 0; j < BFS_PROBE_BATCH; ++j) hit |= (c[j] >= 0) && ((w[j] >> (c[j] & 31)) & 1u);
-    if (hit) return true;
-  }
-  return false;
-}
-
 template <bool HAS_VAL>
 __device__ __forceinline__ bool bfs_row_hits(const int32_t *__restrict__ col, const int32_t *__restrict__ val,
                                              const uint32_t *__restrict__ cur, int s, int e) {
@@ -93,7 +63,6 @@ __device__ __forceinline__ bool bfs_row_hits(const int32_t *__restrict__ col, co
 #define BFS_BLOCK_BIG_ROW 128
 #define BFS_PUSH_BIG_ROW 1024  // a frontier vertex with at least this many out-edges is expanded by the whole grid
 #define BFS_PUSH_BIG_CAP 1024
-#define BFS_COARSE_WORDS 4096  // 131072 coarse bits = 16 KB
 // counters layout (int64 words): 0 reached, 1 TEPS numerator (after finish), 2 arrival word of the peer barrier,
 // 4..5 staging of the level's (vertices, degrees), slot F at BFS_SLOT(F), BFS_SLOT(F) + 1.  The slots are a ring of
 // BFS_SLOT_RING frontiers (a traversal may have any number of levels): the prep kernel of level F zeroes slot F + 2,
@@ -121,13 +90,6 @@ struct BfsBlockState {
   uint32_t big_count;             // hub vertices of the current push level, expanded by the whole grid
   uint32_t pad2;
   int32_t big_list[BFS_PUSH_BIG_CAP];
-  // coarse frontier filter for sparse pull levels: bit b of coarse[level & 1] says "some vertex of
-  // [b << coarse_shift, (b + 1) << coarse_shift) is in the frontier".  16 KB: a pull CTA keeps it in shared memory and
-  // asks it before it probes the full bitmap in L2 (a probe there is one L1TEX->XBAR request each, one per clock per SM;
-  // shared memory answers nine per clock).  Filled by every level's prep (which also zeroes the other copy).
-  uint32_t coarse_shift;  // log2 of vertices per coarse bit (>= 7; at most BFS_COARSE_WORDS * 32 bits cover n_total)
-  uint32_t coarse_on;     // this level's pull uses the filter (sparse frontier)
-  uint32_t coarse[2][BFS_COARSE_WORDS];
 };
 
 // Start of a level, one launch: (a) thread 0 of block 0 applies Beamer's rule to the all-reduced (n_f, m_f) of the
@@ -161,34 +123,12 @@ __global__ void bfs_block_prep_kernel(BfsBlockState *st, long long *counters_rw,
         st->mode = 1;
       }
       st->n_prev = nf;
-      // the filter pays when few coarse bits are set: expected share of set bits < 1/8
-      st->coarse_on = (st->mode == 1 && (nf << st->coarse_shift) < st->n_total / 8ull) ? 1u : 0u;
     }
   }
   if (done) return;
-  const uint32_t cshift = st->coarse_shift - 5;  // frontier words per coarse bit, log2 (>= 2)
-  uint32_t *coarse_cur = st->coarse[level & 1], *coarse_nxt = st->coarse[(level + 1) & 1];
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < BFS_COARSE_WORDS; i += (int64_t)gridDim.x * blockDim.x)
-    coarse_nxt[i] = 0u;
-  const int64_t n_words_padded = (n_words + 31) / 32 * 32;  // whole warps: the ballot below
-  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_words_padded; w += (int64_t)gridDim.x * blockDim.x) {
-    uint32_t bits = w < n_words ? cur[w] : 0u;
-    // coarse bits of the warp's 32 consecutive words (a warp's words share at most 32 >> cshift coarse bits of ONE word
-    // as long as cshift <= 5; above that a coarse bit spans several warps: one bit, same code)
-    const uint32_t nz = __ballot_sync(0xffffffffu, bits != 0u);
-    if ((threadIdx.x & 31) == 0 && nz) {
-      uint32_t cw = 0u;
-      const int64_t cb0 = w >> cshift;  // coarse bit of the warp's first word (w is a multiple of 32 here)
-      for (uint32_t m = nz; m;) {
-        const int l = __ffs(m) - 1;
-        m &= m - 1;
-        cw |= 1u << (((w + l) >> cshift) & 31);
-      }
-      SHB_DEV_CHECK((cb0 >> 5) < BFS_COARSE_WORDS);
-      atomicOr(&coarse_cur[cb0 >> 5], cw);
-    }
-    if (w >= n_words) continue;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (int64_t)gridDim.x * blockDim.x) {
     spare[w] = 0u;
+    uint32_t bits = cur[w];
     if (!bits) continue;
     visited[w] |= bits;
     if (w >= word_lo && w < word_hi) {
@@ -370,12 +310,12 @@ __device__ __forceinline__ void bfs_pull_rows(const int32_t *__restrict__ row_pt
 // memory and stored once into every rank's bitmap.  No CTA barrier: warps stay independent.  RMAT 24 on one GPU:
 // 0.90 -> 0.77 ms for the traversal; groups of 16 or 32 words measured 2-3 % slower than 8.
 #define BFS_PULL_GROUP_WORDS 8
-template <bool HAS_VAL, bool FILTER>
+template <bool HAS_VAL>
 __device__ __forceinline__ void bfs_pull_compact(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
                                                  const int32_t *__restrict__ val, const int32_t *__restrict__ deg,
                                                  const uint32_t *__restrict__ cur, const uint32_t *__restrict__ visited,
                                                  const BfsPeers &next, int32_t *levels, long long *acc, uint32_t level,
-                                                 int64_t n_local, int64_t row_offset, const uint32_t *coarse_s, uint32_t cshift) {
+                                                 int64_t n_local, int64_t row_offset) {
   __shared__ uint8_t s_rows[8][BFS_PULL_GROUP_WORDS * 32];
   __shared__ uint32_t s_bits[8][BFS_PULL_GROUP_WORDS];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -413,8 +353,7 @@ __device__ __forceinline__ void bfs_pull_compact(const int32_t *__restrict__ row
         s = row_ptr[r];
         e = row_ptr[r + 1];
         big = (e - s) >= BFS_BLOCK_BIG_ROW;
-        if (!big) found = FILTER ? bfs_row_hits_filtered<HAS_VAL>(col, val, cur, coarse_s, cshift, s, e)
-                                 : bfs_row_hits<HAS_VAL>(col, val, cur, s, e);
+        if (!big) found = bfs_row_hits<HAS_VAL>(col, val, cur, s, e);
       }
       // hub rows: the whole warp scans, 32 entries per step, until one lane sees a frontier neighbour
       uint32_t bigs = __ballot_sync(0xffffffffu, big);
@@ -428,12 +367,7 @@ __device__ __forceinline__ void bfs_pull_compact(const int32_t *__restrict__ row
           bool h = false;
           if (k < be && !(HAS_VAL && val[k] == 0)) {
             const int32_t c = col[k];
-            bool maybe = true;
-            if (FILTER) {
-              const uint32_t cb = (uint32_t)c >> cshift;
-              maybe = ((coarse_s[cb >> 5] >> (cb & 31)) & 1u) != 0u;
-            }
-            if (maybe) h = ((cur[c >> 5] >> (c & 31)) & 1u) != 0u;
+            h = ((cur[c >> 5] >> (c & 31)) & 1u) != 0u;
           }
           hit = __any_sync(0xffffffffu, h);
         }
@@ -472,19 +406,8 @@ __global__ void __launch_bounds__(256, 8)
                           const uint32_t *__restrict__ visited, const __grid_constant__ BfsPeers next, int32_t *levels,
                           long long *acc, uint32_t level, int64_t n_local, int64_t row_offset, int by_rows) {
   if (st->done || st->mode != 1) return;
-  if (by_rows) {
-    bfs_pull_rows<HAS_VAL>(row_ptr, col, val, deg, cur, visited, next, levels, acc, level, n_local, row_offset);
-  } else if (st->coarse_on) {
-    // sparse frontier: the level's coarse filter (16 KB, filled by this level's prep) into shared memory first
-    __shared__ uint32_t coarse_s[BFS_COARSE_WORDS];
-    const uint32_t *src = st->coarse[level & 1];
-    for (int i = threadIdx.x; i < BFS_COARSE_WORDS; i += blockDim.x) coarse_s[i] = src[i];
-    __syncthreads();
-    bfs_pull_compact<HAS_VAL, true>(row_ptr, col, val, deg, cur, visited, next, levels, acc, level, n_local, row_offset, coarse_s,
-                                    st->coarse_shift);
-  } else {
-    bfs_pull_compact<HAS_VAL, false>(row_ptr, col, val, deg, cur, visited, next, levels, acc, level, n_local, row_offset, nullptr, 0);
-  }
+  if (by_rows) bfs_pull_rows<HAS_VAL>(row_ptr, col, val, deg, cur, visited, next, levels, acc, level, n_local, row_offset);
+  else bfs_pull_compact<HAS_VAL>(row_ptr, col, val, deg, cur, visited, next, levels, acc, level, n_local, row_offset);
 }
 
 // The exchange of a counter slot without a collective library: lane i adds this rank's staged (vertices,
@@ -563,10 +486,6 @@ __global__ void bfs_block_init_kernel(BfsBlockState *st, int32_t *levels, uint32
   st->n_total = n_total;
   st->big_count = 0;
   st->pad2 = 0;
-  uint32_t shift = 7;
-  while ((n_total >> shift) > (unsigned long long)BFS_COARSE_WORDS * 32ull) ++shift;
-  st->coarse_shift = shift;
-  st->coarse_on = 0;
   if (root >= row_offset && root < row_offset + n_local) {  // the owner reports frontier 0 (slot 0 is then exchanged)
     levels[root - row_offset] = 0;
     acc[0] = 1;
@@ -683,7 +602,6 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
     SHB_CUDA(cudaMemcpyAsync((uint32_t *)visited->ptr + (row_offset >> 5), A->empty_row_bits, iso_bytes,
                              cudaMemcpyDeviceToDevice, c->stream));
   }
-  SHB_CUDA(cudaMemsetAsync((char *)state->ptr + offsetof(BfsBlockState, coarse), 0, sizeof(((BfsBlockState *)nullptr)->coarse), c->stream));
   bfs_block_init_kernel<<<1, 1, 0, c->stream>>>((BfsBlockState *)state->ptr, (int32_t *)levels->ptr, (uint32_t *)frontier0->ptr,
                                                 acc, root, row_offset, A->n_rows, deg ? (const int32_t *)deg->ptr : nullptr,
                                                 AT != nullptr, (unsigned long long)nnz_total, (unsigned long long)n_total);

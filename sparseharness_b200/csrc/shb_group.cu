@@ -1,4 +1,5 @@
-// shb_group.cu -- multi-GPU inside the boundary: ONE host thread drives the N devices of a box.
+// shb_group.cu -- multi-GPU inside the boundary: ONE process drives the N devices of a box (a parked host thread per
+// device enqueues that device's share of every batch of steps; the caller's thread takes device 0).
 //
 // The reference is single-device (one queue on one device, inc/harness.h:78-81); the row-partitioned
 // iteration is the north_star's generalisation of its host loops (app/{pr,bfs,sssp}.cpp executeRun).  This file is
@@ -15,6 +16,11 @@
 // The host looks at device 0's copy of the reduced words once per `check_every` iterations.
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "shb_internal.cuh"
@@ -67,7 +73,24 @@ __global__ void grp_publish_kernel(const __grid_constant__ GrpPubArgs a) {
   }
 }
 
+// One parked host thread per device beyond the first.  With a single enqueueing thread eight devices x five launches
+// per BFS level made the traversal launch-bound (1.25 ms at 8 GPUs against 0.49 ms with a process per GPU); the loops
+// below hand every device's share of a batch of steps to its own thread -- the devices agree among themselves through
+// the publish kernels, so the host threads never need to meet inside a batch.
+struct GrpPool {
+  std::vector<std::thread> th;
+  std::mutex m;
+  std::condition_variable go, done_cv;
+  std::function<int(int)> job;
+  uint64_t gen = 0;
+  int pending = 0;
+  bool stop = false;
+  int st[8];
+  std::string err[8];
+};
+
 struct shb_group {
+  GrpPool *pool = nullptr;
   int n = 0;
   int dev[GRP_MAX_DEV];
   shb_ctx *ctx[GRP_MAX_DEV];
@@ -85,6 +108,75 @@ struct shb_gpart {
   shb_csr *AT[GRP_MAX_DEV];  // == A[i] for symmetric operators
   bool symmetric = false;
 };
+
+static void grp_pool_start(shb_group *g) {
+  if (g->n <= 1) return;
+  GrpPool *P = new GrpPool();
+  g->pool = P;
+  for (int d = 1; d < g->n; ++d)
+    P->th.emplace_back([P, d] {
+      uint64_t seen = 0;
+      for (;;) {
+        std::function<int(int)> job;
+        {
+          std::unique_lock<std::mutex> lk(P->m);
+          P->go.wait(lk, [&] { return P->stop || P->gen != seen; });
+          if (P->stop) return;
+          seen = P->gen;
+          job = P->job;
+        }
+        const int st = job(d);
+        std::string err = st != SHB_OK ? std::string(shb_last_error()) : std::string();
+        {
+          std::lock_guard<std::mutex> lk(P->m);
+          P->st[d] = st;
+          P->err[d] = err;
+          if (--P->pending == 0) P->done_cv.notify_one();
+        }
+      }
+    });
+}
+
+static void grp_pool_stop(shb_group *g) {
+  GrpPool *P = g->pool;
+  if (!P) return;
+  {
+    std::lock_guard<std::mutex> lk(P->m);
+    P->stop = true;
+  }
+  P->go.notify_all();
+  for (auto &t : P->th) t.join();
+  delete P;
+  g->pool = nullptr;
+}
+
+// f(d) for every device d, each on its own thread (device 0 on the caller's); the first failure wins
+static int grp_parallel(shb_group *g, const std::function<int(int)> &f) {
+  GrpPool *P = g->pool;
+  if (!P) {
+    for (int d = 0; d < g->n; ++d) SHB_TRY(f(d));
+    return SHB_OK;
+  }
+  {
+    std::lock_guard<std::mutex> lk(P->m);
+    P->job = f;
+    P->pending = g->n - 1;
+    P->gen += 1;
+  }
+  P->go.notify_all();
+  const int st0 = f(0);
+  {
+    std::unique_lock<std::mutex> lk(P->m);
+    P->done_cv.wait(lk, [&] { return P->pending == 0; });
+  }
+  if (st0 != SHB_OK) return st0;
+  for (int d = 1; d < g->n; ++d)
+    if (P->st[d] != SHB_OK) {
+      shb_set_error("%s", P->err[d].c_str());
+      return P->st[d];
+    }
+  return SHB_OK;
+}
 
 #define GRP_CUDA SHB_CUDA
 
@@ -124,12 +216,14 @@ SHB_API int shb_group_create(int n_dev, const int *devices, shb_group **out) {
     GRP_CUDA(cudaMalloc(&g->status[i], 4));
     GRP_CUDA(cudaMemset(g->status[i], 0, 4));
   }
+  if (!getenv("SHB_GROUP_ONE_THREAD")) grp_pool_start(g);  // (the variable keeps the single enqueueing thread, for A/B)
   *out = g;
   return SHB_OK;
 }
 
 SHB_API int shb_group_destroy(shb_group *g) {
   if (!g) return SHB_OK;
+  grp_pool_stop(g);
   for (int i = 0; i < g->n; ++i) {
     if (!g->ctx[i]) continue;
     cudaSetDevice(g->dev[i]);
@@ -162,10 +256,10 @@ static int grp_sync_all(shb_group *g) {
 }
 
 // one publish per device: words[w] of every device receives op over all devices' src, then the barrier
-static int grp_publish(shb_group *g, int n_words, const int *op, const int *src_is_u32, const void *const src[][GRP_MAX_DEV],
-                       long long *const dst[][GRP_MAX_DEV]) {
-  g->seq += 1;
-  for (int d = 0; d < g->n; ++d) {
+// device d's publish with sequence number `seq` (1-based count of publishes on this group)
+static int grp_publish_dev(shb_group *g, int d, unsigned long long seq, int n_words, const int *op, const int *src_is_u32,
+                           const void *const src[][GRP_MAX_DEV], long long *const dst[][GRP_MAX_DEV]) {
+  {
     GrpPubArgs a;
     memset(&a, 0, sizeof a);
     a.n = g->n;
@@ -178,12 +272,19 @@ static int grp_publish(shb_group *g, int n_words, const int *op, const int *src_
       for (int j = 0; j < g->n; ++j) a.dst[w][j] = dst[w][j];
     }
     for (int j = 0; j < g->n; ++j) a.arrive[j] = g->arrive[j];
-    a.target = (unsigned long long)g->n * g->seq;
+    a.target = (unsigned long long)g->n * seq;
     a.status = g->status[d];
     SHB_CUDA(cudaSetDevice(g->dev[d]));
     grp_publish_kernel<<<1, 32, 0, g->ctx[d]->stream>>>(a);
     SHB_CUDA(cudaGetLastError());
   }
+  return SHB_OK;
+}
+
+static int grp_publish(shb_group *g, int n_words, const int *op, const int *src_is_u32, const void *const src[][GRP_MAX_DEV],
+                       long long *const dst[][GRP_MAX_DEV]) {
+  g->seq += 1;
+  for (int d = 0; d < g->n; ++d) SHB_TRY(grp_publish_dev(g, d, g->seq, n_words, op, src_is_u32, src, dst));
   return SHB_OK;
 }
 
@@ -418,9 +519,13 @@ SHB_API int shb_group_iterate(shb_group *g, const shb_gpart *p, int semiring, co
   std::vector<long long> flags(check_every);
   while (done < max_iters && !converged) {
     const uint32_t batch = std::min(check_every, max_iters - done);
-    for (uint32_t b = 0; b < batch; ++b) {
-      const uint32_t it = done + b;
-      for (int d = 0; d < N; ++d) {
+    const unsigned long long seq0 = g->seq;
+    const int cur0 = cur;
+    // every device's thread enqueues its `batch` steps: SpMV with the peer scatter in its epilogue, then the publish
+    SHB_TRY(grp_parallel(g, [&](int d) -> int {
+      for (uint32_t b = 0; b < batch; ++b) {
+        const uint32_t it = done + b;
+        const int c = cur0 ^ (int)(b & 1u);
         shb_buf changed, prev;
         changed = *lf[d];
         changed.ptr = (char *)lf[d]->ptr + 4 * (size_t)it;
@@ -431,19 +536,21 @@ SHB_API int shb_group_iterate(shb_group *g, const shb_gpart *p, int semiring, co
         prev.bytes = 4;
         prev.owned = false;
         const shb_buf *yb = (y_mode == 0 || (y_mode == 1 && it == 0)) ? y0[d] : nullptr;
-        SHB_TRY(shb_spmv_scatter(g->ctx[d], p->A[d], semiring, &lc, x[d][cur], yb, alpha, beta, peer_x[d][cur ^ 1], N,
+        SHB_TRY(shb_spmv_scatter(g->ctx[d], p->A[d], semiring, &lc, x[d][c], yb, alpha, beta, peer_x[d][c ^ 1], N,
                                  p->bounds[d], delta, term_mode, &changed, it ? &prev : nullptr, nullptr));
+        int op[1] = {GRP_OP_MAX}, isu32[1] = {1};
+        const void *src[1][GRP_MAX_DEV];
+        long long *dst[1][GRP_MAX_DEV];
+        for (int j = 0; j < N; ++j) {
+          src[0][j] = (const char *)lf[j]->ptr + 4 * (size_t)it;
+          dst[0][j] = (long long *)gw[j]->ptr + it;
+        }
+        SHB_TRY(grp_publish_dev(g, d, seq0 + b + 1, 1, op, isu32, src, dst));
       }
-      int op[1] = {GRP_OP_MAX}, isu32[1] = {1};
-      const void *src[1][GRP_MAX_DEV];
-      long long *dst[1][GRP_MAX_DEV];
-      for (int d = 0; d < N; ++d) {
-        src[0][d] = (const char *)lf[d]->ptr + 4 * (size_t)it;
-        dst[0][d] = (long long *)gw[d]->ptr + it;
-      }
-      SHB_TRY(grp_publish(g, 1, op, isu32, src, dst));
-      cur ^= 1;
-    }
+      return SHB_OK;
+    }));
+    g->seq = seq0 + batch;
+    if (batch & 1u) cur ^= 1;
     SHB_TRY(shb_buf_download(g->ctx[0], gw[0], (uint64_t)done * 8, flags.data(), (uint64_t)batch * 8, nullptr));
     uint32_t ran = batch;
     for (uint32_t b = 0; b < batch; ++b)
@@ -565,16 +672,18 @@ SHB_API int shb_group_bfs(shb_group *g, const shb_gpart *p, int64_t root, int32_
   uint64_t launches = 0;
   while (!done && level < max_levels) {
     const uint32_t batch = std::min(check_every, max_levels - level);
-    for (uint32_t b = 0; b < batch; ++b) {
-      const uint32_t L = level + b;
-      if (peer) bseq += 1;
-      for (int d = 0; d < N; ++d) {
+    const uint64_t bseq0 = bseq;
+    SHB_TRY(grp_parallel(g, [&](int d) -> int {
+      for (uint32_t b = 0; b < batch; ++b) {
+        const uint32_t L = level + b;
         SHB_TRY(shb_bfs_block_level(g->ctx[d], p->A[d], p->AT[d], p->bounds[d], n, L, deg[d], bm[d][L % 3], peer_bm[d][(L + 1) % 3], N, d,
                                     bm[d][(L + 2) % 3], visited[d], levels[d], counters[d], state[d], peer ? peer_cnt[d] : nullptr,
-                                    peer ? (uint64_t)N * bseq : 0));
-        ++launches;
+                                    peer ? (uint64_t)N * (bseq0 + b + 1) : 0));
       }
-    }
+      return SHB_OK;
+    }));
+    if (peer) bseq += batch;
+    launches += (uint64_t)batch * N;
     SHB_TRY(shb_buf_download(g->ctx[0], counters[0], 0, cw.data(), cbytes, nullptr));
     bool broke = false;
     for (uint32_t b = 0; b < batch; ++b) {
@@ -661,27 +770,32 @@ SHB_API int shb_group_sssp(shb_group *g, const shb_gpart *p, int64_t source, flo
   std::vector<long long> seeds(check_every);
   while (done < max_rounds && !converged) {
     const uint32_t batch = std::min(check_every, max_rounds - done);
-    for (uint32_t r = done; r < done + batch; ++r) {
-      for (int d = 0; d < N; ++d)
+    const unsigned long long seq0 = g->seq;
+    SHB_TRY(grp_parallel(g, [&](int d) -> int {
+      for (uint32_t b = 0; b < batch; ++b) {
+        const uint32_t r = done + b;
         SHB_TRY(shb_sssp_block_seed(g->ctx[d], p->AT[d], p->bounds[d], n, dist[d], prev[d], work[d], N > 1 ? lseed[d] : gseed[d],
                                     N > 1 ? lmin[d] : gmin[d], r));
-      if (N > 1) {
-        int op[2] = {GRP_OP_ADD, GRP_OP_MIN}, isu32[2] = {0, 0};
-        const void *src[2][GRP_MAX_DEV];
-        long long *dst[2][GRP_MAX_DEV];
-        for (int d = 0; d < N; ++d) {
-          src[0][d] = (const long long *)lseed[d]->ptr + r;
-          src[1][d] = (const long long *)lmin[d]->ptr + r;
-          dst[0][d] = (long long *)gseed[d]->ptr + r;
-          dst[1][d] = (long long *)gmin[d]->ptr + r;
+        if (N > 1) {
+          int op[2] = {GRP_OP_ADD, GRP_OP_MIN}, isu32[2] = {0, 0};
+          const void *src[2][GRP_MAX_DEV];
+          long long *dst[2][GRP_MAX_DEV];
+          for (int j = 0; j < N; ++j) {
+            src[0][j] = (const long long *)lseed[j]->ptr + r;
+            src[1][j] = (const long long *)lmin[j]->ptr + r;
+            dst[0][j] = (long long *)gseed[j]->ptr + r;
+            dst[1][j] = (long long *)gmin[j]->ptr + r;
+          }
+          SHB_TRY(grp_publish_dev(g, d, seq0 + 2ull * b + 1, 2, op, isu32, src, dst));
         }
-        SHB_TRY(grp_publish(g, 2, op, isu32, src, dst));
-      }
-      for (int d = 0; d < N; ++d)
         SHB_TRY(shb_sssp_block_solve(g->ctx[d], p->AT[d], p->bounds[d], n, dist[d], peer_dist[d], N, d, p->bounds, prev[d], work[d],
                                      gmin[d], r, window_buckets, 0));
-      if (N > 1) SHB_TRY(grp_barrier(g));  // all peer candidates of this round have landed before anyone's next seed pass
-    }
+        // all peer candidates of this round have landed before anyone's next seed pass
+        if (N > 1) SHB_TRY(grp_publish_dev(g, d, seq0 + 2ull * b + 2, 0, nullptr, nullptr, nullptr, nullptr));
+      }
+      return SHB_OK;
+    }));
+    if (N > 1) g->seq = seq0 + 2ull * batch;
     SHB_TRY(shb_buf_download(g->ctx[0], gseed[0], (uint64_t)done * 8, seeds.data(), (uint64_t)batch * 8, nullptr));
     uint32_t ran = batch;
     for (uint32_t b = 0; b < batch; ++b)

@@ -328,7 +328,7 @@ int shb_sssp_block_solve(shb_ctx *ctx, const shb_csr *AT, int64_t row_offset, in
 int shb_sssp_block_finish(shb_ctx *ctx, const shb_csr *A_rows, int64_t row_offset, const shb_buf *dist,
                           const shb_buf *work, shb_buf *stats_out);
 
-/* ---- multi-GPU in ONE process: a group of devices driven by one host thread ----------
+/* ---- multi-GPU in ONE process: a group of devices driven by one caller ----------
  * Generalises the reference's single queue on a single device (inc/harness.h:78-81): shb_group owns one context
  * + stream per device with peer access enabled between all of them; shb_gpart is an operator row-partitioned over
  * the group (contiguous blocks balanced by non-zeros, bounds multiples of 32, GLOBAL column ids, block i resident

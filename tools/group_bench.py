@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """GTEPS of the row-partitioned drivers INSIDE the boundary (shb_group_*, include/shb.h) at N GPUs of one box:
 PageRank on config 5 (RMAT scale 26, 2^30 non-zeros, 20 sweeps), BFS on config 3 (RMAT scale 24 symmetrised) and
-SSSP on config 4 (8192^2 grid).  ONE process, one host thread, no torch.distributed.
+SSSP on config 4 (8192^2 grid).  ONE process, no torch.distributed.
 
     python tools/group_bench.py --gpus N [--small] [--only pagerank,bfs,sssp]
 

@@ -173,6 +173,21 @@ int shb_csr_slice_rows(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int6
 int shb_spmv(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const shb_buf *x,
              const shb_buf *y, const void *alpha, const void *beta, shb_buf *out, uint64_t *kernel_ns);
 
+/* The stream-schedule SpMV for callers that cannot allocate.  NO counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Same arguments and result as shb_spmv with cfg = {SHB_VARIANT_STREAM} (bit for bit: the same kernels), but the
+ * schedule's scratch (the carry arrays of rows that straddle tiles) lives in a file-scope __device__ array of the
+ * library instead of buffers owned by the operator: 512 KB held by every GPU that loads the library, until exit.
+ * The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  Limit: operators of at most
+ * 65536 tiles = 2^28 stored entries (shb_spmv_stream_static_max_nnz reports it); larger ones are rejected with
+ * SHB_ERR_TOO_LARGE and a message naming the limit.  ALL calls on a device share the array: calls that overlap on
+ * the GPU (two streams, two contexts of one device) race on it -- the caller serialises them.  The array keeps the
+ * last call's contents; nothing needs clearing (every carry a launch reads, the same launch wrote).  Column panels
+ * and the blocked copy of the operator are ignored. */
+int shb_spmv_stream_static(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_buf *x, const shb_buf *y,
+                           const void *alpha, const void *beta, shb_buf *out, uint64_t *kernel_ns);
+int shb_spmv_stream_static_max_nnz(int64_t *max_nnz);
+
 /* Same call with HOST vectors (the reference-facing plugin boundary: x upload, kernel, out download,
  * all inside *total_ns; A stays resident like the reference's idx/vals buffers). */
 int shb_spmv_host(shb_ctx *ctx, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const void *x_host,

@@ -84,6 +84,9 @@ SIGNATURES = {
     "shb_csr_slice_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, c_void_pp]),
     "shb_spmv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p, C.c_void_p,
                            C.c_void_p, C.c_void_p, u64p]),
+    "shb_spmv_stream_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, u64p]),
+    "shb_spmv_stream_static_max_nnz": (C.c_int, [C.POINTER(C.c_int64)]),
     "shb_spmv_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_void_p, C.c_void_p, u64p, u64p]),
     "shb_spmv_host_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(LaunchCfg), C.c_int, c_void_pp, c_void_pp,

@@ -264,6 +264,14 @@ class Context:
                          out.h, C.byref(ns) if timed else None))
         return ns.value
 
+    def spmv_stream_static(self, A: Csr, semiring, x: Buffer, y: Buffer | None, alpha, beta, out: Buffer, timed: bool = True) -> int:
+        """shb_spmv_stream_static: the stream schedule with its scratch in the library's static device array (no allocation)."""
+        a, b = _scalar(semiring, alpha), _scalar(semiring, beta)
+        ns = C.c_uint64(0)
+        _ck(lib.shb_spmv_stream_static(self.h, A.h, semiring, x.h, y.h if y else None, _ptr(a), _ptr(b), out.h,
+                                       C.byref(ns) if timed else None))
+        return ns.value
+
     def spmv_host(self, A: Csr, semiring, x: np.ndarray, y: np.ndarray | None, alpha, beta, out: np.ndarray,
                   cfg: LaunchCfg | None = None):
         a, b = _scalar(semiring, alpha), _scalar(semiring, beta)

@@ -680,6 +680,10 @@ static int default_rpg(int lanes) {
   }
 }
 
+#ifndef SHB_STREAM_SCAN_DEFAULT
+#define SHB_STREAM_SCAN_DEFAULT false  // until measured
+#endif
+
 // BLOCKED: one persistent cooperative kernel, a CTA per SM, producer and consumer warps (pb.cuh).
 // SHB_PB_SPLIT=1 runs the two roles as two launches over a full-size ring (debug / profiling aid).
 template <class S, bool HAS_VAL, int LQ>
@@ -804,10 +808,21 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
       if (merge_env >= 0) merge = merge_env != 0;
       if (d.flags & SHB_F_STREAM_MERGE) merge = true;
       if (d.flags & SHB_F_STREAM_NO_MERGE) merge = false;
+      // the segmented-scan row phase (spmv.cuh, MODE 2): SHB_STREAM_SCAN=0|1 overrides the choice, as do the flags
+      static const int scan_env = [] {
+        const char *e = getenv("SHB_STREAM_SCAN");
+        return e ? atoi(e) : -1;
+      }();
+      bool scan = SHB_STREAM_SCAN_DEFAULT;
+      if (scan_env >= 0) scan = scan_env != 0;
+      if (d.flags & SHB_F_STREAM_SCAN) scan = true;
+      if (d.flags & (SHB_F_STREAM_NO_MERGE | SHB_F_STREAM_MERGE)) scan = false;
+      const int mode = scan ? 2 : (merge ? 1 : 0);
 #define SHB_LAUNCH_STREAM(HV, HN)                                                                                              \
   do {                                                                                                                         \
-    if (merge) spmv_stream_kernel<S, HV, HN, true><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece); \
-    else spmv_stream_kernel<S, HV, HN, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);       \
+    if (mode == 2) spmv_stream_kernel<S, HV, HN, 2><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece); \
+    else if (mode == 1) spmv_stream_kernel<S, HV, HN, 1><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece); \
+    else spmv_stream_kernel<S, HV, HN, 0><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);       \
   } while (0)
       if (has_val) {
         if (hints) SHB_LAUNCH_STREAM(true, true);

@@ -78,8 +78,8 @@ static int launch_stream_static(shb_ctx *c, const shb_csr *A, const void *x, con
     return SHB_OK;
   }
   T *ct = reinterpret_cast<T *>(carry), *ch = reinterpret_cast<T *>(carry + SHB_STATIC_MAX_TILES);
-  if (A->val) spmv_stream_kernel<S, true, true, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, SHB_LONG_PIECE);
-  else spmv_stream_kernel<S, false, true, false><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, SHB_LONG_PIECE);
+  if (A->val) spmv_stream_kernel<S, true, true, 0><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, SHB_LONG_PIECE);
+  else spmv_stream_kernel<S, false, true, 0><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, SHB_LONG_PIECE);
   SHB_CUDA(cudaGetLastError());
   if (A->straddling_rows > 0) {
     const int blocks = std::min((nt + 255) / 256, c->prop.multiProcessorCount * 4);

@@ -15,6 +15,7 @@ ALL_CFGS = [("scalar", dict(variant=shb.VARIANT_SCALAR)), ("stream", dict(varian
             ("stream_nohint", dict(variant=shb.VARIANT_STREAM, flags=shb.F_NO_CACHE_HINTS)),
             ("stream_merge", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_MERGE)),        # merge-path row phase
             ("stream_nomerge", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_NO_MERGE)),   # thread-per-row row phase
+            ("stream_scan", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_SCAN)),          # segmented-scan row phase
             ("blocked", dict(variant=shb.VARIANT_BLOCKED)),          # one row panel on the small fixtures
             ("blocked_rs5", dict(variant=shb.VARIANT_BLOCKED, pb_rows=5))]  # many row panels, tiny pieces
 

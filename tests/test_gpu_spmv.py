@@ -98,7 +98,7 @@ def test_stream_merge_row_phase_short_skewed_rows(ctx, orc, semiring):
     x, y, alpha, beta = semiring_inputs(orc, semiring, n, m, rng)
     want = orc.spmv(semiring, rp, col, val, x, y, alpha, beta)
     A = ctx.csr(n, m, rp, col, val)
-    for label, flags in (("merge", shb.F_STREAM_MERGE), ("nomerge", shb.F_STREAM_NO_MERGE), ("default", 0)):
+    for label, flags in (("merge", shb.F_STREAM_MERGE), ("nomerge", shb.F_STREAM_NO_MERGE), ("scan", shb.F_STREAM_SCAN), ("default", 0)):
         got = run_spmv(ctx, A, semiring, x, y, alpha, beta, n, variant=shb.VARIANT_STREAM, flags=flags)
         assert np.array_equal(got, want), (semiring, label, np.flatnonzero(got != want)[:5])
 

@@ -10,7 +10,14 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <mutex>
+
 #include "shb_internal.cuh"
+
+// The per-operator caches below (row lengths, empty-row bits) are built the first time an operator is traversed.  Two
+// contexts or threads may traverse the same operator: the build is serialised, and finished on the device (stream
+// synchronise) before the pointer is published, because another context's stream is not ordered after this one's.
+static std::mutex g_bfs_cache_mutex;
 
 // does row [s, e) have an in-neighbour in the frontier bitmap?  BFS_PROBE_BATCH entries per step: the column loads and the
 // bitmap probes of a step are issued together, so a row costs e/BATCH dependent round trips instead of e (the early exit
@@ -592,12 +599,16 @@ SHB_API int shb_bfs_block_init(shb_ctx *c, const shb_csr *A, const shb_csr *AT, 
   if (A->n_rows > 0) {
     // the empty-row bits depend on the operator only: one pass the first time it is traversed, a 1-bit-per-row copy after
     const size_t iso_bytes = (size_t)((A->n_rows + 31) / 32) * 4;
-    if (!A->empty_row_bits) {
-      uint32_t *bits = nullptr;
-      SHB_CUDA(cudaMalloc(&bits, iso_bytes));
-      SHB_CUDA(cudaMemsetAsync(bits, 0, iso_bytes, c->stream));
-      bfs_block_mark_isolated_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>(A->row_ptr, bits, A->n_rows, 0);
-      A->empty_row_bits = bits;
+    {
+      std::lock_guard<std::mutex> lk(g_bfs_cache_mutex);
+      if (!A->empty_row_bits) {
+        uint32_t *bits = nullptr;
+        SHB_CUDA(cudaMalloc(&bits, iso_bytes));
+        SHB_CUDA(cudaMemsetAsync(bits, 0, iso_bytes, c->stream));
+        bfs_block_mark_isolated_kernel<<<grid_for(A->n_rows), 256, 0, c->stream>>>(A->row_ptr, bits, A->n_rows, 0);
+        SHB_CUDA(cudaStreamSynchronize(c->stream));
+        A->empty_row_bits = bits;
+      }
     }
     SHB_CUDA(cudaMemcpyAsync((uint32_t *)visited->ptr + (row_offset >> 5), A->empty_row_bits, iso_bytes,
                              cudaMemcpyDeviceToDevice, c->stream));
@@ -734,11 +745,15 @@ SHB_API int shb_bfs(shb_ctx *c, const shb_csr *A, const shb_csr *AT, int64_t roo
   const size_t cnt_bytes = (size_t)BFS_COUNTER_WORDS * 8, st_bytes = (sizeof(BfsBlockState) + 255) / 256 * 256;
   if (max_levels == 0) max_levels = 1u << 30;
   // push degrees of every vertex, cached on the operator (one pass the first time it is traversed)
-  if (AT && !AT->row_len && n > 0) {
-    int32_t *rl = nullptr;
-    SHB_CUDA(cudaMalloc(&rl, (size_t)n * 4));
-    csr_row_lengths_kernel<<<grid_for(n), 256, 0, c->stream>>>(AT->row_ptr, rl, n);
-    AT->row_len = rl;
+  if (AT && n > 0) {
+    std::lock_guard<std::mutex> lk(g_bfs_cache_mutex);
+    if (!AT->row_len) {
+      int32_t *rl = nullptr;
+      SHB_CUDA(cudaMalloc(&rl, (size_t)n * 4));
+      csr_row_lengths_kernel<<<grid_for(n), 256, 0, c->stream>>>(AT->row_ptr, rl, n);
+      SHB_CUDA(cudaStreamSynchronize(c->stream));
+      AT->row_len = rl;
+    }
   }
   char *scratch = nullptr;
   cudaError_t me = cudaMalloc(&scratch, 4 * bm_bytes + cnt_bytes + st_bytes);

@@ -146,7 +146,9 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_nearfar_kernel(const __g
   }
   __syncthreads();
   while (phase < a.max_phases) {
-    const uint32_t ns = *(volatile uint32_t *)&st->near_size[phase % 3];
+    // (the size counter keeps counting past the list's capacity when it overflows -- the entries beyond it were dropped
+    //  and `overflow` is set: never read past the end; the host starts over with a longer list or reports the overflow)
+    const uint32_t ns = min(*(volatile uint32_t *)&st->near_size[phase % 3], a.near_cap);
     const uint2 *near_cur = a.near_q[phase & 1];
     uint2 *near_next = a.near_q[(phase + 1) & 1];
     uint32_t *near_next_size = &st->near_size[(phase + 1) % 3];
@@ -363,8 +365,30 @@ __global__ void reached_stats_kernel(const uint32_t *value, uint32_t unreached, 
   }
 }
 
+// one attempt with a global near list of `near_cap` entries; *overflowed says the list was too small (dist is then
+// lowered but not fully expanded: the caller starts over with a larger list)
+static int sssp_attempt(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t source, shb_buf *dist, uint32_t max_rounds,
+                        shb_graph_stats *stats, uint64_t near_cap, bool *overflowed);
+
 SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t source, shb_buf *dist, uint32_t max_rounds,
                      shb_graph_stats *stats) {
+  SHB_REQUIRE(c && A && dist, "bad arguments");
+  // The global near list takes one entry per successful improvement beyond a CTA's shared list; a vertex can be improved
+  // many times in a phase, so on dense graphs with few vertices n + 1024 entries can be too few.  An overflow is not an
+  // error of the input: start over with a list four times as long (at most n + nnz + 1024: one entry per edge relaxation
+  // of a phase).
+  uint64_t near_cap = (uint64_t)std::max<int64_t>(A->n_rows, 0) + 1024;
+  const uint64_t cap_max = std::min<uint64_t>((uint64_t)A->n_rows + (uint64_t)A->nnz + 1024, 0xfffffff0ull);
+  for (;;) {
+    bool overflowed = false;
+    const int status = sssp_attempt(c, A, AT_in, source, dist, max_rounds, stats, near_cap, &overflowed);
+    if (!overflowed || near_cap >= cap_max) return status;
+    near_cap = std::min<uint64_t>(near_cap * 4, cap_max);
+  }
+}
+
+static int sssp_attempt(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t source, shb_buf *dist, uint32_t max_rounds,
+                        shb_graph_stats *stats, uint64_t near_cap, bool *overflowed) {
   SHB_REQUIRE(c && A && dist, "bad arguments");
   SHB_REQUIRE(A->n_rows == A->n_cols, "Matrix is not square. Failing computation.");
   SHB_REQUIRE(source >= 0 && source < A->n_rows, "source out of range");
@@ -403,7 +427,6 @@ SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t
     if (const char *e = getenv("SHB_SSSP_DELTA")) delta_override = (float)atof(e);
     int per_sm_cap = 1;
     if (const char *e = getenv("SHB_SSSP_CTAS_PER_SM")) per_sm_cap = std::max(1, atoi(e));
-    const uint64_t near_cap = (uint64_t)n + 1024;
     SS_CUDA(cudaMalloc(&st, sizeof(SsspState)));
     SS_CUDA(cudaMalloc(&near_q, (size_t)near_cap * 2 * sizeof(uint2)));
     SS_CUDA(cudaMalloc(&far_q, (size_t)n * 2 * sizeof(int32_t)));
@@ -460,6 +483,7 @@ SHB_API int shb_sssp(shb_ctx *c, const shb_csr *A, const shb_csr *AT_in, int64_t
     if (h.overflow) {
       shb_set_error("near list overflow (capacity %llu entries)", (unsigned long long)near_cap);
       status = SHB_ERR_CUDA;
+      *overflowed = true;
     } else if (!h.done) {
       shb_set_error("phase cap of %u reached before the worklists emptied", max_rounds);
       status = SHB_ERR_NOT_CONVERGED;
@@ -648,7 +672,9 @@ __global__ void __launch_bounds__(SSSP_THREADS, 1) sssp_block_kernel(const __gri
   }
   __syncthreads();
   while (phase < a.max_phases) {
-    const uint32_t ns = *(volatile uint32_t *)&st->near_size[phase % 3];
+    // (the size counter keeps counting past the list's capacity when it overflows -- the entries beyond it were dropped
+    //  and `overflow` is set: never read past the end; the host starts over with a longer list or reports the overflow)
+    const uint32_t ns = min(*(volatile uint32_t *)&st->near_size[phase % 3], a.near_cap);
     const uint2 *near_cur = a.near_q[phase & 1];
     uint2 *near_next = a.near_q[(phase + 1) & 1];
     uint32_t *near_next_size = &st->near_size[(phase + 1) % 3];

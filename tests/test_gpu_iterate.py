@@ -135,6 +135,24 @@ def test_sssp_grid_and_directed(ctx, orc):
     assert np.array_equal(dist.download(np.float32, 4000).view(np.int32), orc.sssp(rp, col, val, 5).view(np.int32))
 
 
+def test_sssp_dense_graph_with_few_vertices(ctx, orc, monkeypatch):
+    """nnz >> n with weights over five orders of magnitude and ONE huge bucket: every vertex is improved many times in a
+    phase, which is what fills the global near list (n + 1024 entries at first; the driver starts over with a list four
+    times as long when it overflows instead of failing a valid input).  Exact against the oracle either way."""
+    rng = np.random.default_rng(77)
+    n, k = 1800, 1500
+    rp = np.arange(n + 1, dtype=np.int64) * k
+    col = np.concatenate([rng.choice(n, k, replace=False) for _ in range(n)]).astype(np.int32)
+    val = np.floor(10.0 ** rng.uniform(0, 5, n * k)).astype(np.float32)
+    A = ctx.csr(n, n, rp, col, val)
+    want = orc.sssp(rp, col, val, 3)
+    for env in ({}, {"SHB_SSSP_DELTA": "1e30"}):
+        for key, v in env.items():
+            monkeypatch.setenv(key, v)
+        dist, st = ctx.sssp(A, 3)
+        assert st.converged and np.array_equal(dist.download(np.float32, n).view(np.int32), want.view(np.int32)), env
+
+
 @pytest.mark.parametrize("env", [{}, {"SHB_SSSP_DELTA": "0.01"}, {"SHB_SSSP_DELTA": "1e30"}, {"SHB_SSSP_C": "2"},
                                  {"SHB_SSSP_CTAS_PER_SM": "2"}])
 def test_sssp_near_far_schedules_reach_the_same_fixed_point(ctx, orc, env, monkeypatch):

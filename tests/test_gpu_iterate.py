@@ -121,6 +121,49 @@ def test_bfs_directed_with_zero_valued_edges(ctx, orc):
         assert np.array_equal(levels.download(np.int32, n), want) and st.iterations == nlev
 
 
+def test_bfs_more_hub_vertices_in_a_level_than_the_hub_list_holds(ctx, orc):
+    """Push levels park vertices with >= 1024 out-edges in a list of 1024 for the whole grid; a level with more hubs than
+    that falls back to the warp expansion for the rest.  Symmetric graph: 3000 vertices with ~1400 random neighbours each,
+    so level 1 is ~1400 hubs.  Also: no edges at all, and a root without edges."""
+    rng = np.random.default_rng(41)
+    n, k = 3000, 800
+    src = np.repeat(np.arange(n, dtype=np.int64), k)
+    dst = rng.integers(0, n, n * k, dtype=np.int64)
+    key = np.unique(np.concatenate([src * n + dst, dst * n + src]))
+    key = key[(key // n) != (key % n)]
+    rows, col = key // n, (key % n).astype(np.int32)
+    rp = np.zeros(n + 1, np.int64)
+    np.cumsum(np.bincount(rows, minlength=n), out=rp[1:])
+    assert np.diff(rp).min() >= 1024
+    A = ctx.csr(n, n, rp, col, None)
+    want, nlev, edges = orc.bfs_levels(rp, col, None, 11)
+    for AT in (A, None):
+        levels, st = ctx.bfs(A, 11, AT=AT)
+        assert np.array_equal(levels.download(np.int32, n), want) and st.iterations == nlev and st.edges_traversed == edges
+    # an operator without entries: only the root is reached
+    E = ctx.csr(50, 50, np.zeros(51, np.int64), np.zeros(0, np.int32), None)
+    for AT in (E, None):
+        levels, st = ctx.bfs(E, 7, AT=AT)
+        got = levels.download(np.int32, 50)
+        assert got[7] == 0 and (np.delete(got, 7) == -1).all() and st.reached == 1
+    dist, st = ctx.sssp(E, 7, AT=E)
+    d = dist.download(np.float32, 50)
+    assert d[7] == 0 and (np.delete(d, 7) == np.float32(3.4028235e38)).all() and st.converged
+
+
+def test_sssp_zero_and_equal_weights(ctx, orc):
+    """All weights zero (bucket width 0: every bucket holds one distinct distance) and all weights equal."""
+    rng = np.random.default_rng(43)
+    n = 5000
+    rp, col = random_ragged(rng, n, n, mean_len=5, long_rows=[(0, 700)], empty_frac=0.1)
+    for w in (0.0, 2.5):
+        val = np.full(len(col), w, np.float32)
+        A = ctx.csr(n, n, rp, col, val)
+        dist, st = ctx.sssp(A, 0)
+        assert st.converged
+        assert np.array_equal(dist.download(np.float32, n).view(np.int32), orc.sssp(rp, col, val, 0).view(np.int32)), w
+
+
 def test_sssp_grid_and_directed(ctx, orc):
     G = ctx.synth_grid2d(96, 61)
     rp, col, val = G.download()

@@ -503,7 +503,10 @@ def run_ours(args):
         line["roofline"]["request_ceilings"] = {
             "l1tex_to_xbar_requests": {"achieved_per_s": req / t, "peak_per_s": n_sm * hz, "frac": req / t / (n_sm * hz)},
             "l2_sectors": {"achieved_per_s": sec / t, "peak_per_s": 6300.0 / 32.0 * hz, "frac": sec / t / (6300.0 / 32.0 * hz)},
-            "note": "derived from ms_per_step and the sampled SM clock; profiles/r02_summary.md section 1 has the ncu counters"}
+            "pure_gather_ms": 0.937,
+            "note": "derived from ms_per_step and the sampled SM clock; profiles/r02_summary.md section 1 has the ncu counters. "
+                    "pure_gather_ms: measured time of a kernel doing ONLY this operator's 268M random gathers from a 64 MB table "
+                    "(tools/microbench/gather_bench.cu, profiles/r02_gather_microbench.jsonl): the floor of any row-major schedule"}
     traffic_file = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
     if os.path.exists(traffic_file):
         try:

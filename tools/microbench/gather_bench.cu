@@ -143,6 +143,52 @@ static void run(const char *name, int cluster, const uint32_t *table, uint32_t t
          name, cluster, grid, per_cta / mean, mean, best, per_cta * grid / (best * 1e-3));
 }
 
+
+// The config-2 access pattern with nothing else around it: every thread issues G independent 4-byte gathers from a
+// 64 MB table per step (distinct 128-byte lines, as 16 uniform-random columns per row give), B CTAs of 256 threads per
+// SM.  What this tops out at is the ceiling any row-major SpMV schedule has on this operator.
+template <int G>
+__global__ void __launch_bounds__(256) pure_gather_kernel(const uint32_t *__restrict__ table, uint32_t mask, int iters,
+                                                          uint32_t *__restrict__ sink) {
+  uint32_t h = mix(blockIdx.x * 256 + threadIdx.x + 1);
+  uint32_t acc = 0;
+  for (int it = 0; it < iters; ++it) {
+    uint32_t v[G];
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      h = h * 1664525u + 1013904223u;
+      v[k] = __ldg(table + ((h >> 4) & mask));
+    }
+#pragma unroll
+    for (int k = 0; k < G; ++k) acc += v[k];
+  }
+  if (acc == 0x12345678u) sink[0] = acc;
+}
+
+template <int G>
+static void run_pure(const uint32_t *table, uint32_t table_words, uint32_t *sink, int n_sm, int ctas_per_sm, double sm_hz) {
+  const long long total = 268435456LL;  // the gathers of one config-2 SpMV
+  const int grid = n_sm * ctas_per_sm;
+  const int iters = (int)(total / ((long long)grid * 256 * G));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0));
+  CK(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; ++rep) {
+    CK(cudaEventRecord(e0));
+    pure_gather_kernel<G><<<grid, 256>>>(table, table_words - 1, iters, sink);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep && ms < best) best = ms;
+  }
+  const double n = (double)grid * 256 * G * iters;
+  printf("{\"case\": \"pure gather, 64 MB table\", \"gathers_in_flight_per_thread\": %d, \"ctas_per_sm\": %d, \"gathers\": %.0f, \"ms\": %.4f, "
+         "\"chip_gathers_per_s\": %.4g, \"gathers_per_clk_per_sm\": %.3f, \"ms_for_268M_gathers\": %.4f}\n",
+         G, ctas_per_sm, n, best, n / (best * 1e-3), n / (best * 1e-3) / (n_sm * sm_hz), best * 268435456.0 / n);
+}
+
 int main() {
   cudaDeviceProp p;
   CK(cudaGetDeviceProperties(&p, 0));
@@ -158,5 +204,11 @@ int main() {
   run<4>("local smem red.add.f32", 1, table, table_words, sink, cycles, p.multiProcessorCount);
   for (int c : {2, 8, 16}) run<3>("dsmem red.add.f32", c, table, table_words, sink, cycles, p.multiProcessorCount);
   run<2>("global 64 MB", 1, table, table_words, sink, cycles, p.multiProcessorCount);
+  const double sm_hz = (double)p.clockRate * 1e3;
+  for (int b : {4, 8}) {
+    run_pure<4>(table, table_words, sink, p.multiProcessorCount, b, sm_hz);
+    run_pure<8>(table, table_words, sink, p.multiProcessorCount, b, sm_hz);
+    run_pure<16>(table, table_words, sink, p.multiProcessorCount, b, sm_hz);
+  }
   return 0;
 }

@@ -337,6 +337,7 @@ SHB_API int shb_csr_destroy(shb_csr *A) {
   cudaFree(A->col);
   cudaFree(A->val);
   cudaFree(A->tile_row);
+  cudaFree(A->row_ids);
   cudaFree(A->carry_tail);
   cudaFree(A->carry_head);
   cudaFree(A->row_len);
@@ -414,7 +415,7 @@ __global__ void csr_gather_lines_kernel(const int32_t *__restrict__ col, int64_t
 // L1TEX request ceiling; everything else keeps its row-major schedule
 static bool blocked_candidate(const shb_csr *A) {
   static const bool enabled = getenv("SHB_AUTO_BLOCKED") && atoi(getenv("SHB_AUTO_BLOCKED")) != 0;  // off until measured
-  if (!enabled) return false;
+  if (!enabled || A->row_ids) return false;  // (a compressed-row panel is never blocked)
   const double mean = A->n_rows > 0 ? (double)A->nnz / (double)A->n_rows : 0.0;
   return A->nnz >= (1ll << 24) && A->n_cols >= (1ll << 18) && mean >= 2.0 && A->gather_lines >= 24.0 &&
          (double)A->max_row_len <= 32.0 * std::max(mean, 1.0) + 64.0;
@@ -855,6 +856,7 @@ static int fill_args(const shb_csr *A, const void *x, const void *y, const void 
   typedef typename S::T T;
   memset(&a, 0, sizeof a);
   a.row_ptr = A->row_ptr;
+  a.row_ids = A->row_ids;
   a.col = A->col;
   a.val = (const T *)A->val;
   a.x = (const T *)x;

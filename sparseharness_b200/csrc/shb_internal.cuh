@@ -104,6 +104,8 @@ struct shb_csr {
   int elem_bytes = 4;
   // schedule metadata (stream variant)
   int32_t *tile_row = nullptr;  // n_tiles + 1: first row touched by each tile
+  // compressed row list (column panels): row r of THIS operator is row row_ids[r] of the vectors; nullptr = identity
+  int32_t *row_ids = nullptr;
   int64_t n_tiles = 0;
   // statistics
   int64_t max_row_len = 0, min_row_len = 0, empty_rows = 0, straddling_rows = 0;

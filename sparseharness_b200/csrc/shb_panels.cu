@@ -11,13 +11,21 @@
 // f(dp, alpha) (+) h(y, beta) with f distributing over (+) (example/<alg>/kernel5.json:3 user functions):
 //   plus-times id = 1, min-plus id = 0 (all operands are |.|), or-and id = 1, max-min id = INT_MAX.
 // Exact for min-plus / or-and / max-min and for integer-valued floats; general floats differ by the summation
-// order (1e-5 relative, like every other schedule).  The last panel writes the caller's destinations and runs the
-// convergence test; the ones before write a scratch accumulator owned by the operator.
+// order (1e-5 relative, like every other schedule).
+//
+// A panel keeps only the rows it HAS entries in (a compressed row list: row r of the panel is row row_ids[r] of the
+// vectors): on a power-law operator most (row, panel) pairs are empty, and a panel launch that visits every row pays
+// for them -- two row_ptr loads, a read and a write of the accumulator each (measured: the row visits, not the entries,
+// bound a config-5 panel launch; profiles/r02_summary.md section 2).  So the loop is
+//     acc   = epi(ZERO, alpha, y, beta)                 every row, one elementwise pass (the h(y, beta) term)
+//     acc   = epi(A_p (x) x, alpha, acc, id)            the rows of panel p only, p = 0 .. P-1, in place
+//     out_i = acc, convergence test                     every row, one elementwise pass (skipped when the caller has one
+//                                                       destination and no test: the panels then work on it directly)
 #include <algorithm>
 #include <cub/device/device_scan.cuh>
 #include <limits.h>
 
-#include "shb_internal.cuh"
+#include "spmv.cuh"
 
 // per row: how many entries fall into each panel
 __global__ void panel_count_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, int64_t n_rows,
@@ -37,6 +45,26 @@ __global__ void panel_count_kernel(const int32_t *__restrict__ row_ptr, const in
 #pragma unroll
     for (int p = 0; p < SHB_MAX_PANELS; ++p)
       if (p < n_panels) counts[(int64_t)p * (n_rows + 1) + r] = cnt[p];
+  }
+}
+
+// after the in-place scan counts[] is the panel's row_ptr over ALL rows; flag the rows that have entries
+__global__ void panel_flag_kernel(const int32_t *__restrict__ rp_full, int64_t n_rows, int32_t *__restrict__ flag) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r <= n_rows; r += (int64_t)gridDim.x * blockDim.x)
+    flag[r] = (r < n_rows && rp_full[r + 1] > rp_full[r]) ? 1 : 0;
+}
+
+// pos = exclusive scan of the flags: the compressed row list and its row_ptr
+__global__ void panel_compact_kernel(const int32_t *__restrict__ rp_full, const int32_t *__restrict__ pos, int64_t n_rows,
+                                     int32_t *__restrict__ row_ids, int32_t *__restrict__ rp_compact) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r <= n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+    if (r == n_rows) {
+      rp_compact[pos[r]] = rp_full[r];  // the end of the last row
+    } else if (rp_full[r + 1] > rp_full[r]) {
+      SHB_DEV_CHECK(pos[r] >= 0 && pos[r] < pos[n_rows]);
+      row_ids[pos[r]] = (int32_t)r;
+      rp_compact[pos[r]] = rp_full[r];
+    }
   }
 }
 
@@ -95,7 +123,7 @@ SHB_API int shb_csr_build_panels(shb_ctx *c, shb_csr *A, int n_panels, int *n_bu
   if (n_panels <= 1 || A->nnz == 0 || A->n_rows == 0) return SHB_OK;
   const uint32_t panel_cols = (uint32_t)((A->n_cols + n_panels - 1) / n_panels);
   const int64_t n = A->n_rows;
-  int32_t *counts = nullptr;
+  int32_t *counts = nullptr, *pos = nullptr;
   void *tmp = nullptr;
   size_t tmp_bytes = 0;
   int status = SHB_OK;
@@ -126,13 +154,25 @@ SHB_API int shb_csr_build_panels(shb_ctx *c, shb_csr *A, int n_panels, int *n_bu
       PN_CUDA(cudaMemcpyAsync(&totals[(size_t)p], cp + n, 4, cudaMemcpyDeviceToHost, c->stream));
     }
     PN_CUDA(cudaStreamSynchronize(c->stream));
+    PN_CUDA(cudaMalloc(&pos, (size_t)(n + 1) * 4));
     for (int p = 0; p < n_panels; ++p) {
+      // the rows this panel has entries in: flags -> positions -> compressed row list + its row_ptr
+      const int32_t *rp_full = counts + (int64_t)p * (n + 1);
+      int32_t m = 0;
+      panel_flag_kernel<<<grid, 256, 0, c->stream>>>(rp_full, n, pos);
+      PN_CUDA(cudaGetLastError());
+      PN_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, pos, pos, (int)(n + 1), c->stream));
+      PN_CUDA(cudaMemcpyAsync(&m, pos + n, 4, cudaMemcpyDeviceToHost, c->stream));
+      PN_CUDA(cudaStreamSynchronize(c->stream));
       shb_csr *B = nullptr;
-      status = shb_csr_alloc(c, n, A->n_cols, totals[(size_t)p], A->val != nullptr, &B);
+      status = shb_csr_alloc(c, m, A->n_cols, totals[(size_t)p], A->val != nullptr, &B);
       if (status != SHB_OK) goto done;
       A->panels[A->n_panels++] = B;
-      PN_CUDA(cudaMemcpyAsync(B->row_ptr, counts + (int64_t)p * (n + 1), (size_t)(n + 1) * 4, cudaMemcpyDeviceToDevice, c->stream));
-      P.row_ptr[p] = B->row_ptr;
+      PN_CUDA(cudaMalloc(&B->row_ids, (size_t)std::max(m, 1) * 4));
+      B->device_bytes += (uint64_t)std::max(m, 1) * 4;
+      panel_compact_kernel<<<grid, 256, 0, c->stream>>>(rp_full, pos, n, B->row_ids, B->row_ptr);
+      PN_CUDA(cudaGetLastError());
+      P.row_ptr[p] = const_cast<int32_t *>(rp_full);  // the fill below places entries by the row_ptr over ALL rows
       P.col[p] = B->col;
       P.val[p] = (uint32_t *)B->val;
     }
@@ -150,9 +190,94 @@ SHB_API int shb_csr_build_panels(shb_ctx *c, shb_csr *A, int n_panels, int *n_bu
 done:
 #undef PN_CUDA
   cudaFree(counts);
+  cudaFree(pos);
   cudaFree(tmp);
   if (status != SHB_OK) shb_panels_free(A);
   return status;
+}
+
+// acc[r] = epi(ZERO, alpha, y[r], beta) for every row: the h(y, beta) term the panels then add their products to
+template <class S>
+__global__ void panel_init_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, typename S::T *__restrict__ acc) {
+  typedef typename S::T T;
+  if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < a.n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t gr = a.row_offset + r;
+    const T yv = a.use_y == 1 ? a.y[gr] : (a.use_y == 2 ? S::one() : S::zero());
+    acc[gr] = S::epi(S::zero(), a.alpha, yv, a.beta);
+  }
+}
+
+// every destination receives acc; the convergence test of the iterative drivers
+template <class S>
+__global__ void panel_finish_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, const typename S::T *__restrict__ acc) {
+  typedef typename S::T T;
+  if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
+  bool differs = false;
+  const int64_t n_padded = (a.n_rows + 31) / 32 * 32;  // whole warps reach the vote
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
+    if (r < a.n_rows) {
+      const int64_t gr = a.row_offset + r;
+      const T o = acc[gr];
+#pragma unroll 1
+      for (int i = 0; i < a.n_out; ++i) a.out[i][gr] = o;
+      if (a.ctl.changed) differs |= shb_row_differs(a.x[gr], o, a.ctl.delta, a.ctl.term_mode);
+    }
+  }
+  shb_publish_changed(a.ctl, differs);
+}
+
+template <class S>
+static int panels_run(shb_ctx *c, const shb_csr *A, int semiring, const shb_launch_cfg *cfg, const void *x, const void *y,
+                      const void *alpha, const void *beta, void *const *outs, int n_out, int64_t row_offset, const IterCtl &ctl,
+                      const void *identity_beta) {
+  typedef typename S::T T;
+  const uint32_t flags = cfg ? cfg->flags : 0u;
+  SpmvArgs<T> a;
+  memset(&a, 0, sizeof a);
+  a.x = (const T *)x;
+  a.y = (const T *)y;
+  a.alpha = *(const T *)alpha;
+  a.beta = *(const T *)beta;
+  for (int i = 0; i < n_out; ++i) a.out[i] = (T *)outs[i];
+  a.n_out = n_out;
+  a.row_offset = row_offset;
+  a.n_rows = A->n_rows;
+  a.vlength = (uint32_t)A->n_cols;
+  a.ctl = ctl;
+  a.use_y = (flags & (SHB_F_INTERNAL_Y_ONE | SHB_F_Y_IS_ONE)) ? 2 : (flags & SHB_F_NO_Y_SKIP) ? 1 : (S::needs_y(a.beta) ? 1 : 0);
+  // one destination and no convergence test: the panels accumulate in the destination itself.  y may alias out (the
+  // init pass reads y[r] and writes out[r] in the same thread); x never does.
+  const bool direct = n_out == 1 && ctl.changed == nullptr;
+  // y and the destinations are indexed by row_offset + r: shift the scratch so that acc[row_offset + r] is its word r
+  T *acc = direct ? (T *)outs[0] : reinterpret_cast<T *>((char *)A->panel_acc - 4 * row_offset);
+  const unsigned grid = grid_for(A->n_rows, 256, c->prop.multiProcessorCount * 16);
+  panel_init_kernel<S><<<grid, 256, 0, c->stream>>>(a, acc);
+  SHB_CUDA(cudaGetLastError());
+  shb_launch_cfg lc = {};
+  if (cfg) lc = *cfg;
+  lc.variant = SHB_VARIANT_AUTO;
+  // tuning aid: SHB_PANEL_LANES=L runs every panel under the vector schedule with L lanes per row
+  static const int panel_lanes = [] {
+    const char *e = getenv("SHB_PANEL_LANES");
+    return e ? atoi(e) : 0;
+  }();
+  if (panel_lanes > 0) {
+    lc.variant = SHB_VARIANT_VECTOR;
+    lc.lanes = panel_lanes;
+  }
+  lc.flags &= ~(uint32_t)(SHB_F_Y_IS_ONE | SHB_F_INTERNAL_Y_ONE);
+  lc.flags |= SHB_F_NO_Y_SKIP;  // the accumulator is always read
+  IterCtl cp = ctl;
+  cp.changed = nullptr;  // the test runs in the finish pass
+  void *acc_out[1] = {acc};
+  for (int p = 0; p < A->n_panels; ++p)
+    SHB_TRY(shb_launch_spmv(c, A->panels[p], semiring, &lc, x, acc, alpha, identity_beta, acc_out, 1, row_offset, cp));
+  if (!direct) {
+    panel_finish_kernel<S><<<grid, 256, 0, c->stream>>>(a, acc);
+    SHB_CUDA(cudaGetLastError());
+  }
+  return SHB_OK;
 }
 
 // the panel loop (called from shb_launch_spmv when the operator has panels and the caller asked for AUTO)
@@ -164,37 +289,18 @@ int shb_launch_spmv_panels(shb_ctx *c, const shb_csr *A, int semiring, const shb
     int32_t i;
   } id;
   switch (semiring) {
-    case SHB_PLUS_TIMES_F32: id.f = 1.0f; break;
-    case SHB_MIN_PLUS_F32: id.f = 0.0f; break;
-    case SHB_OR_AND_I32: id.i = 1; break;
-    case SHB_MAX_MIN_I32: id.i = INT_MAX; break;
+    case SHB_PLUS_TIMES_F32:
+      id.f = 1.0f;
+      return panels_run<PlusTimesF32>(c, A, semiring, cfg, x, y, alpha, beta, outs, n_out, row_offset, ctl, &id);
+    case SHB_MIN_PLUS_F32:
+      id.f = 0.0f;
+      return panels_run<MinPlusF32>(c, A, semiring, cfg, x, y, alpha, beta, outs, n_out, row_offset, ctl, &id);
+    case SHB_OR_AND_I32:
+      id.i = 1;
+      return panels_run<OrAndI32>(c, A, semiring, cfg, x, y, alpha, beta, outs, n_out, row_offset, ctl, &id);
+    case SHB_MAX_MIN_I32:
+      id.i = INT_MAX;
+      return panels_run<MaxMinI32>(c, A, semiring, cfg, x, y, alpha, beta, outs, n_out, row_offset, ctl, &id);
     default: shb_set_error("unknown semiring %d", semiring); return SHB_ERR_UNSUPPORTED;
   }
-  // y and the destinations are indexed by row_offset + r: shift the scratch so that acc[row_offset + r] is its word r
-  char *acc = (char *)A->panel_acc - 4 * row_offset;
-  for (int p = 0; p < A->n_panels; ++p) {
-    const bool first = p == 0, last = p == A->n_panels - 1;
-    shb_launch_cfg lc = {};
-    if (cfg) lc = *cfg;
-    lc.variant = SHB_VARIANT_AUTO;
-    // tuning aid: SHB_PANEL_LANES=L runs every panel under the vector schedule with L lanes per row
-    static const int panel_lanes = [] {
-      const char *e = getenv("SHB_PANEL_LANES");
-      return e ? atoi(e) : 0;
-    }();
-    if (panel_lanes > 0) {
-      lc.variant = SHB_VARIANT_VECTOR;
-      lc.lanes = panel_lanes;
-    }
-    if (!first) {
-      lc.flags &= ~(uint32_t)(SHB_F_Y_IS_ONE | SHB_F_INTERNAL_Y_ONE);
-      lc.flags |= SHB_F_NO_Y_SKIP;
-    }
-    IterCtl cp = ctl;
-    if (!last) cp.changed = nullptr;
-    void *acc_out[1] = {acc};
-    SHB_TRY(shb_launch_spmv(c, A->panels[p], semiring, &lc, x, first ? y : (const void *)acc, alpha, first ? beta : (const void *)&id,
-                            last ? outs : acc_out, last ? n_out : 1, row_offset, cp));
-  }
-  return SHB_OK;
 }

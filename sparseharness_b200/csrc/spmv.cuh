@@ -26,6 +26,7 @@
 
 template <class T> struct SpmvArgs {
   const int32_t *row_ptr;
+  const int32_t *row_ids;  // nullptr, or: row r of the operator is element row_ids[r] of y / out (compressed row list)
   const int32_t *col;
   const T *val;  // nullptr = pattern
   const T *x;
@@ -45,7 +46,7 @@ template <class S>
 __device__ __forceinline__ void shb_finish_row(const SpmvArgs<typename S::T> &a, int64_t r, typename S::T dp,
                                                bool &differs) {
   typedef typename S::T T;
-  const int64_t gr = a.row_offset + r;
+  const int64_t gr = a.row_offset + (a.row_ids ? (int64_t)a.row_ids[r] : r);
   const T yv = a.use_y == 1 ? a.y[gr] : (a.use_y == 2 ? S::one() : S::zero());
   const T o = S::epi(dp, a.alpha, yv, a.beta);
 #pragma unroll 1

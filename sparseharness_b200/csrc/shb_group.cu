@@ -579,17 +579,18 @@ SHB_API int shb_group_pagerank(shb_group *g, const shb_gpart *p, const shb_launc
   const float alpha = 1.0f;
   uint32_t iters = 0;
   uint64_t total = 0;
-  // every device gathers from the full-length x: above the L2 size the sweeps run over column panels
-  // How many: measured on config 5 (ms per sweep, panels none / 2 / 4): 1 GPU 9.33 / 7.40 / 6.99, 4 GPUs 2.50 / 2.02 / 2.36,
-  // 8 GPUs 1.44 / 1.71 / 1.92 -- the more devices, the more of a sweep is peers' results arriving through this device's
-  // L2 (n x 4 bytes per sweep whatever the device count) and the less an x slice stays resident; and the peer stores of
-  // a block all leave in its LAST panel's launch.  So: the default slices (64 MB) up to 2 devices, 128 MB slices up to 4,
-  // no panels beyond.
+  // every device gathers from the full-length x: above the L2 size the sweeps run over column panels.  With
+  // compressed-row panels the default slices (40 MB) are the best measured setting at every device count (config 5, ms
+  // per sweep, no panels / 40 MB / 64 MB / 128 MB slices): 1 GPU 9.33 / 5.81 / 6.72 / 7.40, 2 GPUs 5.40 / 3.09 / 3.53 /
+  // 4.42, 4 GPUs 2.50 / 1.85 / 2.01 / 2.42, 8 GPUs 1.44 / 1.25 / 1.28 (89 MB) / -.
+  // SHB_GROUP_PANEL_BYTES=b overrides the slice size (0 = no panels): the tuning switch
+  int64_t slice = 0;  // shb_csr_build_panels' default
+  if (const char *e = getenv("SHB_GROUP_PANEL_BYTES")) slice = atoll(e) > 0 ? atoll(e) : -1;
   for (int d = 0; d < g->n; ++d)
     if (p->A[d]->n_panels == 0 && (uint64_t)p->n_cols * 4 > shb_panel_threshold_bytes(g->ctx[d]) &&
-        (!cfg || cfg->variant == SHB_VARIANT_AUTO) && g->n <= 4) {
+        (!cfg || cfg->variant == SHB_VARIANT_AUTO) && slice >= 0) {
       int n_panels = 0;  // automatic
-      if (g->n > 2 && !getenv("SHB_PANEL_BYTES")) n_panels = (int)std::max<int64_t>(2, (p->n_cols * 4 + (128ll << 20) - 1) / (128ll << 20));
+      if (slice > 0) n_panels = (int)std::max<int64_t>(2, (p->n_cols * 4 + slice - 1) / slice);
       SHB_TRY(shb_csr_build_panels(g->ctx[d], p->A[d], n_panels, nullptr));
     }
   const int s = shb_group_iterate(g, p, SHB_PLUS_TIMES_F32, cfg, nullptr, bits, nullptr, &alpha, &beta, delta, SHB_TERM_ABSDIFF,

@@ -112,9 +112,10 @@ SHB_API int shb_csr_build_panels(shb_ctx *c, shb_csr *A, int n_panels, int *n_bu
     A->device_bytes -= (uint64_t)A->n_rows * 4;
     shb_panels_free(A);
   }
-  if (n_panels <= 0) {  // automatic: x slices of at most 64 MB (half the L2; measured best on config 5: 16 / 32 / 64 / 128 MB
-                        // slices give 12.5 / 8.4 / 7.0 / 7.4 ms per sweep against 9.3 without panels)
-    int64_t slice = 64ll << 20;
+  if (n_panels <= 0) {  // automatic: x slices of at most 40 MB.  Measured on config 5 with compressed-row panels (ms per
+                        // sweep by slice size): 16 MB 6.32, 24 MB 6.10, 32 MB 5.87, 38 MB 5.81, 45 MB 5.82, 54 MB 6.06,
+                        // 64 MB 6.72; 9.33 without panels
+    int64_t slice = 40ll << 20;
     if (const char *e = getenv("SHB_PANEL_BYTES")) slice = std::max<int64_t>(1 << 16, atoll(e));
     n_panels = (int)std::min<int64_t>(SHB_MAX_PANELS, (A->n_cols * 4 + slice - 1) / slice);
   }

@@ -161,10 +161,11 @@ int shb_csr_build_blocked(shb_ctx *ctx, shb_csr *csr, int rows_per_consumer, int
 int shb_csr_blocked_info(const shb_csr *csr, int32_t *geom /* 8: n_prod, n_pass, n_panel, W, RS, cbuf, slot_cap, depth */, int64_t *entries,
                          uint64_t *device_bytes);
 /* Column panels for operators whose x exceeds the L2 (config 5: 2^26 columns, x = 268 MB): n_panels sub-operators
- * of consecutive column ranges, each a CSR over all the rows with global column ids, so that the gathers of one
- * launch stay inside an L2-resident slice of x; SHB_VARIANT_AUTO then runs panel after panel, carrying the row
- * sums through the epilogue (exact for min-plus / or-and / max-min, summation order for floats).  n_panels 0 =
- * x slices of at most 32 MB; *n_built = 0 when the operator needs no panels.  Doubles the operator's footprint. */
+ * of consecutive column ranges, each a CSR with global column ids over ONLY the rows it has entries in (a compressed
+ * row list), so that the gathers of one launch stay inside an L2-resident slice of x and empty (row, panel) pairs
+ * cost nothing; SHB_VARIANT_AUTO then runs panel after panel, accumulating the row sums through the epilogue (exact
+ * for min-plus / or-and / max-min, summation order for floats).  n_panels 0 = x slices of at most 40 MB;
+ * *n_built = 0 when the operator needs no panels.  Doubles the operator's footprint. */
 int shb_csr_build_panels(shb_ctx *ctx, shb_csr *csr, int n_panels, int *n_built);
 int shb_csr_balance_rows(shb_ctx *ctx, const shb_csr *csr, int parts, int64_t *row_bounds);
 int shb_csr_slice_rows(shb_ctx *ctx, const shb_csr *csr, int64_t row_begin, int64_t row_count, shb_csr **slice);

@@ -312,6 +312,10 @@ int shb_bfs_block_level(shb_ctx *ctx, const shb_csr *A, const shb_csr *AT, int64
                         uint32_t level, const shb_buf *deg, const shb_buf *frontier, shb_buf *const *next, int n_next,
                         int self_index, shb_buf *spare, shb_buf *visited, shb_buf *levels, shb_buf *counters,
                         shb_buf *state, shb_buf *const *peer_counters, uint64_t barrier_target);
+/* after a traversal stopped by its level cap: label the vertices of the last frontier built (frontier `level`) */
+int shb_bfs_block_label_frontier(shb_ctx *ctx, const shb_csr *A, int64_t row_offset, int64_t n_total, uint32_t level,
+                                 const shb_buf *frontier, shb_buf *spare, shb_buf *visited, shb_buf *levels,
+                                 shb_buf *counters, shb_buf *state);
 int shb_bfs_block_finish(shb_ctx *ctx, const shb_csr *A, const shb_buf *levels, shb_buf *counters, const shb_buf *state);
 
 /* Row-partitioned SSSP (new capability; the reference's sssp app is single-device, app/sssp.cpp:97-155):

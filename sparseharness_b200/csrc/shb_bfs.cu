@@ -706,6 +706,27 @@ SHB_API int shb_bfs_block_level(shb_ctx *c, const shb_csr *A, const shb_csr *AT,
   return SHB_OK;
 }
 
+// A traversal stopped by its level cap: the vertices of the last frontier built (frontier `level`, by a push level) get
+// their level -- a push level leaves that to the NEXT level's prep, which the cap cut off.  (shb_bfs does the same.)
+SHB_API int shb_bfs_block_label_frontier(shb_ctx *c, const shb_csr *A, int64_t row_offset, int64_t n_total, uint32_t level,
+                                         const shb_buf *frontier, shb_buf *spare, shb_buf *visited, shb_buf *levels,
+                                         shb_buf *counters, shb_buf *state) {
+  SHB_REQUIRE(c && A && frontier && spare && visited && levels && counters && state, "bad arguments");
+  const int64_t n_words = (n_total + 31) / 32;
+  const uint64_t bm_bytes = (uint64_t)n_words * 4;
+  SHB_REQUIRE(frontier->bytes >= bm_bytes && visited->bytes >= bm_bytes && spare->bytes >= bm_bytes, "bitmap shorter than n_total bits");
+  SHB_REQUIRE(spare->ptr != frontier->ptr, "the spare bitmap aliases the current frontier");
+  SHB_REQUIRE(levels->bytes >= (uint64_t)A->n_rows * 4 && state->bytes >= sizeof(BfsBlockState), "levels / state too short");
+  SHB_CUDA(cudaSetDevice(c->device));
+  const int64_t n_local = A->n_rows, word_lo = row_offset >> 5, word_hi = (row_offset + n_local + 31) >> 5;
+  bfs_block_prep_kernel<<<grid_for(n_words), 256, 0, c->stream>>>((BfsBlockState *)state->ptr, (long long *)counters->ptr,
+                                                                  (const uint32_t *)frontier->ptr, (uint32_t *)visited->ptr,
+                                                                  (uint32_t *)spare->ptr, (int32_t *)levels->ptr, level, n_words,
+                                                                  word_lo, word_hi, row_offset, n_local);
+  SHB_CUDA(cudaGetLastError());
+  return SHB_OK;
+}
+
 // per-rank reached / edge counts from the levels; SHB_ERR_CUDA if a peer barrier timed out during the traversal
 SHB_API int shb_bfs_block_finish(shb_ctx *c, const shb_csr *A, const shb_buf *levels, shb_buf *counters, const shb_buf *state) {
   SHB_REQUIRE(c && A && levels && counters && state, "bad arguments");

@@ -707,6 +707,10 @@ SHB_API int shb_group_bfs(shb_group *g, const shb_gpart *p, int64_t root, int32_
     }
     if (!broke) level += batch;
   }
+  if (!done)  // the level cap cut the traversal: the last frontier built still has to be labelled (as shb_bfs does)
+    for (int d = 0; d < N; ++d)
+      SHB_TRY(shb_bfs_block_label_frontier(g->ctx[d], p->A[d], p->bounds[d], n, level, bm[d][level % 3], bm[d][(level + 2) % 3],
+                                           visited[d], levels[d], counters[d], state[d]));
   uint64_t total = 0;
   SHB_TRY(grp_time_end(g, &total));
   int64_t reached = 0, edges = 0;

@@ -120,3 +120,29 @@ def test_group_adopts_device_built_blocks(orc):
     assert np.array_equal(lv, want) and st.iterations == ref_st.iterations and st.edges_traversed == ref_st.edges_traversed
     part.free()
     g.close()
+
+
+@pytest.mark.parametrize("n_dev", [1, 2])
+def test_group_bfs_level_cap_labels_the_last_frontier(orc, n_dev):
+    """max_levels below the depth of the traversal: SHB_ERR_NOT_CONVERGED, and every level up to the cap is exact -- the
+    last frontier built (by a push level, which leaves the labelling to the next level's prep) included, as in shb_bfs."""
+    import ctypes as C
+
+    from sparseharness_b200._capi import GraphStats, lib
+    if _n_dev() < n_dev:
+        pytest.skip(f"needs {n_dev} GPUs")
+    rp, col, _ = orc.gen_grid2d(60, 40)
+    n = len(rp) - 1
+    want, nlev, _ = orc.bfs_levels(rp, col, None, 0)
+    g = shb.Group(n_dev)
+    part = g.partition_host(n, n, rp, col, None, symmetric=True)
+    for cap in (1, 5, 12):
+        lv = np.full(n, -7, np.int32)
+        st = GraphStats()
+        status = lib.shb_group_bfs(g.h, part.h, 0, lv.ctypes.data_as(C.c_void_p), cap, 4, C.byref(st))
+        assert status == 7 and cap < nlev  # SHB_ERR_NOT_CONVERGED
+        assert np.array_equal(lv, np.where(want <= cap, want, -1)), cap
+    lv, st = g.bfs(part, 0)
+    assert st.converged and np.array_equal(lv, want)
+    part.free()
+    g.close()

@@ -338,6 +338,11 @@ class Context:
                                     frontier.h, arr, len(nxt), self_index, spare.h, visited.h, levels.h, counters.h,
                                     state.h, pc, barrier_target))
 
+    def bfs_block_label_frontier(self, A: Csr, row_offset, n_total, level, frontier: Buffer, spare: Buffer, visited: Buffer,
+                                 levels: Buffer, counters: Buffer, state: Buffer):
+        _ck(lib.shb_bfs_block_label_frontier(self.h, A.h, row_offset, n_total, level, frontier.h, spare.h, visited.h, levels.h,
+                                             counters.h, state.h))
+
     def bfs_block_finish(self, A: Csr, levels: Buffer, counters: Buffer, state: Buffer):
         _ck(lib.shb_bfs_block_finish(self.h, A.h, levels.h, counters.h, state.h))
 

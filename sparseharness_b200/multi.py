@@ -270,6 +270,9 @@ class BfsBackend:
     def read_counts(self, lo: int, hi: int) -> np.ndarray:  # host view of found[lo:hi] (synchronises)
         raise NotImplementedError
 
+    def label_frontier(self, level: int) -> None:  # level cap reached: the vertices of frontier `level` get their level
+        pass
+
 
 def run_bfs(backend: BfsBackend, max_levels: int = 1 << 20, check_every: int = 4):
     """Level-synchronous loop: level L's launch builds frontier L+1; stops after the first level that finds
@@ -291,6 +294,8 @@ def run_bfs(backend: BfsBackend, max_levels: int = 1 << 20, check_every: int = 4
             reached += int(counts[b])
         else:
             level += batch
+    if not done:  # cut by the cap: a push level leaves the labelling of the frontier it built to the next level's prep
+        backend.label_frontier(level)
     # `level` launches did work; the last of them found nothing when done, so levels 0..level-1 are populated
     return (level if done else level + 1), reached, level
 
@@ -370,6 +375,10 @@ class GpuBfsPartition(BfsBackend):
                                  self.peers[(level + 1) % 3], self.self_index, self.bm[(level + 2) % 3], self.visited,
                                  self.levels, self.counters, self.state, self.peer_counters, target)
         self.launches += 1
+
+    def label_frontier(self, level):
+        self.ctx.bfs_block_label_frontier(self.A, self.lo, self.n, level, self.bm[level % 3], self.bm[(level + 2) % 3], self.visited,
+                                          self.levels, self.counters, self.state)
 
     def reduce_count(self, level):
         if self.exchange == "nccl":
@@ -463,6 +472,11 @@ class EmulatedBfsPartition(BfsBackend):
                                      self.levels[k], self.counters[k], self.state[k],
                                      self.counters if self.publish else None, 0)
             self.launches += 1
+
+    def label_frontier(self, level):
+        for k, A in enumerate(self.blocks):
+            self.ctx.bfs_block_label_frontier(A, int(self.bounds[k]), self.n, level, self.bm[k][level % 3], self.bm[k][(level + 2) % 3],
+                                              self.visited[k], self.levels[k], self.counters[k], self.state[k])
 
     def reduce_count(self, level):
         if not self.publish:

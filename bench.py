@@ -456,8 +456,9 @@ def run_ours(args):
     fam = {1: "spmv_scalar_kernel", 2: "spmv_vector_kernel", 3: "spmv_stream_kernel", 4: "pb_fused_kernel"}.get(info.auto_variant, "?")
     kernel_name = {1: f"{fam}<PlusTimesF32,true>", 2: f"{fam}<PlusTimesF32,{info.auto_lanes},2,true,true>",
                    3: f"{fam}<PlusTimesF32,true,true> + spmv_fixup_kernel", 4: f"{fam}<PlusTimesF32,true>"}.get(info.auto_variant, fam)
-    binding = ("not HBM on this operator: every one of the 268M uniform-random x gathers is its own L1TEX->XBAR request "
-               "(ncu: l1tex__m_l1tex2xbar_req_cycles_active 90%, lts__throughput 85%, dram 42%; profiles/r01_summary.md); the same "
+    binding = ("not HBM on this operator: every one of the 268M uniform-random x gathers is its own L1TEX->XBAR request, one per clock "
+               "per SM -- a kernel doing ONLY those gathers takes 0.937 ms on this GPU (profiles/r02_gather_microbench.jsonl; ncu on this "
+               "kernel: l1tex__m_l1tex2xbar_req_cycles_active 90%, lts__throughput 85%, dram 42%, profiles/r02_summary.md); the same "
                "kernels with local gathers are HBM-bound, see roofline_local_gathers") if info.auto_variant != 4 else \
               ("propagation blocking: x slices gathered from shared memory, products through an L2-resident ring, every global "
                "access a coalesced 128-bit stream (sparseharness_b200/csrc/pb.cuh; profiles/r02_summary.md)")

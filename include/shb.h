@@ -76,8 +76,10 @@ enum { SHB_F_NO_CACHE_HINTS = 1u, /* plain ld.global for every stream (A/B exper
        SHB_F_STREAM_MERGE = 32u,  /* STREAM: the merge-path row phase (balanced walk over row ends
                                      and entries; measured slower than the default, kept for A/B)  */
        SHB_F_STREAM_NO_MERGE = 64u, /* STREAM: the thread-per-row row phase                         */
-       SHB_F_STREAM_SCAN = 128u   /* STREAM: the segmented-scan row phase (a row's sum is one shared-
-                                     memory read whatever its length)                              */ };
+       SHB_F_STREAM_SCAN = 128u,  /* STREAM: the segmented-scan row phase (a row's sum is one shared-
+                                     memory read whatever its length)                              */
+       SHB_F_STREAM_TMA = 256u    /* STREAM: the tile's columns and values arrive by TMA bulk copies
+                                     (cp.async.bulk + mbarrier) instead of through the LSU          */ };
 
 typedef struct {
   int32_t variant;        /* shb_variant                                                          */

@@ -15,7 +15,7 @@ PLUS_TIMES, MIN_PLUS, OR_AND, MAX_MIN = 0, 1, 2, 3
 VARIANT_AUTO, VARIANT_SCALAR, VARIANT_VECTOR, VARIANT_STREAM, VARIANT_BLOCKED = 0, 1, 2, 3, 4
 TERM_ABSDIFF, TERM_EQUAL = 0, 1
 F_NO_CACHE_HINTS, F_NO_Y_SKIP, F_REVERSED_ORDER, F_Y_IS_ONE, F_NO_PANELS = 1, 2, 4, 8, 16
-F_STREAM_MERGE, F_STREAM_NO_MERGE, F_STREAM_SCAN = 32, 64, 128
+F_STREAM_MERGE, F_STREAM_NO_MERGE, F_STREAM_SCAN, F_STREAM_TMA = 32, 64, 128, 256
 _DTYPE = {PLUS_TIMES: np.float32, MIN_PLUS: np.float32, OR_AND: np.int32, MAX_MIN: np.int32}
 
 

@@ -682,7 +682,10 @@ static int default_rpg(int lanes) {
 }
 
 #ifndef SHB_STREAM_SCAN_DEFAULT
-#define SHB_STREAM_SCAN_DEFAULT false  // until measured
+#define SHB_STREAM_SCAN_DEFAULT false  // measured: no gain
+#endif
+#ifndef SHB_STREAM_TMA_DEFAULT
+#define SHB_STREAM_TMA_DEFAULT false  // until measured
 #endif
 
 // BLOCKED: one persistent cooperative kernel, a CTA per SM, producer and consumer warps (pb.cuh).
@@ -818,10 +821,20 @@ static int run_spmv(shb_ctx *c, const shb_csr *A, const shb_launch_cfg *cfg, Spm
       if (scan_env >= 0) scan = scan_env != 0;
       if (d.flags & SHB_F_STREAM_SCAN) scan = true;
       if (d.flags & (SHB_F_STREAM_NO_MERGE | SHB_F_STREAM_MERGE)) scan = false;
-      const int mode = scan ? 2 : (merge ? 1 : 0);
+      // phase 1 through the TMA unit (spmv.cuh, MODE 3): SHB_STREAM_TMA=0|1, SHB_F_STREAM_TMA
+      static const int tma_env = [] {
+        const char *e = getenv("SHB_STREAM_TMA");
+        return e ? atoi(e) : -1;
+      }();
+      bool tma = SHB_STREAM_TMA_DEFAULT;
+      if (tma_env >= 0) tma = tma_env != 0;
+      if (d.flags & SHB_F_STREAM_TMA) tma = true;
+      if (d.flags & (SHB_F_STREAM_NO_MERGE | SHB_F_STREAM_MERGE | SHB_F_STREAM_SCAN)) tma = false;
+      const int mode = scan ? 2 : (merge ? 1 : (tma ? 3 : 0));
 #define SHB_LAUNCH_STREAM(HV, HN)                                                                                              \
   do {                                                                                                                         \
     if (mode == 2) spmv_stream_kernel<S, HV, HN, 2><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece); \
+    else if (mode == 3) spmv_stream_kernel<S, HV, HN, 3><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece); \
     else if (mode == 1) spmv_stream_kernel<S, HV, HN, 1><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece); \
     else spmv_stream_kernel<S, HV, HN, 0><<<nt, SHB_STREAM_THREADS, 0, c->stream>>>(a, A->tile_row, nt, (int32_t)A->nnz, ct, ch, long_piece);       \
   } while (0)

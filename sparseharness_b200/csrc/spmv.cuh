@@ -228,7 +228,11 @@ __device__ __forceinline__ int shb_pad(int i) { return i + (i >> 5); }  // 1 pad
 // read -- the element at its last entry -- whatever its length: no per-row loop, no divergence on skewed rows, no
 // separate pass for long rows.  Association order differs from the loop's (deterministic; exact for min-plus / or-and /
 // max-min and integer-valued floats, within the stated 1e-5 for general floats).
-// MODE: 0 = thread-per-row loop, 1 = MERGE, 2 = SCAN.
+// TMA (MODE 3): phase 1 through the TMA unit -- one thread starts two 16 KB bulk copies (cp.async.bulk, completion on an
+// mbarrier) of the tile's columns and values into shared memory and every thread then takes its entries from there, so
+// the operator streams do not go through the LSU / L1TEX request path the gathers saturate.  Row phase = the loop's.
+// MODE: 0 = thread-per-row loop, 1 = MERGE, 2 = SCAN, 3 = TMA.
+__device__ __forceinline__ uint32_t shb_smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 template <class S, bool HAS_VAL, bool HINTS, int MODE>
 __global__ void __launch_bounds__(SHB_STREAM_THREADS)
     spmv_stream_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, const int32_t *__restrict__ tile_row,
@@ -236,11 +240,15 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
                        typename S::T *__restrict__ carry_head, int long_piece) {
   typedef typename S::T T;
   if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
-  __shared__ T prod[SHB_TILE_NNZ + SHB_TILE_NNZ / 32];
+  __shared__ __align__(128) T prod[SHB_TILE_NNZ + SHB_TILE_NNZ / 32];
   __shared__ int long_rows[SHB_TILE_NNZ / SHB_LONG_PIECE_MIN + 2];
   __shared__ int n_long;
   constexpr bool MERGE = MODE == 1;
   constexpr bool SCAN = MODE == 2;
+  constexpr bool TMA = MODE == 3;
+  __shared__ __align__(128) uint32_t tma_col[TMA ? SHB_TILE_NNZ : 4];
+  uint32_t *const tma_val = reinterpret_cast<uint32_t *>(prod);  // the values land where the products go later (a barrier between)
+  __shared__ __align__(8) uint64_t tma_bar;
   static_assert(SHB_TILE_NNZ == 16 * SHB_STREAM_THREADS, "the scan row phase gives every thread 16 consecutive products");
   __shared__ uint32_t flag_s[SCAN ? SHB_TILE_NNZ / 32 : 1];      // bit k: a row starts at entry lo + k
   __shared__ T wtail_s[SCAN ? SHB_STREAM_THREADS / 32 : 1];      // per warp: sum of the segment open at its end
@@ -267,12 +275,43 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
   // phase 1: stream the tile's non-zeros (the arrays are padded to a tile multiple with col = -1)
   constexpr int STEPS = SHB_TILE_NNZ / (SHB_STREAM_THREADS * 4);
   uint4 c4[STEPS], v4[STEPS];
+  if (TMA) {
+    const uint32_t bar = shb_smem_addr(&tma_bar);
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      const uint32_t bytes = SHB_TILE_NNZ * 4u;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(HAS_VAL ? 2u * bytes : bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(shb_smem_addr(tma_col)),
+                   "l"(a.col + lo), "r"(bytes), "r"(bar)
+                   : "memory");
+      if (HAS_VAL)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(shb_smem_addr(tma_val)),
+                     "l"(a.val + lo), "r"(bytes), "r"(bar)
+                     : "memory");
+    }
+    __syncthreads();  // the barrier is initialised before anyone polls it
+    uint32_t ok = 0;
+    while (!ok)
+      asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                   : "=r"(ok)
+                   : "r"(bar), "r"(0u)
+                   : "memory");
 #pragma unroll
-  for (int k = 0; k < STEPS; ++k) {
-    const int i = lo + 4 * (tid + SHB_STREAM_THREADS * k);
-    c4[k] = shb_ld_stream_v4<HINTS>(a.col + i, true, 0xffffffffu, pol_stream);
-    if (HAS_VAL) v4[k] = shb_ld_stream_v4<HINTS>(a.val + i, true, zbits, pol_stream);
-    else v4[k] = make_uint4(obits, obits, obits, obits);
+    for (int k = 0; k < STEPS; ++k) {
+      const int i = 4 * (tid + SHB_STREAM_THREADS * k);
+      c4[k] = *reinterpret_cast<const uint4 *>(tma_col + i);
+      if (HAS_VAL) v4[k] = *reinterpret_cast<const uint4 *>(tma_val + i);
+      else v4[k] = make_uint4(obits, obits, obits, obits);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < STEPS; ++k) {
+      const int i = lo + 4 * (tid + SHB_STREAM_THREADS * k);
+      c4[k] = shb_ld_stream_v4<HINTS>(a.col + i, true, 0xffffffffu, pol_stream);
+      if (HAS_VAL) v4[k] = shb_ld_stream_v4<HINTS>(a.val + i, true, zbits, pol_stream);
+      else v4[k] = make_uint4(obits, obits, obits, obits);
+    }
   }
   if (SCAN) {  // row starts of this tile -> the mask (the loads above are in flight meanwhile)
     const int rf = tile_row[t];
@@ -290,6 +329,7 @@ __global__ void __launch_bounds__(SHB_STREAM_THREADS)
     xb[k][2] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[k].z, a.vlength, zbits, pol_keep);
     xb[k][3] = shb_gather_b32<HINTS>(a.x, (int32_t)c4[k].w, a.vlength, zbits, pol_keep);
   }
+  if (TMA) __syncthreads();  // every thread holds its values in registers before products overwrite them
 #pragma unroll
   for (int k = 0; k < STEPS; ++k) {
     const int i = 4 * (tid + SHB_STREAM_THREADS * k);

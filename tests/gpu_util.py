@@ -16,6 +16,7 @@ ALL_CFGS = [("scalar", dict(variant=shb.VARIANT_SCALAR)), ("stream", dict(varian
             ("stream_merge", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_MERGE)),        # merge-path row phase
             ("stream_nomerge", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_NO_MERGE)),   # thread-per-row row phase
             ("stream_scan", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_SCAN)),          # segmented-scan row phase
+            ("stream_tma", dict(variant=shb.VARIANT_STREAM, flags=shb.F_STREAM_TMA)),            # tile streams by TMA bulk copies
             ("blocked", dict(variant=shb.VARIANT_BLOCKED)),          # one row panel on the small fixtures
             ("blocked_rs5", dict(variant=shb.VARIANT_BLOCKED, pb_rows=5))]  # many row panels, tiny pieces
 

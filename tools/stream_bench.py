@@ -20,9 +20,10 @@ def med(ctx, A, x, out, cfg, reps=12):
 
 def main():
     ctx = shb.Context(0)
-    res = {"SHB_STREAM_LONG": os.environ.get("SHB_STREAM_LONG", "default")}
+    res = {k: os.environ.get(k, "default") for k in ("SHB_STREAM_LONG", "SHB_STREAM_SCAN", "SHB_STREAM_TMA")}
     cfg = shb.launch_cfg(variant=shb.VARIANT_STREAM)
-    for tag, make in (("rmat22", lambda: ctx.synth_rmat(22, 16, seed=0x5EED0022, symmetrise=False, value_mode=1)),
+    for tag, make in (("config2", lambda: ctx.synth_uniform(1 << 24, 1 << 24, 16)),
+                      ("rmat22", lambda: ctx.synth_rmat(22, 16, seed=0x5EED0022, symmetrise=False, value_mode=1)),
                       ("grid8192", lambda: ctx.synth_grid2d(8192, 8192, seed=0x5EED0004))):
         A = make()
         n = A.info.n_rows

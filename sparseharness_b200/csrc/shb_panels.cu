@@ -209,20 +209,54 @@ __global__ void panel_init_kernel(const __grid_constant__ SpmvArgs<typename S::T
   }
 }
 
-// every destination receives acc; the convergence test of the iterative drivers
-template <class S>
-__global__ void panel_finish_kernel(const __grid_constant__ SpmvArgs<typename S::T> a, const typename S::T *__restrict__ acc) {
+// every destination receives acc; the convergence test of the iterative drivers.  VEC: four rows per thread with 128-bit
+// accesses (the caller checked that acc, x and every destination are 16-byte aligned at row 0 of the block); the scalar
+// form ran at 2.2 TB/s (ncu: 360 us for 0.78 GB on config 5), a fifth of a sweep's non-panel time.
+template <class S, bool VEC>
+__global__ void __launch_bounds__(256) panel_finish_kernel(const __grid_constant__ SpmvArgs<typename S::T> a,
+                                                           const typename S::T *__restrict__ acc) {
   typedef typename S::T T;
   if (a.ctl.prev_changed && *a.ctl.prev_changed == 0) return;
   bool differs = false;
-  const int64_t n_padded = (a.n_rows + 31) / 32 * 32;  // whole warps reach the vote
-  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
-    if (r < a.n_rows) {
-      const int64_t gr = a.row_offset + r;
-      const T o = acc[gr];
+  if (VEC) {
+    const int64_t n4 = a.n_rows >> 2;
+    const int64_t n4_padded = (n4 + 31) / 32 * 32;  // whole warps reach the vote
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n4_padded; q += (int64_t)gridDim.x * blockDim.x) {
+      if (q < n4) {
+        const int64_t gr = a.row_offset + 4 * q;
+        const uint4 o = *reinterpret_cast<const uint4 *>(acc + gr);
 #pragma unroll 1
-      for (int i = 0; i < a.n_out; ++i) a.out[i][gr] = o;
-      if (a.ctl.changed) differs |= shb_row_differs(a.x[gr], o, a.ctl.delta, a.ctl.term_mode);
+        for (int i = 0; i < a.n_out; ++i) *reinterpret_cast<uint4 *>(a.out[i] + gr) = o;
+        if (a.ctl.changed) {
+          const uint4 xo = *reinterpret_cast<const uint4 *>(a.x + gr);
+          differs |= shb_row_differs(shb_from_bits<T>(xo.x), shb_from_bits<T>(o.x), a.ctl.delta, a.ctl.term_mode);
+          differs |= shb_row_differs(shb_from_bits<T>(xo.y), shb_from_bits<T>(o.y), a.ctl.delta, a.ctl.term_mode);
+          differs |= shb_row_differs(shb_from_bits<T>(xo.z), shb_from_bits<T>(o.z), a.ctl.delta, a.ctl.term_mode);
+          differs |= shb_row_differs(shb_from_bits<T>(xo.w), shb_from_bits<T>(o.w), a.ctl.delta, a.ctl.term_mode);
+        }
+      }
+    }
+    // the last n_rows % 4 rows: lanes 0..2 of the first warp of block 0
+    if (blockIdx.x == 0 && threadIdx.x < 32) {
+      const int64_t r = 4 * n4 + threadIdx.x;
+      if (r < a.n_rows) {
+        const int64_t gr = a.row_offset + r;
+        const T o = acc[gr];
+#pragma unroll 1
+        for (int i = 0; i < a.n_out; ++i) a.out[i][gr] = o;
+        if (a.ctl.changed) differs |= shb_row_differs(a.x[gr], o, a.ctl.delta, a.ctl.term_mode);
+      }
+    }
+  } else {
+    const int64_t n_padded = (a.n_rows + 31) / 32 * 32;  // whole warps reach the vote
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_padded; r += (int64_t)gridDim.x * blockDim.x) {
+      if (r < a.n_rows) {
+        const int64_t gr = a.row_offset + r;
+        const T o = acc[gr];
+#pragma unroll 1
+        for (int i = 0; i < a.n_out; ++i) a.out[i][gr] = o;
+        if (a.ctl.changed) differs |= shb_row_differs(a.x[gr], o, a.ctl.delta, a.ctl.term_mode);
+      }
     }
   }
   shb_publish_changed(a.ctl, differs);
@@ -275,7 +309,10 @@ static int panels_run(shb_ctx *c, const shb_csr *A, int semiring, const shb_laun
   for (int p = 0; p < A->n_panels; ++p)
     SHB_TRY(shb_launch_spmv(c, A->panels[p], semiring, &lc, x, acc, alpha, identity_beta, acc_out, 1, row_offset, cp));
   if (!direct) {
-    panel_finish_kernel<S><<<grid, 256, 0, c->stream>>>(a, acc);
+    bool vec = (reinterpret_cast<uintptr_t>(acc + row_offset) & 15u) == 0 && (reinterpret_cast<uintptr_t>(a.x + row_offset) & 15u) == 0;
+    for (int i = 0; i < n_out; ++i) vec = vec && (reinterpret_cast<uintptr_t>(a.out[i] + row_offset) & 15u) == 0;
+    if (vec) panel_finish_kernel<S, true><<<grid_for(A->n_rows / 4 + 32, 256, c->prop.multiProcessorCount * 16), 256, 0, c->stream>>>(a, acc);
+    else panel_finish_kernel<S, false><<<grid, 256, 0, c->stream>>>(a, acc);
     SHB_CUDA(cudaGetLastError());
   }
   return SHB_OK;
